@@ -1,0 +1,86 @@
+// Host-side (C++) interface of the tcgen05 contraction kernels.  Internal to the library; the public
+// C ABI lives in include/act_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <string>
+#include "tc_kernel.cuh"
+
+namespace act {
+
+typedef __nv_bfloat16 bf16;
+
+void set_error(const std::string& msg);
+const char* last_error();
+
+#define ACT_CHECK(cond, msg)                                                         \
+  do {                                                                               \
+    if (!(cond)) { ::act::set_error(std::string(__FILE__) + ":" + std::to_string(__LINE__) + " " + (msg)); return -1; } \
+  } while (0)
+#define ACT_CUDA(expr)                                                               \
+  do {                                                                               \
+    cudaError_t _e = (expr);                                                         \
+    if (_e != cudaSuccess) { ::act::set_error(std::string(#expr) + ": " + cudaGetErrorString(_e)); return -2; } \
+  } while (0)
+
+// Logical matrix operand [rows x K] (batched).  K-major: (row,k) at ptr + row*ld + k.
+// MN-major: (row,k) at ptr + k*ld + row.  Batch z = z0 + nz0*z1 adds z0*sz0 + z1*sz1 elements.
+struct MatDesc {
+  const bf16* ptr = nullptr;
+  int mn_major = 0;
+  long long ld = 0, sz0 = 0, sz1 = 0;
+};
+
+struct EpiDesc {
+  uint32_t flags = 0;
+  float alpha = 1.f;
+  const float* bias = nullptr;
+  const float* scale = nullptr;
+  const float* res_f32 = nullptr;
+  const bf16* res_bf16 = nullptr;
+  const bf16* aux_bf16 = nullptr;
+  float* out_f32 = nullptr;
+  bf16* out_bf16 = nullptr;
+  long long ldc = 0, ldr = 0, osz0 = 0, osz1 = 0, rsz0 = 0, rsz1 = 0;
+};
+
+// D[z][M,N] = epi(A[z] * B[z]^T).  bn_hint / stages_hint = 0 -> heuristic.
+int tc_gemm(int M, int N, int K, int nz0, int nz1, const MatDesc& A, const MatDesc& B, const EpiDesc& epi,
+            int ksplit, cudaStream_t stream, int bn_hint = 0, int stages_hint = 0);
+
+// One NHWC plane (possibly a stride-2 parity sub-lattice) addressed by TMA: dims {C, W, H, N}.
+struct PlaneDesc {
+  const bf16* ptr = nullptr;
+  int C = 0, W = 0, H = 0, N = 0;
+  long long sW = 0, sH = 0, sN = 0;     // element strides (channel stride is 1)
+};
+
+struct ConvLaunch {
+  PlaneDesc planes[4];
+  int nplanes = 1;
+  TapDesc taps[16];
+  int ntaps = 0;
+  int Cin = 0, Cout = 0;
+  const bf16* wgt = nullptr;            // [Cout][nslots*Cin] K-major, slot-major then channel
+  long long wgt_ld = 0;
+  int vW = 0, vH = 0, NIMG = 0;         // tile-space extent (one accumulator row per (n,h,w))
+  PixGeom og{}, rg{};
+  EpiDesc epi;                          // ldc/ldr/osz*/rsz* ignored (geometry comes from og / rg)
+};
+int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint = 0, int stages_hint = 0);
+
+struct WgradLaunch {
+  PlaneDesc planes[4];                  // activation planes (tap.map selects)
+  int nplanes = 1;
+  TapDesc taps[16];
+  int ntaps = 0;
+  PlaneDesc dy;                         // gradient wrt the conv output, dims {Cout, vW, vH, N}
+  int Cin = 0, Cout = 0, KK = 0;        // dW fp32 [Cout][Cin][KK], accumulated with atomics (caller zeroes it)
+  float* dw = nullptr;
+  float alpha = 1.f;
+  int ksplit = 0;                       // 0 -> heuristic
+};
+int tc_wgrad(const WgradLaunch& w, cudaStream_t stream);
+
+}  // namespace act

@@ -1,0 +1,268 @@
+// Host launchers for tc_kernel: tensor-map construction (driver entry point fetched at run time so the
+// library loads on machines without libcuda), tile selection, launch.
+#include "tc_api.h"
+#include <mutex>
+#include <cstring>
+#include <algorithm>
+
+namespace act {
+
+static thread_local std::string g_err;
+void set_error(const std::string& msg) { g_err = msg; }
+const char* last_error() { return g_err.c_str(); }
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// bf16 tensor map, 4-D, 128B swizzle, zero OOB fill.  dims/box innermost first; strides (elements) for dims 1..3.
+static int make_tmap(CUtensorMap* m, const bf16* ptr, const long long dims[4], const long long strides_el[3],
+                     const int box[4]) {
+  EncodeTiledFn enc = get_encode();
+  ACT_CHECK(enc != nullptr, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+  cuuint64_t gd[4], gs[3];
+  cuuint32_t bx[4], es[4] = {1, 1, 1, 1};
+  for (int i = 0; i < 4; ++i) { gd[i] = static_cast<cuuint64_t>(std::max(1LL, dims[i])); bx[i] = static_cast<cuuint32_t>(box[i]); }
+  for (int i = 0; i < 3; ++i) gs[i] = static_cast<cuuint64_t>(strides_el[i]) * 2;
+  ACT_CHECK((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA base must be 16-byte aligned");
+  for (int i = 0; i < 3; ++i) ACT_CHECK(gs[i] % 16 == 0 && gs[i] > 0, "TMA stride must be a positive multiple of 16 bytes");
+  ACT_CHECK(box[0] * 2 == 128, "inner box must span the 128B swizzle");
+  for (int i = 0; i < 4; ++i) ACT_CHECK(box[i] >= 1 && box[i] <= 256, "box dim out of range");
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<bf16*>(ptr), gd, gs, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  ACT_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed, code " + std::to_string(static_cast<int>(r)));
+  return 0;
+}
+
+static int make_tmap_2d(CUtensorMap* m, const bf16* ptr, long long inner, long long outer, long long ld, int box_outer) {
+  EncodeTiledFn enc = get_encode();
+  ACT_CHECK(enc != nullptr, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+  cuuint64_t gd[2] = {static_cast<cuuint64_t>(inner), static_cast<cuuint64_t>(outer)};
+  cuuint64_t gs[1] = {static_cast<cuuint64_t>(ld) * 2};
+  cuuint32_t bx[2] = {64, static_cast<cuuint32_t>(box_outer)}, es[2] = {1, 1};
+  ACT_CHECK((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && gs[0] % 16 == 0, "TMA 2D alignment");
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<bf16*>(ptr), gd, gs, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  ACT_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(2d) failed, code " + std::to_string(static_cast<int>(r)));
+  return 0;
+}
+
+static int mat_tmap(CUtensorMap* m, const MatDesc& d, int rows, int K, int nz0, int nz1, int box_rows_kmajor) {
+  long long dims[4], str[3];
+  int box[4] = {64, 64, 1, 1};
+  if (d.mn_major) { dims[0] = rows; dims[1] = K; }
+  else { dims[0] = K; dims[1] = rows; box[1] = box_rows_kmajor; }
+  dims[2] = nz0; dims[3] = nz1;
+  str[0] = d.ld;
+  str[1] = nz0 > 1 ? d.sz0 : d.ld * std::max(1LL, dims[1]);
+  str[2] = nz1 > 1 ? d.sz1 : str[1] * std::max(1, nz0);
+  if (str[1] <= 0) str[1] = 8;
+  if (str[2] <= 0) str[2] = 8;
+  return make_tmap(m, d.ptr, dims, str, box);
+}
+
+static int plane_tmap(CUtensorMap* m, const PlaneDesc& pl, int bw, int bh, int bni) {
+  long long dims[4] = {pl.C, pl.W, pl.H, pl.N};
+  long long str[3] = {pl.sW, pl.sH, pl.sN};
+  int box[4] = {64, bw, bh, bni};
+  return make_tmap(m, pl.ptr, dims, str, box);
+}
+
+template <int MODE, int A_MN, int B_MN, int BN>
+static int launch_inst(dim3 grid, int stages, cudaStream_t stream, const CUtensorMap* am, const CUtensorMap& bm,
+                       const TcParams& p) {
+  using Cfg = TcCfg<MODE, A_MN, B_MN, BN>;
+  auto kern = tc_kernel<MODE, A_MN, B_MN, BN>;
+  const int max_smem = 227 * 1024;
+  const int extra = 1024 + (2 * Cfg::MAX_STAGES + 1) * 8 + 16;
+  stages = std::max(2, std::min(stages, std::min<int>(Cfg::MAX_STAGES, (max_smem - extra) / Cfg::STAGE_BYTES)));
+  const int smem = stages * Cfg::STAGE_BYTES + extra;
+  static int configured = 0;     // per instantiation
+  if (configured < smem) {
+    ACT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+    configured = max_smem;
+  }
+  kern<<<grid, Cfg::THREADS, smem, stream>>>(am[0], am[1], am[2], am[3], bm, p, stages);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+static void fill_epi(TcParams& p, const EpiDesc& e) {
+  p.flags = e.flags; p.alpha = e.alpha; p.bias = e.bias; p.scale = e.scale; p.res_f32 = e.res_f32;
+  p.res_bf16 = e.res_bf16; p.aux_bf16 = e.aux_bf16; p.out_f32 = e.out_f32; p.out_bf16 = e.out_bf16;
+  p.ldc = e.ldc; p.ldr = e.ldr; p.osz0 = e.osz0; p.osz1 = e.osz1; p.rsz0 = e.rsz0; p.rsz1 = e.rsz1;
+}
+
+static int check_epi(const EpiDesc& e) {
+  ACT_CHECK((e.flags & (EPI_OUT_F32 | EPI_OUT_BF16)) != 0, "epilogue without output");
+  if (e.flags & EPI_OUT_F32) ACT_CHECK(e.out_f32 != nullptr, "out_f32 null");
+  if (e.flags & EPI_OUT_BF16) ACT_CHECK(e.out_bf16 != nullptr, "out_bf16 null");
+  if (e.flags & EPI_BIAS) ACT_CHECK(e.bias != nullptr, "bias null");
+  if (e.flags & EPI_SCALE) ACT_CHECK(e.scale != nullptr, "scale null");
+  if (e.flags & EPI_RES_F32) ACT_CHECK(e.res_f32 != nullptr, "res_f32 null");
+  if (e.flags & EPI_RES_BF16) ACT_CHECK(e.res_bf16 != nullptr, "res_bf16 null");
+  if (e.flags & EPI_MASK_POS) ACT_CHECK(e.aux_bf16 != nullptr, "aux null");
+  if (e.flags & EPI_ATOMIC) ACT_CHECK((e.flags & EPI_OUT_F32) && !(e.flags & EPI_OUT_BF16), "atomic epilogue is fp32 only");
+  return 0;
+}
+
+// --------------------------------------------------------------------------------------------- GEMM
+int tc_gemm(int M, int N, int K, int nz0, int nz1, const MatDesc& A, const MatDesc& B, const EpiDesc& epi,
+            int ksplit, cudaStream_t stream, int bn_hint, int stages_hint) {
+  ACT_CHECK(M > 0 && N > 0 && K > 0 && nz0 > 0 && nz1 > 0, "bad GEMM shape");
+  if (check_epi(epi)) return -1;
+  if (ksplit < 1) ksplit = 1;
+  if (ksplit > 1) ACT_CHECK(epi.flags & EPI_ATOMIC, "split-K needs the atomic epilogue");
+  const int nb = nz0 * nz1;
+  const int mt = (M + 127) / 128;
+  int bn = bn_hint;
+  if (bn == 0) {
+    bn = 64;
+    const int cands[3] = {256, 128, 64};
+    for (int c : cands) {
+      if (N < c) continue;
+      const long long tiles = 1LL * mt * ((N + c - 1) / c) * nb * ksplit;
+      if (tiles >= (c == 256 ? 296 : 148)) { bn = c; break; }
+    }
+  }
+  ACT_CHECK(bn == 64 || bn == 128 || bn == 256, "bn must be 64/128/256");
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = M; p.N = N; p.K = K; p.num_k_blocks = (K + 63) / 64; p.nz0 = nz0; p.ksplit = ksplit;
+  fill_epi(p, epi);
+  bool vec = (epi.ldc % 8 == 0) && (epi.osz0 % 8 == 0) && (epi.osz1 % 8 == 0) && (epi.ldr % 8 == 0) &&
+             (epi.rsz0 % 8 == 0) && (epi.rsz1 % 8 == 0) && aligned16(epi.out_f32) && aligned16(epi.out_bf16) &&
+             aligned16(epi.res_f32) && aligned16(epi.res_bf16) && aligned16(epi.aux_bf16);
+  p.vec_ok = vec ? 1 : 0;
+  CUtensorMap am[4], bm;
+  if (mat_tmap(&am[0], A, M, K, nz0, nz1, 128)) return -1;
+  am[1] = am[2] = am[3] = am[0];
+  if (mat_tmap(&bm, B, N, K, nz0, nz1, bn)) return -1;
+  dim3 grid((N + bn - 1) / bn, mt, nb * ksplit);
+  const int st = stages_hint ? stages_hint : (bn == 64 ? 4 : bn == 128 ? 4 : 4);
+  const int key = (A.mn_major ? 2 : 0) | (B.mn_major ? 1 : 0);
+#define GEMM_CASE(AM, BMJ)                                                                     \
+  if (bn == 64) return launch_inst<MODE_GEMM, AM, BMJ, 64>(grid, st, stream, am, bm, p);       \
+  if (bn == 128) return launch_inst<MODE_GEMM, AM, BMJ, 128>(grid, st, stream, am, bm, p);     \
+  return launch_inst<MODE_GEMM, AM, BMJ, 256>(grid, st, stream, am, bm, p);
+  switch (key) {
+    case 0: GEMM_CASE(0, 0)
+    case 1: GEMM_CASE(0, 1)
+    case 2: GEMM_CASE(1, 0)
+    default: GEMM_CASE(1, 1)
+  }
+#undef GEMM_CASE
+}
+
+// --------------------------------------------------------------------------------------------- tiles
+// Pick the pixel box (BW,BH,BNI), BW*BH*BNI <= 128, maximising useful accumulator rows.
+static void pick_tile(int vW, int vH, int nimg, int mult, int max_ni, int* BW, int* BH, int* BNI) {
+  double best = -1;
+  *BW = 1; *BH = 1; *BNI = 1;
+  for (int bw = 1; bw <= std::min(vW, 128); ++bw)
+    for (int bh = 1; bh * bw <= 128 && bh <= vH; ++bh)
+      for (int bni = 1; bni * bh * bw <= 128 && bni <= std::min(nimg, max_ni); ++bni) {
+        if ((bw * bh * bni) % mult) continue;
+        if (bni > 1 && (bh != vH || bw != vW)) continue;      // span images only with whole planes
+        const long long tiles = 1LL * ((vW + bw - 1) / bw) * ((vH + bh - 1) / bh) * ((nimg + bni - 1) / bni);
+        double util = double(vW) * vH * nimg / (double(tiles) * 128.0);
+        util += 1e-4 * bw;                                      // prefer long contiguous rows
+        if (util > best) { best = util; *BW = bw; *BH = bh; *BNI = bni; }
+      }
+}
+
+// --------------------------------------------------------------------------------------------- CONV
+int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint, int stages_hint) {
+  ACT_CHECK(c.Cin % 64 == 0 && c.Cin >= 64, "Cin must be a multiple of 64");
+  ACT_CHECK(c.ntaps >= 1 && c.ntaps <= 16 && c.nplanes >= 1 && c.nplanes <= 4, "bad tap table");
+  if (check_epi(c.epi)) return -1;
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  int BW, BH, BNI;
+  pick_tile(c.vW, c.vH, c.NIMG, 1, 256, &BW, &BH, &BNI);
+  p.BW = BW; p.BH = BH; p.BNI = BNI;
+  p.tiles_w = (c.vW + BW - 1) / BW; p.tiles_h = (c.vH + BH - 1) / BH;
+  const int tiles_n = (c.NIMG + BNI - 1) / BNI;
+  p.NIMG = c.NIMG; p.vH = c.vH; p.vW = c.vW; p.og = c.og; p.rg = c.rg;
+  p.ntaps = c.ntaps; p.cin_blocks = c.Cin / 64; p.num_k_blocks = c.ntaps * p.cin_blocks;
+  p.N = c.Cout; p.nz0 = 1; p.ksplit = 1;
+  for (int i = 0; i < c.ntaps; ++i) p.taps[i] = c.taps[i];
+  fill_epi(p, c.epi);
+  p.vec_ok = (c.og.ld % 8 == 0) && (c.rg.ld % 8 == 0 || !(c.epi.flags & (EPI_RES_F32 | EPI_RES_BF16))) &&
+             aligned16(c.epi.out_f32) && aligned16(c.epi.out_bf16) && aligned16(c.epi.res_f32) &&
+             aligned16(c.epi.res_bf16) && aligned16(c.epi.aux_bf16);
+  const long long mtiles = 1LL * p.tiles_w * p.tiles_h * tiles_n;
+  int bn = bn_hint;
+  if (bn == 0) {
+    bn = 64;
+    const int cands[3] = {256, 128, 64};
+    for (int cc : cands) {
+      if (c.Cout < cc) continue;
+      if (mtiles * ((c.Cout + cc - 1) / cc) >= 148) { bn = cc; break; }
+    }
+  }
+  CUtensorMap am[4], bm;
+  for (int i = 0; i < 4; ++i)
+    if (plane_tmap(&am[i], c.planes[std::min(i, c.nplanes - 1)], BW, BH, BNI)) return -1;
+  if (make_tmap_2d(&bm, c.wgt, c.wgt_ld, c.Cout, c.wgt_ld, bn)) return -1;
+  dim3 grid((c.Cout + bn - 1) / bn, static_cast<unsigned>(mtiles), 1);
+  const int st = stages_hint ? stages_hint : 4;
+  if (bn == 64) return launch_inst<MODE_CONV, 0, 0, 64>(grid, st, stream, am, bm, p);
+  if (bn == 128) return launch_inst<MODE_CONV, 0, 0, 128>(grid, st, stream, am, bm, p);
+  return launch_inst<MODE_CONV, 0, 0, 256>(grid, st, stream, am, bm, p);
+}
+
+// --------------------------------------------------------------------------------------------- WGRAD
+int tc_wgrad(const WgradLaunch& w, cudaStream_t stream) {
+  ACT_CHECK(w.Cin % 64 == 0 && w.Cout % 64 == 0, "channels must be multiples of 64");
+  ACT_CHECK(w.Cin == 64 || w.Cin % 128 == 0, "Cin must be 64 or a multiple of 128");
+  ACT_CHECK(w.dw != nullptr && w.ntaps >= 1 && w.ntaps <= 16, "bad wgrad args");
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  int BW, BH, BNI;
+  pick_tile(w.dy.W, w.dy.H, 1, 16, 1, &BW, &BH, &BNI);
+  ACT_CHECK((BW * BH) % 16 == 0, "no pixel tile with a multiple of 16 pixels");
+  p.BW = BW; p.BH = BH; p.BNI = 1; p.pix_per_box = BW * BH;
+  p.tiles_w = (w.dy.W + BW - 1) / BW; p.tiles_h = (w.dy.H + BH - 1) / BH;
+  p.num_k_blocks = p.tiles_w * p.tiles_h * w.dy.N;
+  p.ntaps = w.ntaps; p.KK = w.KK; p.Cin = w.Cin; p.Cout = w.Cout; p.N = w.Cout;
+  p.taps_per_cta = (w.Cin == 64) ? 2 : 1;
+  for (int i = 0; i < w.ntaps; ++i) p.taps[i] = w.taps[i];
+  p.nz0 = 1; p.alpha = w.alpha; p.out_f32 = w.dw; p.flags = EPI_OUT_F32 | EPI_ATOMIC;
+  const int bn = (w.Cout >= 128) ? 128 : 64;
+  const int ygroups = (p.taps_per_cta == 2) ? (w.ntaps + 1) / 2 : w.ntaps * (w.Cin / 128);
+  const int xt = (w.Cout + bn - 1) / bn;
+  int ks = w.ksplit;
+  if (ks <= 0) {
+    ks = std::max(1, (2 * 148 + ygroups * xt - 1) / (ygroups * xt));
+    ks = std::min(ks, std::max(1, p.num_k_blocks / 4));
+  }
+  ks = std::min(ks, p.num_k_blocks);
+  p.ksplit = ks;
+  CUtensorMap am[4], bm;
+  for (int i = 0; i < 4; ++i)
+    if (plane_tmap(&am[i], w.planes[std::min(i, w.nplanes - 1)], BW, BH, 1)) return -1;
+  if (plane_tmap(&bm, w.dy, BW, BH, 1)) return -1;
+  dim3 grid(xt, ygroups, ks);
+  if (bn == 64) return launch_inst<MODE_WGRAD, 1, 1, 64>(grid, 3, stream, am, bm, p);
+  return launch_inst<MODE_WGRAD, 1, 1, 128>(grid, 3, stream, am, bm, p);
+}
+
+}  // namespace act

@@ -1,0 +1,71 @@
+"""Per-kernel Python entry points over the C ABI (torch tensors in, raw pointers out).
+
+Used by the parity tests and by host code that needs a single kernel; the full policy step goes through the
+engine entry points (``act_engine_*``) instead.  Everything here requires CUDA tensors."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import (EPI_ATOMIC, EPI_BIAS, EPI_MASK_POS, EPI_OUT_BF16, EPI_OUT_F32, EPI_RELU, EPI_RES_BF16,
+                   EPI_RES_F32, EPI_SCALE, Epilogue, check)
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    if t is None:
+        return None
+    assert t.is_cuda, "act_plus_plus_b200 ops need CUDA tensors (no CPU fallback)"
+    return t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def make_epilogue(out_f32=None, out_bf16=None, bias=None, scale=None, res_f32=None, res_bf16=None, aux_bf16=None,
+                  relu=False, alpha=1.0, atomic=False, ldc=0, ldr=0, osz0=0, osz1=0, rsz0=0, rsz1=0) -> Epilogue:
+    e = Epilogue()
+    f = 0
+    if out_f32 is not None: f |= EPI_OUT_F32
+    if out_bf16 is not None: f |= EPI_OUT_BF16
+    if bias is not None: f |= EPI_BIAS
+    if scale is not None: f |= EPI_SCALE
+    if res_f32 is not None: f |= EPI_RES_F32
+    if res_bf16 is not None: f |= EPI_RES_BF16
+    if aux_bf16 is not None: f |= EPI_MASK_POS
+    if relu: f |= EPI_RELU
+    if atomic: f |= EPI_ATOMIC
+    e.flags, e.alpha = f, alpha
+    e.bias, e.scale, e.res_f32, e.res_bf16 = _ptr(bias), _ptr(scale), _ptr(res_f32), _ptr(res_bf16)
+    e.aux_bf16, e.out_f32, e.out_bf16 = _ptr(aux_bf16), _ptr(out_f32), _ptr(out_bf16)
+    e.ldc, e.ldr, e.osz0, e.osz1, e.rsz0, e.rsz1 = ldc, ldr, osz0, osz1, rsz0, rsz1
+    return e
+
+
+def tc_gemm_raw(M, N, K, nz0, nz1, A, a_mn, lda, a_sz0, a_sz1, B, b_mn, ldb, b_sz0, b_sz1, epi: Epilogue,
+                ksplit=1, bn=0, stages=0):
+    rc = _lib.lib().act_tc_gemm(M, N, K, nz0, nz1, _ptr(A), a_mn, lda, a_sz0, a_sz1, _ptr(B), b_mn, ldb, b_sz0,
+                                b_sz1, C.byref(epi), ksplit, bn, stages, _stream())
+    check(rc, "act_tc_gemm")
+
+
+def tc_gemm(a: torch.Tensor, b: torch.Tensor, a_mn=False, b_mn=False, out_dtype=torch.float32, bn=0, stages=0,
+            ksplit=1, **epi_kw) -> torch.Tensor:
+    """Batched D = A @ B^T.  a: [Z,M,K] (or [Z,K,M] if a_mn), b: [Z,N,K] (or [Z,K,N] if b_mn); bf16, contiguous."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    if a.dim() == 2: a = a[None]
+    if b.dim() == 2: b = b[None]
+    Z = a.shape[0]
+    M, K = (a.shape[2], a.shape[1]) if a_mn else (a.shape[1], a.shape[2])
+    N = b.shape[2] if b_mn else b.shape[1]
+    out = torch.zeros((Z, M, N), dtype=out_dtype, device=a.device)
+    kw = dict(epi_kw)
+    if out_dtype == torch.float32: kw["out_f32"] = out
+    else: kw["out_bf16"] = out
+    epi = make_epilogue(ldc=N, osz0=M * N, ldr=kw.pop("ldr", N), rsz0=kw.pop("rsz0", M * N), **kw)
+    tc_gemm_raw(M, N, K, Z, 1, a, int(a_mn), a.stride(1), a.stride(0), 0, b, int(b_mn), b.stride(1), b.stride(0), 0,
+                epi, ksplit, bn, stages)
+    return out
