@@ -1,6 +1,8 @@
 // extern "C" surface of libact_b200.so (declared in include/act_b200.h).
 #include "../../include/act_b200.h"
 #include "tc_api.h"
+#include "conv_ops.h"
+#include "kernels.h"
 
 using namespace act;
 
@@ -23,4 +25,30 @@ extern "C" int act_tc_gemm(int M, int N, int K, int nz0, int nz1, const void* A,
   a.ptr = static_cast<const bf16*>(A); a.mn_major = a_mn; a.ld = lda; a.sz0 = a_sz0; a.sz1 = a_sz1;
   b.ptr = static_cast<const bf16*>(B); b.mn_major = b_mn; b.ld = ldb; b.sz0 = b_sz0; b.sz1 = b_sz1;
   return tc_gemm(M, N, K, nz0, nz1, a, b, to_epi(epi), ksplit, static_cast<cudaStream_t>(stream), bn_hint, stages_hint);
+}
+
+#define ST(s) static_cast<cudaStream_t>(s)
+#define BF(p) static_cast<const bf16*>(p)
+
+extern "C" int act_cast_bf16(const float* src, void* dst, int64_t n, void* stream) {
+  return cast_bf16(src, static_cast<bf16*>(dst), n, ST(stream));
+}
+extern "C" int act_pack_conv_weights(const float* w, const float* scale, void* wpk, void* wpkt, int Cout, int Cin, int KK,
+                                     void* stream) {
+  return pack_conv_weights(w, scale, static_cast<bf16*>(wpk), static_cast<bf16*>(wpkt), Cout, Cin, KK, ST(stream));
+}
+extern "C" int act_conv_fwd(int N, int H, int W, int Cin, int Cout, int KH, int stride, int pad, const void* x,
+                            const void* wpk, const act_epilogue* epi, void* stream) {
+  ConvShape s{N, H, W, Cin, Cout, KH, stride, pad};
+  return conv_fwd(s, BF(x), BF(wpk), to_epi(epi), ST(stream));
+}
+extern "C" int act_conv_dgrad(int N, int H, int W, int Cin, int Cout, int KH, int stride, int pad, const void* dy,
+                              const void* wpkt, const act_epilogue* epi, const void* res_compact, void* stream) {
+  ConvShape s{N, H, W, Cin, Cout, KH, stride, pad};
+  return conv_dgrad(s, BF(dy), BF(wpkt), to_epi(epi), BF(res_compact), ST(stream));
+}
+extern "C" int act_conv_wgrad(int N, int H, int W, int Cin, int Cout, int KH, int stride, int pad, const void* x,
+                              const void* dy, float* dw, float alpha, const float* scale, void* stream) {
+  ConvShape s{N, H, W, Cin, Cout, KH, stride, pad};
+  return conv_wgrad(s, BF(x), BF(dy), dw, alpha, scale, ST(stream));
 }

@@ -1,0 +1,120 @@
+// Convolution forward / data-gradient / weight-gradient as tap tables over the shared tcgen05 kernel.
+// Activations NHWC bf16; packed weights:
+//   forward  : wpk  [Cout][(kh*KW+kw)*Cin + ci]
+//   dgrad    : wpkt [Cin ][(kh*KW+kw)*Cout + co]   (optionally pre-multiplied by the FrozenBN scale of co)
+// Stride-2 access goes through four parity planes of the NHWC tensor (plain tiled TMA maps, zero OOB fill = padding).
+#include "conv_ops.h"
+
+namespace act {
+
+static int floordiv(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
+static int pmod(int a, int b) { int r = a % b; return r < 0 ? r + b : r; }
+
+static void full_plane(PlaneDesc* pl, const bf16* ptr, int N, int H, int W, int C) {
+  pl->ptr = ptr; pl->C = C; pl->W = W; pl->H = H; pl->N = N;
+  pl->sW = C; pl->sH = 1LL * W * C; pl->sN = 1LL * H * W * C;
+}
+// parity plane (ph,pw) of an [N,H,W,C] tensor with even H, W
+static void parity_plane(PlaneDesc* pl, const bf16* ptr, int N, int H, int W, int C, int ph, int pw) {
+  pl->ptr = ptr + (1LL * ph * W + pw) * C; pl->C = C; pl->W = W / 2; pl->H = H / 2; pl->N = N;
+  pl->sW = 2LL * C; pl->sH = 2LL * W * C; pl->sN = 1LL * H * W * C;
+}
+
+int conv_out_dim(int in, int k, int stride, int pad) { return (in + 2 * pad - k) / stride + 1; }
+
+// Builds planes + taps for reading the conv *input* x at the positions each output pixel needs.
+static int input_taps(const ConvShape& s, const bf16* x, PlaneDesc* planes, int* nplanes, TapDesc* taps, int* ntaps) {
+  ACT_CHECK(s.stride == 1 || s.stride == 2, "stride must be 1 or 2");
+  ACT_CHECK(s.KH == 1 || s.KH == 3, "kernel must be 1x1 or 3x3");
+  if (s.stride == 1) {
+    full_plane(&planes[0], x, s.N, s.H, s.W, s.Cin);
+    *nplanes = 1;
+  } else {
+    ACT_CHECK(s.H % 2 == 0 && s.W % 2 == 0, "stride-2 conv needs even input dims");
+    for (int ph = 0; ph < 2; ++ph)
+      for (int pw = 0; pw < 2; ++pw) parity_plane(&planes[ph * 2 + pw], x, s.N, s.H, s.W, s.Cin, ph, pw);
+    *nplanes = 4;
+  }
+  int n = 0;
+  for (int kh = 0; kh < s.KH; ++kh)
+    for (int kw = 0; kw < s.KH; ++kw) {
+      TapDesc t;
+      const int oy = kh - s.pad, ox = kw - s.pad;
+      if (s.stride == 1) { t.map = 0; t.dh = oy; t.dw = ox; }
+      else { t.map = pmod(oy, 2) * 2 + pmod(ox, 2); t.dh = floordiv(oy, 2); t.dw = floordiv(ox, 2); }
+      t.wslot = kh * s.KH + kw;
+      taps[n++] = t;
+    }
+  *ntaps = n;
+  return 0;
+}
+
+int conv_fwd(const ConvShape& s, const bf16* x, const bf16* wpk, const EpiDesc& epi, cudaStream_t stream) {
+  ConvLaunch c;
+  if (input_taps(s, x, c.planes, &c.nplanes, c.taps, &c.ntaps)) return -1;
+  const int Ho = conv_out_dim(s.H, s.KH, s.stride, s.pad), Wo = conv_out_dim(s.W, s.KH, s.stride, s.pad);
+  c.Cin = s.Cin; c.Cout = s.Cout; c.wgt = wpk; c.wgt_ld = 1LL * s.KH * s.KH * s.Cin;
+  c.vW = Wo; c.vH = Ho; c.NIMG = s.N;
+  c.og = PixGeom{Ho, Wo, 1, 1, 0, 0, s.Cout};
+  c.rg = c.og;
+  c.epi = epi;
+  return tc_conv(c, stream);
+}
+
+// dx[n,y,x,ci] = sum_{kh,kw,co} dy[n,(y+pad-kh)/s,(x+pad-kw)/s,co] * W[co,ci,kh,kw]   (exact divisions only)
+// epi.res_* (optional) is indexed like dx when stride == 1; for stride 2 `res_compact` is a [N,H/2,W/2,Cin]
+// tensor added to parity class (0,0) only (the 1x1/s2 downsample branch).  epi.aux_bf16 masks with dx geometry.
+int conv_dgrad(const ConvShape& s, const bf16* dy, const bf16* wpkt, EpiDesc epi, const bf16* res_compact,
+               cudaStream_t stream) {
+  const int Ho = conv_out_dim(s.H, s.KH, s.stride, s.pad), Wo = conv_out_dim(s.W, s.KH, s.stride, s.pad);
+  const int nclass = (s.stride == 1) ? 1 : 4;
+  for (int cls = 0; cls < nclass; ++cls) {
+    const int py = cls >> 1, px = cls & 1;
+    ConvLaunch c;
+    full_plane(&c.planes[0], dy, s.N, Ho, Wo, s.Cout);
+    c.nplanes = 1;
+    int n = 0;
+    for (int kh = 0; kh < s.KH; ++kh)
+      for (int kw = 0; kw < s.KH; ++kw) {
+        const int ay = py + s.pad - kh, ax = px + s.pad - kw;
+        if (s.stride == 2 && ((ay & 1) || (ax & 1))) continue;
+        TapDesc t;
+        t.map = 0; t.dh = (s.stride == 1) ? ay : ay / 2; t.dw = (s.stride == 1) ? ax : ax / 2;   // ay even -> exact
+        t.wslot = kh * s.KH + kw;
+        c.taps[n++] = t;
+      }
+    c.ntaps = n;
+    c.Cin = s.Cout; c.Cout = s.Cin; c.wgt = wpkt; c.wgt_ld = 1LL * s.KH * s.KH * s.Cout;
+    c.vW = s.W / s.stride; c.vH = s.H / s.stride; c.NIMG = s.N;
+    c.og = PixGeom{s.H, s.W, s.stride, s.stride, py, px, s.Cin};
+    c.rg = c.og;
+    c.epi = epi;
+    if (s.stride == 2) {
+      c.epi.flags &= ~(EPI_RES_F32 | EPI_RES_BF16);
+      c.epi.res_bf16 = nullptr; c.epi.res_f32 = nullptr;
+      if (cls == 0 && res_compact) {
+        c.epi.flags |= EPI_RES_BF16; c.epi.res_bf16 = res_compact;
+        c.rg = PixGeom{s.H / 2, s.W / 2, 1, 1, 0, 0, s.Cin};
+      }
+    }
+    if (n == 0) {
+      // no tap reaches this parity class (1x1/s2): dx there is the residual or zero -> handled by caller's memset
+      continue;
+    }
+    if (tc_conv(c, stream)) return -1;
+  }
+  return 0;
+}
+
+// dW[co,ci,kh,kw] += alpha * scale[co]? (scale folded by caller through alpha only) * sum_pix dy[pix,co] * x[pix(+tap),ci]
+int conv_wgrad(const ConvShape& s, const bf16* x, const bf16* dy, float* dw, float alpha, const float* scale,
+               cudaStream_t stream) {
+  WgradLaunch w;
+  if (input_taps(s, x, w.planes, &w.nplanes, w.taps, &w.ntaps)) return -1;
+  const int Ho = conv_out_dim(s.H, s.KH, s.stride, s.pad), Wo = conv_out_dim(s.W, s.KH, s.stride, s.pad);
+  full_plane(&w.dy, dy, s.N, Ho, Wo, s.Cout);
+  w.Cin = s.Cin; w.Cout = s.Cout; w.KK = s.KH * s.KH; w.dw = dw; w.alpha = alpha; w.scale = scale;
+  return tc_wgrad(w, stream);
+}
+
+}  // namespace act

@@ -79,6 +79,7 @@ struct WgradLaunch {
   int Cin = 0, Cout = 0, KK = 0;        // dW fp32 [Cout][Cin][KK], accumulated with atomics (caller zeroes it)
   float* dw = nullptr;
   float alpha = 1.f;
+  const float* scale = nullptr;         // optional per-Cout factor (FrozenBN scale)
   int ksplit = 0;                       // 0 -> heuristic
 };
 int tc_wgrad(const WgradLaunch& w, cudaStream_t stream);

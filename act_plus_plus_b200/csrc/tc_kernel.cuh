@@ -264,7 +264,10 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
           const int co = gn0 + j;
-          if (co < p.Cout) atomicAdd(p.out_f32 + static_cast<long long>(co) * p.Cin * p.KK + o_off, __uint_as_float(v[j]) * p.alpha);
+          if (co < p.Cout) {
+            const float sc = (p.flags & EPI_SCALE) ? __ldg(p.scale + co) * p.alpha : p.alpha;
+            atomicAdd(p.out_f32 + static_cast<long long>(co) * p.Cin * p.KK + o_off, __uint_as_float(v[j]) * sc);
+          }
         }
         continue;
       }

@@ -69,3 +69,48 @@ def tc_gemm(a: torch.Tensor, b: torch.Tensor, a_mn=False, b_mn=False, out_dtype=
     tc_gemm_raw(M, N, K, Z, 1, a, int(a_mn), a.stride(1), a.stride(0), 0, b, int(b_mn), b.stride(1), b.stride(0), 0,
                 epi, ksplit, bn, stages)
     return out
+
+
+# ------------------------------------------------------------------------------------------- convolutions
+def pack_conv_weights(w: torch.Tensor, scale: Optional[torch.Tensor] = None):
+    """fp32 [Cout,Cin,KH,KW] -> (wpk [Cout, KK*Cin], wpkt [Cin, KK*Cout] * scale) bf16."""
+    Cout, Cin, KH, KW = w.shape
+    w = w.contiguous()
+    wpk = torch.empty((Cout, KH * KW * Cin), dtype=torch.bfloat16, device=w.device)
+    wpkt = torch.empty((Cin, KH * KW * Cout), dtype=torch.bfloat16, device=w.device)
+    check(_lib.lib().act_pack_conv_weights(_ptr(w), _ptr(scale), _ptr(wpk), _ptr(wpkt), Cout, Cin, KH * KW, _stream()),
+          "act_pack_conv_weights")
+    return wpk, wpkt
+
+
+def conv_fwd(x, wpk, Cout, KH, stride, pad, out_dtype=torch.bfloat16, **epi_kw):
+    """x NHWC bf16 -> y NHWC."""
+    N, H, W, Cin = x.shape
+    Ho, Wo = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KH) // stride + 1
+    y = torch.empty((N, Ho, Wo, Cout), dtype=out_dtype, device=x.device)
+    kw = dict(epi_kw)
+    kw["out_bf16" if out_dtype == torch.bfloat16 else "out_f32"] = y
+    epi = make_epilogue(**kw)
+    check(_lib.lib().act_conv_fwd(N, H, W, Cin, Cout, KH, stride, pad, _ptr(x), _ptr(wpk), C.byref(epi), _stream()),
+          "act_conv_fwd")
+    return y
+
+
+def conv_dgrad(dy, wpkt, H, W, Cin, KH, stride, pad, res_compact=None, **epi_kw):
+    """dy NHWC bf16 [N,Ho,Wo,Cout] -> dx NHWC bf16 [N,H,W,Cin]."""
+    N, Ho, Wo, Cout = dy.shape
+    dx = torch.zeros((N, H, W, Cin), dtype=torch.bfloat16, device=dy.device)
+    epi = make_epilogue(out_bf16=dx, **epi_kw)
+    check(_lib.lib().act_conv_dgrad(N, H, W, Cin, Cout, KH, stride, pad, _ptr(dy), _ptr(wpkt), C.byref(epi),
+                                    _ptr(res_compact), _stream()), "act_conv_dgrad")
+    return dx
+
+
+def conv_wgrad(x, dy, KH, stride, pad, alpha=1.0, scale=None, dw=None):
+    N, H, W, Cin = x.shape
+    Cout = dy.shape[3]
+    if dw is None:
+        dw = torch.zeros((Cout, Cin, KH, KH), dtype=torch.float32, device=x.device)
+    check(_lib.lib().act_conv_wgrad(N, H, W, Cin, Cout, KH, stride, pad, _ptr(x), _ptr(dy), _ptr(dw), alpha,
+                                    _ptr(scale), _stream()), "act_conv_wgrad")
+    return dw

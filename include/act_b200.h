@@ -46,6 +46,26 @@ int act_tc_gemm(int M, int N, int K, int nz0, int nz1,
                 const void* B, int b_mn, int64_t ldb, int64_t b_sz0, int64_t b_sz1,
                 const act_epilogue* epi, int ksplit, int bn_hint, int stages_hint, void* stream);
 
+
+/* ---- convolutions over NHWC bf16 (implicit GEMM on tcgen05, TMA tap boxes).  Replace torchvision resnet18's
+ *      nn.Conv2d + FrozenBatchNorm2d (backbone.py:47-57,121-124) and their autograd backward (cuDNN in the
+ *      reference).  Kernels are 1x1 or 3x3, stride 1 or 2.
+ *      wpk  : bf16 [Cout][(kh*KW+kw)*Cin + ci]           (forward operand)
+ *      wpkt : bf16 [Cin][(kh*KW+kw)*Cout + co] * scale   (data-gradient operand)                         ---- */
+int act_cast_bf16(const float* src, void* dst, int64_t n, void* stream);
+int act_pack_conv_weights(const float* w, const float* scale, void* wpk, void* wpkt, int Cout, int Cin, int KK,
+                          void* stream);
+/* y[N,Ho,Wo,Cout] = epilogue(conv(x[N,H,W,Cin], w)); epilogue geometry (ldc etc.) is implied by the shape. */
+int act_conv_fwd(int N, int H, int W, int Cin, int Cout, int KH, int stride, int pad, const void* x, const void* wpk,
+                 const act_epilogue* epi, void* stream);
+/* dx[N,H,W,Cin] = epilogue(conv_transpose(dy[N,Ho,Wo,Cout], w)); for stride 2 `res_compact` ([N,H/2,W/2,Cin] bf16,
+ * may be NULL) is added on the even/even pixels and epi's own residual is ignored. */
+int act_conv_dgrad(int N, int H, int W, int Cin, int Cout, int KH, int stride, int pad, const void* dy,
+                   const void* wpkt, const act_epilogue* epi, const void* res_compact, void* stream);
+/* dw[Cout][Cin][KH][KW] (fp32) += alpha * scale[co] * sum_pixels dy * x  (atomic accumulation). */
+int act_conv_wgrad(int N, int H, int W, int Cin, int Cout, int KH, int stride, int pad, const void* x, const void* dy,
+                   float* dw, float alpha, const float* scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
