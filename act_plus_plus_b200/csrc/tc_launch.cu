@@ -176,8 +176,10 @@ int tc_gemm(int M, int N, int K, int nz0, int nz1, const MatDesc& A, const MatDe
 static void pick_tile(int vW, int vH, int nimg, int mult, int max_ni, int* BW, int* BH, int* BNI) {
   double best = -1;
   *BW = 1; *BH = 1; *BNI = 1;
-  for (int bw = 1; bw <= std::min(vW, 128); ++bw)
-    for (int bh = 1; bh * bw <= 128 && bh <= vH; ++bh)
+  // boxes may overhang the plane (TMA zero-fills); needed when the pixel count must be a multiple of `mult`
+  const int maxw = (mult > 1) ? std::max(vW, mult) : vW, maxh = (mult > 1) ? std::max(vH, mult) : vH;
+  for (int bw = 1; bw <= std::min(maxw, 128); ++bw)
+    for (int bh = 1; bh * bw <= 128 && bh <= maxh; ++bh)
       for (int bni = 1; bni * bh * bw <= 128 && bni <= std::min(nimg, max_ni); ++bni) {
         if ((bw * bh * bni) % mult) continue;
         if (bni > 1 && (bh != vH || bw != vW)) continue;      // span images only with whole planes

@@ -7,7 +7,7 @@ if [ ${#files[@]} -eq 0 ]; then files=(tests/test_*.py); fi
 : > gpurun_out/tests_summary.txt
 for f in "${files[@]}"; do
   name=$(basename "$f" .py)
-  timeout 600 python -m pytest "$f" -q -m gpu -x --no-header -p no:cacheprovider > "gpurun_out/tests_${name}.log" 2>&1
+  timeout 600 python -m pytest "$f" -q -m gpu --no-header -p no:cacheprovider > "gpurun_out/tests_${name}.log" 2>&1
   rc=$?
   echo "$name rc=$rc $(tail -1 gpurun_out/tests_${name}.log)" | tee -a gpurun_out/tests_summary.txt
 done
