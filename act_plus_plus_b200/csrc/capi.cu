@@ -52,3 +52,65 @@ extern "C" int act_conv_wgrad(int N, int H, int W, int Cin, int Cout, int KH, in
   ConvShape s{N, H, W, Cin, Cout, KH, stride, pad};
   return conv_wgrad(s, BF(x), BF(dy), dw, alpha, scale, ST(stream));
 }
+
+#define BFM(p) static_cast<bf16*>(p)
+extern "C" int act_ln_fwd(const float* t, const float* gamma, const float* beta, const float* pos, int L, float* y,
+                          void* yb, void* ypb, float* mean, float* rstd, int M, int D, void* stream) {
+  return ln_fwd(t, gamma, beta, pos, L, y, BFM(yb), BFM(ypb), mean, rstd, M, D, ST(stream));
+}
+extern "C" int act_ln_bwd(const float* dy, const float* dy2, const float* t, const float* mean, const float* rstd,
+                          const float* gamma, float* dt, void* dtb, float* dgamma, float* dbeta, int M, int D, void* stream) {
+  return ln_bwd(dy, dy2, t, mean, rstd, gamma, dt, BFM(dtb), dgamma, dbeta, M, D, ST(stream));
+}
+extern "C" int act_add_pos_cast(const float* x, const float* pos, int L, void* xb, void* xpb, int M, int D, void* stream) {
+  return add_pos_cast(x, pos, L, BFM(xb), BFM(xpb), M, D, ST(stream));
+}
+extern "C" int act_softmax_fwd(const float* S, const uint8_t* mask, void* P, int R, int L, int Lp, int rpb, void* stream) {
+  return softmax_fwd(S, mask, BFM(P), R, L, Lp, rpb, ST(stream));
+}
+extern "C" int act_softmax_bwd(const void* P, const float* dP, void* dS, int R, int L, int Lp, float scale, void* stream) {
+  return softmax_bwd(BF(P), dP, BFM(dS), R, L, Lp, scale, ST(stream));
+}
+extern "C" int act_colsum_bf16(const void* X, int64_t ld, int M, int N, float* out, void* stream) {
+  return colsum_bf16(BF(X), ld, M, N, out, ST(stream));
+}
+static IdxMap to_map(const int64_t* m) { IdxMap r; r.rpb = static_cast<int>(m[0]); r.bs = m[1]; r.s = m[2]; return r; }
+extern "C" int act_sgemm(int I, int J, int R, const float* A, const int64_t* a_i, const int64_t* a_r, const float* B,
+                         const int64_t* b_r, const int64_t* b_j, float* C, const int64_t* c_i, const int64_t* c_j,
+                         const float* bias, float alpha, int accumulate, void* stream) {
+  SgemmArgs a;
+  a.I = I; a.J = J; a.R = R; a.A = A; a.ai = to_map(a_i); a.ar = to_map(a_r); a.B = B; a.br = to_map(b_r);
+  a.bj = to_map(b_j); a.C = C; a.ci = to_map(c_i); a.cj = to_map(c_j); a.bias = bias; a.alpha = alpha; a.accumulate = accumulate;
+  return sgemm_generic(a, ST(stream));
+}
+extern "C" int act_loss(const float* a_hat, const float* actions, int64_t abs_, const uint8_t* is_pad, int64_t pbs,
+                        const float* mu, const float* logvar, int B, int nq, int A, int Z, float klw, float gscale,
+                        float* losses, float* d_a_hat, float* d_mu, float* d_logvar, void* stream) {
+  return act::act_loss(a_hat, actions, abs_, is_pad, pbs, mu, logvar, B, nq, A, Z, klw, gscale, losses, d_a_hat, d_mu,
+                       d_logvar, ST(stream));
+}
+extern "C" int act_reparam_fwd(const float* info, const float* eps, float* mu, float* logvar, float* z, int B, int Z, void* stream) {
+  return reparam_fwd(info, eps, mu, logvar, z, B, Z, ST(stream));
+}
+extern "C" int act_reparam_bwd(const float* dz, const float* eps, const float* logvar, const float* dmu, const float* dlv,
+                               float* d_info, int B, int Z, void* stream) {
+  return reparam_bwd(dz, eps, logvar, dmu, dlv, d_info, B, Z, ST(stream));
+}
+extern "C" int act_maxpool_fwd(const void* x, void* y, uint8_t* idx, int N, int H, int W, int C, void* stream) {
+  return maxpool_fwd(BF(x), BFM(y), idx, N, H, W, C, ST(stream));
+}
+extern "C" int act_maxpool_bwd(const void* dy, const uint8_t* idx, const void* x, void* dx, int N, int H, int W, int C, void* stream) {
+  return maxpool_bwd(BF(dy), idx, BF(x), BFM(dx), N, H, W, C, ST(stream));
+}
+extern "C" int act_im2col_conv1(const float* image, int64_t img_bs, void* out, int B, int H, int W, int KP, void* stream) {
+  return im2col_conv1(image, img_bs, BFM(out), B, H, W, KP, ST(stream));
+}
+extern "C" int act_adamw_step(float* p, const float* g, float* m, float* v, void* shadow, int64_t n, float lr, float b1,
+                              float b2, float eps, float wd, int step, int mode, void* stream) {
+  AdamWArgs a{p, g, m, v, BFM(shadow), n, lr, b1, b2, eps, wd, step, mode};
+  return adamw_step(a, ST(stream));
+}
+extern "C" int act_temporal_agg_step(float* ring, const float* chunks, const int* t, double* out, int E, int nq, int A,
+                                     double k, void* stream) {
+  return temporal_agg_step(ring, chunks, t, out, E, nq, A, k, ST(stream));
+}

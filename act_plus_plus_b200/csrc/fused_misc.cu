@@ -1,0 +1,295 @@
+// Small fused kernels of the ACT path: strided fp32 mini-GEMM (the K<=32 / N<=64 projections and their gradients),
+// L1+KL loss with its gradients, reparametrisation, max-pool fwd/bwd, conv1 im2col with fused ImageNet normalise.
+#include "kernels.h"
+
+namespace act {
+
+// ------------------------------------------------------------------------------------------ mini GEMM (fp32)
+// C(i,j) (+)= alpha * sum_r A(i,r) * B(r,j) (+ bias[j]); every index uses a batched-affine address
+// off(idx) = (idx / rpb) * bs + (idx % rpb) * s, so token-buffer rows, transposes and broadcasts need no copies.
+__device__ __forceinline__ long long ioff(const IdxMap& m, int idx) {
+  return static_cast<long long>(idx / m.rpb) * m.bs + static_cast<long long>(idx % m.rpb) * m.s;
+}
+__global__ void sgemm_generic_kernel(SgemmArgs a) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = blockIdx.y;
+  if (j >= a.J || i >= a.I) return;
+  const int rchunk = (a.R + gridDim.z - 1) / gridDim.z;
+  const int r0 = blockIdx.z * rchunk, r1 = min(a.R, r0 + rchunk);
+  const float* Ai = a.A + ioff(a.ai, i);
+  const float* Bj = a.B + ioff(a.bj, j);
+  float acc = 0.f;
+  for (int r = r0; r < r1; ++r) acc += Ai[ioff(a.ar, r)] * Bj[ioff(a.br, r)];
+  acc *= a.alpha;
+  if (a.bias && blockIdx.z == 0) acc += a.bias[j];
+  float* c = a.C + ioff(a.ci, i) + ioff(a.cj, j);
+  if (a.accumulate || gridDim.z > 1) atomicAdd(c, acc);
+  else *c = acc;
+}
+int sgemm_generic(const SgemmArgs& a, cudaStream_t st) {
+  if (a.I <= 0 || a.J <= 0) return 0;
+  int split = 1;
+  if (a.R > 512) { split = std::min(64, (a.R + 255) / 256); }
+  ACT_CHECK(split == 1 || a.accumulate, "split reduction needs accumulate (zero-initialised output)");
+  const int threads = a.J >= 128 ? 128 : (a.J >= 64 ? 64 : 32);
+  dim3 grid((a.J + threads - 1) / threads, a.I, split);
+  ACT_CHECK(a.I <= 65535, "sgemm_generic: too many rows");
+  sgemm_generic_kernel<<<grid, threads, 0, st>>>(a);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ loss
+// policy.py:314-318 + 378-391:  l1 = mean over B*nq*A of |a - a_hat| * ~pad ; kl = mean_b sum_z -0.5(1+lv-mu^2-e^lv)
+// loss = l1 + kl_weight * kl.  Also emits dL/da_hat, and the KL part of dL/dmu, dL/dlogvar (scaled by `gscale`).
+__global__ void act_loss_kernel(const float* __restrict__ a_hat, const float* __restrict__ actions, long long act_bs,
+                                const uint8_t* __restrict__ is_pad, long long pad_bs, const float* __restrict__ mu,
+                                const float* __restrict__ logvar, int B, int nq, int A, int Z, float kl_weight,
+                                float gscale, float* __restrict__ losses, float* __restrict__ d_a_hat,
+                                float* __restrict__ d_mu, float* __restrict__ d_logvar) {
+  __shared__ float red[32];
+  __shared__ float tot[2];
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const long long n = 1LL * B * nq * A;
+  const float inv_n = 1.f / static_cast<float>(n);
+  float s = 0.f;
+  for (long long i = tid; i < n; i += nthr) {
+    const int a = static_cast<int>(i % A);
+    const long long r = i / A;
+    const int q = static_cast<int>(r % nq), b = static_cast<int>(r / nq);
+    const float diff = a_hat[i] - actions[b * act_bs + static_cast<long long>(q) * A + a];
+    const bool pad = is_pad[b * pad_bs + q] != 0;
+    if (!pad) s += fabsf(diff);
+    if (d_a_hat) d_a_hat[i] = pad ? 0.f : gscale * inv_n * ((diff > 0.f) ? 1.f : (diff < 0.f ? -1.f : 0.f));
+  }
+  float k = 0.f;
+  for (int i = tid; i < B * Z; i += nthr) {
+    const float m = mu[i], lv = logvar[i], e = __expf(lv);
+    k += -0.5f * (1.f + lv - m * m - e);
+    if (d_mu) d_mu[i] = gscale * kl_weight * m / B;
+    if (d_logvar) d_logvar[i] = gscale * kl_weight * 0.5f * (e - 1.f) / B;
+  }
+  for (int pass = 0; pass < 2; ++pass) {
+    float v = pass == 0 ? s : k;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((tid & 31) == 0) red[tid >> 5] = v;
+    __syncthreads();
+    if (tid < 32) {
+      float w = tid < (nthr >> 5) ? red[tid] : 0.f;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xffffffffu, w, o);
+      if (tid == 0) tot[pass] = w;
+    }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    const float l1 = tot[0] * inv_n, kl = tot[1] / B;
+    losses[0] = l1; losses[1] = kl; losses[2] = l1 + kl_weight * kl;
+  }
+}
+int act_loss(const float* a_hat, const float* actions, long long act_bs, const uint8_t* is_pad, long long pad_bs,
+             const float* mu, const float* logvar, int B, int nq, int A, int Z, float kl_weight, float gscale,
+             float* losses, float* d_a_hat, float* d_mu, float* d_logvar, cudaStream_t st) {
+  act_loss_kernel<<<1, 1024, 0, st>>>(a_hat, actions, act_bs, is_pad, pad_bs, mu, logvar, B, nq, A, Z, kl_weight, gscale,
+                                      losses, d_a_hat, d_mu, d_logvar);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ latent
+// detr_vae.py:19-22,147-150: mu = info[:, :Z], logvar = info[:, Z:], z = mu + exp(logvar/2) * eps
+__global__ void reparam_fwd_kernel(const float* info, const float* eps, float* mu, float* logvar, float* z, int B, int Z) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * Z) return;
+  const int b = i / Z, k = i % Z;
+  const float m = info[b * 2 * Z + k], lv = info[b * 2 * Z + Z + k];
+  mu[i] = m; logvar[i] = lv;
+  z[i] = m + __expf(0.5f * lv) * eps[i];
+}
+int reparam_fwd(const float* info, const float* eps, float* mu, float* logvar, float* z, int B, int Z, cudaStream_t st) {
+  reparam_fwd_kernel<<<(B * Z + 127) / 128, 128, 0, st>>>(info, eps, mu, logvar, z, B, Z);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+// d_info[:, :Z] = d_mu_kl + dz ; d_info[:, Z:] = d_lv_kl + dz * eps * 0.5 * exp(lv/2)
+__global__ void reparam_bwd_kernel(const float* dz, const float* eps, const float* logvar, const float* d_mu_kl,
+                                   const float* d_lv_kl, float* d_info, int B, int Z) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * Z) return;
+  const int b = i / Z, k = i % Z;
+  d_info[b * 2 * Z + k] = d_mu_kl[i] + dz[i];
+  d_info[b * 2 * Z + Z + k] = d_lv_kl[i] + dz[i] * eps[i] * 0.5f * __expf(0.5f * logvar[i]);
+}
+int reparam_bwd(const float* dz, const float* eps, const float* logvar, const float* d_mu_kl, const float* d_lv_kl,
+                float* d_info, int B, int Z, cudaStream_t st) {
+  reparam_bwd_kernel<<<(B * Z + 127) / 128, 128, 0, st>>>(dz, eps, logvar, d_mu_kl, d_lv_kl, d_info, B, Z);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ max-pool 3x3 / s2 / p1
+// NHWC bf16, 8 channels (16 B) per thread.  Forward also records the arg-max tap (first max in kh,kw scan order,
+// as torch) so the backward is a gather.
+__global__ void maxpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, int N,
+                                   int H, int W, int C, int Ho, int Wo) {
+  const int C8 = C / 8;
+  const long long total = 1LL * N * Ho * Wo * C8;
+  for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
+    const int c8 = static_cast<int>(i % C8);
+    long long r = i / C8;
+    const int ox = static_cast<int>(r % Wo); r /= Wo;
+    const int oy = static_cast<int>(r % Ho);
+    const int n = static_cast<int>(r / Ho);
+    float best[8];
+    uint8_t bi[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { best[e] = -INFINITY; bi[e] = 0; }
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const int iy = 2 * oy + kh - 1;
+      if (iy < 0 || iy >= H) continue;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int ix = 2 * ox + kw - 1;
+        if (ix < 0 || ix >= W) continue;
+        const uint4 v = *reinterpret_cast<const uint4*>(x + ((1LL * n * H + iy) * W + ix) * C + c8 * 8);
+        const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = __bfloat1622float2(h2[e]);
+          if (f.x > best[2 * e]) { best[2 * e] = f.x; bi[2 * e] = kh * 3 + kw; }
+          if (f.y > best[2 * e + 1]) { best[2 * e + 1] = f.y; bi[2 * e + 1] = kh * 3 + kw; }
+        }
+      }
+    }
+    uint4 o;
+    __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(best[2 * e], best[2 * e + 1]);
+    const long long ooff = ((1LL * n * Ho + oy) * Wo + ox) * C + c8 * 8;
+    *reinterpret_cast<uint4*>(y + ooff) = o;
+    if (idx) {
+      uint2 p;
+      p.x = bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24);
+      p.y = bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24);
+      *reinterpret_cast<uint2*>(idx + ooff) = p;
+    }
+  }
+}
+int maxpool_fwd(const bf16* x, bf16* y, uint8_t* idx, int N, int H, int W, int C, cudaStream_t st) {
+  ACT_CHECK(C % 8 == 0, "maxpool needs C % 8 == 0");
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  const long long total = 1LL * N * Ho * Wo * (C / 8);
+  const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
+  maxpool_fwd_kernel<<<blocks, 256, 0, st>>>(x, y, idx, N, H, W, C, Ho, Wo);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// dx[n,iy,ix,c] = (x > 0 ? 1 : 0) * sum over windows whose arg-max is (iy,ix) of dy   (ReLU of the conv1 block fused)
+__global__ void maxpool_bwd_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx, const bf16* __restrict__ x,
+                                   bf16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo) {
+  const int C8 = C / 8;
+  const long long total = 1LL * N * H * W * C8;
+  for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
+    const int c8 = static_cast<int>(i % C8);
+    long long r = i / C8;
+    const int ix = static_cast<int>(r % W); r /= W;
+    const int iy = static_cast<int>(r % H);
+    const int n = static_cast<int>(r / H);
+    float acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+    // windows containing row iy: 2*oy-1 <= iy <= 2*oy+1  ->  oy in [iy/2, (iy+1)/2]
+    for (int oy = iy / 2; oy <= (iy + 1) / 2; ++oy) {
+      if (oy < 0 || oy >= Ho) continue;
+      const int kh = iy - 2 * oy + 1;
+      if (kh < 0 || kh > 2) continue;
+      for (int ox = ix / 2; ox <= (ix + 1) / 2; ++ox) {
+        if (ox < 0 || ox >= Wo) continue;
+        const int kw = ix - 2 * ox + 1;
+        if (kw < 0 || kw > 2) continue;
+        const long long ooff = ((1LL * n * Ho + oy) * Wo + ox) * C + c8 * 8;
+        const uint2 p = *reinterpret_cast<const uint2*>(idx + ooff);
+        const uint4 g = *reinterpret_cast<const uint4*>(dy + ooff);
+        const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&g);
+        const int me = kh * 3 + kw;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int id = ((e < 4 ? p.x : p.y) >> (8 * (e & 3))) & 0xff;
+          if (id == me) {
+            const float2 f = __bfloat1622float2(g2[e >> 1]);
+            acc[e] += (e & 1) ? f.y : f.x;
+          }
+        }
+      }
+    }
+    const long long xoff = ((1LL * n * H + iy) * W + ix) * C + c8 * 8;
+    const uint4 xv = *reinterpret_cast<const uint4*>(x + xoff);
+    const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&xv);
+    uint4 o;
+    __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(x2[e]);
+      o2[e] = __floats2bfloat162_rn(f.x > 0.f ? acc[2 * e] : 0.f, f.y > 0.f ? acc[2 * e + 1] : 0.f);
+    }
+    *reinterpret_cast<uint4*>(dx + xoff) = o;
+  }
+}
+int maxpool_bwd(const bf16* dy, const uint8_t* idx, const bf16* x, bf16* dx, int N, int H, int W, int C, cudaStream_t st) {
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  const long long total = 1LL * N * H * W * (C / 8);
+  const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
+  maxpool_bwd_kernel<<<blocks, 256, 0, st>>>(dy, idx, x, dx, N, H, W, C, Ho, Wo);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ conv1 im2col
+// image fp32 [B, K, 3, H, W] (values in [0,1]) of camera `cam` -> A [B*Ho*Wo, KP] bf16 with column (c*7+kh)*7+kw,
+// ImageNet normalisation (policy.py:268-272) fused, zero padding applied in normalised space, columns >= 147 zero.
+__global__ void im2col_conv1_kernel(const float* __restrict__ img, long long img_bs, bf16* __restrict__ out, int B, int H,
+                                    int W, int Ho, int Wo, int KP) {
+  const float mean[3] = {0.485f, 0.456f, 0.406f};
+  const float istd[3] = {1.f / 0.229f, 1.f / 0.224f, 1.f / 0.225f};
+  const int G = KP / 8;
+  const long long total = 1LL * B * Ho * Wo * G;
+  for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
+    const int g = static_cast<int>(i % G);
+    long long r = i / G;
+    const int ox = static_cast<int>(r % Wo); r /= Wo;
+    const int oy = static_cast<int>(r % Ho);
+    const int b = static_cast<int>(r / Ho);
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int k = g * 8 + e;
+      float val = 0.f;
+      if (k < 147) {
+        const int c = k / 49, kh = (k % 49) / 7, kw = k % 7;
+        const int iy = 2 * oy + kh - 3, ix = 2 * ox + kw - 3;
+        if (iy >= 0 && iy < H && ix >= 0 && ix < W)
+          val = (__ldg(img + b * img_bs + (1LL * c * H + iy) * W + ix) - mean[c]) * istd[c];
+      }
+      v[e] = val;
+    }
+    uint4 o;
+    __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+    *reinterpret_cast<uint4*>(out + (i / G) * KP + g * 8) = o;
+  }
+}
+int im2col_conv1(const float* img_cam, long long img_bs, bf16* out, int B, int H, int W, int KP, cudaStream_t st) {
+  ACT_CHECK(KP % 8 == 0 && KP >= 152, "conv1 im2col width must be a multiple of 8 >= 152");
+  const int Ho = (H + 6 - 7) / 2 + 1, Wo = (W + 6 - 7) / 2 + 1;
+  const long long total = 1LL * B * Ho * Wo * (KP / 8);
+  const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 32));
+  im2col_conv1_kernel<<<blocks, 256, 0, st>>>(img_cam, img_bs, out, B, H, W, Ho, Wo, KP);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace act

@@ -5,8 +5,59 @@
 
 namespace act {
 
+// ---- pack.cu
 int cast_bf16(const float* src, bf16* dst, long long n, cudaStream_t st);
 int pack_conv_weights(const float* w, const float* scale, bf16* wpk, bf16* wpkt, int Cout, int Cin, int KK, cudaStream_t st);
 int bn_fold(const float* w, const float* b, const float* rm, const float* rv, float* scale, float* shift, int n, cudaStream_t st);
+int pack_conv1_weights(const float* w, bf16* wpk, int KP, cudaStream_t st);     // [64,147] fp32 -> [64,KP] bf16, zero padded
+
+// ---- fused_norm.cu
+int ln_fwd(const float* t, const float* gamma, const float* beta, const float* pos, int L, float* y, bf16* yb, bf16* ypb,
+           float* mean, float* rstd, int M, int D, cudaStream_t st);
+int ln_bwd(const float* dy, const float* dy2, const float* t, const float* mean, const float* rstd, const float* gamma,
+           float* dt, bf16* dtb, float* dgamma, float* dbeta, int M, int D, cudaStream_t st);
+int add_pos_cast(const float* x, const float* pos, int L, bf16* xb, bf16* xpb, int M, int D, cudaStream_t st);
+int softmax_fwd(const float* S, const uint8_t* mask, bf16* P, int R, int L, int Lp, int rows_per_batch, cudaStream_t st);
+int softmax_bwd(const bf16* P, const float* dP, bf16* dS, int R, int L, int Lp, float scale, cudaStream_t st);
+int colsum_bf16(const bf16* X, long long ld, int M, int N, float* out, cudaStream_t st);
+
+// ---- fused_misc.cu
+struct IdxMap {            // off(idx) = (idx / rpb) * bs + (idx % rpb) * s
+  int rpb = 1 << 30;
+  long long bs = 0, s = 0;
+};
+inline IdxMap lin(long long s) { IdxMap m; m.s = s; return m; }
+inline IdxMap batched(int rpb, long long bs, long long s) { IdxMap m; m.rpb = rpb; m.bs = bs; m.s = s; return m; }
+struct SgemmArgs {         // C(i,j) (+)= alpha * sum_r A(i,r) * B(r,j) (+ bias[j])
+  int I = 0, J = 0, R = 0;
+  const float* A = nullptr; IdxMap ai, ar;
+  const float* B = nullptr; IdxMap br, bj;
+  float* C = nullptr; IdxMap ci, cj;
+  const float* bias = nullptr;
+  float alpha = 1.f;
+  int accumulate = 0;
+};
+int sgemm_generic(const SgemmArgs& a, cudaStream_t st);
+int act_loss(const float* a_hat, const float* actions, long long act_bs, const uint8_t* is_pad, long long pad_bs,
+             const float* mu, const float* logvar, int B, int nq, int A, int Z, float kl_weight, float gscale,
+             float* losses, float* d_a_hat, float* d_mu, float* d_logvar, cudaStream_t st);
+int reparam_fwd(const float* info, const float* eps, float* mu, float* logvar, float* z, int B, int Z, cudaStream_t st);
+int reparam_bwd(const float* dz, const float* eps, const float* logvar, const float* d_mu_kl, const float* d_lv_kl,
+                float* d_info, int B, int Z, cudaStream_t st);
+int maxpool_fwd(const bf16* x, bf16* y, uint8_t* idx, int N, int H, int W, int C, cudaStream_t st);
+int maxpool_bwd(const bf16* dy, const uint8_t* idx, const bf16* x, bf16* dx, int N, int H, int W, int C, cudaStream_t st);
+int im2col_conv1(const float* img_cam, long long img_bs, bf16* out, int B, int H, int W, int KP, cudaStream_t st);
+
+// ---- optim.cu
+struct AdamWArgs {
+  float* p; const float* g; float* m; float* v; bf16* shadow;   // shadow may be null
+  long long n;
+  float lr, beta1, beta2, eps, wd;
+  int step;          // 1-based
+  int mode;          // 0 = full AdamW, 1 = weight decay only (gradient identically zero)
+};
+int adamw_step(const AdamWArgs& a, cudaStream_t st);
+int temporal_agg_step(float* ring, const float* chunks, const int* t, double* out, int E, int nq, int A, double k,
+                      cudaStream_t st);
 
 }  // namespace act

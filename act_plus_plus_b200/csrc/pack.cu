@@ -66,3 +66,17 @@ int bn_fold(const float* w, const float* b, const float* rm, const float* rv, fl
 }
 
 }  // namespace act
+
+namespace act {
+__global__ void pack_conv1_kernel(const float* __restrict__ w, bf16* __restrict__ wpk, int KP) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 64 * KP) return;
+  const int co = i / KP, k = i % KP;
+  wpk[i] = __float2bfloat16_rn(k < 147 ? w[co * 147 + k] : 0.f);
+}
+int pack_conv1_weights(const float* w, bf16* wpk, int KP, cudaStream_t st) {
+  pack_conv1_kernel<<<(64 * KP + 255) / 256, 256, 0, st>>>(w, wpk, KP);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+}  // namespace act

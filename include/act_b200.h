@@ -66,6 +66,49 @@ int act_conv_dgrad(int N, int H, int W, int Cin, int Cout, int KH, int stride, i
 int act_conv_wgrad(int N, int H, int W, int Cin, int Cout, int KH, int stride, int pad, const void* x, const void* dy,
                    float* dw, float alpha, const float* scale, void* stream);
 
+/* ---- fused bandwidth-bound kernels (warp-shuffle reductions, 128-bit accesses) -------------------------------- */
+/* nn.LayerNorm(d) of transformer.py:200-201,261-263,35: y = LN(t)*gamma+beta (eps 1e-5), d in {256,512}.  Optional
+ * outputs: y fp32, bf16(y), bf16(y + pos[row % L]) (with_pos_embed, transformer.py:205-206), mean, rstd. */
+int act_ln_fwd(const float* t, const float* gamma, const float* beta, const float* pos, int L, float* y, void* y_bf16,
+               void* ypos_bf16, float* mean, float* rstd, int M, int D, void* stream);
+/* backward of the above for dy (+ optional second addend dy2); dgamma / dbeta are accumulated (atomics). */
+int act_ln_bwd(const float* dy, const float* dy2, const float* t, const float* mean, const float* rstd,
+               const float* gamma, float* dt, void* dt_bf16, float* dgamma, float* dbeta, int M, int D, void* stream);
+int act_add_pos_cast(const float* x, const float* pos, int L, void* x_bf16, void* xpos_bf16, int M, int D, void* stream);
+/* softmax over keys of nn.MultiheadAttention (transformer.py:194,254-255): S fp32 [R, Lp] -> P bf16 [R, Lp];
+ * key_padding_mask uint8 [B, L] (may be NULL), batch of row r is r / rows_per_batch; columns >= L are written 0. */
+int act_softmax_fwd(const float* S, const uint8_t* key_padding_mask, void* P, int R, int L, int Lp, int rows_per_batch,
+                    void* stream);
+int act_softmax_bwd(const void* P, const float* dP, void* dS, int R, int L, int Lp, float scale, void* stream);
+int act_colsum_bf16(const void* X, int64_t ld, int M, int N, float* out_accum, void* stream);
+/* fp32 mini-GEMM for the K<=32 / N<=64 projections (detr_vae.py:57-63,81-97) and their gradients:
+ * C(i,j) (+)= alpha*sum_r A(i,r)B(r,j) (+bias[j]); each index maps as (idx/rpb)*bs + (idx%rpb)*s (maps = 3 int64). */
+int act_sgemm(int I, int J, int R, const float* A, const int64_t* a_i, const int64_t* a_r, const float* B,
+              const int64_t* b_r, const int64_t* b_j, float* C, const int64_t* c_i, const int64_t* c_j,
+              const float* bias, float alpha, int accumulate, void* stream);
+/* L1 + KL loss of policy.py:314-318,378-391 -> losses[3] = {l1, kl, loss}; optional gradients (scaled by gscale). */
+int act_loss(const float* a_hat, const float* actions, int64_t actions_batch_stride, const uint8_t* is_pad,
+             int64_t is_pad_batch_stride, const float* mu, const float* logvar, int B, int nq, int A, int Z,
+             float kl_weight, float gscale, float* losses, float* d_a_hat, float* d_mu, float* d_logvar, void* stream);
+/* reparametrize of detr_vae.py:19-22 with injected noise: latent_info [B,2Z] -> mu, logvar, z = mu + exp(lv/2)*eps */
+int act_reparam_fwd(const float* latent_info, const float* eps, float* mu, float* logvar, float* z, int B, int Z,
+                    void* stream);
+int act_reparam_bwd(const float* dz, const float* eps, const float* logvar, const float* d_mu_kl,
+                    const float* d_logvar_kl, float* d_latent_info, int B, int Z, void* stream);
+/* resnet stem: max-pool 3x3/s2/p1 on NHWC bf16 (+arg-max bytes) and its ReLU-fused backward; conv1 im2col with the
+ * ImageNet normalisation of policy.py:268-272 fused (image fp32 [B,3,H,W] with batch stride img_bs elements). */
+int act_maxpool_fwd(const void* x, void* y, uint8_t* argmax, int N, int H, int W, int C, void* stream);
+int act_maxpool_bwd(const void* dy, const uint8_t* argmax, const void* x, void* dx, int N, int H, int W, int C,
+                    void* stream);
+int act_im2col_conv1(const float* image, int64_t img_bs, void* out, int B, int H, int W, int KP, void* stream);
+/* torch.optim.AdamW single step over one flat segment (detr/main.py:102-110); mode 1 = decay only (zero gradient). */
+int act_adamw_step(float* p, const float* g, float* m, float* v, void* shadow_bf16, int64_t n, float lr, float beta1,
+                   float beta2, float eps, float weight_decay, int step, int mode, void* stream);
+/* temporal ensemble of imitate_episodes.py:339,403-411 for E environments at once: ring fp32 [E,nq,nq,A],
+ * chunks fp32 [E,nq,A] (the policy output at step t[e]), out float64 [E,A]. */
+int act_temporal_agg_step(float* ring, const float* chunks, const int* t, double* out, int E, int nq, int A, double k,
+                          void* stream);
+
 #ifdef __cplusplus
 }
 #endif
