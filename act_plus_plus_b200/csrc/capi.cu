@@ -3,6 +3,8 @@
 #include "tc_api.h"
 #include "conv_ops.h"
 #include "kernels.h"
+#include "engine.h"
+#include <cstring>
 
 using namespace act;
 
@@ -114,3 +116,53 @@ extern "C" int act_temporal_agg_step(float* ring, const float* chunks, const int
                                      double k, void* stream) {
   return temporal_agg_step(ring, chunks, t, out, E, nq, A, k, ST(stream));
 }
+
+struct act_engine { Engine* eng; };
+
+extern "C" int act_engine_create(const act_engine_config* c, act_engine** out) {
+  if (!c || !out) { set_error("null argument"); return -1; }
+  EngineConfig k;
+  k.batch_max = c->batch_max; k.num_cameras = c->num_cameras; k.img_h = c->img_h; k.img_w = c->img_w;
+  k.hidden_dim = c->hidden_dim; k.nheads = c->nheads; k.dim_ff = c->dim_feedforward; k.enc_layers = c->enc_layers;
+  k.dec_layers = c->dec_layers; k.num_queries = c->num_queries; k.state_dim = c->state_dim; k.action_dim = c->action_dim;
+  k.latent_dim = c->latent_dim; k.kl_weight = c->kl_weight; k.lr = c->lr; k.lr_backbone = c->lr_backbone;
+  k.weight_decay = c->weight_decay; k.beta1 = c->beta1; k.beta2 = c->beta2; k.adam_eps = c->adam_eps;
+  k.faithful_decoder = c->faithful_decoder; k.train = c->train;
+  Engine* e = new Engine(k);
+  if (e->init() != 0) { delete e; return -1; }
+  *out = new act_engine{e};
+  return 0;
+}
+extern "C" void act_engine_destroy(act_engine* e) { if (e) { delete e->eng; delete e; } }
+extern "C" int act_engine_num_tensors(const act_engine* e) { return static_cast<int>(e->eng->tensors().size()); }
+extern "C" int64_t act_engine_total_floats(const act_engine* e) { return e->eng->total_floats(); }
+extern "C" int64_t act_engine_workspace_bytes(const act_engine* e) { return e->eng->workspace_bytes(); }
+extern "C" int act_engine_tensor_info(const act_engine* e, int i, char* name, int name_cap, int64_t shape[4], int* ndim,
+                                      int64_t* offset, int64_t* numel, int* kind, int* region) {
+  const auto& ts = e->eng->tensors();
+  if (i < 0 || i >= static_cast<int>(ts.size())) { set_error("tensor index out of range"); return -1; }
+  const TensorEntry& t = ts[i];
+  if (name && name_cap > 0) { strncpy(name, t.name.c_str(), name_cap - 1); name[name_cap - 1] = 0; }
+  for (int k = 0; k < 4; ++k) shape[k] = t.shape[k];
+  *ndim = t.ndim; *offset = t.offset; *numel = t.numel; *kind = t.kind; *region = t.region;
+  return 0;
+}
+extern "C" int act_engine_region(const act_engine* e, int region, int64_t* offset, int64_t* count) {
+  if (region < 0 || region >= R_COUNT) { set_error("bad region"); return -1; }
+  long long o, n;
+  e->eng->region(region, &o, &n);
+  *offset = o; *count = n;
+  return 0;
+}
+extern "C" int act_engine_bind(act_engine* e, float* params, float* grads, float* m, float* v) { return e->eng->bind(params, grads, m, v); }
+extern "C" int act_engine_refresh(act_engine* e, void* stream) { return e->eng->refresh_shadows(ST(stream)); }
+extern "C" int act_engine_forward(act_engine* e, int B, const float* qpos, const float* image, const float* actions,
+                                  int64_t actions_bs, const uint8_t* is_pad, int64_t is_pad_bs, const float* eps,
+                                  float* a_hat, float* is_pad_hat, float* mu, float* logvar, float* losses, void* stream) {
+  return e->eng->forward(B, qpos, image, actions, actions_bs, is_pad, is_pad_bs, eps, a_hat, is_pad_hat, mu, logvar, losses, ST(stream));
+}
+extern "C" int act_engine_backward(act_engine* e, int stage, float loss_grad, void* stream) { return e->eng->backward(stage, loss_grad, ST(stream)); }
+extern "C" int act_engine_zero_grad(act_engine* e, void* stream) { return e->eng->zero_grad(ST(stream)); }
+extern "C" int act_engine_adamw_step(act_engine* e, int step, void* stream) { return e->eng->adamw(step, ST(stream)); }
+extern "C" int act_engine_set_lr(act_engine* e, float lr, float lr_backbone) { e->eng->set_lr(lr, lr_backbone); return 0; }
+extern "C" int act_engine_launches(act_engine* e, int reset) { const int n = e->eng->launches(); if (reset) e->eng->reset_launches(); return n; }

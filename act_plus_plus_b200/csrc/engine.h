@@ -1,0 +1,182 @@
+// ACT DETRVAE engine: owns the parameter layout, bf16 operand shadows, activation workspace and the kernel
+// sequences of the forward (train / inference), backward and optimizer steps.  One engine per device per process;
+// all calls are stream-ordered and not thread-safe (the reference is single-threaded too, imitate_episodes.py:561-612).
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+#include "conv_ops.h"
+#include "kernels.h"
+
+namespace act {
+
+struct EngineConfig {
+  int batch_max = 8;
+  int num_cameras = 1;
+  int img_h = 480, img_w = 640;
+  int hidden_dim = 512, nheads = 8, dim_ff = 3200, enc_layers = 4, dec_layers = 7;
+  int num_queries = 100, state_dim = 14, action_dim = 16, latent_dim = 32;
+  float kl_weight = 10.f;
+  float lr = 1e-5f, lr_backbone = 1e-5f, weight_decay = 1e-4f, beta1 = 0.9f, beta2 = 0.999f, adam_eps = 1e-8f;
+  int faithful_decoder = 0;   // 1: also execute decoder layers 1.. (dead work in the reference, detr_vae.py:245)
+  int train = 1;              // 0: inference-only engine (no backward workspace)
+};
+
+enum TensorKind { T_PARAM = 0, T_PARAM_DEAD = 1, T_PARAM_NOGRAD = 2, T_PARAM_BACKBONE = 3, T_BUFFER = 4 };
+enum Region { R_MAIN = 0, R_CVAE = 1, R_DEAD = 2, R_NOGRAD = 3, R_BACKBONE = 4, R_BUFFER = 5, R_COUNT = 6 };
+
+struct TensorEntry {
+  std::string name;
+  int ndim = 0;
+  long long shape[4] = {1, 1, 1, 1};
+  long long numel = 0, offset = 0;   // offset in floats into the flat buffers
+  int kind = T_PARAM;
+  int region = R_MAIN;
+  int order = 0;                     // position in the reference's state_dict order
+};
+
+struct LinW { const bf16* w = nullptr; const float* b = nullptr; const float* w32 = nullptr; float* gw = nullptr; float* gb = nullptr; int N = 0, K = 0; };
+struct LnW { const float* g = nullptr; const float* b = nullptr; float* gg = nullptr; float* gb = nullptr; };
+struct MhaW { LinW qk, q, k, v, o; };
+struct EncW { MhaW sa; LinW l1, l2; LnW n1, n2; };
+struct DecW { MhaW sa, ca; LinW l1, l2; LnW n1, n2, n3; };
+struct ConvW {
+  int Cin = 0, Cout = 0, KH = 0, stride = 1, pad = 0;
+  const float* w32 = nullptr; float* gw = nullptr;
+  const float* bn[4] = {nullptr, nullptr, nullptr, nullptr};   // weight, bias, running_mean, running_var
+  bf16* wpk = nullptr; bf16* wpkt = nullptr;                   // packed shadows (engine-owned)
+  float* scale = nullptr; float* shift = nullptr;              // folded FrozenBN (engine-owned)
+};
+
+struct BlockW { ConvW c1, c2, ds; bool has_ds = false; };
+struct CamW { ConvW stem; BlockW blk[8]; };
+
+struct EncActs {       // saved activations of one post-norm encoder layer over M = B*L rows
+  bf16 *xb = nullptr, *xpb = nullptr, *qk = nullptr, *v = nullptr, *P = nullptr, *o = nullptr, *x1b = nullptr, *hh = nullptr;
+  float *t1 = nullptr, *mean1 = nullptr, *rstd1 = nullptr, *x1 = nullptr, *t2 = nullptr, *mean2 = nullptr, *rstd2 = nullptr, *x2 = nullptr;
+};
+struct DecActs {
+  bf16 *xb = nullptr, *xpb = nullptr, *qk = nullptr, *v = nullptr, *P = nullptr, *o = nullptr;     // self-attention
+  float *t1 = nullptr, *mean1 = nullptr, *rstd1 = nullptr, *y1 = nullptr; bf16* y1pb = nullptr;
+  bf16 *q = nullptr, *k = nullptr, *cv = nullptr, *cP = nullptr, *co = nullptr;                     // cross-attention
+  float *t2 = nullptr, *mean2 = nullptr, *rstd2 = nullptr, *y2 = nullptr; bf16* y2b = nullptr;
+  bf16* hh = nullptr;
+  float *t3 = nullptr, *mean3 = nullptr, *rstd3 = nullptr, *y3 = nullptr;
+};
+struct BlockActs { bf16 *a = nullptr, *y = nullptr, *ds = nullptr; };   // conv1 relu out, block out, downsample out
+struct CamActs {
+  bf16 *y1 = nullptr, *p1 = nullptr; uint8_t* pidx = nullptr;           // stem
+  BlockActs blk[8];
+};
+
+class Engine {
+ public:
+  explicit Engine(const EngineConfig& cfg);
+  ~Engine();
+  int init();                                   // builds the tensor table, allocates workspace
+  // parameter plumbing
+  const std::vector<TensorEntry>& tensors() const { return tensors_; }
+  long long total_floats() const { return total_floats_; }
+  void region(int r, long long* off, long long* n) const { *off = region_off_[r]; *n = region_n_[r]; }
+  int bind(float* params, float* grads, float* exp_avg, float* exp_avg_sq);
+  int refresh_shadows(cudaStream_t st);         // fp32 params -> bf16 mirrors / packed conv weights / BN folds / pos rows
+  // steps
+  int forward(int B, const float* qpos, const float* image, const float* actions, long long actions_bs,
+              const uint8_t* is_pad, long long is_pad_bs, const float* eps, float* a_hat, float* is_pad_hat, float* mu,
+              float* logvar, float* losses, cudaStream_t st);
+  int backward(int stage, float loss_grad, cudaStream_t st);      // stage: 0 = all, 1 = transformer, 2 = cvae, 3 = backbone
+  int zero_grad(cudaStream_t st);
+  int adamw(int step, cudaStream_t st);
+  const EngineConfig& cfg() const { return cfg_; }
+  long long workspace_bytes() const { return ws_bytes_; }
+  int launches() const { return launches_; }
+  void reset_launches() { launches_ = 0; }
+  void set_lr(float lr, float lr_backbone) { cfg_.lr = lr; cfg_.lr_backbone = lr_backbone; }
+
+ private:
+  // ---- helpers (engine_fwd.cu / engine_bwd.cu)
+  int linear(const bf16* X, int M, const LinW& w, uint32_t flags, const float* res_f32, float* out_f32, bf16* out_bf16,
+             const bf16* aux, cudaStream_t st);
+  int linear_dx(const bf16* dY, int M, const LinW& w, uint32_t flags, const float* res_f32, const bf16* aux, float* out_f32,
+                bf16* out_bf16, cudaStream_t st);
+  int linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cudaStream_t st);
+  int attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv, const uint8_t* mask,
+               bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st);
+  int attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv,
+               const bf16* P, bf16* dQ, long long lddq, bf16* dK, long long lddk, bf16* dV, long long lddv, int B, int Lq,
+               int Lk, cudaStream_t st);
+  int enc_layer_fwd(const EncW& w, EncActs& a, const float* x, const float* pos, const float* next_pos, int L,
+                    const uint8_t* mask, int B, bool emit_next, bf16* next_xb, bf16* next_xpb, cudaStream_t st);
+  int enc_layer_bwd(const EncW& w, EncActs& a, const float* x_in, const float* dx2, const float* dx2b, float* dx_out,
+                    float* gxp_out, int L, int B, cudaStream_t st);
+  int backbone_fwd(int cam, int B, const float* image, cudaStream_t st);
+  int backbone_bwd(int cam, int B, cudaStream_t st);
+  int dec_layer_fwd(int B, cudaStream_t st);
+  int transformer_bwd(float loss_grad, cudaStream_t st);
+  int cvae_fwd(int B, const float* qpos, const float* actions, long long actions_bs, const uint8_t* is_pad,
+               long long is_pad_bs, const float* eps, cudaStream_t st);
+  int cvae_bwd(cudaStream_t st);
+
+  template <typename T> T* alloc(long long n);
+  TensorEntry* find(const std::string& name);
+  float* P(const std::string& name) { return params_ + find(name)->offset; }
+  float* G(const std::string& name) { return grads_ ? grads_ + find(name)->offset : nullptr; }
+  const bf16* S(const std::string& name) { return shadow_ + find(name)->offset; }
+  LinW lin(const std::string& wname, const std::string& bname, int K, int row0 = 0, int rows = -1);
+  ConvW convw(const std::string& wname, const std::string& bnprefix, int Cin, int Cout, int KH, int stride, int pad);
+  LnW lnw(const std::string& prefix);
+  void build_tensor_table();
+  void setup_views();
+  int alloc_workspace();
+
+  EngineConfig cfg_;
+  std::vector<TensorEntry> tensors_;
+  std::map<std::string, int> index_;
+  long long total_floats_ = 0;
+  long long region_off_[R_COUNT] = {0}, region_n_[R_COUNT] = {0};
+  float *params_ = nullptr, *grads_ = nullptr, *m_ = nullptr, *v_ = nullptr;
+  bf16* shadow_ = nullptr;
+  std::vector<void*> allocs_;
+  long long ws_bytes_ = 0;
+  int launches_ = 0;
+
+  // geometry
+  int Hf_ = 0, Wf_ = 0, L_ = 0, Lp_ = 0, Lc_ = 0, Lcp_ = 0, nqp_ = 0;
+  int fh_[6] = {0}, fw_[6] = {0};   // spatial dims: [0] image, [1] conv1 out, [2] pool out (layer1), [3] layer2, [4] layer3, [5] layer4
+  int cur_B_ = 0;
+  bool have_actions_ = false;
+
+  // weights
+  std::vector<EncW> enc_w_, cvae_w_;
+  std::vector<DecW> dec_w_;
+  LnW dec_norm_;
+  std::vector<CamW> cam_w_;
+  LinW input_proj_;
+
+  // workspace
+  std::vector<EncActs> enc_a_, cvae_a_;
+  DecActs dec_a_;
+  std::vector<CamActs> cam_a_;
+  bf16* im2col_ = nullptr;
+  float *tokC_ = nullptr, *src_ = nullptr, *pos_main_ = nullptr, *tgt0_ = nullptr;
+  bf16 *mem_b_ = nullptr, *mem_pb_ = nullptr;
+  uint8_t* maskC_ = nullptr;
+  float *Sbuf_ = nullptr; bf16* dSbuf_ = nullptr;
+  float *latent_info_ = nullptr, *mu_ = nullptr, *logvar_ = nullptr, *z_ = nullptr, *eps_ = nullptr;
+  float *hs_ = nullptr, *hs_mean_ = nullptr, *hs_rstd_ = nullptr, *a_hat_ = nullptr, *is_pad_hat_ = nullptr, *losses_ = nullptr;
+  float* one_ = nullptr;
+  // saved input pointers of the last forward (for the backward)
+  const float *in_qpos_ = nullptr, *in_image_ = nullptr, *in_actions_ = nullptr;
+  long long in_actions_bs_ = 0;
+  const uint8_t* in_is_pad_ = nullptr; long long in_is_pad_bs_ = 0;
+  // backward scratch
+  float *d_a_hat_ = nullptr, *d_mu_ = nullptr, *d_logvar_ = nullptr, *d_hs_ = nullptr, *dz_ = nullptr, *d_info_ = nullptr;
+  float *gA_ = nullptr, *gB_ = nullptr, *gC_ = nullptr, *gD_ = nullptr, *gE_ = nullptr;   // fp32 [Mmax, 512] ping-pong gradient buffers
+  float *gMem_ = nullptr, *gMemPos_ = nullptr;
+  bf16 *gb1_ = nullptr, *gb2_ = nullptr, *gbqk_ = nullptr, *gbhh_ = nullptr, *gbv_ = nullptr, *gbk_ = nullptr;
+  float* d_src_ = nullptr; float* d_tokC_ = nullptr;
+  bf16 *cg_[4] = {nullptr, nullptr, nullptr, nullptr};   // backbone gradient ping-pong (NHWC bf16, max size)
+  bf16* d_feat_ = nullptr;
+};
+
+}  // namespace act

@@ -1,0 +1,267 @@
+// Engine: tensor table (reference state_dict names), flat layout by optimizer region, bf16 shadows, AdamW.
+#include "engine.h"
+#include <cmath>
+#include <cstring>
+
+namespace act {
+
+Engine::Engine(const EngineConfig& cfg) : cfg_(cfg) {}
+
+Engine::~Engine() {
+  for (void* p : allocs_) cudaFree(p);
+}
+
+template <typename T>
+T* Engine::alloc(long long n) {
+  if (n <= 0) n = 1;
+  void* p = nullptr;
+  const size_t bytes = (static_cast<size_t>(n) * sizeof(T) + 255) & ~size_t(255);
+  if (cudaMalloc(&p, bytes) != cudaSuccess) { set_error("cudaMalloc failed for " + std::to_string(bytes) + " bytes"); return nullptr; }
+  cudaMemset(p, 0, bytes);
+  allocs_.push_back(p);
+  ws_bytes_ += bytes;
+  return static_cast<T*>(p);
+}
+template float* Engine::alloc<float>(long long);
+template bf16* Engine::alloc<bf16>(long long);
+template uint8_t* Engine::alloc<uint8_t>(long long);
+
+TensorEntry* Engine::find(const std::string& name) {
+  auto it = index_.find(name);
+  if (it == index_.end()) { set_error("unknown tensor " + name); return &tensors_[0]; }
+  return &tensors_[it->second];
+}
+
+static const char* kStages[4] = {"layer1", "layer2", "layer3", "layer4"};
+static const int kStageCin[4] = {64, 64, 128, 256}, kStageCout[4] = {64, 128, 256, 512}, kStageStride[4] = {1, 2, 2, 2};
+
+// Same order as the reference's state_dict (detr_vae.py:38-105 registration order; oracle/act_oracle.py:state_spec).
+void Engine::build_tensor_table() {
+  const int d = cfg_.hidden_dim, ff = cfg_.dim_ff, nq = cfg_.num_queries, S = cfg_.state_dim, A = cfg_.action_dim, Z = cfg_.latent_dim;
+  auto add = [&](const std::string& name, std::vector<long long> shape, int kind, int region) {
+    TensorEntry t;
+    t.name = name; t.ndim = static_cast<int>(shape.size()); t.numel = 1;
+    for (size_t i = 0; i < shape.size(); ++i) { t.shape[i] = shape[i]; t.numel *= shape[i]; }
+    t.kind = kind; t.region = region; t.order = static_cast<int>(tensors_.size());
+    tensors_.push_back(t);
+  };
+  auto enc_layer = [&](const std::string& p, int kind, int region) {
+    add(p + "self_attn.in_proj_weight", {3 * d, d}, kind, region); add(p + "self_attn.in_proj_bias", {3 * d}, kind, region);
+    add(p + "self_attn.out_proj.weight", {d, d}, kind, region); add(p + "self_attn.out_proj.bias", {d}, kind, region);
+    add(p + "linear1.weight", {ff, d}, kind, region); add(p + "linear1.bias", {ff}, kind, region);
+    add(p + "linear2.weight", {d, ff}, kind, region); add(p + "linear2.bias", {d}, kind, region);
+    add(p + "norm1.weight", {d}, kind, region); add(p + "norm1.bias", {d}, kind, region);
+    add(p + "norm2.weight", {d}, kind, region); add(p + "norm2.bias", {d}, kind, region);
+  };
+  auto dec_layer = [&](const std::string& p, int kind, int region) {
+    add(p + "self_attn.in_proj_weight", {3 * d, d}, kind, region); add(p + "self_attn.in_proj_bias", {3 * d}, kind, region);
+    add(p + "self_attn.out_proj.weight", {d, d}, kind, region); add(p + "self_attn.out_proj.bias", {d}, kind, region);
+    add(p + "multihead_attn.in_proj_weight", {3 * d, d}, kind, region); add(p + "multihead_attn.in_proj_bias", {3 * d}, kind, region);
+    add(p + "multihead_attn.out_proj.weight", {d, d}, kind, region); add(p + "multihead_attn.out_proj.bias", {d}, kind, region);
+    add(p + "linear1.weight", {ff, d}, kind, region); add(p + "linear1.bias", {ff}, kind, region);
+    add(p + "linear2.weight", {d, ff}, kind, region); add(p + "linear2.bias", {d}, kind, region);
+    for (int i = 1; i <= 3; ++i) {
+      add(p + "norm" + std::to_string(i) + ".weight", {d}, kind, region);
+      add(p + "norm" + std::to_string(i) + ".bias", {d}, kind, region);
+    }
+  };
+  auto bn = [&](const std::string& p, int c) {
+    add(p + "weight", {c}, T_BUFFER, R_BUFFER); add(p + "bias", {c}, T_BUFFER, R_BUFFER);
+    add(p + "running_mean", {c}, T_BUFFER, R_BUFFER); add(p + "running_var", {c}, T_BUFFER, R_BUFFER);
+  };
+  add("pos_table", {1, nq + 2, d}, T_BUFFER, R_BUFFER);
+  for (int i = 0; i < cfg_.enc_layers; ++i) enc_layer("transformer.encoder.layers." + std::to_string(i) + ".", T_PARAM, R_MAIN);
+  for (int i = 0; i < cfg_.dec_layers; ++i)
+    dec_layer("transformer.decoder.layers." + std::to_string(i) + ".", i == 0 ? T_PARAM : T_PARAM_DEAD, i == 0 ? R_MAIN : R_DEAD);
+  add("transformer.decoder.norm.weight", {d}, T_PARAM, R_MAIN); add("transformer.decoder.norm.bias", {d}, T_PARAM, R_MAIN);
+  for (int i = 0; i < cfg_.enc_layers; ++i) enc_layer("encoder.layers." + std::to_string(i) + ".", T_PARAM, R_CVAE);
+  add("action_head.weight", {A, d}, T_PARAM, R_MAIN); add("action_head.bias", {A}, T_PARAM, R_MAIN);
+  add("is_pad_head.weight", {1, d}, T_PARAM_NOGRAD, R_NOGRAD); add("is_pad_head.bias", {1}, T_PARAM_NOGRAD, R_NOGRAD);
+  add("query_embed.weight", {nq, d}, T_PARAM, R_MAIN);
+  add("input_proj.weight", {d, 512, 1, 1}, T_PARAM, R_MAIN); add("input_proj.bias", {d}, T_PARAM, R_MAIN);
+  for (int k = 0; k < cfg_.num_cameras; ++k) {
+    const std::string p = "backbones." + std::to_string(k) + ".0.body.";
+    add(p + "conv1.weight", {64, 3, 7, 7}, T_PARAM_BACKBONE, R_BACKBONE);
+    bn(p + "bn1.", 64);
+    for (int s = 0; s < 4; ++s)
+      for (int b = 0; b < 2; ++b) {
+        const std::string q = p + kStages[s] + "." + std::to_string(b) + ".";
+        const int cin = b == 0 ? kStageCin[s] : kStageCout[s], cout = kStageCout[s];
+        add(q + "conv1.weight", {cout, cin, 3, 3}, T_PARAM_BACKBONE, R_BACKBONE); bn(q + "bn1.", cout);
+        add(q + "conv2.weight", {cout, cout, 3, 3}, T_PARAM_BACKBONE, R_BACKBONE); bn(q + "bn2.", cout);
+        if (b == 0 && (kStageStride[s] != 1 || cin != cout)) {
+          add(q + "downsample.0.weight", {cout, cin, 1, 1}, T_PARAM_BACKBONE, R_BACKBONE); bn(q + "downsample.1.", cout);
+        }
+      }
+  }
+  add("input_proj_robot_state.weight", {d, S}, T_PARAM, R_MAIN); add("input_proj_robot_state.bias", {d}, T_PARAM, R_MAIN);
+  add("cls_embed.weight", {1, d}, T_PARAM, R_CVAE);
+  add("encoder_action_proj.weight", {d, A}, T_PARAM, R_CVAE); add("encoder_action_proj.bias", {d}, T_PARAM, R_CVAE);
+  add("encoder_joint_proj.weight", {d, S}, T_PARAM, R_CVAE); add("encoder_joint_proj.bias", {d}, T_PARAM, R_CVAE);
+  add("latent_proj.weight", {2 * Z, d}, T_PARAM, R_CVAE); add("latent_proj.bias", {2 * Z}, T_PARAM, R_CVAE);
+  add("latent_out_proj.weight", {d, Z}, T_PARAM, R_MAIN); add("latent_out_proj.bias", {d}, T_PARAM, R_MAIN);
+  add("additional_pos_embed.weight", {2, d}, T_PARAM, R_MAIN);
+
+  // flat layout: regions in all-reduce order, tensors 8-float aligned (bf16 shadow stays 16-byte aligned for TMA)
+  long long off = 0;
+  const int order[R_COUNT] = {R_MAIN, R_CVAE, R_BACKBONE, R_DEAD, R_NOGRAD, R_BUFFER};
+  for (int ri = 0; ri < R_COUNT; ++ri) {
+    const int r = order[ri];
+    region_off_[r] = off;
+    for (auto& t : tensors_)
+      if (t.region == r) { t.offset = off; off += (t.numel + 7) / 8 * 8; }
+    region_n_[r] = off - region_off_[r];
+  }
+  total_floats_ = off;
+  for (size_t i = 0; i < tensors_.size(); ++i) index_[tensors_[i].name] = static_cast<int>(i);
+}
+
+LinW Engine::lin(const std::string& wname, const std::string& bname, int K, int row0, int rows) {
+  LinW l;
+  TensorEntry* w = find(wname);
+  const int N = rows < 0 ? static_cast<int>(w->shape[0]) : rows;
+  l.N = N; l.K = K;
+  l.w = shadow_ + w->offset + 1LL * row0 * K;
+  l.w32 = params_ + w->offset + 1LL * row0 * K;
+  l.gw = grads_ ? grads_ + w->offset + 1LL * row0 * K : nullptr;
+  if (!bname.empty()) { TensorEntry* b = find(bname); l.b = params_ + b->offset + row0; l.gb = grads_ ? grads_ + b->offset + row0 : nullptr; }
+  return l;
+}
+LnW Engine::lnw(const std::string& prefix) {
+  LnW l;
+  l.g = P(prefix + "weight"); l.b = P(prefix + "bias"); l.gg = G(prefix + "weight"); l.gb = G(prefix + "bias");
+  return l;
+}
+ConvW Engine::convw(const std::string& wname, const std::string& bnp, int Cin, int Cout, int KH, int stride, int pad) {
+  ConvW c;
+  c.Cin = Cin; c.Cout = Cout; c.KH = KH; c.stride = stride; c.pad = pad;
+  c.w32 = P(wname); c.gw = G(wname);
+  c.bn[0] = P(bnp + "weight"); c.bn[1] = P(bnp + "bias"); c.bn[2] = P(bnp + "running_mean"); c.bn[3] = P(bnp + "running_var");
+  return c;
+}
+
+void Engine::setup_views() {
+  const int d = cfg_.hidden_dim, ff = cfg_.dim_ff;
+  auto enc = [&](const std::string& p) {
+    EncW w;
+    w.sa.qk = lin(p + "self_attn.in_proj_weight", p + "self_attn.in_proj_bias", d, 0, 2 * d);
+    w.sa.q = lin(p + "self_attn.in_proj_weight", p + "self_attn.in_proj_bias", d, 0, d);
+    w.sa.k = lin(p + "self_attn.in_proj_weight", p + "self_attn.in_proj_bias", d, d, d);
+    w.sa.v = lin(p + "self_attn.in_proj_weight", p + "self_attn.in_proj_bias", d, 2 * d, d);
+    w.sa.o = lin(p + "self_attn.out_proj.weight", p + "self_attn.out_proj.bias", d);
+    w.l1 = lin(p + "linear1.weight", p + "linear1.bias", d);
+    w.l2 = lin(p + "linear2.weight", p + "linear2.bias", ff);
+    w.n1 = lnw(p + "norm1."); w.n2 = lnw(p + "norm2.");
+    return w;
+  };
+  enc_w_.clear(); cvae_w_.clear(); dec_w_.clear();
+  for (int i = 0; i < cfg_.enc_layers; ++i) enc_w_.push_back(enc("transformer.encoder.layers." + std::to_string(i) + "."));
+  for (int i = 0; i < cfg_.enc_layers; ++i) cvae_w_.push_back(enc("encoder.layers." + std::to_string(i) + "."));
+  for (int i = 0; i < cfg_.dec_layers; ++i) {
+    const std::string p = "transformer.decoder.layers." + std::to_string(i) + ".";
+    DecW w;
+    w.sa.qk = lin(p + "self_attn.in_proj_weight", p + "self_attn.in_proj_bias", d, 0, 2 * d);
+    w.sa.v = lin(p + "self_attn.in_proj_weight", p + "self_attn.in_proj_bias", d, 2 * d, d);
+    w.sa.o = lin(p + "self_attn.out_proj.weight", p + "self_attn.out_proj.bias", d);
+    w.ca.q = lin(p + "multihead_attn.in_proj_weight", p + "multihead_attn.in_proj_bias", d, 0, d);
+    w.ca.k = lin(p + "multihead_attn.in_proj_weight", p + "multihead_attn.in_proj_bias", d, d, d);
+    w.ca.v = lin(p + "multihead_attn.in_proj_weight", p + "multihead_attn.in_proj_bias", d, 2 * d, d);
+    w.ca.o = lin(p + "multihead_attn.out_proj.weight", p + "multihead_attn.out_proj.bias", d);
+    w.l1 = lin(p + "linear1.weight", p + "linear1.bias", d);
+    w.l2 = lin(p + "linear2.weight", p + "linear2.bias", ff);
+    w.n1 = lnw(p + "norm1."); w.n2 = lnw(p + "norm2."); w.n3 = lnw(p + "norm3.");
+    dec_w_.push_back(w);
+  }
+  dec_norm_ = lnw("transformer.decoder.norm.");
+  input_proj_ = lin("input_proj.weight", "input_proj.bias", 512);
+  for (int k = 0; k < cfg_.num_cameras; ++k) {
+    const std::string p = "backbones." + std::to_string(k) + ".0.body.";
+    CamW& c = cam_w_[k];
+    ConvW keep = c.stem;
+    c.stem = convw(p + "conv1.weight", p + "bn1.", 3, 64, 7, 2, 3);
+    c.stem.wpk = keep.wpk; c.stem.scale = keep.scale; c.stem.shift = keep.shift;
+    for (int s = 0; s < 4; ++s)
+      for (int b = 0; b < 2; ++b) {
+        BlockW& bw = c.blk[s * 2 + b];
+        const std::string q = p + kStages[s] + "." + std::to_string(b) + ".";
+        const int cin = b == 0 ? kStageCin[s] : kStageCout[s], cout = kStageCout[s], st = b == 0 ? kStageStride[s] : 1;
+        auto carry = [&](ConvW& dst, ConvW src) { src.wpk = dst.wpk; src.wpkt = dst.wpkt; src.scale = dst.scale; src.shift = dst.shift; dst = src; };
+        carry(bw.c1, convw(q + "conv1.weight", q + "bn1.", cin, cout, 3, st, 1));
+        carry(bw.c2, convw(q + "conv2.weight", q + "bn2.", cout, cout, 3, 1, 1));
+        bw.has_ds = (b == 0 && (st != 1 || cin != cout));
+        if (bw.has_ds) carry(bw.ds, convw(q + "downsample.0.weight", q + "downsample.1.", cin, cout, 1, st, 0));
+      }
+  }
+}
+
+int Engine::bind(float* params, float* grads, float* exp_avg, float* exp_avg_sq) {
+  ACT_CHECK(params != nullptr, "params must not be null");
+  ACT_CHECK((reinterpret_cast<uintptr_t>(params) & 15) == 0, "flat parameter buffer must be 16-byte aligned");
+  params_ = params; grads_ = grads; m_ = exp_avg; v_ = exp_avg_sq;
+  setup_views();
+  return 0;
+}
+
+int Engine::refresh_shadows(cudaStream_t st) {
+  ACT_CHECK(params_ != nullptr, "engine not bound");
+  // linear / embedding operands: flat bf16 mirror of the trainable regions (AdamW keeps it fresh afterwards)
+  const long long n_mirror = region_off_[R_BUFFER];
+  if (cast_bf16(params_, shadow_, n_mirror, st)) return -1;
+  for (int k = 0; k < cfg_.num_cameras; ++k) {
+    CamW& c = cam_w_[k];
+    if (bn_fold(c.stem.bn[0], c.stem.bn[1], c.stem.bn[2], c.stem.bn[3], c.stem.scale, c.stem.shift, 64, st)) return -1;
+    if (pack_conv1_weights(c.stem.w32, c.stem.wpk, 192, st)) return -1;
+    for (int i = 0; i < 8; ++i) {
+      BlockW& b = c.blk[i];
+      ConvW* cs[3] = {&b.c1, &b.c2, b.has_ds ? &b.ds : nullptr};
+      for (ConvW* w : cs) {
+        if (!w) continue;
+        if (bn_fold(w->bn[0], w->bn[1], w->bn[2], w->bn[3], w->scale, w->shift, w->Cout, st)) return -1;
+        if (pack_conv_weights(w->w32, w->scale, w->wpk, w->wpkt, w->Cout, w->Cin, w->KH * w->KH, st)) return -1;
+      }
+    }
+  }
+  return 0;
+}
+
+int Engine::zero_grad(cudaStream_t st) {
+  ACT_CHECK(grads_ != nullptr, "no gradient buffer bound");
+  const long long n = region_off_[R_DEAD];     // MAIN | CVAE | BACKBONE are contiguous and first
+  ACT_CUDA(cudaMemsetAsync(grads_, 0, n * sizeof(float), st));
+  return 0;
+}
+
+int Engine::adamw(int step, cudaStream_t st) {
+  ACT_CHECK(params_ && grads_ && m_ && v_, "optimizer state not bound");
+  auto run = [&](int r, float lr, int mode, bool shadow) {
+    AdamWArgs a;
+    const long long o = region_off_[r];
+    a.p = params_ + o; a.g = grads_ + o; a.m = m_ + o; a.v = v_ + o; a.shadow = shadow ? shadow_ + o : nullptr;
+    a.n = region_n_[r]; a.lr = lr; a.beta1 = cfg_.beta1; a.beta2 = cfg_.beta2; a.eps = cfg_.adam_eps; a.wd = cfg_.weight_decay;
+    a.step = step; a.mode = mode;
+    ++launches_;
+    return adamw_step(a, st);
+  };
+  if (run(R_MAIN, cfg_.lr, 0, true)) return -1;
+  if (have_actions_ || true) { if (run(R_CVAE, cfg_.lr, 0, true)) return -1; }
+  if (run(R_BACKBONE, cfg_.lr_backbone, 0, false)) return -1;
+  if (run(R_DEAD, cfg_.lr, 1, cfg_.faithful_decoder != 0)) return -1;
+  // packed conv operands (transposed / scaled layouts) are rebuilt from the fp32 masters
+  for (int k = 0; k < cfg_.num_cameras; ++k) {
+    CamW& c = cam_w_[k];
+    if (pack_conv1_weights(c.stem.w32, c.stem.wpk, 192, st)) return -1;
+    ++launches_;
+    for (int i = 0; i < 8; ++i) {
+      BlockW& b = c.blk[i];
+      ConvW* cs[3] = {&b.c1, &b.c2, b.has_ds ? &b.ds : nullptr};
+      for (ConvW* w : cs) {
+        if (!w) continue;
+        if (pack_conv_weights(w->w32, w->scale, w->wpk, w->wpkt, w->Cout, w->Cin, w->KH * w->KH, st)) return -1;
+        ++launches_;
+      }
+    }
+  }
+  return 0;
+}
+
+}  // namespace act

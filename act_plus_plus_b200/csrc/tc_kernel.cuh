@@ -35,6 +35,7 @@ struct TapDesc {     // one filter tap of an implicit-GEMM convolution
 struct PixGeom {
   int H, W, sh, sw, oh, ow;
   long long ld;
+  long long sn;      // image stride in elements; 0 -> H*W*ld (dense NHWC)
 };
 
 struct TcParams {
@@ -83,7 +84,8 @@ struct TcCfg {
 };
 
 __device__ __forceinline__ long long pix_off(const PixGeom& g, int n, int h, int w) {
-  return ((static_cast<long long>(n) * g.H + (h * g.sh + g.oh)) * g.W + (w * g.sw + g.ow)) * g.ld;
+  const long long sn = g.sn ? g.sn : static_cast<long long>(g.H) * g.W * g.ld;
+  return n * sn + (static_cast<long long>(h * g.sh + g.oh) * g.W + (w * g.sw + g.ow)) * g.ld;
 }
 
 template <int MODE, int A_MN, int B_MN, int BN>

@@ -1,0 +1,174 @@
+"""Python handle over the C-ABI policy engine (``act_engine_*`` in include/act_b200.h).
+
+Owns the flat fp32 parameter / gradient / Adam-moment tensors (torch CUDA memory) and exposes each reference
+``state_dict`` entry as a view into them, so checkpoints interchange with the reference by name and shape."""
+from __future__ import annotations
+
+import ctypes as C
+from collections import OrderedDict
+from typing import Dict, Optional
+
+import torch
+
+from . import _lib
+from ._lib import check
+
+KIND_PARAM, KIND_DEAD, KIND_NOGRAD, KIND_BACKBONE, KIND_BUFFER = range(5)
+R_MAIN, R_CVAE, R_DEAD, R_NOGRAD, R_BACKBONE, R_BUFFER = range(6)
+
+
+class EngineConfig(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("batch_max", "num_cameras", "img_h", "img_w", "hidden_dim", "nheads",
+                                      "dim_feedforward", "enc_layers", "dec_layers", "num_queries", "state_dim",
+                                      "action_dim", "latent_dim")] + \
+               [(n, C.c_float) for n in ("kl_weight", "lr", "lr_backbone", "weight_decay", "beta1", "beta2", "adam_eps")] + \
+               [("faithful_decoder", C.c_int), ("train", C.c_int)]
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+class ActEngine:
+    def __init__(self, batch_max=8, num_cameras=1, img_h=480, img_w=640, hidden_dim=512, nheads=8,
+                 dim_feedforward=3200, enc_layers=4, dec_layers=7, num_queries=100, state_dim=14, action_dim=16,
+                 latent_dim=32, kl_weight=10.0, lr=1e-5, lr_backbone=1e-5, weight_decay=1e-4, betas=(0.9, 0.999),
+                 eps=1e-8, train=True, device: Optional[torch.device] = None):
+        if not torch.cuda.is_available():
+            raise _lib.ActB200Error("act_plus_plus_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.lib = _lib.lib()
+        cfg = EngineConfig(batch_max, num_cameras, img_h, img_w, hidden_dim, nheads, dim_feedforward, enc_layers,
+                           dec_layers, num_queries, state_dim, action_dim, latent_dim, kl_weight, lr, lr_backbone,
+                           weight_decay, betas[0], betas[1], eps, 0, 1 if train else 0)
+        self.cfg = cfg
+        self.train_enabled = bool(train)
+        self._h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            check(self.lib.act_engine_create(C.byref(cfg), C.byref(self._h)), "act_engine_create")
+            n = self.lib.act_engine_total_floats(self._h)
+            self.flat_params = torch.zeros(n, dtype=torch.float32, device=self.device)
+            self.flat_grads = torch.zeros(n, dtype=torch.float32, device=self.device) if train else None
+            self.exp_avg = torch.zeros(n, dtype=torch.float32, device=self.device) if train else None
+            self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=self.device) if train else None
+            check(self.lib.act_engine_bind(self._h, self.flat_params.data_ptr(),
+                                           self.flat_grads.data_ptr() if train else None,
+                                           self.exp_avg.data_ptr() if train else None,
+                                           self.exp_avg_sq.data_ptr() if train else None), "act_engine_bind")
+        self.tensors: "OrderedDict[str, dict]" = OrderedDict()
+        name = C.create_string_buffer(256)
+        shape = (C.c_int64 * 4)()
+        ndim, kind, region = C.c_int(), C.c_int(), C.c_int()
+        off, numel = C.c_int64(), C.c_int64()
+        for i in range(self.lib.act_engine_num_tensors(self._h)):
+            check(self.lib.act_engine_tensor_info(self._h, i, name, 256, shape, C.byref(ndim), C.byref(off),
+                                                  C.byref(numel), C.byref(kind), C.byref(region)), "tensor_info")
+            shp = tuple(int(shape[k]) for k in range(ndim.value))
+            self.tensors[name.value.decode()] = dict(shape=shp, offset=off.value, numel=numel.value, kind=kind.value,
+                                                     region=region.value)
+        self.step_count = 0
+
+    # ------------------------------------------------------------------ parameters
+    def view(self, name: str, flat: Optional[torch.Tensor] = None) -> torch.Tensor:
+        t = self.tensors[name]
+        flat = self.flat_params if flat is None else flat
+        return flat[t["offset"]:t["offset"] + t["numel"]].view(t["shape"])
+
+    def grad_view(self, name: str) -> torch.Tensor:
+        return self.view(name, self.flat_grads)
+
+    def region(self, r: int):
+        off, n = C.c_int64(), C.c_int64()
+        check(self.lib.act_engine_region(self._h, r, C.byref(off), C.byref(n)), "act_engine_region")
+        return off.value, n.value
+
+    def state_dict(self) -> "OrderedDict[str, torch.Tensor]":
+        return OrderedDict((k, self.view(k)) for k in self.tensors)
+
+    def load_state_dict(self, sd: Dict[str, torch.Tensor], strict: bool = True):
+        missing = [k for k in self.tensors if k not in sd]
+        unexpected = [k for k in sd if k not in self.tensors]
+        if strict and (missing or unexpected):
+            raise RuntimeError(f"state_dict mismatch: missing {missing[:5]}... unexpected {unexpected[:5]}...")
+        with torch.no_grad():
+            for k, v in sd.items():
+                if k in self.tensors:
+                    dst = self.view(k)
+                    if tuple(v.shape) != tuple(dst.shape):
+                        raise RuntimeError(f"size mismatch for {k}: {tuple(v.shape)} vs {tuple(dst.shape)}")
+                    dst.copy_(v.to(device=self.device, dtype=torch.float32))
+        self.refresh()
+        return missing, unexpected
+
+    def refresh(self):
+        check(self.lib.act_engine_refresh(self._h, _stream()), "act_engine_refresh")
+
+    # ------------------------------------------------------------------ steps
+    def forward(self, qpos, image, actions=None, is_pad=None, eps=None, want_is_pad_hat=False):
+        """Returns dict(a_hat[, is_pad_hat, mu, logvar, losses]) -- all fp32 CUDA tensors."""
+        c = self.cfg
+        B = qpos.shape[0]
+        assert qpos.is_cuda and image.is_cuda, "inputs must be CUDA tensors"
+        qpos = qpos.contiguous().float()
+        image = image.contiguous().float()
+        assert image.shape == (B, c.num_cameras, 3, c.img_h, c.img_w), f"image shape {tuple(image.shape)}"
+        assert qpos.shape[1] == c.state_dim
+        out = dict(a_hat=torch.empty((B, c.num_queries, c.action_dim), dtype=torch.float32, device=self.device))
+        iph = torch.empty((B, c.num_queries, 1), dtype=torch.float32, device=self.device) if want_is_pad_hat else None
+        a_ptr = p_ptr = e_ptr = mu_ptr = lv_ptr = ls_ptr = None
+        abs_ = pbs = 0
+        keep = []
+        if actions is not None:
+            actions = actions.float()
+            if actions.stride(2) != 1 or actions.stride(1) != actions.shape[2]:
+                actions = actions.contiguous()
+            pad8 = is_pad.to(torch.uint8) if is_pad.dtype != torch.uint8 else is_pad
+            if is_pad.dtype == torch.bool:
+                pad8 = is_pad.view(torch.uint8)
+            if pad8.stride(1) != 1:
+                pad8 = pad8.contiguous()
+            assert actions.shape[1] >= c.num_queries and pad8.shape[1] >= c.num_queries
+            if eps is None:
+                eps = torch.randn((B, c.latent_dim), dtype=torch.float32, device=self.device)
+            eps = eps.contiguous().float()
+            out["mu"] = torch.empty((B, c.latent_dim), dtype=torch.float32, device=self.device)
+            out["logvar"] = torch.empty_like(out["mu"])
+            out["losses"] = torch.empty(3, dtype=torch.float32, device=self.device)
+            a_ptr, p_ptr, e_ptr = actions.data_ptr(), pad8.data_ptr(), eps.data_ptr()
+            abs_, pbs = actions.stride(0), pad8.stride(0)
+            mu_ptr, lv_ptr, ls_ptr = out["mu"].data_ptr(), out["logvar"].data_ptr(), out["losses"].data_ptr()
+            keep += [actions, pad8, eps]
+        self._keep = keep + [qpos, image]          # inputs must stay alive until the backward has run
+        check(self.lib.act_engine_forward(self._h, B, qpos.data_ptr(), image.data_ptr(), a_ptr, abs_, p_ptr, pbs, e_ptr,
+                                          out["a_hat"].data_ptr(), iph.data_ptr() if iph is not None else None,
+                                          mu_ptr, lv_ptr, ls_ptr, _stream()), "act_engine_forward")
+        if iph is not None:
+            out["is_pad_hat"] = iph
+        return out
+
+    def backward(self, stage: int = 0, loss_grad: float = 1.0):
+        check(self.lib.act_engine_backward(self._h, stage, float(loss_grad), _stream()), "act_engine_backward")
+
+    def zero_grad(self):
+        check(self.lib.act_engine_zero_grad(self._h, _stream()), "act_engine_zero_grad")
+
+    def adamw_step(self):
+        self.step_count += 1
+        check(self.lib.act_engine_adamw_step(self._h, self.step_count, _stream()), "act_engine_adamw_step")
+
+    def set_lr(self, lr: float, lr_backbone: float):
+        check(self.lib.act_engine_set_lr(self._h, lr, lr_backbone), "act_engine_set_lr")
+
+    def launches(self, reset: bool = False) -> int:
+        return self.lib.act_engine_launches(self._h, 1 if reset else 0)
+
+    def workspace_bytes(self) -> int:
+        return self.lib.act_engine_workspace_bytes(self._h)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None) and self._h.value:
+                self.lib.act_engine_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass

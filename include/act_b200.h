@@ -109,6 +109,48 @@ int act_adamw_step(float* p, const float* g, float* m, float* v, void* shadow_bf
 int act_temporal_agg_step(float* ring, const float* chunks, const int* t, double* out, int E, int nq, int A, double k,
                           void* stream);
 
+/* ---- the policy engine: DETRVAE forward / backward / AdamW as one stream-ordered object -----------------------
+ * Replaces detr/main.py:92-112 (build_ACT_model_and_optimizer), ACTPolicy.__call__ (policy.py:264-332),
+ * loss.backward() / optimizer.step() of imitate_episodes.py:603-607.  Parameters, gradients and Adam moments are
+ * caller-owned flat fp32 device buffers (torch tensors on the Python side); the tensor table tells where each
+ * reference state_dict entry lives inside them.  Workspace is owned by the handle. */
+typedef struct act_engine act_engine;
+typedef struct {
+  int batch_max, num_cameras, img_h, img_w;
+  int hidden_dim, nheads, dim_feedforward, enc_layers, dec_layers;
+  int num_queries, state_dim, action_dim, latent_dim;
+  float kl_weight, lr, lr_backbone, weight_decay, beta1, beta2, adam_eps;
+  int faithful_decoder;   /* reserved: execute the dead decoder layers 1.. as the reference does */
+  int train;              /* 0: inference-only workspace */
+} act_engine_config;
+
+int act_engine_create(const act_engine_config* cfg, act_engine** out);
+void act_engine_destroy(act_engine* e);
+int act_engine_num_tensors(const act_engine* e);
+int64_t act_engine_total_floats(const act_engine* e);
+int64_t act_engine_workspace_bytes(const act_engine* e);
+/* kind: 0 param, 1 param with identically-zero grad (dead decoder layers), 2 param without grad (is_pad_head),
+ * 3 backbone param (lr_backbone), 4 buffer.  region: 0 main, 1 cvae, 2 dead, 3 nograd, 4 backbone, 5 buffer. */
+int act_engine_tensor_info(const act_engine* e, int i, char* name, int name_cap, int64_t shape[4], int* ndim,
+                           int64_t* offset, int64_t* numel, int* kind, int* region);
+int act_engine_region(const act_engine* e, int region, int64_t* offset, int64_t* count);
+int act_engine_bind(act_engine* e, float* params, float* grads, float* exp_avg, float* exp_avg_sq);
+/* rebuild the bf16 / packed operand shadows from the fp32 parameters (after load_state_dict or any external write) */
+int act_engine_refresh(act_engine* e, void* stream);
+/* qpos [B,S] f32, image [B,K,3,H,W] f32 in [0,1]; training/validation call when actions != NULL
+ * (actions [B,>=nq,A] with batch stride actions_bs, is_pad uint8 [B,>=nq] with batch stride is_pad_bs, eps [B,Z]).
+ * Outputs (each may be NULL): a_hat [B,nq,A], is_pad_hat [B,nq], mu/logvar [B,Z], losses[3] = {l1, kl, loss}. */
+int act_engine_forward(act_engine* e, int B, const float* qpos, const float* image, const float* actions,
+                       int64_t actions_bs, const uint8_t* is_pad, int64_t is_pad_bs, const float* eps, float* a_hat,
+                       float* is_pad_hat, float* mu, float* logvar, float* losses, void* stream);
+/* gradients of loss_grad * loss into the bound gradient buffer.  stage 0 = everything; 1 = heads + transformer,
+ * 2 = CVAE encoder, 3 = backbones (run 1,2,3 in order to overlap the gradient all-reduce of finished regions). */
+int act_engine_backward(act_engine* e, int stage, float loss_grad, void* stream);
+int act_engine_zero_grad(act_engine* e, void* stream);
+int act_engine_adamw_step(act_engine* e, int step, void* stream);
+int act_engine_set_lr(act_engine* e, float lr, float lr_backbone);
+int act_engine_launches(act_engine* e, int reset);
+
 #ifdef __cplusplus
 }
 #endif
