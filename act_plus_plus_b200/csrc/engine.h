@@ -176,7 +176,9 @@ class Engine {
   bf16 *gb1_ = nullptr, *gb2_ = nullptr, *gbqk_ = nullptr, *gbhh_ = nullptr, *gbv_ = nullptr, *gbk_ = nullptr;
   float* d_src_ = nullptr; float* d_tokC_ = nullptr;
   bf16 *cg_[4] = {nullptr, nullptr, nullptr, nullptr};   // backbone gradient ping-pong (NHWC bf16, max size)
-  bf16* d_feat_ = nullptr;
+  bf16* d_feat_ = nullptr;      // [K][B*Hf*Wf*512] gradient wrt each camera's layer4 output (ReLU-masked)
+  float* conv1_tmp_ = nullptr;  // [64][192] split-K accumulator of the stem weight gradient
+  int input_grads(int B, cudaStream_t st);
 };
 
 }  // namespace act

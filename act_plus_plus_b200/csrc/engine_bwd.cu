@@ -1,12 +1,367 @@
-// Engine: backward pass (filled in incrementally).
+// Engine: backward pass.  Hand-derived reverse of engine_fwd.cu (the reference relies on torch autograd,
+// imitate_episodes.py:605-606).  Every weight gradient is accumulated with fp32 atomics into the zeroed flat
+// gradient buffer, so split-K, shared weights (input_proj across cameras) and stage-wise execution all compose.
 #include "engine.h"
+#include <cmath>
 
 namespace act {
 
+#define RUN(expr) do { ++launches_; if ((expr) != 0) return -1; } while (0)
+
+static int roundup(int a, int b) { return (a + b - 1) / b * b; }
+
+__global__ void add_out_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out, long long n4) {
+  for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * 1LL * blockDim.x) {
+    const float4 x = reinterpret_cast<const float4*>(a)[i], y = reinterpret_cast<const float4*>(b)[i];
+    reinterpret_cast<float4*>(out)[i] = make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w);
+  }
+}
+static int add_out(const float* a, const float* b, float* out, long long n, cudaStream_t st) {
+  const long long n4 = n / 4;
+  add_out_kernel<<<static_cast<int>(std::min<long long>((n4 + 255) / 256, 148 * 8)), 256, 0, st>>>(a, b, out, n4);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// gradient rows of one camera's feature tokens: src fp32 [B, L, d] rows (2 + y*WfK + cam*Wf + x) -> bf16 [B*Hf*Wf, d]
+__global__ void gather_tokens_kernel(const float* __restrict__ src, bf16* __restrict__ out, int B, int L, int Hf, int Wf,
+                                     int K, int cam, int d4) {
+  const long long total = 1LL * B * Hf * Wf * d4;
+  for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
+    const int c = static_cast<int>(i % d4);
+    long long r = i / d4;
+    const int x = static_cast<int>(r % Wf); r /= Wf;
+    const int y = static_cast<int>(r % Hf);
+    const int b = static_cast<int>(r / Hf);
+    const long long row = 1LL * b * L + 2 + (1LL * y * K + cam) * Wf + x;
+    const float4 v = reinterpret_cast<const float4*>(src)[row * d4 + c];
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 o;
+    o.x = *reinterpret_cast<uint32_t*>(&lo); o.y = *reinterpret_cast<uint32_t*>(&hi);
+    reinterpret_cast<uint2*>(out)[i] = o;
+  }
+}
+
+// conv1 weight gradient epilogue: dw[64][147] += scale[co] * tmp[64][KP]
+__global__ void conv1_grad_fold_kernel(const float* __restrict__ tmp, const float* __restrict__ scale, float* __restrict__ dw, int KP) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 64 * 147) return;
+  const int co = i / 147, k = i % 147;
+  dw[i] += scale[co] * tmp[co * KP + k];
+}
+
+// dX[M,K] = dY[M,N] * W[N,K]   (A = dY K-major, B = W read MN-major)
+int Engine::linear_dx(const bf16* dY, int M, const LinW& w, uint32_t flags, const float* res_f32, const bf16* aux,
+                      float* out_f32, bf16* out_bf16, cudaStream_t st) {
+  MatDesc A, B;
+  A.ptr = dY; A.ld = w.N; B.ptr = w.w; B.mn_major = 1; B.ld = w.K;
+  EpiDesc e;
+  e.flags = flags | (out_f32 ? EPI_OUT_F32 : 0) | (out_bf16 ? EPI_OUT_BF16 : 0) | (res_f32 ? EPI_RES_F32 : 0) | (aux ? EPI_MASK_POS : 0);
+  e.res_f32 = res_f32; e.out_f32 = out_f32; e.out_bf16 = out_bf16; e.aux_bf16 = aux; e.ldc = w.K; e.ldr = w.K;
+  ++launches_;
+  return tc_gemm(M, w.K, w.N, 1, 1, A, B, e, 1, st);
+}
+
+// dW[N,K] += dY^T X ; db[N] += colsum(dY)
+int Engine::linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cudaStream_t st) {
+  MatDesc A, B;
+  A.ptr = dY; A.mn_major = 1; A.ld = w.N; B.ptr = X; B.mn_major = 1; B.ld = w.K;
+  EpiDesc e;
+  e.flags = EPI_OUT_F32 | EPI_ATOMIC; e.out_f32 = w.gw; e.ldc = w.K;
+  const int bn = w.K >= 1024 ? 128 : 64;
+  const long long tiles = 1LL * ((w.N + 127) / 128) * ((w.K + bn - 1) / bn);
+  const int kblocks = (M + 63) / 64;
+  int ks = static_cast<int>(std::max<long long>(1, (148 * 2 + tiles - 1) / tiles));
+  ks = std::max(1, std::min(ks, kblocks / 2));
+  ++launches_;
+  if (tc_gemm(w.N, w.K, M, 1, 1, A, B, e, ks, st, bn)) return -1;
+  if (w.gb) RUN(colsum_bf16(dY, w.N, M, w.N, w.gb, st));
+  return 0;
+}
+
+int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv,
+                     const bf16* P, bf16* dQ, long long lddq, bf16* dK, long long lddk, bf16* dV, long long lddv, int B,
+                     int Lq, int Lk, cudaStream_t st) {
+  const int h = cfg_.nheads, hd = 64, Lkp = roundup(Lk, 8);
+  const long long ph = 1LL * Lq * Lkp, pb = 1LL * h * Lq * Lkp;
+  {  // dV[j,d] = sum_i P[i,j] dO[i,d]
+    MatDesc a, b; EpiDesc e;
+    a.ptr = P; a.mn_major = 1; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
+    b.ptr = dO; b.mn_major = 1; b.ld = 512; b.sz0 = hd; b.sz1 = 1LL * Lq * 512;
+    e.flags = EPI_OUT_BF16; e.out_bf16 = dV; e.ldc = lddv; e.osz0 = hd; e.osz1 = Lk * lddv;
+    ++launches_;
+    if (tc_gemm(Lk, hd, Lq, h, B, a, b, e, 1, st)) return -1;
+  }
+  {  // dP[i,j] = sum_d dO[i,d] V[j,d]
+    MatDesc a, b; EpiDesc e;
+    a.ptr = dO; a.ld = 512; a.sz0 = hd; a.sz1 = 1LL * Lq * 512;
+    b.ptr = V; b.ld = ldv; b.sz0 = hd; b.sz1 = Lk * ldv;
+    e.flags = EPI_OUT_F32; e.out_f32 = Sbuf_; e.ldc = Lkp; e.osz0 = ph; e.osz1 = pb;
+    ++launches_;
+    if (tc_gemm(Lq, Lk, hd, h, B, a, b, e, 1, st)) return -1;
+  }
+  RUN(softmax_bwd(P, Sbuf_, dSbuf_, B * h * Lq, Lk, Lkp, 0.125f, st));
+  {  // dQ[i,d] = sum_j dS[i,j] K[j,d]
+    MatDesc a, b; EpiDesc e;
+    a.ptr = dSbuf_; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
+    b.ptr = K; b.mn_major = 1; b.ld = ldk; b.sz0 = hd; b.sz1 = Lk * ldk;
+    e.flags = EPI_OUT_BF16; e.out_bf16 = dQ; e.ldc = lddq; e.osz0 = hd; e.osz1 = Lq * lddq;
+    ++launches_;
+    if (tc_gemm(Lq, hd, Lk, h, B, a, b, e, 1, st)) return -1;
+  }
+  {  // dK[j,d] = sum_i dS[i,j] Q[i,d]
+    MatDesc a, b; EpiDesc e;
+    a.ptr = dSbuf_; a.mn_major = 1; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
+    b.ptr = Q; b.mn_major = 1; b.ld = ldq; b.sz0 = hd; b.sz1 = Lq * ldq;
+    e.flags = EPI_OUT_BF16; e.out_bf16 = dK; e.ldc = lddk; e.osz0 = hd; e.osz1 = Lk * lddk;
+    ++launches_;
+    if (tc_gemm(Lk, hd, Lq, h, B, a, b, e, 1, st)) return -1;
+  }
+  return 0;
+}
+
+// Reverse of enc_layer_fwd.  Input gradient = dx2 (+ dx2b); outputs dx_out (wrt x) and gxp_out (wrt x + pos, i.e. the
+// q/k branch) -- the caller adds them (and reduces gxp_out into learned position embeddings where they exist).
+int Engine::enc_layer_bwd(const EncW& w, EncActs& a, const float* x_in, const float* dx2, const float* dx2b, float* dx_out,
+                          float* gxp_out, int L, int B, cudaStream_t st) {
+  (void)x_in;
+  const int M = B * L, d = cfg_.hidden_dim;
+  RUN(ln_bwd(dx2, dx2b, a.t2, a.mean2, a.rstd2, w.n2.g, gA_, gb1_, w.n2.gg, w.n2.gb, M, d, st));
+  if (linear_dwb(gb1_, M, w.l2, a.hh, st)) return -1;
+  if (linear_dx(gb1_, M, w.l2, 0, nullptr, a.hh, nullptr, gbhh_, st)) return -1;
+  if (linear_dwb(gbhh_, M, w.l1, a.x1b, st)) return -1;
+  if (linear_dx(gbhh_, M, w.l1, 0, gA_, nullptr, gB_, nullptr, st)) return -1;
+  RUN(ln_bwd(gB_, nullptr, a.t1, a.mean1, a.rstd1, w.n1.g, gA_, gb1_, w.n1.gg, w.n1.gb, M, d, st));
+  if (linear_dwb(gb1_, M, w.sa.o, a.o, st)) return -1;
+  if (linear_dx(gb1_, M, w.sa.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
+  if (attn_bwd(gb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gbqk_, 2 * d, gbqk_ + d, 2 * d, gbv_, d, B, L, L, st)) return -1;
+  if (linear_dwb(gbqk_, M, w.sa.qk, a.xpb, st)) return -1;
+  if (linear_dwb(gbv_, M, w.sa.v, a.xb, st)) return -1;
+  if (linear_dx(gbqk_, M, w.sa.qk, 0, nullptr, nullptr, gxp_out, nullptr, st)) return -1;
+  if (linear_dx(gbv_, M, w.sa.v, 0, gA_, nullptr, dx_out, nullptr, st)) return -1;
+  return 0;
+}
+
+
+// Heads, final norm, decoder layer 0, main encoder, then the gradients of the token-producing projections.
+int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
+  const int B = cur_B_, d = cfg_.hidden_dim, nq = cfg_.num_queries, A = cfg_.action_dim, Z = cfg_.latent_dim;
+  const int Md = B * nq, Me = B * L_;
+  const DecW& w = dec_w_[0];
+  DecActs& a = dec_a_;
+  RUN(act_loss(a_hat_, in_actions_, in_actions_bs_, in_is_pad_, in_is_pad_bs_, mu_, logvar_, B, nq, A, Z, cfg_.kl_weight,
+               loss_grad, losses_ + 4, d_a_hat_, d_mu_, d_logvar_, st));
+  SgemmArgs g;
+  // action_head: dW[a,c] += sum_m d_a[m,a] hs[m,c]; db; d_hs = d_a W
+  g = SgemmArgs(); g.I = A; g.J = d; g.R = Md; g.A = d_a_hat_; g.ai = act::lin(1); g.ar = act::lin(A);
+  g.B = hs_; g.br = act::lin(d); g.bj = act::lin(1); g.C = G("action_head.weight"); g.ci = act::lin(d); g.cj = act::lin(1); g.accumulate = 1;
+  RUN(sgemm_generic(g, st));
+  g = SgemmArgs(); g.I = 1; g.J = A; g.R = Md; g.A = one_; g.ai = act::lin(0); g.ar = act::lin(0);
+  g.B = d_a_hat_; g.br = act::lin(A); g.bj = act::lin(1); g.C = G("action_head.bias"); g.ci = act::lin(0); g.cj = act::lin(1); g.accumulate = 1;
+  RUN(sgemm_generic(g, st));
+  g = SgemmArgs(); g.I = Md; g.J = d; g.R = A; g.A = d_a_hat_; g.ai = act::lin(A); g.ar = act::lin(1);
+  g.B = P("action_head.weight"); g.br = act::lin(d); g.bj = act::lin(1); g.C = d_hs_; g.ci = act::lin(d); g.cj = act::lin(1);
+  RUN(sgemm_generic(g, st));
+  // shared final norm, norm3, FFN
+  RUN(ln_bwd(d_hs_, nullptr, a.y3, hs_mean_, hs_rstd_, dec_norm_.g, gA_, nullptr, dec_norm_.gg, dec_norm_.gb, Md, d, st));
+  RUN(ln_bwd(gA_, nullptr, a.t3, a.mean3, a.rstd3, w.n3.g, gB_, gb1_, w.n3.gg, w.n3.gb, Md, d, st));
+  if (linear_dwb(gb1_, Md, w.l2, a.hh, st)) return -1;
+  if (linear_dx(gb1_, Md, w.l2, 0, nullptr, a.hh, nullptr, gbhh_, st)) return -1;
+  if (linear_dwb(gbhh_, Md, w.l1, a.y2b, st)) return -1;
+  if (linear_dx(gbhh_, Md, w.l1, 0, gB_, nullptr, gA_, nullptr, st)) return -1;
+  // norm2, cross-attention
+  RUN(ln_bwd(gA_, nullptr, a.t2, a.mean2, a.rstd2, w.n2.g, gB_, gb1_, w.n2.gg, w.n2.gb, Md, d, st));
+  if (linear_dwb(gb1_, Md, w.ca.o, a.co, st)) return -1;
+  if (linear_dx(gb1_, Md, w.ca.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
+  if (attn_bwd(gb2_, a.q, d, a.k, d, a.cv, d, a.cP, gbqk_, d, gbk_, d, gbv_, d, B, nq, L_, st)) return -1;
+  if (linear_dwb(gbqk_, Md, w.ca.q, a.y1pb, st)) return -1;
+  if (linear_dx(gbqk_, Md, w.ca.q, 0, nullptr, nullptr, gE_, nullptr, st)) return -1;          // wrt y1 + query_pos
+  if (linear_dwb(gbk_, Me, w.ca.k, mem_pb_, st)) return -1;
+  if (linear_dx(gbk_, Me, w.ca.k, 0, nullptr, nullptr, gMemPos_, nullptr, st)) return -1;      // wrt memory + pos
+  if (linear_dwb(gbv_, Me, w.ca.v, mem_b_, st)) return -1;
+  if (linear_dx(gbv_, Me, w.ca.v, 0, nullptr, nullptr, gMem_, nullptr, st)) return -1;         // wrt memory
+  auto reduce_batch = [&](const float* src, long long batch_stride, int n, float* dst) {       // dst[j] += sum_b src[b*bs + j]
+    SgemmArgs r;
+    r.I = 1; r.J = n; r.R = B; r.A = one_; r.ai = act::lin(0); r.ar = act::lin(0);
+    r.B = src; r.br = act::lin(batch_stride); r.bj = act::lin(1); r.C = dst; r.ci = act::lin(0); r.cj = act::lin(1); r.accumulate = 1;
+    ++launches_;
+    return sgemm_generic(r, st);
+  };
+  float* g_addpos = G("additional_pos_embed.weight");
+  float* g_query = G("query_embed.weight");
+  if (reduce_batch(gMemPos_, 1LL * L_ * d, 2 * d, g_addpos)) return -1;
+  if (reduce_batch(gE_, 1LL * nq * d, nq * d, g_query)) return -1;
+  // norm1 (input gradient = dt2 + query branch), self-attention over the queries
+  RUN(ln_bwd(gB_, gE_, a.t1, a.mean1, a.rstd1, w.n1.g, gA_, gb1_, w.n1.gg, w.n1.gb, Md, d, st));
+  if (linear_dwb(gb1_, Md, w.sa.o, a.o, st)) return -1;
+  if (linear_dx(gb1_, Md, w.sa.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
+  if (attn_bwd(gb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gbqk_, 2 * d, gbqk_ + d, 2 * d, gbv_, d, B, nq, nq, st)) return -1;
+  if (linear_dwb(gbqk_, Md, w.sa.qk, a.xpb, st)) return -1;
+  if (linear_dwb(gbv_, Md, w.sa.v, a.xb, st)) return -1;
+  if (linear_dx(gbqk_, Md, w.sa.qk, 0, nullptr, nullptr, gE_, nullptr, st)) return -1;
+  if (reduce_batch(gE_, 1LL * nq * d, nq * d, g_query)) return -1;
+  // main encoder, last layer first
+  const float* dx2 = gMem_;
+  const float* dx2b = gMemPos_;
+  for (int l = cfg_.enc_layers - 1; l >= 0; --l) {
+    if (enc_layer_bwd(enc_w_[l], enc_a_[l], nullptr, dx2, dx2b, gC_, gD_, L_, B, st)) return -1;
+    if (reduce_batch(gD_, 1LL * L_ * d, 2 * d, g_addpos)) return -1;
+    dx2 = gC_; dx2b = gD_;
+  }
+  RUN(add_out(gC_, gD_, d_src_, 1LL * Me * d, st));
+  // token 0 <- latent_out_proj(z), token 1 <- input_proj_robot_state(qpos)
+  const long long ts = 1LL * L_ * d;
+  g = SgemmArgs(); g.I = d; g.J = Z; g.R = B; g.A = d_src_; g.ai = act::lin(1); g.ar = act::lin(ts);
+  g.B = z_; g.br = act::lin(Z); g.bj = act::lin(1); g.C = G("latent_out_proj.weight"); g.ci = act::lin(Z); g.cj = act::lin(1); g.accumulate = 1;
+  RUN(sgemm_generic(g, st));
+  if (reduce_batch(d_src_, ts, d, G("latent_out_proj.bias"))) return -1;
+  g = SgemmArgs(); g.I = B; g.J = Z; g.R = d; g.A = d_src_; g.ai = act::lin(ts); g.ar = act::lin(1);
+  g.B = P("latent_out_proj.weight"); g.br = act::lin(Z); g.bj = act::lin(1); g.C = dz_; g.ci = act::lin(Z); g.cj = act::lin(1);
+  RUN(sgemm_generic(g, st));
+  const int S = cfg_.state_dim;
+  g = SgemmArgs(); g.I = d; g.J = S; g.R = B; g.A = d_src_ + d; g.ai = act::lin(1); g.ar = act::lin(ts);
+  g.B = in_qpos_; g.br = act::lin(S); g.bj = act::lin(1); g.C = G("input_proj_robot_state.weight"); g.ci = act::lin(S); g.cj = act::lin(1); g.accumulate = 1;
+  RUN(sgemm_generic(g, st));
+  if (reduce_batch(d_src_ + d, ts, d, G("input_proj_robot_state.bias"))) return -1;
+  // image tokens <- input_proj(layer4 features) per camera
+  const int Mf = B * Hf_ * Wf_;
+  for (int k = 0; k < cfg_.num_cameras; ++k) {
+    const long long total = 1LL * Mf * (d / 4);
+    gather_tokens_kernel<<<static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 8)), 256, 0, st>>>(
+        d_src_, gb2_, B, L_, Hf_, Wf_, cfg_.num_cameras, k, d / 4);
+    ++launches_;
+    ACT_CUDA(cudaGetLastError());
+    const bf16* feat = cam_a_[k].blk[7].y;
+    if (linear_dwb(gb2_, Mf, input_proj_, feat, st)) return -1;
+    if (linear_dx(gb2_, Mf, input_proj_, 0, nullptr, feat, nullptr, d_feat_ + 1LL * k * cfg_.batch_max * Hf_ * Wf_ * 512, st)) return -1;
+  }
+  return 0;
+}
+
+// Reverse of cvae_fwd: reparametrisation + KL, latent_proj, the 4 masked encoder layers, the token projections.
+int Engine::cvae_bwd(cudaStream_t st) {
+  const int B = cur_B_, d = cfg_.hidden_dim, nq = cfg_.num_queries, A = cfg_.action_dim, Z = cfg_.latent_dim, S = cfg_.state_dim;
+  const int Mc = B * Lc_, nl = cfg_.enc_layers;
+  const long long ts = 1LL * Lc_ * d;
+  RUN(reparam_bwd(dz_, eps_, logvar_, d_mu_, d_logvar_, d_info_, B, Z, st));
+  SgemmArgs g;
+  const float* cls_out = cvae_a_[nl - 1].x2;
+  g = SgemmArgs(); g.I = 2 * Z; g.J = d; g.R = B; g.A = d_info_; g.ai = act::lin(1); g.ar = act::lin(2 * Z);
+  g.B = cls_out; g.br = act::lin(ts); g.bj = act::lin(1); g.C = G("latent_proj.weight"); g.ci = act::lin(d); g.cj = act::lin(1); g.accumulate = 1;
+  RUN(sgemm_generic(g, st));
+  g = SgemmArgs(); g.I = 1; g.J = 2 * Z; g.R = B; g.A = one_; g.ai = act::lin(0); g.ar = act::lin(0);
+  g.B = d_info_; g.br = act::lin(2 * Z); g.bj = act::lin(1); g.C = G("latent_proj.bias"); g.ci = act::lin(0); g.cj = act::lin(1); g.accumulate = 1;
+  RUN(sgemm_generic(g, st));
+  // gradient wrt the encoder output: only the cls rows are non-zero
+  ACT_CUDA(cudaMemsetAsync(gC_, 0, sizeof(float) * Mc * d, st));
+  g = SgemmArgs(); g.I = B; g.J = d; g.R = 2 * Z; g.A = d_info_; g.ai = act::lin(2 * Z); g.ar = act::lin(1);
+  g.B = P("latent_proj.weight"); g.br = act::lin(d); g.bj = act::lin(1); g.C = gC_; g.ci = act::lin(ts); g.cj = act::lin(1);
+  RUN(sgemm_generic(g, st));
+  const float* dx2 = gC_;
+  const float* dx2b = nullptr;
+  for (int l = nl - 1; l >= 0; --l) {
+    if (enc_layer_bwd(cvae_w_[l], cvae_a_[l], nullptr, dx2, dx2b, gC_, gD_, Lc_, B, st)) return -1;
+    dx2 = gC_; dx2b = gD_;
+  }
+  RUN(add_out(gC_, gD_, d_tokC_, 1LL * Mc * d, st));
+  // token 0: cls_embed ; token 1: encoder_joint_proj(qpos) ; tokens 2..: encoder_action_proj(actions)
+  g = SgemmArgs(); g.I = 1; g.J = d; g.R = B; g.A = one_; g.ai = act::lin(0); g.ar = act::lin(0);
+  g.B = d_tokC_; g.br = act::lin(ts); g.bj = act::lin(1); g.C = G("cls_embed.weight"); g.ci = act::lin(0); g.cj = act::lin(1); g.accumulate = 1;
+  RUN(sgemm_generic(g, st));
+  g = SgemmArgs(); g.I = d; g.J = S; g.R = B; g.A = d_tokC_ + d; g.ai = act::lin(1); g.ar = act::lin(ts);
+  g.B = in_qpos_; g.br = act::lin(S); g.bj = act::lin(1); g.C = G("encoder_joint_proj.weight"); g.ci = act::lin(S); g.cj = act::lin(1); g.accumulate = 1;
+  RUN(sgemm_generic(g, st));
+  g = SgemmArgs(); g.I = 1; g.J = d; g.R = B; g.A = one_; g.ai = act::lin(0); g.ar = act::lin(0);
+  g.B = d_tokC_ + d; g.br = act::lin(ts); g.bj = act::lin(1); g.C = G("encoder_joint_proj.bias"); g.ci = act::lin(0); g.cj = act::lin(1); g.accumulate = 1;
+  RUN(sgemm_generic(g, st));
+  g = SgemmArgs(); g.I = d; g.J = A; g.R = B * nq; g.A = d_tokC_ + 2 * d; g.ai = act::lin(1); g.ar = batched(nq, ts, d);
+  g.B = in_actions_; g.br = batched(nq, in_actions_bs_, A); g.bj = act::lin(1); g.C = G("encoder_action_proj.weight"); g.ci = act::lin(A); g.cj = act::lin(1); g.accumulate = 1;
+  RUN(sgemm_generic(g, st));
+  g = SgemmArgs(); g.I = 1; g.J = d; g.R = B * nq; g.A = one_; g.ai = act::lin(0); g.ar = act::lin(0);
+  g.B = d_tokC_ + 2 * d; g.br = batched(nq, ts, d); g.bj = act::lin(1); g.C = G("encoder_action_proj.bias"); g.ci = act::lin(0); g.cj = act::lin(1); g.accumulate = 1;
+  RUN(sgemm_generic(g, st));
+  return 0;
+}
+
+
+// Reverse of backbone_fwd for one camera.  The incoming gradient (d_feat_) is already masked by the ReLU of layer4.
+// FrozenBN: wrt the conv output the gradient is scale[co] * g; the scale is folded into the packed dgrad weights
+// (wpkt) and applied per output channel in the wgrad epilogue, so no elementwise pass is needed.
+int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
+  CamW& cw = cam_w_[cam];
+  CamActs& ca = cam_a_[cam];
+  const bf16* g = d_feat_ + 1LL * cam * cfg_.batch_max * Hf_ * Wf_ * 512;
+  bf16* bufs[3] = {cg_[1], cg_[2], cg_[3]};
+  int gi = -1;                                       // index in bufs holding g (-1: d_feat_)
+  for (int i = 7; i >= 0; --i) {
+    BlockW& bw = cw.blk[i];
+    BlockActs& ba = ca.blk[i];
+    const int s = i / 2;
+    const int Ho = fh_[2 + s], Wo = fw_[2 + s];
+    const int st1 = bw.c1.stride;
+    const int Hc = (st1 == 2) ? fh_[1 + s] : Ho, Wc = (st1 == 2) ? fw_[1 + s] : Wo;
+    const bf16* x_in = (i == 0) ? ca.p1 : ca.blk[i - 1].y;
+    const int ga_i = (gi + 1 + 3) % 3;
+    bf16* ga = bufs[ga_i];
+    int dx_i = (ga_i + 1) % 3;
+    if (dx_i == gi) dx_i = (dx_i + 1) % 3;
+    bf16* dx = bufs[dx_i];
+    ConvShape s2{B, Ho, Wo, bw.c2.Cin, bw.c2.Cout, 3, 1, 1};
+    ConvShape s1{B, Hc, Wc, bw.c1.Cin, bw.c1.Cout, 3, st1, 1};
+    RUN(conv_wgrad(s2, ba.a, g, bw.c2.gw, 1.f, bw.c2.scale, st));
+    {
+      EpiDesc e; e.flags = EPI_OUT_BF16 | EPI_MASK_POS; e.out_bf16 = ga; e.aux_bf16 = ba.a;
+      RUN(conv_dgrad(s2, g, bw.c2.wpkt, e, nullptr, st));
+    }
+    RUN(conv_wgrad(s1, x_in, ga, bw.c1.gw, 1.f, bw.c1.scale, st));
+    EpiDesc e1; e1.flags = EPI_OUT_BF16; e1.out_bf16 = dx;
+    if (i > 0) { e1.flags |= EPI_MASK_POS; e1.aux_bf16 = x_in; }     // x_in = relu output of the previous block
+    if (bw.has_ds) {
+      ConvShape sd{B, Hc, Wc, bw.ds.Cin, bw.ds.Cout, 1, st1, 0};
+      RUN(conv_wgrad(sd, x_in, g, bw.ds.gw, 1.f, bw.ds.scale, st));
+      ConvShape sdc{B, Ho, Wo, bw.ds.Cin, bw.ds.Cout, 1, 1, 0};      // 1x1 data gradient on the compact (strided) grid
+      EpiDesc ec; ec.flags = EPI_OUT_BF16; ec.out_bf16 = cg_[0];
+      RUN(conv_dgrad(sdc, g, bw.ds.wpkt, ec, nullptr, st));
+      RUN(conv_dgrad(s1, ga, bw.c1.wpkt, e1, cg_[0], st));
+      launches_ += 3;                                                // four parity-class launches
+    } else {
+      e1.flags |= EPI_RES_BF16; e1.res_bf16 = g;
+      RUN(conv_dgrad(s1, ga, bw.c1.wpkt, e1, nullptr, st));
+    }
+    g = dx; gi = dx_i;
+  }
+  // stem: max-pool backward (+ReLU mask), then dW1 = scale * dy1^T im2col(normalised image)
+  const int H1 = fh_[1], W1 = fw_[1];
+  RUN(maxpool_bwd(g, ca.pidx, ca.y1, cg_[0], B, H1, W1, 64, st));
+  const float* img = in_image_ + 1LL * cam * 3 * fh_[0] * fw_[0];
+  RUN(im2col_conv1(img, 1LL * cfg_.num_cameras * 3 * fh_[0] * fw_[0], im2col_, B, fh_[0], fw_[0], 192, st));
+  ACT_CUDA(cudaMemsetAsync(conv1_tmp_, 0, sizeof(float) * 64 * 192, st));
+  {
+    MatDesc a, b; EpiDesc e;
+    const int Mpix = B * H1 * W1;
+    a.ptr = cg_[0]; a.mn_major = 1; a.ld = 64; b.ptr = im2col_; b.mn_major = 1; b.ld = 192;
+    e.flags = EPI_OUT_F32 | EPI_ATOMIC; e.out_f32 = conv1_tmp_; e.ldc = 192;
+    const int kb = (Mpix + 63) / 64;
+    const int ks = std::max(1, std::min(kb / 4, 96));
+    ++launches_;
+    if (tc_gemm(64, 192, Mpix, 1, 1, a, b, e, ks, st, 64)) return -1;
+  }
+  conv1_grad_fold_kernel<<<(64 * 147 + 255) / 256, 256, 0, st>>>(conv1_tmp_, cw.stem.scale, cw.stem.gw, 192);
+  ++launches_;
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int Engine::backward(int stage, float loss_grad, cudaStream_t st) {
-  (void)stage; (void)loss_grad; (void)st;
-  set_error("backward not implemented yet");
-  return -1;
+  ACT_CHECK(cfg_.train && grads_ != nullptr, "engine has no training workspace / gradient buffer");
+  ACT_CHECK(have_actions_ && cur_B_ > 0, "backward needs a preceding training forward (with actions)");
+  if (stage == 0 || stage == 1) { if (transformer_bwd(loss_grad, st)) return -1; }
+  if (stage == 0 || stage == 2) { if (cvae_bwd(st)) return -1; }
+  if (stage == 0 || stage == 3) {
+    for (int k = 0; k < cfg_.num_cameras; ++k)
+      if (backbone_bwd(k, cur_B_, st)) return -1;
+  }
+  return 0;
 }
 
 }  // namespace act

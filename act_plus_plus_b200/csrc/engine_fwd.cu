@@ -121,7 +121,8 @@ int Engine::alloc_workspace() {
     d_src_ = A_(float, Me * d); d_tokC_ = A_(float, Mc * d);
     const long long cmax = 1LL * Bm * fh_[1] * fw_[1] * 64;        // largest NHWC activation (conv1 output)
     for (int i = 0; i < 4; ++i) { cg_[i] = A_(bf16, i == 0 ? cmax : cmax / 4); }
-    d_feat_ = A_(bf16, 1LL * Bm * Hf_ * Wf_ * 512);
+    d_feat_ = A_(bf16, 1LL * cfg_.num_cameras * Bm * Hf_ * Wf_ * 512);
+    conv1_tmp_ = A_(float, 64 * 192);
   }
 #undef A_
   // static part of the encoder position table: rows 2.. = PositionEmbeddingSine (position_encoding.py:30-52,
