@@ -33,7 +33,7 @@ class ActEngine:
     def __init__(self, batch_max=8, num_cameras=1, img_h=480, img_w=640, hidden_dim=512, nheads=8,
                  dim_feedforward=3200, enc_layers=4, dec_layers=7, num_queries=100, state_dim=14, action_dim=16,
                  latent_dim=32, kl_weight=10.0, lr=1e-5, lr_backbone=1e-5, weight_decay=1e-4, betas=(0.9, 0.999),
-                 eps=1e-8, train=True, device: Optional[torch.device] = None):
+                 eps=1e-8, train=True, device: Optional[torch.device] = None, share: "Optional[ActEngine]" = None):
         if not torch.cuda.is_available():
             raise _lib.ActB200Error("act_plus_plus_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
@@ -47,10 +47,19 @@ class ActEngine:
         with torch.cuda.device(self.device):
             check(self.lib.act_engine_create(C.byref(cfg), C.byref(self._h)), "act_engine_create")
             n = self.lib.act_engine_total_floats(self._h)
-            self.flat_params = torch.zeros(n, dtype=torch.float32, device=self.device)
-            self.flat_grads = torch.zeros(n, dtype=torch.float32, device=self.device) if train else None
-            self.exp_avg = torch.zeros(n, dtype=torch.float32, device=self.device) if train else None
-            self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=self.device) if train else None
+            if share is not None:
+                # several engines (different batch / image geometry, train vs inference workspace) over ONE set of
+                # master tensors; `_shared` carries the optimizer step count and the parameter version
+                assert share.flat_params.numel() == n, "engines sharing parameters must have the same model config"
+                self.flat_params, self._shared = share.flat_params, share._shared
+                self.flat_grads, self.exp_avg, self.exp_avg_sq = share.flat_grads, share.exp_avg, share.exp_avg_sq
+                train = train and self.flat_grads is not None
+            else:
+                self.flat_params = torch.zeros(n, dtype=torch.float32, device=self.device)
+                self.flat_grads = torch.zeros(n, dtype=torch.float32, device=self.device) if train else None
+                self.exp_avg = torch.zeros(n, dtype=torch.float32, device=self.device) if train else None
+                self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=self.device) if train else None
+                self._shared = dict(step=0, version=0, params={})
             check(self.lib.act_engine_bind(self._h, self.flat_params.data_ptr(),
                                            self.flat_grads.data_ptr() if train else None,
                                            self.exp_avg.data_ptr() if train else None,
@@ -66,7 +75,8 @@ class ActEngine:
             shp = tuple(int(shape[k]) for k in range(ndim.value))
             self.tensors[name.value.decode()] = dict(shape=shp, offset=off.value, numel=numel.value, kind=kind.value,
                                                      region=region.value)
-        self.step_count = 0
+        self._synced_version = -1 if share is not None else 0
+        self.last_was_train = False
 
     # ------------------------------------------------------------------ parameters
     def view(self, name: str, flat: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -97,11 +107,39 @@ class ActEngine:
                     if tuple(v.shape) != tuple(dst.shape):
                         raise RuntimeError(f"size mismatch for {k}: {tuple(v.shape)} vs {tuple(dst.shape)}")
                     dst.copy_(v.to(device=self.device, dtype=torch.float32))
+        self.mark_params_changed()
         self.refresh()
         return missing, unexpected
 
+    @classmethod
+    def sharing(cls, master: "ActEngine", batch_max: int, img_h: int, img_w: int, train: bool) -> "ActEngine":
+        c = master.cfg
+        return cls(batch_max=batch_max, num_cameras=c.num_cameras, img_h=img_h, img_w=img_w, hidden_dim=c.hidden_dim,
+                   nheads=c.nheads, dim_feedforward=c.dim_feedforward, enc_layers=c.enc_layers, dec_layers=c.dec_layers,
+                   num_queries=c.num_queries, state_dim=c.state_dim, action_dim=c.action_dim, latent_dim=c.latent_dim,
+                   kl_weight=c.kl_weight, lr=c.lr, lr_backbone=c.lr_backbone, weight_decay=c.weight_decay,
+                   betas=(c.beta1, c.beta2), eps=c.adam_eps, train=train, device=master.device, share=master)
+
+    @property
+    def step_count(self) -> int:
+        return self._shared["step"]
+
+    def param(self, name: str) -> torch.nn.Parameter:
+        """nn.Parameter aliasing the flat storage (its .grad aliases the flat gradient buffer)."""
+        cache = self._shared["params"]
+        if name not in cache:
+            p = torch.nn.Parameter(self.view(name), requires_grad=self.tensors[name]["kind"] != KIND_BUFFER)
+            if self.flat_grads is not None and self.tensors[name]["kind"] not in (KIND_BUFFER, KIND_NOGRAD):
+                p.grad = self.grad_view(name)
+            cache[name] = p
+        return cache[name]
+
+    def mark_params_changed(self):
+        self._shared["version"] += 1
+
     def refresh(self):
         check(self.lib.act_engine_refresh(self._h, _stream()), "act_engine_refresh")
+        self._synced_version = self._shared["version"]
 
     # ------------------------------------------------------------------ steps
     def forward(self, qpos, image, actions=None, is_pad=None, eps=None, want_is_pad_hat=False):
@@ -139,6 +177,9 @@ class ActEngine:
             mu_ptr, lv_ptr, ls_ptr = out["mu"].data_ptr(), out["logvar"].data_ptr(), out["losses"].data_ptr()
             keep += [actions, pad8, eps]
         self._keep = keep + [qpos, image]          # inputs must stay alive until the backward has run
+        if self._synced_version != self._shared["version"]:
+            self.refresh()                         # another engine stepped the shared parameters
+        self.last_was_train = actions is not None
         check(self.lib.act_engine_forward(self._h, B, qpos.data_ptr(), image.data_ptr(), a_ptr, abs_, p_ptr, pbs, e_ptr,
                                           out["a_hat"].data_ptr(), iph.data_ptr() if iph is not None else None,
                                           mu_ptr, lv_ptr, ls_ptr, _stream()), "act_engine_forward")
@@ -153,8 +194,10 @@ class ActEngine:
         check(self.lib.act_engine_zero_grad(self._h, _stream()), "act_engine_zero_grad")
 
     def adamw_step(self):
-        self.step_count += 1
-        check(self.lib.act_engine_adamw_step(self._h, self.step_count, _stream()), "act_engine_adamw_step")
+        self._shared["step"] += 1
+        check(self.lib.act_engine_adamw_step(self._h, self._shared["step"], _stream()), "act_engine_adamw_step")
+        self._shared["version"] += 1
+        self._synced_version = self._shared["version"]     # the fused step refreshed this engine's own shadows
 
     def set_lr(self, lr: float, lr_backbone: float):
         check(self.lib.act_engine_set_lr(self._h, lr, lr_backbone), "act_engine_set_lr")

@@ -1,0 +1,103 @@
+"""The reference-facing surface (policy.ACTPolicy / build_ACT_model_and_optimizer) driven the way
+imitate_episodes.py drives it: make_policy -> forward_pass -> loss.backward() -> optimizer.step() -> eval call."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _policy_config(K=1, lr=1e-5):
+    # imitate_episodes.py:78-94
+    return {'lr': lr, 'num_queries': 100, 'kl_weight': 10, 'hidden_dim': 512, 'dim_feedforward': 3200,
+            'lr_backbone': 1e-5, 'backbone': 'resnet18', 'enc_layers': 4, 'dec_layers': 7, 'nheads': 8,
+            'camera_names': [f'cam{k}' for k in range(K)], 'vq': False, 'vq_class': None, 'vq_dim': None,
+            'action_dim': 16, 'no_encoder': False}
+
+
+def _load_case(case):
+    from oracle import act_oracle as O
+    gold = np.load(os.path.join(GOLDEN, f"act_{case}.npz"))
+    B, H, W, K, seed = [int(x) for x in gold["meta"]]
+    cfg = O.make_cfg(num_cameras=K)
+    sd = O.init_state_dict(cfg, seed)
+    batch = {k: v.cuda() for k, v in O.make_inputs(cfg, B, H, W, seed).items()}
+    # episodes are longer than the chunk: the policy slices [:, :num_queries] (policy.py:289-290)
+    batch["actions"] = torch.cat([batch["actions"], torch.randn(B, 7, 16, device="cuda")], 1)
+    batch["is_pad"] = torch.cat([batch["is_pad"], torch.ones(B, 7, dtype=torch.bool, device="cuda")], 1)
+    return gold, cfg, sd, batch, K
+
+
+def test_train_step_like_imitate_episodes():
+    from act_plus_plus_b200.policy import ACTPolicy
+    gold, cfg, sd, batch, K = _load_case("small_k1")
+    policy = ACTPolicy(_policy_config(K))
+    status = policy.deserialize({"model." + k: v for k, v in sd.items()})
+    assert not status.missing_keys and not status.unexpected_keys
+    policy.cuda(); policy.train()
+    optimizer = policy.configure_optimizers()
+    assert policy.model.num_queries == 100 and policy.model.encoder is not None and policy.kl_weight == 10
+    before = {k: v.clone() for k, v in policy.serialize().items()}
+    optimizer.zero_grad()
+    out = policy(batch["qpos"], batch["image"], batch["actions"], batch["is_pad"])     # actions longer than nq: sliced
+    assert set(out) == {"l1", "kl", "loss"}
+    loss = out["loss"]
+    assert loss.requires_grad and loss.dim() == 0
+    # l1 is independent of the reparametrisation noise up to its effect through z; kl is exactly noise-free
+    assert abs(out["kl"].item() - float(gold["kl"])) / float(gold["kl"]) < 1e-3
+    loss.backward()
+    eng = policy.model._master
+    g = {k: eng.grad_view(k).clone() for k in eng.tensors}
+    assert float(g["action_head.weight"].abs().sum()) > 0
+    assert float(g["transformer.decoder.layers.3.linear1.weight"].abs().sum()) == 0
+    optimizer.step()
+    torch.cuda.synchronize()
+    after = policy.serialize()
+    lr, wd = 1e-5, 1e-4
+    for name in ("model.action_head.weight", "model.encoder.layers.2.linear1.weight", "model.backbones.0.0.body.layer3.0.conv1.weight",
+                 "model.additional_pos_embed.weight"):
+        p0, gg = before[name], g[name[6:]]
+        m = 0.1 * gg
+        v = 0.001 * gg * gg
+        ref = p0 * (1 - lr * wd) - (lr / 0.1) * m / (v.sqrt() / (0.001 ** 0.5) + 1e-8)
+        assert (after[name] - ref).abs().max().item() < 2e-7, name
+    n = "model.transformer.decoder.layers.5.linear2.weight"          # dead layer: decoupled decay only
+    assert (after[n] - before[n] * (1 - lr * wd)).abs().max().item() < 1e-9
+    for n in ("model.is_pad_head.weight", "model.pos_table", "model.backbones.0.0.body.bn1.running_var"):
+        assert torch.equal(after[n], before[n]), n                   # no grad / buffers: untouched
+    # next forward uses the updated weights (shadows refreshed by the fused optimizer)
+    out2 = policy(batch["qpos"], batch["image"], batch["actions"], batch["is_pad"])
+    assert out2["loss"].item() != loss.item()
+
+
+def test_inference_and_validation_calls():
+    from act_plus_plus_b200.policy import ACTPolicy
+    gold, cfg, sd, batch, K = _load_case("small_k3")
+    policy = ACTPolicy(_policy_config(K))
+    policy.deserialize({"model." + k: v for k, v in sd.items()})
+    policy.eval()
+    with torch.inference_mode():
+        a_hat = policy(batch["qpos"], batch["image"])
+        val = policy(batch["qpos"], batch["image"], batch["actions"], batch["is_pad"])
+    assert a_hat.shape == (batch["qpos"].shape[0], 100, 16)
+    assert (a_hat.cpu() - torch.from_numpy(gold["a_hat_infer"])).abs().max().item() <= 1e-2
+    assert not val["loss"].requires_grad
+    assert abs(val["kl"].item() - float(gold["kl"])) / float(gold["kl"]) < 1e-3
+    # model() keeps the reference's 5-tuple (detr_vae.py:254)
+    a2, pad_hat, (mu, logvar), probs, binaries = policy.model(batch["qpos"], batch["image"], None)
+    assert pad_hat.shape == (batch["qpos"].shape[0], 100, 1) and mu is None and probs is None and binaries is None
+
+
+def test_unsupported_configs_raise():
+    from act_plus_plus_b200.policy import ACTPolicy
+    bad = _policy_config()
+    bad["vq"] = True
+    with pytest.raises(NotImplementedError):
+        ACTPolicy(bad)
+    bad = _policy_config()
+    bad["backbone"] = "resnet50"
+    with pytest.raises(ValueError):
+        ACTPolicy(bad)
