@@ -166,3 +166,8 @@ extern "C" int act_engine_zero_grad(act_engine* e, void* stream) { return e->eng
 extern "C" int act_engine_adamw_step(act_engine* e, int step, void* stream) { return e->eng->adamw(step, ST(stream)); }
 extern "C" int act_engine_set_lr(act_engine* e, float lr, float lr_backbone) { e->eng->set_lr(lr, lr_backbone); return 0; }
 extern "C" int act_engine_launches(act_engine* e, int reset) { const int n = e->eng->launches(); if (reset) e->eng->reset_launches(); return n; }
+
+extern "C" int act_tc_profile_begin(void) { tc_profile_begin(); return 0; }
+extern "C" int act_tc_profile_end(double* total_ms, double* total_flops, int* launches, double* max_ms) {
+  return tc_profile_end(total_ms, total_flops, launches, max_ms);
+}

@@ -84,4 +84,8 @@ struct WgradLaunch {
 };
 int tc_wgrad(const WgradLaunch& w, cudaStream_t stream);
 
+// CUDA-event timing of every tensor-core launch between begin and end (algorithmic FLOPs summed per launch)
+void tc_profile_begin();
+int tc_profile_end(double* total_ms, double* total_flops, int* launches, double* max_ms);
+
 }  // namespace act

@@ -1,0 +1,33 @@
+"""One optimisation step on the engine: zero_grad -> forward(+loss) -> backward -> AdamW, optionally data-parallel
+(batch sharded across ranks, gradients averaged with NCCL over NVLink while later backward stages still run)."""
+from __future__ import annotations
+
+import torch
+
+from .engine import R_BACKBONE, R_CVAE, R_MAIN, ActEngine
+
+
+def backward_data_parallel(eng: ActEngine, group, loss_grad: float = 1.0):
+    """Staged backward: as soon as a parameter region's gradients are final its all-reduce is enqueued (NCCL runs on
+    its own stream, ordered after the compute stream at enqueue time), so the transfer of the transformer gradients
+    overlaps the CVAE-encoder and backbone backward.  Regions are contiguous slices of the flat gradient buffer."""
+    import torch.distributed as dist
+    works = []
+    for stage, region in ((1, R_MAIN), (2, R_CVAE), (3, R_BACKBONE)):
+        eng.backward(stage, loss_grad)
+        off, n = eng.region(region)
+        works.append(dist.all_reduce(eng.flat_grads[off:off + n], op=dist.ReduceOp.AVG, group=group, async_op=True))
+    for w in works:
+        w.wait()
+
+
+def train_step(eng: ActEngine, qpos, image, actions, is_pad, eps=None, dp_group=None) -> torch.Tensor:
+    """Returns the device tensor [l1, kl, loss] of this rank's shard."""
+    eng.zero_grad()
+    out = eng.forward(qpos, image, actions, is_pad, eps)
+    if dp_group is None:
+        eng.backward(0, 1.0)
+    else:
+        backward_data_parallel(eng, dp_group, 1.0)
+    eng.adamw_step()
+    return out["losses"]
