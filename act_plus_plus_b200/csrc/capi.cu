@@ -171,3 +171,4 @@ extern "C" int act_tc_profile_begin(void) { tc_profile_begin(); return 0; }
 extern "C" int act_tc_profile_end(double* total_ms, double* total_flops, int* launches, double* max_ms) {
   return tc_profile_end(total_ms, total_flops, launches, max_ms);
 }
+extern "C" int act_tc_profile_set_dump(const char* path) { tc_profile_set_dump(path); return 0; }

@@ -86,6 +86,7 @@ int tc_wgrad(const WgradLaunch& w, cudaStream_t stream);
 
 // CUDA-event timing of every tensor-core launch between begin and end (algorithmic FLOPs summed per launch)
 void tc_profile_begin();
+void tc_profile_set_dump(const char* path);   // per-launch CSV written by tc_profile_end (empty: off)
 int tc_profile_end(double* total_ms, double* total_flops, int* launches, double* max_ms);
 
 }  // namespace act

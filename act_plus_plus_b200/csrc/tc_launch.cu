@@ -5,6 +5,7 @@
 #include <cstring>
 #include <algorithm>
 #include <vector>
+#include <cstdio>
 
 namespace act {
 
@@ -85,24 +86,31 @@ static int plane_tmap(CUtensorMap* m, const PlaneDesc& pl, int bw, int bh, int b
 }
 
 // ---- optional per-launch CUDA-event timing of the tensor-core kernels (bench.py roofline leg)
-struct TcProf { bool on = false; std::vector<cudaEvent_t> ev; std::vector<double> flops; };
+struct TcProf { bool on = false; std::vector<cudaEvent_t> ev; std::vector<double> flops; std::vector<std::string> label; };
 static TcProf g_prof;
 static double g_next_flops = 0.0;
+static std::string g_next_label;
+static std::string g_dump_path;
+void tc_profile_set_dump(const char* path) { g_dump_path = path ? path : ""; }
 void tc_profile_begin() {
   for (cudaEvent_t e : g_prof.ev) cudaEventDestroy(e);
-  g_prof.ev.clear(); g_prof.flops.clear(); g_prof.on = true;
+  g_prof.ev.clear(); g_prof.flops.clear(); g_prof.label.clear(); g_prof.on = true;
 }
 int tc_profile_end(double* total_ms, double* total_flops, int* launches, double* max_ms) {
   g_prof.on = false;
   double ms = 0, fl = 0, mx = 0;
   const int n = static_cast<int>(g_prof.flops.size());
+  FILE* f = g_dump_path.empty() ? nullptr : fopen(g_dump_path.c_str(), "w");
+  if (f) fprintf(f, "idx,label,ms,gflop,tflops\n");
   for (int i = 0; i < n; ++i) {
     float t = 0.f;
     if (cudaEventSynchronize(g_prof.ev[2 * i + 1]) != cudaSuccess || cudaEventElapsedTime(&t, g_prof.ev[2 * i], g_prof.ev[2 * i + 1]) != cudaSuccess) {
       set_error("tc_profile_end: event query failed"); return -1;
     }
     ms += t; fl += g_prof.flops[i]; if (t > mx) mx = t;
+    if (f) fprintf(f, "%d,%s,%.5f,%.4f,%.2f\n", i, g_prof.label[i].c_str(), t, g_prof.flops[i] / 1e9, g_prof.flops[i] / (t * 1e9 + 1e-9));
   }
+  if (f) fclose(f);
   for (cudaEvent_t e : g_prof.ev) cudaEventDestroy(e);
   g_prof.ev.clear(); g_prof.flops.clear();
   *total_ms = ms; *total_flops = fl; *launches = n; *max_ms = mx;
@@ -126,7 +134,7 @@ static int launch_inst(dim3 grid, int stages, cudaStream_t stream, const CUtenso
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
   kern<<<grid, Cfg::THREADS, smem, stream>>>(am[0], am[1], am[2], am[3], bm, p, stages);
-  if (g_prof.on) { cudaEventRecord(e1, stream); g_prof.ev.push_back(e0); g_prof.ev.push_back(e1); g_prof.flops.push_back(g_next_flops); }
+  if (g_prof.on) { cudaEventRecord(e1, stream); g_prof.ev.push_back(e0); g_prof.ev.push_back(e1); g_prof.flops.push_back(g_next_flops); g_prof.label.push_back(g_next_label); }
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -186,6 +194,7 @@ int tc_gemm(int M, int N, int K, int nz0, int nz1, const MatDesc& A, const MatDe
   if (mat_tmap(&bm, B, N, K, nz0, nz1, bn)) return -1;
   dim3 grid((N + bn - 1) / bn, mt, nb * ksplit);
   g_next_flops = 2.0 * M * N * K * nb;
+  if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "gemm M=%d N=%d K=%d z=%d amn=%d bmn=%d bn=%d ks=%d grid=%ux%ux%u", M, N, K, nb, A.mn_major, B.mn_major, bn, ksplit, grid.x, grid.y, grid.z); g_next_label = buf; }
   const int st = stages_hint ? stages_hint : (bn == 64 ? 4 : bn == 128 ? 4 : 4);
   const int key = (A.mn_major ? 2 : 0) | (B.mn_major ? 1 : 0);
 #define GEMM_CASE(AM, BMJ)                                                                     \
@@ -256,6 +265,7 @@ int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint, int stages_hi
   if (make_tmap_2d(&bm, c.wgt, c.wgt_ld, c.Cout, c.wgt_ld, bn)) return -1;
   dim3 grid((c.Cout + bn - 1) / bn, static_cast<unsigned>(mtiles), 1);
   g_next_flops = 2.0 * c.vW * c.vH * c.NIMG * c.Cout * c.Cin * c.ntaps;
+  if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "conv %dx%dx%d Cin=%d Cout=%d taps=%d box=%dx%dx%d bn=%d grid=%ux%u", c.NIMG, c.vH, c.vW, c.Cin, c.Cout, c.ntaps, BNI, BH, BW, bn, grid.x, grid.y); g_next_label = buf; }
   const int st = stages_hint ? stages_hint : 4;
   if (bn == 64) return launch_inst<MODE_CONV, 0, 0, 64>(grid, st, stream, am, bm, p);
   if (bn == 128) return launch_inst<MODE_CONV, 0, 0, 128>(grid, st, stream, am, bm, p);
@@ -296,6 +306,7 @@ int tc_wgrad(const WgradLaunch& w, cudaStream_t stream) {
   if (plane_tmap(&bm, w.dy, BW, BH, 1)) return -1;
   dim3 grid(xt, ygroups, ks);
   g_next_flops = 2.0 * w.dy.W * w.dy.H * w.dy.N * w.Cout * w.Cin * w.ntaps;
+  if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "wgrad %dx%dx%d Cin=%d Cout=%d taps=%d box=%dx%d bn=%d ks=%d grid=%ux%ux%u", w.dy.N, w.dy.H, w.dy.W, w.Cin, w.Cout, w.ntaps, BH, BW, bn, ks, grid.x, grid.y, grid.z); g_next_label = buf; }
   if (bn == 64) return launch_inst<MODE_WGRAD, 1, 1, 64>(grid, 3, stream, am, bm, p);
   return launch_inst<MODE_WGRAD, 1, 1, 128>(grid, 3, stream, am, bm, p);
 }

@@ -154,6 +154,7 @@ int act_engine_launches(act_engine* e, int reset);
 /* ---- measurement hook: CUDA-event timing of every tcgen05 kernel launched between begin and end on its own stream;
  *      returns summed device time, summed algorithmic FLOPs (2*M*N*K per launch), launch count, longest launch. */
 int act_tc_profile_begin(void);
+int act_tc_profile_set_dump(const char* csv_path);   /* optional per-launch CSV written by act_tc_profile_end */
 int act_tc_profile_end(double* total_ms, double* total_flops, int* launches, double* max_ms);
 
 #ifdef __cplusplus
