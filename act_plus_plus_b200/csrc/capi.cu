@@ -13,6 +13,7 @@ extern "C" int act_abi_version(void) { return 1; }
 
 static EpiDesc to_epi(const act_epilogue* e) {
   EpiDesc d;
+  if (e == nullptr) { d.flags = 0; return d; }      // rejected by check_epi ("epilogue without output")
   d.flags = e->flags; d.alpha = e->alpha; d.bias = e->bias; d.scale = e->scale; d.res_f32 = e->res_f32;
   d.res_bf16 = static_cast<const bf16*>(e->res_bf16); d.aux_bf16 = static_cast<const bf16*>(e->aux_bf16);
   d.out_f32 = e->out_f32; d.out_bf16 = static_cast<bf16*>(e->out_bf16);

@@ -166,14 +166,8 @@ class DETRVAE(nn.Module):
         if self._dp_group is None:
             eng.backward(0, loss_grad)
             return
-        import torch.distributed as dist
-        works = []
-        for stage, region in ((1, R_MAIN), (2, R_CVAE), (3, R_BACKBONE)):
-            eng.backward(stage, loss_grad)
-            off, n = eng.region(region)
-            works.append(dist.all_reduce(eng.flat_grads[off:off + n], op=dist.ReduceOp.AVG, group=self._dp_group, async_op=True))
-        for w in works:
-            w.wait()
+        from .train import backward_data_parallel
+        backward_data_parallel(eng, self._dp_group, loss_grad)
 
     # -------------------------------------------------------------- nn.Module surface
     def forward(self, qpos, image, env_state, actions=None, is_pad=None, vq_sample=None, pointcloud=None, depth_img=None):

@@ -4,21 +4,20 @@ from __future__ import annotations
 
 import torch
 
+from .dp import GradReducer
 from .engine import R_BACKBONE, R_CVAE, R_MAIN, ActEngine
 
 
-def backward_data_parallel(eng: ActEngine, group, loss_grad: float = 1.0):
+def backward_data_parallel(eng: ActEngine, group, loss_grad: float = 1.0, bucket_elems: int = 0):
     """Staged backward: as soon as a parameter region's gradients are final its all-reduce is enqueued (NCCL runs on
     its own stream, ordered after the compute stream at enqueue time), so the transfer of the transformer gradients
     overlaps the CVAE-encoder and backbone backward.  Regions are contiguous slices of the flat gradient buffer."""
-    import torch.distributed as dist
-    works = []
+    red = GradReducer(eng.flat_grads, group, bucket_elems)
     for stage, region in ((1, R_MAIN), (2, R_CVAE), (3, R_BACKBONE)):
         eng.backward(stage, loss_grad)
         off, n = eng.region(region)
-        works.append(dist.all_reduce(eng.flat_grads[off:off + n], op=dist.ReduceOp.AVG, group=group, async_op=True))
-    for w in works:
-        w.wait()
+        red.reduce(off, n)
+    red.wait()
 
 
 def train_step(eng: ActEngine, qpos, image, actions, is_pad, eps=None, dp_group=None) -> torch.Tensor:
