@@ -2,6 +2,9 @@
 //   MODE_GEMM  : batched D[z][M,N] = A[z][M,K] * B[z][N,K]^T, each operand K-major or MN-major
 //   MODE_CONV  : implicit-GEMM convolution / transposed convolution over NHWC bf16 (tap table, TMA boxes)
 //   MODE_WGRAD : convolution weight gradient, reduction over pixels, both operands MN-major, split-K atomics
+// The kernel is PERSISTENT: one CTA per SM walks the tile list (tile = blockIdx.x + i*gridDim.x) so that the TMA
+// producer runs ahead across tile boundaries (the smem ring never drains) and the epilogue of tile i overlaps the
+// MMAs of tile i+1 through two TMEM accumulator buffers.
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer,
 // warps 2..5 = epilogue (TMEM -> registers -> fused epilogue -> global).
 // Operands land in 128B-swizzled shared memory via TMA; accumulators live in TMEM (fp32).
@@ -43,7 +46,8 @@ struct TcParams {
   int M, N, K;                 // GEMM: per-batch sizes. CONV: N = Cout, K unused. WGRAD: see below
   int num_k_blocks;            // GEMM/CONV: k-blocks of 64 per CTA. WGRAD: total pixel tiles
   int nz0;                     // batch index z = z0 + nz0*z1
-  int ksplit;                  // split-K factor (grid.z = batches*ksplit); requires EPI_ATOMIC when > 1
+  int ksplit;                  // split-K factor (gz = batches*ksplit); requires EPI_ATOMIC when > 1
+  int gx, gy, gz;              // tile grid: x = N tiles (fastest), y = M tiles / pixel tiles / wgrad row groups, z = batch*split
   // conv geometry
   int ntaps, cin_blocks;       // k-block kb -> tap kb / cin_blocks, channel block kb % cin_blocks
   int BW, BH, BNI;             // A box = {64, BW, BH, BNI} pixels (BW*BH*BNI <= 128)
@@ -78,7 +82,8 @@ struct TcCfg {
   static constexpr int A_BYTES = (MODE == MODE_WGRAD) ? 2 * PMAX * 128 : BM * 128;
   static constexpr int B_BYTES = (MODE == MODE_WGRAD) ? (BN / 64) * PMAX * 128 : BN * 128;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int TMEM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+  static constexpr int ACC_COLS = BN;                                   // one accumulator buffer
+  static constexpr int TMEM_COLS = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;
   static constexpr int THREADS = 192;
   static constexpr int MAX_STAGES = 8;
 };
@@ -86,6 +91,52 @@ struct TcCfg {
 __device__ __forceinline__ long long pix_off(const PixGeom& g, int n, int h, int w) {
   const long long sn = g.sn ? g.sn : static_cast<long long>(g.H) * g.W * g.ld;
   return n * sn + (static_cast<long long>(h * g.sh + g.oh) * g.W + (w * g.sw + g.ow)) * g.ld;
+}
+
+// Per-tile coordinates, recomputed by each warp role from the linear tile index.
+struct TileCoord {
+  int n0, z0, z1, m0, tn, th, tw, kb_begin, nkb, wg_tap0, wg_ci0;
+};
+
+template <int MODE, int BN>
+__device__ __forceinline__ TileCoord decode_tile(const TcParams& p, int t) {
+  TileCoord c;
+  const int bx = t % p.gx; t /= p.gx;
+  const int by = t % p.gy;
+  int z = t / p.gy;
+  c.n0 = bx * BN;
+  int split = 0;
+  if (p.ksplit > 1) { split = z % p.ksplit; z = z / p.ksplit; }
+  c.z0 = z % p.nz0; c.z1 = z / p.nz0;
+  c.m0 = 0; c.tn = 0; c.th = 0; c.tw = 0; c.wg_tap0 = 0; c.wg_ci0 = 0;
+  if (MODE == MODE_GEMM) {
+    c.m0 = by * 128;
+  } else if (MODE == MODE_CONV) {
+    int u = by;
+    c.tw = u % p.tiles_w; u /= p.tiles_w;
+    c.th = u % p.tiles_h; c.tn = u / p.tiles_h;
+  } else {
+    const int ci_tiles = (p.taps_per_cta == 2) ? 1 : (p.Cin / 128);
+    c.wg_ci0 = (by % ci_tiles) * 128;
+    c.wg_tap0 = (by / ci_tiles) * p.taps_per_cta;
+  }
+  int kb_begin = 0, kb_end = p.num_k_blocks;
+  if (p.ksplit > 1) {
+    const int per = (p.num_k_blocks + p.ksplit - 1) / p.ksplit;
+    kb_begin = split * per;
+    kb_end = min(p.num_k_blocks, kb_begin + per);
+  }
+  c.kb_begin = kb_begin;
+  c.nkb = max(0, kb_end - kb_begin);
+  return c;
+}
+
+__device__ __forceinline__ void ldg32(const float* __restrict__ ptr, float (&dst)[32]) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 4) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(ptr + j));
+    dst[j] = t.x; dst[j + 1] = t.y; dst[j + 2] = t.z; dst[j + 3] = t.w;
+  }
 }
 
 template <int MODE, int A_MN, int B_MN, int BN>
@@ -99,46 +150,20 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + num_stages * Cfg::STAGE_BYTES);
   uint64_t* empty_bar = full_bar + Cfg::MAX_STAGES;
-  uint64_t* accum_bar = empty_bar + Cfg::MAX_STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+  uint64_t* tfull_bar = empty_bar + Cfg::MAX_STAGES;      // [2] accumulator buffer complete (MMA -> epilogue)
+  uint64_t* tempty_bar = tfull_bar + 2;                   // [2] accumulator buffer drained (epilogue -> MMA)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-
-  // ---------------------------------------------------------------- tile coordinates
-  const int n0 = blockIdx.x * BN;
-  int z = blockIdx.z, split = 0;
-  if (p.ksplit > 1) { split = z % p.ksplit; z = z / p.ksplit; }
-  const int z0 = z % p.nz0, z1 = z / p.nz0;
-  int m0 = 0, tn = 0, th = 0, tw = 0;         // GEMM row origin / CONV tile origin
-  int kb_begin = 0, kb_end = p.num_k_blocks;
-  if (MODE == MODE_GEMM) {
-    m0 = blockIdx.y * Cfg::BM;
-  } else if (MODE == MODE_CONV) {
-    int t = blockIdx.y;
-    tw = t % p.tiles_w; t /= p.tiles_w;
-    th = t % p.tiles_h; tn = t / p.tiles_h;
-  }
-  if (p.ksplit > 1) {
-    int per = (p.num_k_blocks + p.ksplit - 1) / p.ksplit;
-    kb_begin = split * per;
-    kb_end = min(p.num_k_blocks, kb_begin + per);
-  }
-  const int nkb = max(0, kb_end - kb_begin);
-  // WGRAD: blockIdx.y = (tap group, ci tile); blockIdx.x = co tile
-  int wg_tap0 = 0, wg_ci0 = 0;
-  if (MODE == MODE_WGRAD) {
-    const int ci_tiles = (p.taps_per_cta == 2) ? 1 : (p.Cin / 128);
-    wg_ci0 = (blockIdx.y % ci_tiles) * 128;
-    wg_tap0 = (blockIdx.y / ci_tiles) * p.taps_per_cta;
-  }
+  const int total_tiles = p.gx * p.gy * p.gz;
 
   // ---------------------------------------------------------------- setup
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&amap0);
     prefetch_tmap(&bmap);
     for (int s = 0; s < num_stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    mbar_init(accum_bar, 1);
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 4); }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
@@ -151,54 +176,58 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
     // ============================================================== TMA producer
     if (lane == 0) {
       const CUtensorMap* amaps[4] = {&amap0, &amap1, &amap2, &amap3};
-      for (int i = 0; i < nkb; ++i) {
-        const int kb = kb_begin + i;
-        const int s = i % num_stages;
-        const uint32_t ph = (i / num_stages) & 1;
-        mbar_wait(&empty_bar[s], ph ^ 1);
-        uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
-        uint8_t* sb = sa + Cfg::A_BYTES;
-        if (MODE == MODE_GEMM) {
-          const uint32_t a_bytes = Cfg::BM * 128;
-          const uint32_t b_bytes = BN * 128;
-          mbar_expect_tx(&full_bar[s], a_bytes + b_bytes);
-          if (A_MN) {
-            tma_load_4d(sa, &amap0, &full_bar[s], m0, kb * 64, z0, z1);
-            tma_load_4d(sa + 64 * 128, &amap0, &full_bar[s], m0 + 64, kb * 64, z0, z1);
-          } else {
-            tma_load_4d(sa, &amap0, &full_bar[s], kb * 64, m0, z0, z1);
-          }
-          if (B_MN) {
+      uint32_t it = 0;                                  // running k-block counter across tiles (ring position)
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const TileCoord c = decode_tile<MODE, BN>(p, t);
+        for (int i = 0; i < c.nkb; ++i, ++it) {
+          const int kb = c.kb_begin + i;
+          const int s = it % num_stages;
+          const uint32_t ph = (it / num_stages) & 1;
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
+          uint8_t* sb = sa + Cfg::A_BYTES;
+          if (MODE == MODE_GEMM) {
+            const uint32_t a_bytes = Cfg::BM * 128;
+            const uint32_t b_bytes = BN * 128;
+            mbar_expect_tx(&full_bar[s], a_bytes + b_bytes);
+            if (A_MN) {
+              tma_load_4d(sa, &amap0, &full_bar[s], c.m0, kb * 64, c.z0, c.z1);
+              tma_load_4d(sa + 64 * 128, &amap0, &full_bar[s], c.m0 + 64, kb * 64, c.z0, c.z1);
+            } else {
+              tma_load_4d(sa, &amap0, &full_bar[s], kb * 64, c.m0, c.z0, c.z1);
+            }
+            if (B_MN) {
 #pragma unroll
-            for (int c = 0; c < BN / 64; ++c)
-              tma_load_4d(sb + c * 64 * 128, &bmap, &full_bar[s], n0 + c * 64, kb * 64, z0, z1);
-          } else {
-            tma_load_4d(sb, &bmap, &full_bar[s], kb * 64, n0, z0, z1);
-          }
-        } else if (MODE == MODE_CONV) {
-          const int tap = kb / p.cin_blocks, cb = kb % p.cin_blocks;
-          const TapDesc td = p.taps[tap];
-          const uint32_t a_bytes = p.BW * p.BH * p.BNI * 128;
-          mbar_expect_tx(&full_bar[s], a_bytes + BN * 128);
-          tma_load_4d(sa, amaps[td.map], &full_bar[s], cb * 64, tw * p.BW + td.dw, th * p.BH + td.dh, tn * p.BNI);
-          tma_load_2d(sb, &bmap, &full_bar[s], (td.wslot * p.cin_blocks + cb) * 64, n0);
-        } else {
-          // WGRAD: kb = pixel tile index -> (n, ht, wt)
-          int t = kb;
-          const int wt = t % p.tiles_w; t /= p.tiles_w;
-          const int ht = t % p.tiles_h; const int n = t / p.tiles_h;
-          const uint32_t box = p.pix_per_box * 128;
-          mbar_expect_tx(&full_bar[s], box * (2 + BN / 64));
-#pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            const int tap = (p.taps_per_cta == 2) ? min(wg_tap0 + c, p.ntaps - 1) : wg_tap0;
-            const int ci = (p.taps_per_cta == 2) ? 0 : wg_ci0 + c * 64;
+              for (int q = 0; q < BN / 64; ++q)
+                tma_load_4d(sb + q * 64 * 128, &bmap, &full_bar[s], c.n0 + q * 64, kb * 64, c.z0, c.z1);
+            } else {
+              tma_load_4d(sb, &bmap, &full_bar[s], kb * 64, c.n0, c.z0, c.z1);
+            }
+          } else if (MODE == MODE_CONV) {
+            const int tap = kb / p.cin_blocks, cb = kb % p.cin_blocks;
             const TapDesc td = p.taps[tap];
-            tma_load_4d(sa + c * box, amaps[td.map], &full_bar[s], ci, wt * p.BW + td.dw, ht * p.BH + td.dh, n);
-          }
+            const uint32_t a_bytes = p.BW * p.BH * p.BNI * 128;
+            mbar_expect_tx(&full_bar[s], a_bytes + BN * 128);
+            tma_load_4d(sa, amaps[td.map], &full_bar[s], cb * 64, c.tw * p.BW + td.dw, c.th * p.BH + td.dh, c.tn * p.BNI);
+            tma_load_2d(sb, &bmap, &full_bar[s], (td.wslot * p.cin_blocks + cb) * 64, c.n0);
+          } else {
+            // WGRAD: kb = pixel tile index -> (n, ht, wt)
+            int u = kb;
+            const int wt = u % p.tiles_w; u /= p.tiles_w;
+            const int ht = u % p.tiles_h; const int n = u / p.tiles_h;
+            const uint32_t box = p.pix_per_box * 128;
+            mbar_expect_tx(&full_bar[s], box * (2 + BN / 64));
 #pragma unroll
-          for (int c = 0; c < BN / 64; ++c)
-            tma_load_4d(sb + c * box, &bmap, &full_bar[s], n0 + c * 64, wt * p.BW, ht * p.BH, n);
+            for (int q = 0; q < 2; ++q) {
+              const int tap = (p.taps_per_cta == 2) ? min(c.wg_tap0 + q, p.ntaps - 1) : c.wg_tap0;
+              const int ci = (p.taps_per_cta == 2) ? 0 : c.wg_ci0 + q * 64;
+              const TapDesc td = p.taps[tap];
+              tma_load_4d(sa + q * box, amaps[td.map], &full_bar[s], ci, wt * p.BW + td.dw, ht * p.BH + td.dh, n);
+            }
+#pragma unroll
+            for (int q = 0; q < BN / 64; ++q)
+              tma_load_4d(sb + q * box, &bmap, &full_bar[s], c.n0 + q * 64, wt * p.BW, ht * p.BH, n);
+          }
         }
       }
     }
@@ -208,156 +237,189 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
       constexpr uint32_t idesc = make_idesc_bf16(Cfg::BM, BN, A_MN, B_MN);
       const int ksteps = (MODE == MODE_WGRAD) ? (p.pix_per_box / 16) : 4;
       const uint32_t lbo = (MODE == MODE_WGRAD) ? p.pix_per_box * 128 : 64 * 128;
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % num_stages;
-        const uint32_t ph = (i / num_stages) & 1;
-        mbar_wait(&full_bar[s], ph);
+      uint32_t it = 0, lt = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
+        const TileCoord c = decode_tile<MODE, BN>(p, t);
+        const uint32_t acc = lt & 1;
+        mbar_wait(&tempty_bar[acc], ((lt >> 1) & 1) ^ 1);      // epilogue drained this buffer (first use: immediate)
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + s * Cfg::STAGE_BYTES);
-        const uint32_t sb = sa + Cfg::A_BYTES;
-        for (int k = 0; k < ksteps; ++k) {
-          const uint64_t ad = A_MN ? make_smem_desc(sa + k * 2048, lbo, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
-          const uint64_t bd = B_MN ? make_smem_desc(sb + k * 2048, lbo, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
-          umma_bf16(tmem_base, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+        const uint32_t tmem_d = tmem_base + acc * Cfg::ACC_COLS;
+        for (int i = 0; i < c.nkb; ++i, ++it) {
+          const int s = it % num_stages;
+          const uint32_t ph = (it / num_stages) & 1;
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * Cfg::STAGE_BYTES);
+          const uint32_t sb = sa + Cfg::A_BYTES;
+          for (int k = 0; k < ksteps; ++k) {
+            const uint64_t ad = A_MN ? make_smem_desc(sa + k * 2048, lbo, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
+            const uint64_t bd = B_MN ? make_smem_desc(sb + k * 2048, lbo, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
+            umma_bf16(tmem_d, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[s]);          // frees this smem stage when the MMAs above retire
         }
-        umma_commit(&empty_bar[s]);          // frees this smem stage when the MMAs above retire
+        umma_commit(&tfull_bar[acc]);          // accumulator complete
       }
-      umma_commit(accum_bar);                // accumulator complete
     }
   } else {
     // ============================================================== epilogue warps (2..5)
     const int q = warp & 3;                  // TMEM lane quadrant this warp may access
     const int r = q * 32 + lane;             // accumulator row handled by this thread
-    mbar_wait(accum_bar, 0);
-    tc_fence_after();
+    uint32_t lt = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
+      const TileCoord c = decode_tile<MODE, BN>(p, t);
+      const uint32_t acc = lt & 1;
+      const int n0 = c.n0;
 
-    bool row_ok = false;
-    long long o_off = 0, r_off = 0;
-    if (MODE == MODE_GEMM) {
-      const int gm = m0 + r;
-      row_ok = gm < p.M;
-      o_off = z0 * p.osz0 + z1 * p.osz1 + static_cast<long long>(gm) * p.ldc;
-      r_off = z0 * p.rsz0 + z1 * p.rsz1 + static_cast<long long>(gm) * p.ldr;
-    } else if (MODE == MODE_CONV) {
-      const int w = r % p.BW, h = (r / p.BW) % p.BH, ni = r / (p.BW * p.BH);
-      const int gw = tw * p.BW + w, gh = th * p.BH + h, gn = tn * p.BNI + ni;
-      row_ok = (ni < p.BNI) && gw < p.vW && gh < p.vH && gn < p.NIMG;
-      o_off = pix_off(p.og, gn, gh, gw);
-      r_off = pix_off(p.rg, gn, gh, gw);
-    } else {
-      // WGRAD: row -> (tap, ci)
-      int tap, ci;
-      if (p.taps_per_cta == 2) { tap = wg_tap0 + (r >> 6); ci = r & 63; }
-      else { tap = wg_tap0; ci = wg_ci0 + r; }
-      row_ok = tap < p.ntaps && ci < p.Cin;
-      o_off = static_cast<long long>(ci) * p.KK + p.taps[min(tap, p.ntaps - 1)].wslot;
-    }
-    if (nkb == 0) row_ok = false;            // nothing accumulated (empty split): TMEM is garbage
+      bool row_ok = false;
+      long long o_off = 0, r_off = 0;
+      if (MODE == MODE_GEMM) {
+        const int gm = c.m0 + r;
+        row_ok = gm < p.M;
+        o_off = c.z0 * p.osz0 + c.z1 * p.osz1 + static_cast<long long>(gm) * p.ldc;
+        r_off = c.z0 * p.rsz0 + c.z1 * p.rsz1 + static_cast<long long>(gm) * p.ldr;
+      } else if (MODE == MODE_CONV) {
+        const int w = r % p.BW, h = (r / p.BW) % p.BH, ni = r / (p.BW * p.BH);
+        const int gw = c.tw * p.BW + w, gh = c.th * p.BH + h, gn = c.tn * p.BNI + ni;
+        row_ok = (ni < p.BNI) && gw < p.vW && gh < p.vH && gn < p.NIMG;
+        o_off = pix_off(p.og, gn, gh, gw);
+        r_off = pix_off(p.rg, gn, gh, gw);
+      } else {
+        // WGRAD: row -> (tap, ci)
+        int tap, ci;
+        if (p.taps_per_cta == 2) { tap = c.wg_tap0 + (r >> 6); ci = r & 63; }
+        else { tap = c.wg_tap0; ci = c.wg_ci0 + r; }
+        row_ok = tap < p.ntaps && ci < p.Cin;
+        o_off = static_cast<long long>(ci) * p.KK + p.taps[min(tap, p.ntaps - 1)].wslot;
+      }
+      if (c.nkb == 0) row_ok = false;          // nothing accumulated (empty split): TMEM is garbage
+
+      mbar_wait(&tfull_bar[acc], (lt >> 1) & 1);
+      tc_fence_after();
+      const uint32_t tmem_acc = tmem_base + acc * Cfg::ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
 
 #pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
-      uint32_t v[32];
-      __syncwarp();
-      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
-      tmem_ld_wait();
-      if (!row_ok) continue;
-      const int gn0 = n0 + c0;
-      if (MODE == MODE_WGRAD) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int co = gn0 + j;
-          if (co < p.Cout) {
-            const float sc = (p.flags & EPI_SCALE) ? __ldg(p.scale + co) * p.alpha : p.alpha;
-            atomicAdd(p.out_f32 + static_cast<long long>(co) * p.Cin * p.KK + o_off, __uint_as_float(v[j]) * sc);
-          }
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t v[32];
+        __syncwarp();
+        tmem_ld_32x32(tmem_acc + c0, v);
+        tmem_ld_wait();
+        if (c0 + 32 >= BN) {                   // last chunk is in registers: hand the accumulator back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty_bar[acc]);
         }
-        continue;
-      }
-      float f[32];
+        if (!row_ok) continue;
+        const int gn0 = n0 + c0;
+        if (MODE == MODE_WGRAD) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
-      const bool full = p.vec_ok && (gn0 + 32 <= p.N);
-      if (p.flags & EPI_SCALE) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) if (full || gn0 + j < p.N) f[j] *= __ldg(p.scale + gn0 + j);
-      }
-      if (p.flags & EPI_BIAS) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) if (full || gn0 + j < p.N) f[j] += __ldg(p.bias + gn0 + j);
-      }
-      if (p.flags & EPI_RES_F32) {
-        const float* rp = p.res_f32 + r_off + gn0;
-        if (full) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 t = *reinterpret_cast<const float4*>(rp + j);
-            f[j] += t.x; f[j + 1] += t.y; f[j + 2] += t.z; f[j + 3] += t.w;
-          }
-        } else {
-          for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += rp[j];
-        }
-      }
-      if (p.flags & EPI_RES_BF16) {
-        const __nv_bfloat16* rp = p.res_bf16 + r_off + gn0;
-        if (full) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            const uint4 t = *reinterpret_cast<const uint4*>(rp + j);
-            const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&t);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) { const float2 x = __bfloat1622float2(h2[e]); f[j + 2 * e] += x.x; f[j + 2 * e + 1] += x.y; }
-          }
-        } else {
-          for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += __bfloat162float(rp[j]);
-        }
-      }
-      if (p.flags & EPI_RELU) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-      }
-      if (p.flags & EPI_MASK_POS) {
-        const __nv_bfloat16* ap = p.aux_bf16 + o_off + gn0;
-        if (full) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            const uint4 t = *reinterpret_cast<const uint4*>(ap + j);
-            const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&t);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float2 x = __bfloat1622float2(h2[e]);
-              if (!(x.x > 0.f)) f[j + 2 * e] = 0.f;
-              if (!(x.y > 0.f)) f[j + 2 * e + 1] = 0.f;
+          for (int j = 0; j < 32; ++j) {
+            const int co = gn0 + j;
+            if (co < p.Cout) {
+              const float sc = (p.flags & EPI_SCALE) ? __ldg(p.scale + co) * p.alpha : p.alpha;
+              atomicAdd(p.out_f32 + static_cast<long long>(co) * p.Cin * p.KK + o_off, __uint_as_float(v[j]) * sc);
             }
           }
-        } else {
-          for (int j = 0; j < 32; ++j) if (gn0 + j < p.N && !(__bfloat162float(ap[j]) > 0.f)) f[j] = 0.f;
+          continue;
         }
-      }
-      if (p.flags & EPI_OUT_F32) {
-        float* op = p.out_f32 + o_off + gn0;
-        if (p.flags & EPI_ATOMIC) {
+        float f[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) if (full || gn0 + j < p.N) atomicAdd(op + j, f[j]);
-        } else if (full) {
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
+        const bool full = p.vec_ok && (gn0 + 32 <= p.N);
+        if (p.flags & EPI_SCALE) {
+          if (full) {
+            float sc[32];
+            ldg32(p.scale + gn0, sc);
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
-        } else {
-          for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) op[j] = f[j];
-        }
-      }
-      if (p.flags & EPI_OUT_BF16) {
-        __nv_bfloat16* op = p.out_bf16 + o_off + gn0;
-        if (full) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            uint4 t;
-            __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&t);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) h2[e] = __floats2bfloat162_rn(f[j + 2 * e], f[j + 2 * e + 1]);
-            *reinterpret_cast<uint4*>(op + j) = t;
+            for (int j = 0; j < 32; ++j) f[j] *= sc[j];
+          } else {
+            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] *= __ldg(p.scale + gn0 + j);
           }
-        } else {
-          for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) op[j] = __float2bfloat16_rn(f[j]);
+        }
+        if (p.flags & EPI_BIAS) {
+          if (full) {
+            float bi[32];
+            ldg32(p.bias + gn0, bi);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] += bi[j];
+          } else {
+            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += __ldg(p.bias + gn0 + j);
+          }
+        }
+        if (p.flags & EPI_RES_F32) {
+          const float* rp = p.res_f32 + r_off + gn0;
+          if (full) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 u = *reinterpret_cast<const float4*>(rp + j);
+              f[j] += u.x; f[j + 1] += u.y; f[j + 2] += u.z; f[j + 3] += u.w;
+            }
+          } else {
+            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += rp[j];
+          }
+        }
+        if (p.flags & EPI_RES_BF16) {
+          const __nv_bfloat16* rp = p.res_bf16 + r_off + gn0;
+          if (full) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              const uint4 u = *reinterpret_cast<const uint4*>(rp + j);
+              const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) { const float2 x = __bfloat1622float2(h2[e]); f[j + 2 * e] += x.x; f[j + 2 * e + 1] += x.y; }
+            }
+          } else {
+            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += __bfloat162float(rp[j]);
+          }
+        }
+        if (p.flags & EPI_RELU) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        if (p.flags & EPI_MASK_POS) {
+          const __nv_bfloat16* ap = p.aux_bf16 + o_off + gn0;
+          if (full) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              const uint4 u = *reinterpret_cast<const uint4*>(ap + j);
+              const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float2 x = __bfloat1622float2(h2[e]);
+                if (!(x.x > 0.f)) f[j + 2 * e] = 0.f;
+                if (!(x.y > 0.f)) f[j + 2 * e + 1] = 0.f;
+              }
+            }
+          } else {
+            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N && !(__bfloat162float(ap[j]) > 0.f)) f[j] = 0.f;
+          }
+        }
+        if (p.flags & EPI_OUT_F32) {
+          float* op = p.out_f32 + o_off + gn0;
+          if (p.flags & EPI_ATOMIC) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (full || gn0 + j < p.N) atomicAdd(op + j, f[j]);
+          } else if (full) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+          } else {
+            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) op[j] = f[j];
+          }
+        }
+        if (p.flags & EPI_OUT_BF16) {
+          __nv_bfloat16* op = p.out_bf16 + o_off + gn0;
+          if (full) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 u;
+              __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) h2[e] = __floats2bfloat162_rn(f[j + 2 * e], f[j + 2 * e + 1]);
+              *reinterpret_cast<uint4*>(op + j) = u;
+            }
+          } else {
+            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) op[j] = __float2bfloat16_rn(f[j]);
+          }
         }
       }
     }

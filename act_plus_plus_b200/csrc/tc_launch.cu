@@ -117,26 +117,61 @@ int tc_profile_end(double* total_ms, double* total_flops, int* launches, double*
   return 0;
 }
 
+static int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) n = v;
+    else n = 148;
+  }
+  return n;
+}
+
+// Persistent launch: `tiles` = logical tile grid (x fastest); the kernel runs min(#tiles, #SMs) CTAs, one per SM
+// (the smem ring is sized to own the SM), each walking tiles blockIdx.x, blockIdx.x + gridDim.x, ...
 template <int MODE, int A_MN, int B_MN, int BN>
-static int launch_inst(dim3 grid, int stages, cudaStream_t stream, const CUtensorMap* am, const CUtensorMap& bm,
-                       const TcParams& p) {
+static int launch_inst(dim3 tiles, int stages, cudaStream_t stream, const CUtensorMap* am, const CUtensorMap& bm,
+                       TcParams p) {
   using Cfg = TcCfg<MODE, A_MN, B_MN, BN>;
   auto kern = tc_kernel<MODE, A_MN, B_MN, BN>;
   const int max_smem = 227 * 1024;
-  const int extra = 1024 + (2 * Cfg::MAX_STAGES + 1) * 8 + 16;
+  const int extra = 1024 + (2 * Cfg::MAX_STAGES + 4) * 8 + 16;
+  const int fit = std::min<int>(Cfg::MAX_STAGES, (200 * 1024) / Cfg::STAGE_BYTES);
+  if (stages <= 0) stages = fit;
   stages = std::max(2, std::min(stages, std::min<int>(Cfg::MAX_STAGES, (max_smem - extra) / Cfg::STAGE_BYTES)));
-  const int smem = stages * Cfg::STAGE_BYTES + extra;
-  static int configured = 0;     // per instantiation
-  if (configured < smem) {
+  // never let two persistent CTAs share an SM (they would serialise on the TMEM allocation)
+  const int smem = std::max(stages * Cfg::STAGE_BYTES + extra, 116 * 1024);
+  static bool configured = false;     // per instantiation
+  if (!configured) {
     ACT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-    configured = max_smem;
+    configured = true;
   }
+  p.gx = static_cast<int>(tiles.x); p.gy = static_cast<int>(tiles.y); p.gz = static_cast<int>(tiles.z);
+  const long long total = 1LL * tiles.x * tiles.y * tiles.z;
+  ACT_CHECK(total > 0 && total < (1LL << 30), "bad tile grid");
+  const unsigned ctas = static_cast<unsigned>(std::min<long long>(total, num_sms()));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
-  kern<<<grid, Cfg::THREADS, smem, stream>>>(am[0], am[1], am[2], am[3], bm, p, stages);
+  kern<<<ctas, Cfg::THREADS, smem, stream>>>(am[0], am[1], am[2], am[3], bm, p, stages);
   if (g_prof.on) { cudaEventRecord(e1, stream); g_prof.ev.push_back(e0); g_prof.ev.push_back(e1); g_prof.flops.push_back(g_next_flops); g_prof.label.push_back(g_next_label); }
   ACT_CUDA(cudaGetLastError());
   return 0;
+}
+
+// Tile width for a persistent launch: minimise rounds x tile cost (cost ~ BN, plus a fixed per-tile term),
+// ties go to the wider tile (fewer re-reads of the A operand).
+static int pick_bn(int N, long long row_tiles) {
+  int best = 64;
+  double best_cost = 1e30;
+  const int cands[3] = {64, 128, 256};
+  for (int c : cands) {
+    if (c > 64 && N < c) continue;
+    const long long tiles = row_tiles * ((N + c - 1) / c);
+    const long long rounds = (tiles + num_sms() - 1) / num_sms();
+    const double cost = static_cast<double>(rounds) * (c + 24);
+    if (cost <= best_cost * 1.0001) { best_cost = std::min(cost, best_cost); best = c; }
+  }
+  return best;
 }
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -170,15 +205,7 @@ int tc_gemm(int M, int N, int K, int nz0, int nz1, const MatDesc& A, const MatDe
   const int nb = nz0 * nz1;
   const int mt = (M + 127) / 128;
   int bn = bn_hint;
-  if (bn == 0) {
-    bn = 64;
-    const int cands[3] = {256, 128, 64};
-    for (int c : cands) {
-      if (N < c) continue;
-      const long long tiles = 1LL * mt * ((N + c - 1) / c) * nb * ksplit;
-      if (tiles >= (c == 256 ? 296 : 148)) { bn = c; break; }
-    }
-  }
+  if (bn == 0) bn = pick_bn(N, 1LL * mt * nb * ksplit);
   ACT_CHECK(bn == 64 || bn == 128 || bn == 256, "bn must be 64/128/256");
   TcParams p;
   memset(&p, 0, sizeof(p));
@@ -195,7 +222,7 @@ int tc_gemm(int M, int N, int K, int nz0, int nz1, const MatDesc& A, const MatDe
   dim3 grid((N + bn - 1) / bn, mt, nb * ksplit);
   g_next_flops = 2.0 * M * N * K * nb;
   if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "gemm M=%d N=%d K=%d z=%d amn=%d bmn=%d bn=%d ks=%d grid=%ux%ux%u", M, N, K, nb, A.mn_major, B.mn_major, bn, ksplit, grid.x, grid.y, grid.z); g_next_label = buf; }
-  const int st = stages_hint ? stages_hint : (bn == 64 ? 4 : bn == 128 ? 4 : 4);
+  const int st = stages_hint;
   const int key = (A.mn_major ? 2 : 0) | (B.mn_major ? 1 : 0);
 #define GEMM_CASE(AM, BMJ)                                                                     \
   if (bn == 64) return launch_inst<MODE_GEMM, AM, BMJ, 64>(grid, st, stream, am, bm, p);       \
@@ -251,14 +278,7 @@ int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint, int stages_hi
              aligned16(c.epi.res_bf16) && aligned16(c.epi.aux_bf16);
   const long long mtiles = 1LL * p.tiles_w * p.tiles_h * tiles_n;
   int bn = bn_hint;
-  if (bn == 0) {
-    bn = 64;
-    const int cands[3] = {256, 128, 64};
-    for (int cc : cands) {
-      if (c.Cout < cc) continue;
-      if (mtiles * ((c.Cout + cc - 1) / cc) >= 148) { bn = cc; break; }
-    }
-  }
+  if (bn == 0) bn = pick_bn(c.Cout, mtiles);
   CUtensorMap am[4], bm;
   for (int i = 0; i < 4; ++i)
     if (plane_tmap(&am[i], c.planes[std::min(i, c.nplanes - 1)], BW, BH, BNI)) return -1;
@@ -266,7 +286,7 @@ int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint, int stages_hi
   dim3 grid((c.Cout + bn - 1) / bn, static_cast<unsigned>(mtiles), 1);
   g_next_flops = 2.0 * c.vW * c.vH * c.NIMG * c.Cout * c.Cin * c.ntaps;
   if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "conv %dx%dx%d Cin=%d Cout=%d taps=%d box=%dx%dx%d bn=%d grid=%ux%u", c.NIMG, c.vH, c.vW, c.Cin, c.Cout, c.ntaps, BNI, BH, BW, bn, grid.x, grid.y); g_next_label = buf; }
-  const int st = stages_hint ? stages_hint : 4;
+  const int st = stages_hint;
   if (bn == 64) return launch_inst<MODE_CONV, 0, 0, 64>(grid, st, stream, am, bm, p);
   if (bn == 128) return launch_inst<MODE_CONV, 0, 0, 128>(grid, st, stream, am, bm, p);
   return launch_inst<MODE_CONV, 0, 0, 256>(grid, st, stream, am, bm, p);
@@ -307,8 +327,8 @@ int tc_wgrad(const WgradLaunch& w, cudaStream_t stream) {
   dim3 grid(xt, ygroups, ks);
   g_next_flops = 2.0 * w.dy.W * w.dy.H * w.dy.N * w.Cout * w.Cin * w.ntaps;
   if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "wgrad %dx%dx%d Cin=%d Cout=%d taps=%d box=%dx%d bn=%d ks=%d grid=%ux%ux%u", w.dy.N, w.dy.H, w.dy.W, w.Cin, w.Cout, w.ntaps, BH, BW, bn, ks, grid.x, grid.y, grid.z); g_next_label = buf; }
-  if (bn == 64) return launch_inst<MODE_WGRAD, 1, 1, 64>(grid, 3, stream, am, bm, p);
-  return launch_inst<MODE_WGRAD, 1, 1, 128>(grid, 3, stream, am, bm, p);
+  if (bn == 64) return launch_inst<MODE_WGRAD, 1, 1, 64>(grid, 0, stream, am, bm, p);
+  return launch_inst<MODE_WGRAD, 1, 1, 128>(grid, 0, stream, am, bm, p);
 }
 
 }  // namespace act
