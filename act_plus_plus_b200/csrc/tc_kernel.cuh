@@ -73,6 +73,7 @@ struct TcParams {
   long long ldc, ldr;                   // GEMM: row strides of out / residual
   long long osz0, osz1, rsz0, rsz1;     // GEMM: batch strides of out / residual
   int vec_ok;                           // all epilogue pointers / strides allow 16-byte vector access
+  int debug;                            // experiment switches (ACT_TC_DEBUG): 1 = skip epilogue math+stores, 2 = skip TMA loads
 };
 
 template <int MODE, int A_MN, int B_MN, int BN>
@@ -174,7 +175,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
 
   if (warp == 0) {
     // ============================================================== TMA producer
-    if (lane == 0) {
+    if (elect_one()) {
       const CUtensorMap* amaps[4] = {&amap0, &amap1, &amap2, &amap3};
       uint32_t it = 0;                                  // running k-block counter across tiles (ring position)
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -186,6 +187,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
           mbar_wait(&empty_bar[s], ph ^ 1);
           uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
           uint8_t* sb = sa + Cfg::A_BYTES;
+          if (p.debug & 2) { mbar_arrive(&full_bar[s]); continue; }
           if (MODE == MODE_GEMM) {
             const uint32_t a_bytes = Cfg::BM * 128;
             const uint32_t b_bytes = BN * 128;
@@ -233,10 +235,13 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
     }
   } else if (warp == 1) {
     // ============================================================== MMA issuer (one elected lane)
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16(Cfg::BM, BN, A_MN, B_MN);
       const int ksteps = (MODE == MODE_WGRAD) ? (p.pix_per_box / 16) : 4;
       const uint32_t lbo = (MODE == MODE_WGRAD) ? p.pix_per_box * 128 : 64 * 128;
+      const uint32_t sbase = smem_u32(smem);
+      const uint64_t adesc0 = A_MN ? make_smem_desc(sbase, lbo, 1024) : make_smem_desc(sbase, 16, 1024);
+      const uint64_t bdesc0 = B_MN ? make_smem_desc(sbase + Cfg::A_BYTES, lbo, 1024) : make_smem_desc(sbase + Cfg::A_BYTES, 16, 1024);
       uint32_t it = 0, lt = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
         const TileCoord c = decode_tile<MODE, BN>(p, t);
@@ -249,12 +254,15 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
           const uint32_t ph = (it / num_stages) & 1;
           mbar_wait(&full_bar[s], ph);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + s * Cfg::STAGE_BYTES);
-          const uint32_t sb = sa + Cfg::A_BYTES;
-          for (int k = 0; k < ksteps; ++k) {
-            const uint64_t ad = A_MN ? make_smem_desc(sa + k * 2048, lbo, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
-            const uint64_t bd = B_MN ? make_smem_desc(sb + k * 2048, lbo, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
-            umma_bf16(tmem_d, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          // descriptors differ from the stage-0 / k-0 ones only in the 14-bit start-address field (16-byte units)
+          const uint32_t soff = static_cast<uint32_t>(s * Cfg::STAGE_BYTES) >> 4;
+          uint64_t ad = adesc0 + soff, bd = bdesc0 + soff;
+          if (MODE == MODE_WGRAD) {
+            for (int k = 0; k < ksteps; ++k, ad += 128, bd += 128) umma_bf16(tmem_d, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k, ad += (A_MN ? 128 : 2), bd += (B_MN ? 128 : 2))
+              umma_bf16(tmem_d, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
           umma_commit(&empty_bar[s]);          // frees this smem stage when the MMAs above retire
         }
@@ -309,7 +317,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty_bar[acc]);
         }
-        if (!row_ok) continue;
+        if (!row_ok || (p.debug & 1)) continue;
         const int gn0 = n0 + c0;
         if (MODE == MODE_WGRAD) {
 #pragma unroll
@@ -397,8 +405,13 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
         if (p.flags & EPI_OUT_F32) {
           float* op = p.out_f32 + o_off + gn0;
           if (p.flags & EPI_ATOMIC) {
+            if (full) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) if (full || gn0 + j < p.N) atomicAdd(op + j, f[j]);
+              for (int j = 0; j < 32; j += 4) red_add_v4(op + j, f[j], f[j + 1], f[j + 2], f[j + 3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) atomicAdd(op + j, f[j]);
+            }
           } else if (full) {
 #pragma unroll
             for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);

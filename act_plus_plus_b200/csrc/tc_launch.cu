@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <vector>
 #include <cstdio>
+#include <cstdlib>
 
 namespace act {
 
@@ -146,6 +147,7 @@ static int launch_inst(dim3 tiles, int stages, cudaStream_t stream, const CUtens
     ACT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
     configured = true;
   }
+  { static int dbg = -1; if (dbg < 0) { const char* e = getenv("ACT_TC_DEBUG"); dbg = e ? atoi(e) : 0; } p.debug = dbg; }
   p.gx = static_cast<int>(tiles.x); p.gy = static_cast<int>(tiles.y); p.gz = static_cast<int>(tiles.z);
   const long long total = 1LL * tiles.x * tiles.y * tiles.z;
   ACT_CHECK(total > 0 && total < (1LL << 30), "bad tile grid");
@@ -158,9 +160,11 @@ static int launch_inst(dim3 tiles, int stages, cudaStream_t stream, const CUtens
   return 0;
 }
 
-// Tile width for a persistent launch: minimise rounds x tile cost (cost ~ BN, plus a fixed per-tile term),
-// ties go to the wider tile (fewer re-reads of the A operand).
-static int pick_bn(int N, long long row_tiles) {
+// Tile width for a persistent launch.  Measured on B200 (tools/bench_kernels.py floor): one tcgen05.mma of M=128 costs
+// ~55 ns for N<=128 and ~75 ns for N=256 whatever N is, and a full-chip launch is bounded by L2->SM fill (~85 GB/s per
+// SM when all 148 load), so wide tiles win unless they leave SMs idle.  cost = rounds x (k-blocks x ns/k-block + tile
+// overhead); ties go to the wider tile.
+static int pick_bn(int N, long long row_tiles, int kblocks) {
   int best = 64;
   double best_cost = 1e30;
   const int cands[3] = {64, 128, 256};
@@ -168,7 +172,11 @@ static int pick_bn(int N, long long row_tiles) {
     if (c > 64 && N < c) continue;
     const long long tiles = row_tiles * ((N + c - 1) / c);
     const long long rounds = (tiles + num_sms() - 1) / num_sms();
-    const double cost = static_cast<double>(rounds) * (c + 24);
+    const double active = std::min<double>(1.0, double(tiles) / num_sms());
+    const double kb = 16.0 + c / 8.0;                                   // KB of smem fill per k-block
+    const double load_ns = kb * std::max(5.0, 12.0 * active);
+    const double mma_ns = c == 256 ? 300.0 : 225.0;
+    const double cost = static_cast<double>(rounds) * (kblocks * std::max(load_ns, mma_ns) + 800.0 + 6.0 * c);
     if (cost <= best_cost * 1.0001) { best_cost = std::min(cost, best_cost); best = c; }
   }
   return best;
@@ -205,7 +213,7 @@ int tc_gemm(int M, int N, int K, int nz0, int nz1, const MatDesc& A, const MatDe
   const int nb = nz0 * nz1;
   const int mt = (M + 127) / 128;
   int bn = bn_hint;
-  if (bn == 0) bn = pick_bn(N, 1LL * mt * nb * ksplit);
+  if (bn == 0) bn = pick_bn(N, 1LL * mt * nb * ksplit, std::max(1, ((K + 63) / 64) / ksplit));
   ACT_CHECK(bn == 64 || bn == 128 || bn == 256, "bn must be 64/128/256");
   TcParams p;
   memset(&p, 0, sizeof(p));
@@ -278,7 +286,7 @@ int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint, int stages_hi
              aligned16(c.epi.res_bf16) && aligned16(c.epi.aux_bf16);
   const long long mtiles = 1LL * p.tiles_w * p.tiles_h * tiles_n;
   int bn = bn_hint;
-  if (bn == 0) bn = pick_bn(c.Cout, mtiles);
+  if (bn == 0) bn = pick_bn(c.Cout, mtiles, c.ntaps * (c.Cin / 64));
   CUtensorMap am[4], bm;
   for (int i = 0; i < 4; ++i)
     if (plane_tmap(&am[i], c.planes[std::min(i, c.nplanes - 1)], BW, BH, BNI)) return -1;

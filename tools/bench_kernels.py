@@ -43,7 +43,7 @@ GEMMS = [  # name, M, N, K, a_mn, b_mn, ksplit
     ("dw_ffn1", 3200, 512, 2416, 1, 1, 2), ("dw_ffn2", 512, 3200, 2416, 1, 1, 3), ("dw_attn", 512, 512, 2416, 1, 1, 10),
     ("stem_gemm", 614400, 64, 192, 0, 0, 1), ("big", 8192, 8192, 8192, 0, 0, 1),
 ]
-ATTN = [("enc_qkT", 302, 302, 64, 64, 0, 0), ("enc_pv", 302, 64, 302, 64, 0, 1), ("cvae_qkT", 102, 102, 64, 64, 0, 0)]
+ATTN = [("enc_qkT", 302, 302, 64, 64, 0, 0), ("enc_pv", 302, 64, 304, 64, 0, 1), ("cvae_qkT", 102, 102, 64, 64, 0, 0)]
 CONVS = [(8, 120, 160, 64, 64, 3, 1), (8, 60, 80, 128, 128, 3, 1), (8, 30, 40, 256, 256, 3, 1), (8, 15, 20, 512, 512, 3, 1),
          (8, 120, 160, 64, 128, 3, 2), (8, 60, 80, 128, 256, 3, 2)]
 
@@ -131,3 +131,25 @@ if __name__ == "__main__":
         bench_conv(rows, wgrad=True)
     if len(sys.argv) > 2:
         json.dump(rows, open(sys.argv[2], "w"), indent=1)
+
+
+def bench_floor():
+    """MMA issue floor per operand layout / tile width: run with ACT_TC_DEBUG=3 (no loads, no epilogue)."""
+    M = N = K = 4096
+    for amn in (0, 1):
+        for bmn in (0, 1):
+            a = torch.randn((K, M) if amn else (M, K), device="cuda").bfloat16()
+            b = torch.randn((K, N) if bmn else (N, K), device="cuda").bfloat16()
+            out = torch.zeros(M, N, device="cuda", dtype=torch.bfloat16)
+            epi = ops.make_epilogue(out_bf16=out, ldc=N)
+            for bn in (64, 128, 256):
+                t = graph_time(lambda: ops.tc_gemm_raw(M, N, K, 1, 1, a, amn, M if amn else K, 0, 0, b, bmn, N if bmn else K, 0, 0, epi, 1, bn, 0), rep=5)
+                tiles = (M // 128) * (N // bn)
+                rounds = -(-tiles // 148)
+                mmas = rounds * (K // 16)
+                print(json.dumps(dict(kind="floor", a_mn=amn, b_mn=bmn, bn=bn, us=round(t, 1), tflops=round(2.0 * M * N * K / t / 1e6, 1),
+                                      ns_per_mma=round(t * 1e3 / mmas, 1))), flush=True)
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "floor":
+    bench_floor()
