@@ -246,20 +246,22 @@ int Engine::adamw(int step, cudaStream_t st) {
   if (have_actions_ || true) { if (run(R_CVAE, cfg_.lr, 0, true)) return -1; }
   if (run(R_BACKBONE, cfg_.lr_backbone, 0, false)) return -1;
   if (run(R_DEAD, cfg_.lr, 1, cfg_.faithful_decoder != 0)) return -1;
-  // packed conv operands (transposed / scaled layouts) are rebuilt from the fp32 masters
+  // packed conv operands (transposed / scaled layouts) are rebuilt from the fp32 masters, one launch per camera
   for (int k = 0; k < cfg_.num_cameras; ++k) {
     CamW& c = cam_w_[k];
     if (pack_conv1_weights(c.stem.w32, c.stem.wpk, 192, st)) return -1;
     ++launches_;
+    PackJobs jobs;
     for (int i = 0; i < 8; ++i) {
       BlockW& b = c.blk[i];
       ConvW* cs[3] = {&b.c1, &b.c2, b.has_ds ? &b.ds : nullptr};
       for (ConvW* w : cs) {
         if (!w) continue;
-        if (pack_conv_weights(w->w32, w->scale, w->wpk, w->wpkt, w->Cout, w->Cin, w->KH * w->KH, st)) return -1;
-        ++launches_;
+        jobs.job[jobs.n++] = PackJob{w->w32, w->scale, w->wpk, w->wpkt, w->Cout, w->Cin, w->KH * w->KH, 0};
       }
     }
+    if (pack_conv_batched(jobs, st)) return -1;
+    ++launches_;
   }
   return 0;
 }

@@ -10,31 +10,58 @@ namespace act {
 __device__ __forceinline__ long long ioff(const IdxMap& m, int idx) {
   return static_cast<long long>(idx / m.rpb) * m.bs + static_cast<long long>(idx % m.rpb) * m.s;
 }
-__global__ void sgemm_generic_kernel(SgemmArgs a) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+// Block = 32 output columns x 8 reduction slices: thread (tx, ty) accumulates r = r0+ty, r0+ty+8, ... for column j,
+// the 8 partial sums meet in shared memory.  grid.z splits long reductions further (atomic accumulate).
+__global__ void __launch_bounds__(256) sgemm_generic_kernel(SgemmArgs a) {
+  __shared__ float part[8][33];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int j = blockIdx.x * 32 + tx;
   const int i = blockIdx.y;
-  if (j >= a.J || i >= a.I) return;
   const int rchunk = (a.R + gridDim.z - 1) / gridDim.z;
   const int r0 = blockIdx.z * rchunk, r1 = min(a.R, r0 + rchunk);
-  const float* Ai = a.A + ioff(a.ai, i);
-  const float* Bj = a.B + ioff(a.bj, j);
   float acc = 0.f;
-  for (int r = r0; r < r1; ++r) acc += Ai[ioff(a.ar, r)] * Bj[ioff(a.br, r)];
-  acc *= a.alpha;
-  if (a.bias && blockIdx.z == 0) acc += a.bias[j];
-  float* c = a.C + ioff(a.ci, i) + ioff(a.cj, j);
-  if (a.accumulate || gridDim.z > 1) atomicAdd(c, acc);
-  else *c = acc;
+  if (j < a.J) {
+    const float* Ai = a.A + ioff(a.ai, i);
+    const float* Bj = a.B + ioff(a.bj, j);
+    const bool flat = a.ar.rpb >= a.R && a.br.rpb >= a.R;       // no batched index maps on the reduction axis
+    if (flat) {
+      const long long sa = a.ar.s, sb = a.br.s;
+      int r = r0 + ty;
+      for (; r + 24 < r1; r += 32) {
+        const float a0 = Ai[r * sa], a1 = Ai[(r + 8) * sa], a2 = Ai[(r + 16) * sa], a3 = Ai[(r + 24) * sa];
+        const float b0 = Bj[r * sb], b1 = Bj[(r + 8) * sb], b2 = Bj[(r + 16) * sb], b3 = Bj[(r + 24) * sb];
+        acc += a0 * b0 + a1 * b1 + a2 * b2 + a3 * b3;
+      }
+      for (; r < r1; r += 8) acc += Ai[r * sa] * Bj[r * sb];
+    } else {
+      for (int r = r0 + ty; r < r1; r += 8) acc += Ai[ioff(a.ar, r)] * Bj[ioff(a.br, r)];
+    }
+  }
+  part[ty][tx] = acc;
+  __syncthreads();
+  if (ty == 0 && j < a.J) {
+    float v = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v += part[q][tx];
+    v *= a.alpha;
+    if (a.bias && blockIdx.z == 0) v += a.bias[j];
+    float* c = a.C + ioff(a.ci, i) + ioff(a.cj, j);
+    if (a.accumulate || gridDim.z > 1) atomicAdd(c, v);
+    else *c = v;
+  }
 }
 int sgemm_generic(const SgemmArgs& a, cudaStream_t st) {
   if (a.I <= 0 || a.J <= 0) return 0;
+  const int jb = (a.J + 31) / 32;
   int split = 1;
-  if (a.R > 512) { split = std::min(64, (a.R + 255) / 256); }
-  ACT_CHECK(split == 1 || a.accumulate, "split reduction needs accumulate (zero-initialised output)");
-  const int threads = a.J >= 128 ? 128 : (a.J >= 64 ? 64 : 32);
-  dim3 grid((a.J + threads - 1) / threads, a.I, split);
+  if (a.accumulate && a.R > 64) {
+    // enough blocks to fill the chip, at least 32 reduction steps per block
+    const long long blocks = 1LL * jb * a.I;
+    split = static_cast<int>(std::max<long long>(1, std::min<long long>((a.R + 31) / 32, (2 * 148 + blocks - 1) / blocks)));
+  }
+  dim3 grid(jb, a.I, split);
   ACT_CHECK(a.I <= 65535, "sgemm_generic: too many rows");
-  sgemm_generic_kernel<<<grid, threads, 0, st>>>(a);
+  sgemm_generic_kernel<<<grid, dim3(32, 8), 0, st>>>(a);
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -243,6 +270,37 @@ int maxpool_bwd(const bf16* dy, const uint8_t* idx, const bf16* x, bf16* dx, int
   const long long total = 1LL * N * H * W * (C / 8);
   const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
   maxpool_bwd_kernel<<<blocks, 256, 0, st>>>(dy, idx, x, dx, N, H, W, C, Ho, Wo);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ stem image pack
+// policy.py:268-272 normalisation fused with the layout change the implicit-GEMM stem conv reads: pixel x of row y
+// lands at out[b][y][x + 3][0..3] = {R, G, B, 0} (bf16), columns [0,3) and [W+3, Wp) are zero (horizontal padding).
+__global__ void stem_pack_image_kernel(const float* __restrict__ img, long long img_bs, bf16* __restrict__ out, int B,
+                                       int H, int W, int Wp) {
+  const float mean[3] = {0.485f, 0.456f, 0.406f};
+  const float istd[3] = {1.f / 0.229f, 1.f / 0.224f, 1.f / 0.225f};
+  const long long total = 1LL * B * H * Wp;
+  for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
+    const int xp = static_cast<int>(i % Wp);
+    const long long r = i / Wp;
+    const int y = static_cast<int>(r % H), b = static_cast<int>(r / H);
+    const int x = xp - 3;
+    float v[3] = {0.f, 0.f, 0.f};
+    if (x >= 0 && x < W) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[c] = (__ldg(img + b * img_bs + (1LL * c * H + y) * W + x) - mean[c]) * istd[c];
+    }
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], 0.f);
+    uint2 o;
+    o.x = *reinterpret_cast<uint32_t*>(&lo); o.y = *reinterpret_cast<uint32_t*>(&hi);
+    reinterpret_cast<uint2*>(out)[i] = o;
+  }
+}
+int stem_pack_image(const float* img_cam, long long img_bs, bf16* out, int B, int H, int W, int Wp, cudaStream_t st) {
+  const long long total = 1LL * B * H * Wp;
+  stem_pack_image_kernel<<<static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16)), 256, 0, st>>>(img_cam, img_bs, out, B, H, W, Wp);
   ACT_CUDA(cudaGetLastError());
   return 0;
 }

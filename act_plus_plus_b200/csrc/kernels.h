@@ -8,7 +8,11 @@ namespace act {
 // ---- pack.cu
 int cast_bf16(const float* src, bf16* dst, long long n, cudaStream_t st);
 int pack_conv_weights(const float* w, const float* scale, bf16* wpk, bf16* wpkt, int Cout, int Cin, int KK, cudaStream_t st);
+struct PackJob { const float* w; const float* scale; bf16* wpk; bf16* wpkt; int Cout, Cin, KK, tile0; };
+struct PackJobs { static constexpr int MAX = 64; int n = 0; PackJob job[MAX]; };
+int pack_conv_batched(PackJobs& jobs, cudaStream_t st);   // all jobs in one launch
 int bn_fold(const float* w, const float* b, const float* rm, const float* rv, float* scale, float* shift, int n, cudaStream_t st);
+int pack_stem_weights(const float* w, bf16* wpk, cudaStream_t st);              // [64,3,7,7] fp32 -> [64][7*64] bf16 (row-window layout)
 int pack_conv1_weights(const float* w, bf16* wpk, int KP, cudaStream_t st);     // [64,147] fp32 -> [64,KP] bf16, zero padded
 
 // ---- fused_norm.cu
@@ -46,6 +50,8 @@ int reparam_bwd(const float* dz, const float* eps, const float* logvar, const fl
                 float* d_info, int B, int Z, cudaStream_t st);
 int maxpool_fwd(const bf16* x, bf16* y, uint8_t* idx, int N, int H, int W, int C, cudaStream_t st);
 int maxpool_bwd(const bf16* dy, const uint8_t* idx, const bf16* x, bf16* dx, int N, int H, int W, int C, cudaStream_t st);
+// image fp32 [B,3,H,W] (batch stride img_bs) -> ImageNet-normalised NHWC4 bf16 [B][H][Wp][4], 3 zero pixels left pad
+int stem_pack_image(const float* img_cam, long long img_bs, bf16* out, int B, int H, int W, int Wp, cudaStream_t st);
 int im2col_conv1(const float* img_cam, long long img_bs, bf16* out, int B, int H, int W, int KP, cudaStream_t st);
 
 // ---- optim.cu

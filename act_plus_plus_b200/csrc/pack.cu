@@ -50,6 +50,53 @@ int pack_conv_weights(const float* w, const float* scale, bf16* wpk, bf16* wpkt,
   return 0;
 }
 
+// Batched re-pack of every conv of a backbone in ONE launch (runs after each AdamW step).  A block owns a 32(co) x
+// 32(ci) x KK tile: coalesced fp32 reads of w[co][ci0..ci0+32][*] into shared memory, then 64-byte bf16 runs along ci
+// (wpk) and along co (wpkt).
+__global__ void __launch_bounds__(256) pack_conv_batched_kernel(const __grid_constant__ PackJobs jobs) {
+  __shared__ float tile[32][32 * 9 + 1];
+  int b = blockIdx.x, j = 0;
+  while (j + 1 < jobs.n && b >= jobs.job[j + 1].tile0) ++j;
+  const PackJob& jb = jobs.job[j];
+  b -= jb.tile0;
+  const int ci_tiles = (jb.Cin + 31) / 32;
+  const int co0 = (b / ci_tiles) * 32, ci0 = (b % ci_tiles) * 32;
+  const int KK = jb.KK, run = 32 * KK;                      // floats per co row of the tile (contiguous in w)
+  for (int idx = threadIdx.x; idx < 32 * run; idx += 256) {
+    const int co = idx / run, o = idx % run;
+    float v = 0.f;
+    if (co0 + co < jb.Cout && ci0 + o / KK < jb.Cin) v = jb.w[(1LL * (co0 + co) * jb.Cin + ci0) * KK + o];
+    tile[co][o] = v;
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 32 * run; idx += 256) {  // wpk[co][t*Cin + ci]: ci fastest
+    const int ci = idx % 32, t = (idx / 32) % KK, co = idx / (32 * KK);
+    if (co0 + co < jb.Cout && ci0 + ci < jb.Cin)
+      jb.wpk[(1LL * (co0 + co) * KK + t) * jb.Cin + ci0 + ci] = __float2bfloat16_rn(tile[co][ci * KK + t]);
+  }
+  if (jb.wpkt) {
+    for (int idx = threadIdx.x; idx < 32 * run; idx += 256) {  // wpkt[ci][t*Cout + co]: co fastest
+      const int co = idx % 32, t = (idx / 32) % KK, ci = idx / (32 * KK);
+      if (co0 + co < jb.Cout && ci0 + ci < jb.Cin) {
+        const float sc = jb.scale ? jb.scale[co0 + co] : 1.f;
+        jb.wpkt[(1LL * (ci0 + ci) * KK + t) * jb.Cout + co0 + co] = __float2bfloat16_rn(tile[co][ci * KK + t] * sc);
+      }
+    }
+  }
+}
+int pack_conv_batched(PackJobs& jobs, cudaStream_t st) {
+  ACT_CHECK(jobs.n >= 1 && jobs.n <= PackJobs::MAX, "pack_conv_batched: 1..64 jobs");
+  int tiles = 0;
+  for (int i = 0; i < jobs.n; ++i) {
+    ACT_CHECK(jobs.job[i].KK == 1 || jobs.job[i].KK == 9, "pack_conv_batched: 1x1 or 3x3 kernels");
+    jobs.job[i].tile0 = tiles;
+    tiles += ((jobs.job[i].Cout + 31) / 32) * ((jobs.job[i].Cin + 31) / 32);
+  }
+  pack_conv_batched_kernel<<<tiles, 256, 0, st>>>(jobs);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // FrozenBatchNorm2d fold (backbone.py:47-57): scale = w * rsqrt(rv + 1e-5); shift = b - rm * scale
 __global__ void bn_fold_kernel(const float* w, const float* b, const float* rm, const float* rv, float* scale, float* shift, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -76,6 +123,22 @@ __global__ void pack_conv1_kernel(const float* __restrict__ w, bf16* __restrict_
 }
 int pack_conv1_weights(const float* w, bf16* wpk, int KP, cudaStream_t st) {
   pack_conv1_kernel<<<(64 * KP + 255) / 256, 256, 0, st>>>(w, wpk, KP);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+}  // namespace act
+
+namespace act {
+// Stem (7x7/s2, 3 -> 64) weights for the implicit-GEMM formulation: one k-block per kernel row kh, 64 columns =
+// 16 pixels x 4 channels of the padded NHWC4 image window; column kw*4 + c holds w[co][c][kh][kw] (kw < 7, c < 3).
+__global__ void pack_stem_kernel(const float* __restrict__ w, bf16* __restrict__ wpk) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 64 * 448) return;
+  const int co = i / 448, kh = (i % 448) / 64, e = i % 64, kw = e >> 2, c = e & 3;
+  wpk[i] = __float2bfloat16_rn((kw < 7 && c < 3) ? w[((co * 3 + c) * 7 + kh) * 7 + kw] : 0.f);
+}
+int pack_stem_weights(const float* w, bf16* wpk, cudaStream_t st) {
+  pack_stem_kernel<<<(64 * 448 + 255) / 256, 256, 0, st>>>(w, wpk);
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
