@@ -65,6 +65,7 @@ struct DecActs {
 };
 struct BlockActs { bf16 *a = nullptr, *y = nullptr, *ds = nullptr; };   // conv1 relu out, block out, downsample out
 struct CamActs {
+  bf16 *xp = nullptr;                                                   // normalised NHWC4 image, padded rows [B][H][Wp][4]
   bf16 *y1 = nullptr, *p1 = nullptr; uint8_t* pidx = nullptr;           // stem
   BlockActs blk[8];
 };
@@ -157,7 +158,7 @@ class Engine {
   std::vector<EncActs> enc_a_, cvae_a_;
   DecActs dec_a_;
   std::vector<CamActs> cam_a_;
-  bf16* im2col_ = nullptr;
+  int Wp_ = 0;                  // padded row length (pixels) of the stem input
   float *tokC_ = nullptr, *src_ = nullptr, *pos_main_ = nullptr, *tgt0_ = nullptr;
   bf16 *mem_b_ = nullptr, *mem_pb_ = nullptr;
   uint8_t* maskC_ = nullptr;
@@ -177,7 +178,8 @@ class Engine {
   float* d_src_ = nullptr; float* d_tokC_ = nullptr;
   bf16 *cg_[4] = {nullptr, nullptr, nullptr, nullptr};   // backbone gradient ping-pong (NHWC bf16, max size)
   bf16* d_feat_ = nullptr;      // [K][B*Hf*Wf*512] gradient wrt each camera's layer4 output (ReLU-masked)
-  float* conv1_tmp_ = nullptr;  // [64][192] split-K accumulator of the stem weight gradient
+  float* conv1_tmp_ = nullptr;  // [64][64][7] accumulator of the stem weight gradient (window-element layout)
+  int stem_launch(int cam, int B, ConvLaunch* c, WgradLaunch* w);
   int input_grads(int B, cudaStream_t st);
 };
 

@@ -42,12 +42,12 @@ __global__ void gather_tokens_kernel(const float* __restrict__ src, bf16* __rest
   }
 }
 
-// conv1 weight gradient epilogue: dw[64][147] += scale[co] * tmp[64][KP]
-__global__ void conv1_grad_fold_kernel(const float* __restrict__ tmp, const float* __restrict__ scale, float* __restrict__ dw, int KP) {
+// conv1 weight gradient epilogue: dw[co][c][kh][kw] += scale[co] * tmp[co][kw*4 + c][kh]
+__global__ void conv1_grad_fold_kernel(const float* __restrict__ tmp, const float* __restrict__ scale, float* __restrict__ dw) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= 64 * 147) return;
-  const int co = i / 147, k = i % 147;
-  dw[i] += scale[co] * tmp[co * KP + k];
+  const int co = i / 147, k = i % 147, c = k / 49, kh = (k % 49) / 7, kw = k % 7;
+  dw[i] += scale[co] * tmp[(co * 64 + kw * 4 + c) * 7 + kh];
 }
 
 // dX[M,K] = dY[M,N] * W[N,K]   (A = dY K-major, B = W read MN-major)
@@ -333,20 +333,17 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
   // stem: max-pool backward (+ReLU mask), then dW1 = scale * dy1^T im2col(normalised image)
   const int H1 = fh_[1], W1 = fw_[1];
   RUN(maxpool_bwd(g, ca.pidx, ca.y1, cg_[0], B, H1, W1, 64, st));
-  const float* img = in_image_ + 1LL * cam * 3 * fh_[0] * fw_[0];
-  RUN(im2col_conv1(img, 1LL * cfg_.num_cameras * 3 * fh_[0] * fw_[0], im2col_, B, fh_[0], fw_[0], 192, st));
-  ACT_CUDA(cudaMemsetAsync(conv1_tmp_, 0, sizeof(float) * 64 * 192, st));
+  // dW1 over the same row-window operand the forward read (ca.xp is still resident): tmp[co][kw*4+c][kh]
+  ACT_CUDA(cudaMemsetAsync(conv1_tmp_, 0, sizeof(float) * 64 * 64 * 7, st));
   {
-    MatDesc a, b; EpiDesc e;
-    const int Mpix = B * H1 * W1;
-    a.ptr = cg_[0]; a.mn_major = 1; a.ld = 64; b.ptr = im2col_; b.mn_major = 1; b.ld = 192;
-    e.flags = EPI_OUT_F32 | EPI_ATOMIC; e.out_f32 = conv1_tmp_; e.ldc = 192;
-    const int kb = (Mpix + 63) / 64;
-    const int ks = std::max(1, std::min(kb / 4, 96));
-    ++launches_;
-    if (tc_gemm(64, 192, Mpix, 1, 1, a, b, e, ks, st, 64)) return -1;
+    WgradLaunch w;
+    if (stem_launch(cam, B, nullptr, &w)) return -1;
+    w.dy.ptr = cg_[0]; w.dy.C = 64; w.dy.W = W1; w.dy.H = H1; w.dy.N = B;
+    w.dy.sW = 64; w.dy.sH = 64LL * W1; w.dy.sN = 64LL * W1 * H1;
+    w.dw = conv1_tmp_; w.alpha = 1.f; w.scale = nullptr;
+    RUN(tc_wgrad(w, st));
   }
-  conv1_grad_fold_kernel<<<(64 * 147 + 255) / 256, 256, 0, st>>>(conv1_tmp_, cw.stem.scale, cw.stem.gw, 192);
+  conv1_grad_fold_kernel<<<(64 * 147 + 255) / 256, 256, 0, st>>>(conv1_tmp_, cw.stem.scale, cw.stem.gw);
   ++launches_;
   ACT_CUDA(cudaGetLastError());
   return 0;

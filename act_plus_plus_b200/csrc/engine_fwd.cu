@@ -42,7 +42,7 @@ int Engine::alloc_workspace() {
   // packed conv operands + folded BN
   for (int k = 0; k < cfg_.num_cameras; ++k) {
     CamW& c = cam_w_[k];
-    c.stem.wpk = A_(bf16, 64 * 192); c.stem.scale = A_(float, 64); c.stem.shift = A_(float, 64);
+    c.stem.wpk = A_(bf16, 64 * 448); c.stem.scale = A_(float, 64); c.stem.shift = A_(float, 64);
     static const int cin_[4] = {64, 64, 128, 256}, cout_[4] = {64, 128, 256, 512};
     for (int s = 0; s < 4; ++s)
       for (int b = 0; b < 2; ++b) {
@@ -60,10 +60,11 @@ int Engine::alloc_workspace() {
   }
   // backbone activations
   cam_a_.resize(cfg_.num_cameras);
-  im2col_ = A_(bf16, 1LL * Bm * fh_[1] * fw_[1] * 192);
+  Wp_ = roundup(2 * (fw_[1] - 1) + 16, 2);                 // last output pixel reads padded pixels [2(Wo-1), 2(Wo-1)+16)
   static const int cout_[4] = {64, 128, 256, 512};
   for (int k = 0; k < cfg_.num_cameras; ++k) {
     CamActs& a = cam_a_[k];
+    a.xp = A_(bf16, 1LL * Bm * fh_[0] * Wp_ * 4 + 64);
     a.y1 = A_(bf16, 1LL * Bm * fh_[1] * fw_[1] * 64);
     a.p1 = A_(bf16, 1LL * Bm * fh_[2] * fw_[2] * 64);
     a.pidx = A_(uint8_t, 1LL * Bm * fh_[2] * fw_[2] * 64);
@@ -122,7 +123,7 @@ int Engine::alloc_workspace() {
     const long long cmax = 1LL * Bm * fh_[1] * fw_[1] * 64;        // largest NHWC activation (conv1 output)
     for (int i = 0; i < 4; ++i) { cg_[i] = A_(bf16, i == 0 ? cmax : cmax / 4); }
     d_feat_ = A_(bf16, 1LL * cfg_.num_cameras * Bm * Hf_ * Wf_ * 512);
-    conv1_tmp_ = A_(float, 64 * 192);
+    conv1_tmp_ = A_(float, 64 * 64 * 7);
   }
 #undef A_
   // static part of the encoder position table: rows 2.. = PositionEmbeddingSine (position_encoding.py:30-52,
@@ -254,6 +255,41 @@ int Engine::cvae_fwd(int B, const float* qpos, const float* actions, long long a
   return 0;
 }
 
+// Stem conv 7x7/s2/p3 (3 -> 64) as an implicit GEMM over the padded NHWC4 image: one tap per kernel row kh, whose
+// A row for output pixel (h, w) is the 16-pixel x 4-channel window starting at padded pixel 2w of input row 2h+kh-3
+// (a TMA dimension with a 16-byte stride; rows outside the image are TMA zero fill).  K = 7 x 64, 147 of them non-zero.
+int Engine::stem_launch(int cam, int B, ConvLaunch* c, WgradLaunch* w) {
+  ACT_CHECK(fh_[0] % 2 == 0, "stem needs an even image height");
+  const CamW& cw = cam_w_[cam];
+  const CamActs& ca = cam_a_[cam];
+  const int H = fh_[0], Ho = fh_[1], Wo = fw_[1];
+  PlaneDesc pl[2];
+  for (int ph = 0; ph < 2; ++ph) {
+    pl[ph].ptr = ca.xp + 1LL * ph * Wp_ * 4; pl[ph].C = 64; pl[ph].W = Wo; pl[ph].H = H / 2; pl[ph].N = B;
+    pl[ph].sW = 8; pl[ph].sH = 2LL * Wp_ * 4; pl[ph].sN = 1LL * H * Wp_ * 4;
+  }
+  TapDesc taps[7];
+  for (int kh = 0; kh < 7; ++kh) {
+    const int oy = kh - 3;
+    taps[kh].map = static_cast<int16_t>(((oy % 2) + 2) % 2);
+    taps[kh].dh = static_cast<int16_t>(oy >= 0 ? oy / 2 : -((-oy + 1) / 2));
+    taps[kh].dw = 0; taps[kh].wslot = static_cast<int16_t>(kh);
+  }
+  if (c) {
+    c->planes[0] = pl[0]; c->planes[1] = pl[1]; c->nplanes = 2; c->ntaps = 7;
+    for (int i = 0; i < 7; ++i) c->taps[i] = taps[i];
+    c->Cin = 64; c->Cout = 64; c->wgt = cw.stem.wpk; c->wgt_ld = 448;
+    c->vW = Wo; c->vH = Ho; c->NIMG = B;
+    c->og = PixGeom{Ho, Wo, 1, 1, 0, 0, 64, 0}; c->rg = c->og;
+  }
+  if (w) {
+    w->planes[0] = pl[0]; w->planes[1] = pl[1]; w->nplanes = 2; w->ntaps = 7;
+    for (int i = 0; i < 7; ++i) w->taps[i] = taps[i];
+    w->Cin = 64; w->Cout = 64; w->KK = 7;
+  }
+  return 0;
+}
+
 // ResNet-18 trunk with FrozenBatchNorm folded into the conv epilogues (backbone.py:47-57,121-124), then the
 // 1x1 input_proj (detr_vae.py:184) written straight into the encoder token buffer [B, L, d] at this camera's columns.
 int Engine::backbone_fwd(int cam, int B, const float* image, cudaStream_t st) {
@@ -261,15 +297,13 @@ int Engine::backbone_fwd(int cam, int B, const float* image, cudaStream_t st) {
   CamW& cw = cam_w_[cam];
   CamActs& ca = cam_a_[cam];
   const float* img = image + 1LL * cam * 3 * H * W;
-  RUN(im2col_conv1(img, 1LL * K * 3 * H * W, im2col_, B, H, W, 192, st));
+  RUN(stem_pack_image(img, 1LL * K * 3 * H * W, ca.xp, B, H, W, Wp_, st));
   {
-    MatDesc a, b;
-    a.ptr = im2col_; a.ld = 192; b.ptr = cw.stem.wpk; b.ld = 192;
-    EpiDesc e;
-    e.flags = EPI_SCALE | EPI_BIAS | EPI_RELU | EPI_OUT_BF16; e.scale = cw.stem.scale; e.bias = cw.stem.shift;
-    e.out_bf16 = ca.y1; e.ldc = 64;
-    ++launches_;
-    if (tc_gemm(B * fh_[1] * fw_[1], 64, 192, 1, 1, a, b, e, 1, st)) return -1;
+    ConvLaunch c;
+    if (stem_launch(cam, B, &c, nullptr)) return -1;
+    c.epi.flags = EPI_SCALE | EPI_BIAS | EPI_RELU | EPI_OUT_BF16; c.epi.scale = cw.stem.scale; c.epi.bias = cw.stem.shift;
+    c.epi.out_bf16 = ca.y1;
+    RUN(tc_conv(c, st));
   }
   RUN(maxpool_fwd(ca.y1, ca.p1, cfg_.train ? ca.pidx : nullptr, B, fh_[1], fw_[1], 64, st));
   const bf16* x = ca.p1;

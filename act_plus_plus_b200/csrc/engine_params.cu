@@ -210,7 +210,7 @@ int Engine::refresh_shadows(cudaStream_t st) {
   for (int k = 0; k < cfg_.num_cameras; ++k) {
     CamW& c = cam_w_[k];
     if (bn_fold(c.stem.bn[0], c.stem.bn[1], c.stem.bn[2], c.stem.bn[3], c.stem.scale, c.stem.shift, 64, st)) return -1;
-    if (pack_conv1_weights(c.stem.w32, c.stem.wpk, 192, st)) return -1;
+    if (pack_stem_weights(c.stem.w32, c.stem.wpk, st)) return -1;
     for (int i = 0; i < 8; ++i) {
       BlockW& b = c.blk[i];
       ConvW* cs[3] = {&b.c1, &b.c2, b.has_ds ? &b.ds : nullptr};
@@ -249,7 +249,7 @@ int Engine::adamw(int step, cudaStream_t st) {
   // packed conv operands (transposed / scaled layouts) are rebuilt from the fp32 masters, one launch per camera
   for (int k = 0; k < cfg_.num_cameras; ++k) {
     CamW& c = cam_w_[k];
-    if (pack_conv1_weights(c.stem.w32, c.stem.wpk, 192, st)) return -1;
+    if (pack_stem_weights(c.stem.w32, c.stem.wpk, st)) return -1;
     ++launches_;
     PackJobs jobs;
     for (int i = 0; i < 8; ++i) {
