@@ -101,3 +101,32 @@ def test_unsupported_configs_raise():
     bad["backbone"] = "resnet50"
     with pytest.raises(ValueError):
         ACTPolicy(bad)
+
+
+def test_batched_rollout_matches_reference_ensemble_lines():
+    """BatchedRollout (policy query + ring-buffer ensemble kernel, 3 envs) == the literal imitate_episodes.py:403-411
+    buffer fed with the same policy outputs; also env sharding and the device-side (de)normalisation."""
+    from oracle import act_oracle as O
+    from act_plus_plus_b200.rollout import BatchedRollout
+    from act_plus_plus_b200.policy import ACTPolicy
+    torch.manual_seed(0)
+    pol = ACTPolicy(dict(_policy_config(1), seed=5))
+    pol.eval()
+    E, T, H, W = 3, 6, 96, 128
+    nq, A = pol.model.num_queries, pol.model.action_dim
+    stats = dict(qpos_mean=torch.randn(14), qpos_std=torch.rand(14) + 0.5, action_mean=torch.randn(A), action_std=torch.rand(A) + 0.5)
+    ro = BatchedRollout(pol, num_envs_global=E, stats=stats)
+    half = BatchedRollout(pol, num_envs_global=E, rank=1, world=2)
+    assert (ro.E, half.lo, half.hi) == (3, 2, 3)
+    oracles = [O.TemporalAggOracle(T, nq, A) for _ in range(E)]
+    g = torch.Generator().manual_seed(1)
+    for t in range(T):
+        qpos = torch.randn((E, 14), generator=g).cuda()
+        image = torch.rand((E, 1, 3, H, W), generator=g).cuda()
+        out = ro.step(qpos, image)
+        assert out.dtype == torch.float64 and out.shape == (E, A)
+        with torch.inference_mode():
+            chunks = pol((qpos - stats["qpos_mean"].cuda()) / stats["qpos_std"].cuda(), image).cpu()
+        for e in range(E):
+            ref = oracles[e].step(t, chunks[e][None])[0] * stats["action_std"].double() + stats["action_mean"].double()
+            assert torch.allclose(out[e].cpu(), ref, rtol=1e-12, atol=1e-12), (t, e)
