@@ -32,6 +32,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="launch kernels directly instead of replaying a CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-infer", action="store_true", help="skip the batched-inference / latency legs")
+    ap.add_argument("--infer-envs", type=int, default=128, help="environments per GPU in the rollout leg (1024/8)")
     return ap.parse_args()
 
 
@@ -133,6 +135,45 @@ def run_reference(args):
                 cpu_baseline=dict(value=value, unit="samples/s", cores=threads, kind="port", sample=sample),
                 e2e=dict(value=value, unit="samples/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
     print(json.dumps(line))
+
+
+def infer_legs(eng, dev, envs, steps):
+    """Batched rollout inference (BASELINE configs[4]: 1024 envs over 8 GPUs = 128 per GPU, one policy query per env per
+    step + temporal_agg ensemble) -> chunks/s on this GPU; and the B=1 query latency (p50 over synchronised calls)."""
+    import torch
+    from act_plus_plus_b200.engine import ActEngine
+    from act_plus_plus_b200.rollout import TemporalEnsembler
+    out = {}
+    g = torch.Generator(device="cpu").manual_seed(7)
+    big = ActEngine.sharing(eng, envs, H, W, False)
+    ens = TemporalEnsembler(envs, NQ, A_DIM, device=dev)
+    imgs = [torch.rand((envs, K_CAM, 3, H, W), generator=g).to(dev) for _ in range(2)]     # 2 x 472 MB > L2
+    qpos = torch.randn((envs, S_DIM), generator=g).to(dev)
+    for i in range(3):
+        ens.step(big.forward(qpos, imgs[i % 2])["a_hat"], i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        act = ens.step(big.forward(qpos, imgs[i % 2])["a_hat"], 3 + i)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    out.update(envs_per_gpu=envs, ms_per_env_step_batch=ms, chunks_per_s=envs / ms * 1e3,
+               tflops=34.9e9 * envs / ms / 1e9, action_checksum=float(act.sum()))
+    del big, imgs
+    one = ActEngine.sharing(eng, 1, H, W, False)
+    img1 = torch.rand((1, K_CAM, 3, H, W), generator=g).to(dev)
+    q1 = qpos[:1].contiguous()
+    lat = []
+    for i in range(30):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        a = one.forward(q1, img1)["a_hat"]
+        torch.cuda.synchronize()
+        lat.append((time.perf_counter() - t0) * 1e3)
+    lat = sorted(lat[5:])
+    out.update(p50_latency_ms_b1=lat[len(lat) // 2], p90_latency_ms_b1=lat[int(len(lat) * 0.9)])
+    return out
 
 
 def run_ours(args):
@@ -290,6 +331,11 @@ def run_ours(args):
                               tc_share_of_step=tc_ms_step / (ms / args.steps), longest_launch_ms=mx.value,
                               whole_step_tflops=FLOP_PER_SAMPLE_TRAIN * B / (ms / args.steps / 1e3) / 1e12),
                 clocks=clk)
+    if not args.no_infer:
+        try:
+            line["inference"] = infer_legs(eng, dev, args.infer_envs, max(3, min(args.steps, 10)))
+        except Exception as ex:
+            line["inference"] = dict(error=str(ex)[:200])
     if not args.no_cpu_baseline and world == 1:
         try:
             v, threads, sample = cpu_train_sample(2)
