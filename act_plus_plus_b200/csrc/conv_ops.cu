@@ -106,15 +106,90 @@ int conv_dgrad(const ConvShape& s, const bf16* dy, const bf16* wpkt, EpiDesc epi
   return 0;
 }
 
-// dW[co,ci,kh,kw] += alpha * scale[co]? (scale folded by caller through alpha only) * sum_pix dy[pix,co] * x[pix(+tap),ci]
+// ---- weight gradient: tc_wgrad accumulates into a staging buffer T[KK][Cout][Cin] (each warp-level reduction covers one
+// contiguous 128-byte line instead of nine lines at stride KK); this pass folds it into dW.
+static float* g_stage = nullptr;
+static long long g_stage_n = 0;
+int conv_wgrad_reserve(long long elems) {
+  if (elems <= g_stage_n) return 0;
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  (void)cs;
+  if (g_stage) ACT_CUDA(cudaFree(g_stage));
+  g_stage = nullptr; g_stage_n = 0;
+  ACT_CUDA(cudaMalloc(&g_stage, sizeof(float) * elems));
+  ACT_CUDA(cudaMemset(g_stage, 0, sizeof(float) * elems));
+  g_stage_n = elems;
+  return 0;
+}
+
+// block = 32(co) x 32(ci) x KK tile of one job: T rows along ci read coalesced, dW written in contiguous ci*KK runs
+__global__ void __launch_bounds__(256) wgrad_fold_kernel(const __grid_constant__ FoldJobs jobs) {
+  __shared__ float tile[32][32 * 9 + 1];
+  int b = blockIdx.x, j = 0;
+  while (j + 1 < jobs.n && b >= jobs.job[j + 1].tile0) ++j;
+  const FoldJob& jb = jobs.job[j];
+  b -= jb.tile0;
+  const int Cout = jb.Cout, Cin = jb.Cin, KK = jb.KK;
+  const int ci_tiles = (Cin + 31) / 32;
+  const int co0 = (b / ci_tiles) * 32, ci0 = (b % ci_tiles) * 32;
+  const int run = 32 * KK;
+  for (int idx = threadIdx.x; idx < 32 * run; idx += 256) {
+    const int ci = idx % 32, co = (idx / 32) % 32, t = idx / 1024;
+    float v = 0.f;
+    if (co0 + co < Cout && ci0 + ci < Cin) v = __ldg(jb.T + (1LL * t * Cout + co0 + co) * Cin + ci0 + ci);
+    tile[co][ci * KK + t] = v;
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 32 * run; idx += 256) {
+    const int co = idx / run, o = idx % run;
+    if (co0 + co < Cout && ci0 + o / KK < Cin)
+      jb.dw[(1LL * (co0 + co) * Cin + ci0) * KK + o] += jb.alpha * (jb.scale ? jb.scale[co0 + co] : 1.f) * tile[co][o];
+  }
+}
+int wgrad_fold_batched(FoldJobs& jobs, cudaStream_t stream) {
+  ACT_CHECK(jobs.n >= 1 && jobs.n <= FoldJobs::MAX, "wgrad_fold_batched: 1..64 jobs");
+  int tiles = 0;
+  for (int i = 0; i < jobs.n; ++i) {
+    ACT_CHECK(jobs.job[i].KK >= 1 && jobs.job[i].KK <= 9, "wgrad_fold_batched: KK <= 9");
+    jobs.job[i].tile0 = tiles;
+    tiles += ((jobs.job[i].Cout + 31) / 32) * ((jobs.job[i].Cin + 31) / 32);
+  }
+  wgrad_fold_kernel<<<tiles, 256, 0, stream>>>(jobs);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// staged weight gradient only: T[KK][Cout][Cin] += sum_pix dy[pix,co] * x[pix(+tap),ci]  (T zeroed by the caller)
+int conv_wgrad_staged(const ConvShape& s, const bf16* x, const bf16* dy, float* T, cudaStream_t stream) {
+  WgradLaunch w;
+  if (input_taps(s, x, w.planes, &w.nplanes, w.taps, &w.ntaps)) return -1;
+  const int Ho = conv_out_dim(s.H, s.KH, s.stride, s.pad), Wo = conv_out_dim(s.W, s.KH, s.stride, s.pad);
+  full_plane(&w.dy, dy, s.N, Ho, Wo, s.Cout);
+  w.Cin = s.Cin; w.Cout = s.Cout; w.KK = s.KH * s.KH; w.dw = T; w.alpha = 1.f; w.scale = nullptr;
+  return tc_wgrad(w, stream);
+}
+
+// dW[co,ci,kh,kw] += alpha * scale[co] * sum_pix dy[pix,co] * x[pix(+tap),ci]
 int conv_wgrad(const ConvShape& s, const bf16* x, const bf16* dy, float* dw, float alpha, const float* scale,
                cudaStream_t stream) {
   WgradLaunch w;
   if (input_taps(s, x, w.planes, &w.nplanes, w.taps, &w.ntaps)) return -1;
   const int Ho = conv_out_dim(s.H, s.KH, s.stride, s.pad), Wo = conv_out_dim(s.W, s.KH, s.stride, s.pad);
   full_plane(&w.dy, dy, s.N, Ho, Wo, s.Cout);
-  w.Cin = s.Cin; w.Cout = s.Cout; w.KK = s.KH * s.KH; w.dw = dw; w.alpha = alpha; w.scale = scale;
-  return tc_wgrad(w, stream);
+  const int KK = s.KH * s.KH;
+  const long long n = 1LL * KK * s.Cin * s.Cout;
+  if (n > g_stage_n) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(stream, &cs);
+    ACT_CHECK(cs == cudaStreamCaptureStatusNone, "conv_wgrad staging buffer must be reserved before stream capture");
+    if (conv_wgrad_reserve(n)) return -1;
+  }
+  (void)w; (void)Ho; (void)Wo;
+  ACT_CUDA(cudaMemsetAsync(g_stage, 0, sizeof(float) * n, stream));
+  if (conv_wgrad_staged(s, x, dy, g_stage, stream)) return -1;
+  FoldJobs jobs;
+  jobs.n = 1; jobs.job[0] = FoldJob{g_stage, scale, dw, alpha, s.Cout, s.Cin, KK, 0};
+  return wgrad_fold_batched(jobs, stream);
 }
 
 }  // namespace act

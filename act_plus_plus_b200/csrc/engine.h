@@ -178,6 +178,7 @@ class Engine {
   float* d_src_ = nullptr; float* d_tokC_ = nullptr;
   bf16 *cg_[4] = {nullptr, nullptr, nullptr, nullptr};   // backbone gradient ping-pong (NHWC bf16, max size)
   bf16* d_feat_ = nullptr;      // [K][B*Hf*Wf*512] gradient wrt each camera's layer4 output (ReLU-masked)
+  float* wstage_ = nullptr; long long wstage_n_ = 0;   // staged conv weight gradients T[KK][Cout][Cin] of one backbone
   float* conv1_tmp_ = nullptr;  // [64][64][7] accumulator of the stem weight gradient (window-element layout)
   int stem_launch(int cam, int B, ConvLaunch* c, WgradLaunch* w);
   int input_grads(int B, cudaStream_t st);

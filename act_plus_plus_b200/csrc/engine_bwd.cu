@@ -42,12 +42,12 @@ __global__ void gather_tokens_kernel(const float* __restrict__ src, bf16* __rest
   }
 }
 
-// conv1 weight gradient epilogue: dw[co][c][kh][kw] += scale[co] * tmp[co][kw*4 + c][kh]
+// conv1 weight gradient epilogue: dw[co][c][kh][kw] += scale[co] * T[kh][co][kw*4 + c]  (staged layout of tc_wgrad)
 __global__ void conv1_grad_fold_kernel(const float* __restrict__ tmp, const float* __restrict__ scale, float* __restrict__ dw) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= 64 * 147) return;
   const int co = i / 147, k = i % 147, c = k / 49, kh = (k % 49) / 7, kw = k % 7;
-  dw[i] += scale[co] * tmp[(co * 64 + kw * 4 + c) * 7 + kh];
+  dw[i] += scale[co] * tmp[(kh * 64 + co) * 64 + kw * 4 + c];
 }
 
 // dX[M,K] = dY[M,N] * W[N,K]   (A = dY K-major, B = W read MN-major)
@@ -292,6 +292,19 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
   CamActs& ca = cam_a_[cam];
   const bf16* g = d_feat_ + 1LL * cam * cfg_.batch_max * Hf_ * Wf_ * 512;
   bf16* bufs[3] = {cg_[1], cg_[2], cg_[3]};
+  // conv weight gradients accumulate in staged layout (line-coalesced reductions) and are folded into dW by ONE launch
+  ACT_CUDA(cudaMemsetAsync(wstage_, 0, sizeof(float) * wstage_n_, st));
+  FoldJobs folds;
+  long long woff = 0;
+  auto wgrad = [&](const ConvShape& cs, const bf16* xin, const bf16* dy, const ConvW& cw2) -> int {
+    const long long n = 1LL * cs.KH * cs.KH * cs.Cin * cs.Cout;
+    ACT_CHECK(woff + n <= wstage_n_ && folds.n < FoldJobs::MAX, "weight-gradient staging overflow");
+    float* T = wstage_ + woff;
+    woff += n;
+    folds.job[folds.n++] = FoldJob{T, cw2.scale, cw2.gw, 1.f, cs.Cout, cs.Cin, cs.KH * cs.KH, 0};
+    ++launches_;
+    return conv_wgrad_staged(cs, xin, dy, T, st);
+  };
   int gi = -1;                                       // index in bufs holding g (-1: d_feat_)
   for (int i = 7; i >= 0; --i) {
     BlockW& bw = cw.blk[i];
@@ -308,17 +321,17 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
     bf16* dx = bufs[dx_i];
     ConvShape s2{B, Ho, Wo, bw.c2.Cin, bw.c2.Cout, 3, 1, 1};
     ConvShape s1{B, Hc, Wc, bw.c1.Cin, bw.c1.Cout, 3, st1, 1};
-    RUN(conv_wgrad(s2, ba.a, g, bw.c2.gw, 1.f, bw.c2.scale, st));
+    if (wgrad(s2, ba.a, g, bw.c2)) return -1;
     {
       EpiDesc e; e.flags = EPI_OUT_BF16 | EPI_MASK_POS; e.out_bf16 = ga; e.aux_bf16 = ba.a;
       RUN(conv_dgrad(s2, g, bw.c2.wpkt, e, nullptr, st));
     }
-    RUN(conv_wgrad(s1, x_in, ga, bw.c1.gw, 1.f, bw.c1.scale, st));
+    if (wgrad(s1, x_in, ga, bw.c1)) return -1;
     EpiDesc e1; e1.flags = EPI_OUT_BF16; e1.out_bf16 = dx;
     if (i > 0) { e1.flags |= EPI_MASK_POS; e1.aux_bf16 = x_in; }     // x_in = relu output of the previous block
     if (bw.has_ds) {
       ConvShape sd{B, Hc, Wc, bw.ds.Cin, bw.ds.Cout, 1, st1, 0};
-      RUN(conv_wgrad(sd, x_in, g, bw.ds.gw, 1.f, bw.ds.scale, st));
+      if (wgrad(sd, x_in, g, bw.ds)) return -1;
       ConvShape sdc{B, Ho, Wo, bw.ds.Cin, bw.ds.Cout, 1, 1, 0};      // 1x1 data gradient on the compact (strided) grid
       EpiDesc ec; ec.flags = EPI_OUT_BF16; ec.out_bf16 = cg_[0];
       RUN(conv_dgrad(sdc, g, bw.ds.wpkt, ec, nullptr, st));
@@ -330,6 +343,7 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
     }
     g = dx; gi = dx_i;
   }
+  RUN(wgrad_fold_batched(folds, st));
   // stem: max-pool backward (+ReLU mask), then dW1 = scale * dy1^T im2col(normalised image)
   const int H1 = fh_[1], W1 = fw_[1];
   RUN(maxpool_bwd(g, ca.pidx, ca.y1, cg_[0], B, H1, W1, 64, st));

@@ -124,6 +124,15 @@ int Engine::alloc_workspace() {
     for (int i = 0; i < 4; ++i) { cg_[i] = A_(bf16, i == 0 ? cmax : cmax / 4); }
     d_feat_ = A_(bf16, 1LL * cfg_.num_cameras * Bm * Hf_ * Wf_ * 512);
     conv1_tmp_ = A_(float, 64 * 64 * 7);
+    {
+      static const int ci_[4] = {64, 64, 128, 256}, co_[4] = {64, 128, 256, 512};
+      wstage_n_ = 0;
+      for (int s4 = 0; s4 < 4; ++s4) {
+        wstage_n_ += 9LL * ci_[s4] * co_[s4] + 3 * 9LL * co_[s4] * co_[s4];     // b0.c1, b0.c2, b1.c1, b1.c2
+        if (s4 > 0) wstage_n_ += 1LL * ci_[s4] * co_[s4];                       // downsample 1x1
+      }
+      wstage_ = A_(float, wstage_n_);
+    }
   }
 #undef A_
   // static part of the encoder position table: rows 2.. = PositionEmbeddingSine (position_encoding.py:30-52,

@@ -76,10 +76,10 @@ struct WgradLaunch {
   TapDesc taps[16];
   int ntaps = 0;
   PlaneDesc dy;                         // gradient wrt the conv output, dims {Cout, vW, vH, N}
-  int Cin = 0, Cout = 0, KK = 0;        // dW fp32 [Cout][Cin][KK], accumulated with atomics (caller zeroes it)
-  float* dw = nullptr;
+  int Cin = 0, Cout = 0, KK = 0;        // staged output T fp32 [KK][Cout][Cin] (ci contiguous), accumulated with
+  float* dw = nullptr;                  // vector atomics (caller zeroes it and folds it into dW[Cout][Cin][KK])
   float alpha = 1.f;
-  const float* scale = nullptr;         // optional per-Cout factor (FrozenBN scale)
+  const float* scale = nullptr;         // unused by the kernel (applied by the fold)
   int ksplit = 0;                       // 0 -> heuristic
 };
 int tc_wgrad(const WgradLaunch& w, cudaStream_t stream);

@@ -57,7 +57,7 @@ struct TcParams {
   PixGeom og, rg;              // output / residual geometry
   TapDesc taps[16];
   // wgrad
-  int KK, Cin, Cout;           // dW[co][ci][KK] fp32, atomically accumulated
+  int KK, Cin, Cout;           // staged dW: T[KK][Cout][Cin] fp32, atomically accumulated (line-coalesced reductions)
   int taps_per_cta;            // 1, or 2 when Cin == 64 (two taps stacked along M)
   int pix_per_box;             // BW*BH
   // epilogue
@@ -298,7 +298,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
         if (p.taps_per_cta == 2) { tap = c.wg_tap0 + (r >> 6); ci = r & 63; }
         else { tap = c.wg_tap0; ci = c.wg_ci0 + r; }
         row_ok = tap < p.ntaps && ci < p.Cin;
-        o_off = static_cast<long long>(ci) * p.KK + p.taps[min(tap, p.ntaps - 1)].wslot;
+        o_off = static_cast<long long>(p.taps[min(tap, p.ntaps - 1)].wslot) * p.Cout * p.Cin + ci;
       }
       if (c.nkb == 0) row_ok = false;          // nothing accumulated (empty split): TMEM is garbage
 
@@ -320,14 +320,12 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
         if (!row_ok || (p.debug & 1)) continue;
         const int gn0 = n0 + c0;
         if (MODE == MODE_WGRAD) {
+          // staged layout T[wslot][co][ci]: the 32 lanes of a warp hold 32 consecutive ci, so every reduction
+          // instruction covers one contiguous 128-byte line; the caller folds T into dW[co][ci][kk]
+          float* op = p.out_f32 + o_off + static_cast<long long>(gn0) * p.Cin;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int co = gn0 + j;
-            if (co < p.Cout) {
-              const float sc = (p.flags & EPI_SCALE) ? __ldg(p.scale + co) * p.alpha : p.alpha;
-              atomicAdd(p.out_f32 + static_cast<long long>(co) * p.Cin * p.KK + o_off, __uint_as_float(v[j]) * sc);
-            }
-          }
+          for (int j = 0; j < 32; ++j)
+            if (gn0 + j < p.Cout) atomicAdd(op + static_cast<long long>(j) * p.Cin, __uint_as_float(v[j]) * p.alpha);
           continue;
         }
         float f[32];

@@ -317,7 +317,6 @@ int tc_wgrad(const WgradLaunch& w, cudaStream_t stream) {
   p.taps_per_cta = (w.Cin == 64) ? 2 : 1;
   for (int i = 0; i < w.ntaps; ++i) p.taps[i] = w.taps[i];
   p.nz0 = 1; p.alpha = w.alpha; p.out_f32 = w.dw; p.flags = EPI_OUT_F32 | EPI_ATOMIC;
-  if (w.scale) { p.flags |= EPI_SCALE; p.scale = w.scale; }
   const int bn = (w.Cout >= 128) ? 128 : 64;
   const int ygroups = (p.taps_per_cta == 2) ? (w.ntaps + 1) / 2 : w.ntaps * (w.Cin / 128);
   const int xt = (w.Cout + bn - 1) / bn;

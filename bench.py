@@ -218,7 +218,7 @@ def run_ours(args):
     for i in range(max(3, args.warmup)):
         losses = step_direct(devb[i % NB])
     torch.cuda.synchronize()
-    use_graph = not args.no_graph and world == 1
+    use_graph = not args.no_graph and (world == 1 or os.environ.get("ACT_DP_GRAPH", "1") == "1")
     graph = None
     if use_graph:
         try:
@@ -306,9 +306,10 @@ def run_ours(args):
     tot_ms, tot_fl, nl, mx = C.c_double(), C.c_double(), C.c_int(), C.c_double()
     _lib.check(lib.act_tc_profile_end(C.byref(tot_ms), C.byref(tot_fl), C.byref(nl), C.byref(mx)), "tc_profile_end")
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+        # a captured graph that contains NCCL kernels keeps the communicator busy on teardown: leave without it
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        os._exit(0)
     peaks = measured_peaks()
     n_samples = B * world * args.steps
     value = n_samples / (ms / 1e3)
@@ -344,7 +345,9 @@ def run_ours(args):
             line["cpu_baseline"] = dict(value=None, unit="samples/s", cores=os.cpu_count(), kind="port", sample=f"failed: {ex}")
     print(json.dumps(line))
     if world > 1:
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":
