@@ -68,11 +68,8 @@ int Engine::linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cuda
   A.ptr = dY; A.mn_major = 1; A.ld = w.N; B.ptr = X; B.mn_major = 1; B.ld = w.K;
   EpiDesc e;
   e.flags = EPI_OUT_F32 | EPI_ATOMIC; e.out_f32 = w.gw; e.ldc = w.K;
-  const int bn = w.K >= 1024 ? 128 : 64;
-  const long long tiles = 1LL * ((w.N + 127) / 128) * ((w.K + bn - 1) / bn);
-  const int kblocks = (M + 63) / 64;
-  int ks = static_cast<int>(std::max<long long>(1, (148 * 2 + tiles - 1) / tiles));
-  ks = std::max(1, std::min(ks, kblocks / 2));
+  int bn = 64, ks = 1;
+  plan_splitk(w.N, w.K, M, &bn, &ks);
   ++launches_;
   if (tc_gemm(w.N, w.K, M, 1, 1, A, B, e, ks, st, bn)) return -1;
   if (w.gb) RUN(colsum_bf16(dY, w.N, M, w.N, w.gb, st));

@@ -49,6 +49,8 @@ struct EpiDesc {
 int tc_gemm(int M, int N, int K, int nz0, int nz1, const MatDesc& A, const MatDesc& B, const EpiDesc& epi,
             int ksplit, cudaStream_t stream, int bn_hint = 0, int stages_hint = 0);
 
+void plan_splitk(int M, int N, int K, int* bn, int* ksplit);   // tile width + split for reduction-heavy GEMMs
+
 // One NHWC plane (possibly a stride-2 parity sub-lattice) addressed by TMA: dims {C, W, H, N}.
 struct PlaneDesc {
   const bf16* ptr = nullptr;

@@ -182,6 +182,28 @@ static int pick_bn(int N, long long row_tiles, int kblocks) {
   return best;
 }
 
+// Split-K plan for a reduction-heavy GEMM (weight gradients: K = tokens): tile width and split minimising
+// rounds x (k-blocks per split x ns/k-block + atomic epilogue) on a persistent launch.
+void plan_splitk(int M, int N, int K, int* bn_out, int* ks_out) {
+  const int mt = (M + 127) / 128, kb = (K + 63) / 64;
+  double best = 1e30;
+  *bn_out = 64; *ks_out = 1;
+  const int cands[3] = {64, 128, 256};
+  for (int c : cands) {
+    if (c > 64 && N < c) continue;
+    const long long base = 1LL * mt * ((N + c - 1) / c);
+    const double t_epi = 1500.0 + 12.0 * c;
+    for (int k = 1; k <= std::min(64, kb); ++k) {
+      const long long tiles = base * k;
+      const long long rounds = (tiles + num_sms() - 1) / num_sms();
+      const double active = std::min<double>(1.0, double(tiles) / num_sms());
+      const double t_kb = std::max((16.0 + c / 8.0) * std::max(5.0, 12.0 * active), c == 256 ? 300.0 : 228.0);
+      const double cost = rounds * (((kb + k - 1) / k) * t_kb + t_epi);
+      if (cost < best * 0.999) { best = cost; *bn_out = c; *ks_out = k; }
+    }
+  }
+}
+
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 static void fill_epi(TcParams& p, const EpiDesc& e) {
@@ -322,8 +344,16 @@ int tc_wgrad(const WgradLaunch& w, cudaStream_t stream) {
   const int xt = (w.Cout + bn - 1) / bn;
   int ks = w.ksplit;
   if (ks <= 0) {
-    ks = std::max(1, (2 * 148 + ygroups * xt - 1) / (ygroups * xt));
-    ks = std::min(ks, std::max(1, p.num_k_blocks / 4));
+    // persistent launch: rounds x (k-blocks per split x MMA time + epilogue); pick the split with the lowest cost
+    const long long base = 1LL * ygroups * xt;
+    const double t_kb = (p.pix_per_box / 16) * 57.0, t_epi = 2500.0;
+    double best = 1e30;
+    ks = 1;
+    for (int c = 1; c <= std::min(96, p.num_k_blocks); ++c) {
+      const long long rounds = (base * c + num_sms() - 1) / num_sms();
+      const double cost = rounds * (((p.num_k_blocks + c - 1) / c) * t_kb + t_epi);
+      if (cost < best * 0.999) { best = cost; ks = c; }
+    }
   }
   ks = std::min(ks, p.num_k_blocks);
   p.ksplit = ks;
