@@ -13,6 +13,7 @@ __device__ __forceinline__ long long ioff(const IdxMap& m, int idx) {
 // Block = 32 output columns x 8 reduction slices: thread (tx, ty) accumulates r = r0+ty, r0+ty+8, ... for column j,
 // the 8 partial sums meet in shared memory.  grid.z splits long reductions further (atomic accumulate).
 __global__ void __launch_bounds__(256) sgemm_generic_kernel(SgemmArgs a) {
+  pdl_trigger(); pdl_wait();
   __shared__ float part[8][33];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int j = blockIdx.x * 32 + tx;
@@ -61,7 +62,7 @@ int sgemm_generic(const SgemmArgs& a, cudaStream_t st) {
   }
   dim3 grid(jb, a.I, split);
   ACT_CHECK(a.I <= 65535, "sgemm_generic: too many rows");
-  sgemm_generic_kernel<<<grid, dim3(32, 8), 0, st>>>(a);
+  ACT_CUDA(launch_pdl(sgemm_generic_kernel, grid, dim3(32, 8), 0, st, a));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }

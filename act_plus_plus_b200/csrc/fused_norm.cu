@@ -30,6 +30,7 @@ template <int V>   // D = 128 * V
 __global__ void ln_fwd_kernel(const float* __restrict__ t, const float* __restrict__ gamma, const float* __restrict__ beta,
                               const float* __restrict__ pos, int L, float* __restrict__ y, bf16* __restrict__ yb,
                               bf16* __restrict__ ypb, float* __restrict__ mean, float* __restrict__ rstd, int M) {
+  pdl_trigger(); pdl_wait();
   constexpr int D = 128 * V;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
@@ -77,8 +78,8 @@ int ln_fwd(const float* t, const float* gamma, const float* beta, const float* p
   if (M <= 0) return 0;
   const int wpb = 4;
   dim3 grid((M + wpb - 1) / wpb), block(32 * wpb);
-  if (D == 512) ln_fwd_kernel<4><<<grid, block, 0, st>>>(t, gamma, beta, pos, L > 0 ? L : 1, y, yb, ypb, mean, rstd, M);
-  else ln_fwd_kernel<2><<<grid, block, 0, st>>>(t, gamma, beta, pos, L > 0 ? L : 1, y, yb, ypb, mean, rstd, M);
+  if (D == 512) ACT_CUDA(launch_pdl(ln_fwd_kernel<4>, dim3(grid), dim3(block), 0, st, t, gamma, beta, pos, L > 0 ? L : 1, y, yb, ypb, mean, rstd, M));
+  else ACT_CUDA(launch_pdl(ln_fwd_kernel<2>, dim3(grid), dim3(block), 0, st, t, gamma, beta, pos, L > 0 ? L : 1, y, yb, ypb, mean, rstd, M));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -91,6 +92,7 @@ __global__ void ln_bwd_kernel(const float* __restrict__ dy, const float* __restr
                               const float* __restrict__ mean, const float* __restrict__ rstd,
                               const float* __restrict__ gamma, float* __restrict__ dt, bf16* __restrict__ dtb,
                               float* __restrict__ dgamma, float* __restrict__ dbeta, int M, int rows_per_block) {
+  pdl_trigger(); pdl_wait();
   constexpr int D = 128 * V;
   constexpr int WARPS = 4;
   __shared__ float red[2][WARPS][D];
@@ -159,8 +161,8 @@ int ln_bwd(const float* dy, const float* dy2, const float* t, const float* mean,
   int rpb = 16;
   while (rpb > 4 && (M + rpb - 1) / rpb < 148 * 2) rpb >>= 1;
   dim3 grid((M + rpb - 1) / rpb), block(128);
-  if (D == 512) ln_bwd_kernel<4><<<grid, block, 0, st>>>(dy, dy2, t, mean, rstd, gamma, dt, dtb, dgamma, dbeta, M, rpb);
-  else ln_bwd_kernel<2><<<grid, block, 0, st>>>(dy, dy2, t, mean, rstd, gamma, dt, dtb, dgamma, dbeta, M, rpb);
+  if (D == 512) ACT_CUDA(launch_pdl(ln_bwd_kernel<4>, dim3(grid), dim3(block), 0, st, dy, dy2, t, mean, rstd, gamma, dt, dtb, dgamma, dbeta, M, rpb));
+  else ACT_CUDA(launch_pdl(ln_bwd_kernel<2>, dim3(grid), dim3(block), 0, st, dy, dy2, t, mean, rstd, gamma, dt, dtb, dgamma, dbeta, M, rpb));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -169,6 +171,7 @@ int ln_bwd(const float* dy, const float* dy2, const float* t, const float* mean,
 // xb = bf16(x), xpb = bf16(x + pos[row % L])   (with_pos_embed of transformer.py:205-206 feeding q/k only)
 __global__ void add_pos_cast_kernel(const float* __restrict__ x, const float* __restrict__ pos, int L, int D4,
                                     bf16* __restrict__ xb, bf16* __restrict__ xpb, long long n4) {
+  pdl_trigger(); pdl_wait();
   for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * 1LL * blockDim.x) {
     const float4 v = reinterpret_cast<const float4*>(x)[i];
     if (xb) reinterpret_cast<uint2*>(xb)[i] = pack4_bf16(v.x, v.y, v.z, v.w);
@@ -187,7 +190,7 @@ int add_pos_cast(const float* x, const float* pos, int L, bf16* xb, bf16* xpb, i
   const long long n4 = 1LL * M * D / 4;
   if (n4 <= 0) return 0;
   const int blocks = static_cast<int>(std::min<long long>((n4 + 255) / 256, 148 * 8));
-  add_pos_cast_kernel<<<blocks, 256, 0, st>>>(x, pos, L > 0 ? L : 1, D / 4, xb, xpb, n4);
+  ACT_CUDA(launch_pdl(add_pos_cast_kernel, dim3(blocks), dim3(256), 0, st, x, pos, L > 0 ? L : 1, D / 4, xb, xpb, n4));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -197,6 +200,7 @@ int add_pos_cast(const float* x, const float* pos, int L, bf16* xb, bf16* xpb, i
 // One warp per row; rows R = B * heads * Lq, b = r / rows_per_batch.  Lp <= 1024.
 __global__ void softmax_fwd_kernel(const float* __restrict__ S, const uint8_t* __restrict__ mask, bf16* __restrict__ P,
                                    int R, int L, int Lp, int rows_per_batch) {
+  pdl_trigger(); pdl_wait();
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= R) return;
@@ -231,7 +235,7 @@ int softmax_fwd(const float* S, const uint8_t* mask, bf16* P, int R, int L, int 
   ACT_CHECK(Lp <= 1024 && L <= Lp, "softmax row too long (max 1024 keys)");
   if (R <= 0) return 0;
   const int wpb = 4;
-  softmax_fwd_kernel<<<(R + wpb - 1) / wpb, 32 * wpb, 0, st>>>(S, mask, P, R, L, Lp, rows_per_batch > 0 ? rows_per_batch : 1);
+  ACT_CUDA(launch_pdl(softmax_fwd_kernel, dim3((R + wpb - 1) / wpb), dim3(32 * wpb), 0, st, S, mask, P, R, L, Lp, rows_per_batch > 0 ? rows_per_batch : 1));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -239,6 +243,7 @@ int softmax_fwd(const float* S, const uint8_t* mask, bf16* P, int R, int L, int 
 // dS = scale * P * (dP - sum_j P*dP)  -> bf16, pad columns zero
 __global__ void softmax_bwd_kernel(const bf16* __restrict__ P, const float* __restrict__ dP, bf16* __restrict__ dS,
                                    int R, int L, int Lp, float scale) {
+  pdl_trigger(); pdl_wait();
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= R) return;
@@ -266,7 +271,7 @@ int softmax_bwd(const bf16* P, const float* dP, bf16* dS, int R, int L, int Lp, 
   ACT_CHECK(Lp <= 1024 && L <= Lp, "softmax row too long (max 1024 keys)");
   if (R <= 0) return 0;
   const int wpb = 4;
-  softmax_bwd_kernel<<<(R + wpb - 1) / wpb, 32 * wpb, 0, st>>>(P, dP, dS, R, L, Lp, scale);
+  ACT_CUDA(launch_pdl(softmax_bwd_kernel, dim3((R + wpb - 1) / wpb), dim3(32 * wpb), 0, st, P, dP, dS, R, L, Lp, scale));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -275,6 +280,7 @@ int softmax_bwd(const bf16* P, const float* dP, bf16* dS, int R, int L, int Lp, 
 // out[n] += sum_m X[m*ld + n]  (bias gradients).  Block = 32 x 8 threads: 64 columns (bf16x2 per thread) x row stripes.
 __global__ void colsum_bf16_kernel(const bf16* __restrict__ X, long long ld, int M, int N, float* __restrict__ out,
                                    int rows_per_block) {
+  pdl_trigger(); pdl_wait();
   __shared__ float2 red[8][32];
   const int c = blockIdx.x * 64 + threadIdx.x * 2;
   const int r0 = blockIdx.y * rows_per_block, r1 = min(M, r0 + rows_per_block);
@@ -303,7 +309,7 @@ int colsum_bf16(const bf16* X, long long ld, int M, int N, float* out, cudaStrea
   int rpb = 256;
   while (rpb > 32 && 1LL * cb * ((M + rpb - 1) / rpb) < 148 * 2) rpb >>= 1;
   dim3 grid(cb, (M + rpb - 1) / rpb), block(32, 8);
-  colsum_bf16_kernel<<<grid, block, 0, st>>>(X, ld, M, N, out, rpb);
+  ACT_CUDA(launch_pdl(colsum_bf16_kernel, dim3(grid), dim3(block), 0, st, X, ld, M, N, out, rpb));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }

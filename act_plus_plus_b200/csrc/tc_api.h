@@ -24,6 +24,19 @@ const char* last_error();
     if (_e != cudaSuccess) { ::act::set_error(std::string(#expr) + ": " + cudaGetErrorString(_e)); return -2; } \
   } while (0)
 
+// Launch with the programmatic-stream-serialization attribute (PDL); ACT_PDL=0 in the environment turns it off.
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // Logical matrix operand [rows x K] (batched).  K-major: (row,k) at ptr + row*ld + k.
 // MN-major: (row,k) at ptr + k*ld + row.  Batch z = z0 + nz0*z1 adds z0*sz0 + z1*sz1 elements.
 struct MatDesc {

@@ -159,7 +159,8 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
   const int lane = threadIdx.x & 31;
   const int total_tiles = p.gx * p.gy * p.gz;
 
-  // ---------------------------------------------------------------- setup
+  // ---------------------------------------------------------------- setup (overlaps the previous kernel's tail)
+  pdl_trigger();
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&amap0);
     prefetch_tmap(&bmap);
@@ -172,6 +173,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                                  // operands / residuals written by the previous kernel are visible from here
 
   if (warp == 0) {
     // ============================================================== TMA producer

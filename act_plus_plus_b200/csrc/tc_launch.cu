@@ -14,6 +14,12 @@ static thread_local std::string g_err;
 void set_error(const std::string& msg) { g_err = msg; }
 const char* last_error() { return g_err.c_str(); }
 
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("ACT_PDL"); on = (e && e[0] == '0') ? 0 : 1; }
+  return on == 1;
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -154,7 +160,7 @@ static int launch_inst(dim3 tiles, int stages, cudaStream_t stream, const CUtens
   const unsigned ctas = static_cast<unsigned>(std::min<long long>(total, num_sms()));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
-  kern<<<ctas, Cfg::THREADS, smem, stream>>>(am[0], am[1], am[2], am[3], bm, p, stages);
+  ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(Cfg::THREADS), static_cast<size_t>(smem), stream, am[0], am[1], am[2], am[3], bm, p, stages));
   if (g_prof.on) { cudaEventRecord(e1, stream); g_prof.ev.push_back(e0); g_prof.ev.push_back(e1); g_prof.flops.push_back(g_next_flops); g_prof.label.push_back(g_next_label); }
   ACT_CUDA(cudaGetLastError());
   return 0;
