@@ -124,6 +124,7 @@ int conv_wgrad_reserve(long long elems) {
 
 // block = 32(co) x 32(ci) x KK tile of one job: T rows along ci read coalesced, dW written in contiguous ci*KK runs
 __global__ void __launch_bounds__(256) wgrad_fold_kernel(const __grid_constant__ FoldJobs jobs) {
+  pdl_trigger(); pdl_wait();
   __shared__ float tile[32][32 * 9 + 1];
   int b = blockIdx.x, j = 0;
   while (j + 1 < jobs.n && b >= jobs.job[j + 1].tile0) ++j;
@@ -154,7 +155,7 @@ int wgrad_fold_batched(FoldJobs& jobs, cudaStream_t stream) {
     jobs.job[i].tile0 = tiles;
     tiles += ((jobs.job[i].Cout + 31) / 32) * ((jobs.job[i].Cin + 31) / 32);
   }
-  wgrad_fold_kernel<<<tiles, 256, 0, stream>>>(jobs);
+  ACT_CUDA(launch_pdl(wgrad_fold_kernel, dim3(tiles), dim3(256), 0, stream, jobs));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }

@@ -161,6 +161,7 @@ int reparam_bwd(const float* dz, const float* eps, const float* logvar, const fl
 // as torch) so the backward is a gather.
 __global__ void maxpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, int N,
                                    int H, int W, int C, int Ho, int Wo) {
+  pdl_trigger(); pdl_wait();
   const int C8 = C / 8;
   const long long total = 1LL * N * Ho * Wo * C8;
   for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
@@ -210,7 +211,7 @@ int maxpool_fwd(const bf16* x, bf16* y, uint8_t* idx, int N, int H, int W, int C
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   const long long total = 1LL * N * Ho * Wo * (C / 8);
   const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
-  maxpool_fwd_kernel<<<blocks, 256, 0, st>>>(x, y, idx, N, H, W, C, Ho, Wo);
+  ACT_CUDA(launch_pdl(maxpool_fwd_kernel, dim3(blocks), dim3(256), 0, st, x, y, idx, N, H, W, C, Ho, Wo));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -218,6 +219,7 @@ int maxpool_fwd(const bf16* x, bf16* y, uint8_t* idx, int N, int H, int W, int C
 // dx[n,iy,ix,c] = (x > 0 ? 1 : 0) * sum over windows whose arg-max is (iy,ix) of dy   (ReLU of the conv1 block fused)
 __global__ void maxpool_bwd_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx, const bf16* __restrict__ x,
                                    bf16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo) {
+  pdl_trigger(); pdl_wait();
   const int C8 = C / 8;
   const long long total = 1LL * N * H * W * C8;
   for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
@@ -270,7 +272,7 @@ int maxpool_bwd(const bf16* dy, const uint8_t* idx, const bf16* x, bf16* dx, int
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   const long long total = 1LL * N * H * W * (C / 8);
   const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
-  maxpool_bwd_kernel<<<blocks, 256, 0, st>>>(dy, idx, x, dx, N, H, W, C, Ho, Wo);
+  ACT_CUDA(launch_pdl(maxpool_bwd_kernel, dim3(blocks), dim3(256), 0, st, dy, idx, x, dx, N, H, W, C, Ho, Wo));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -280,6 +282,7 @@ int maxpool_bwd(const bf16* dy, const uint8_t* idx, const bf16* x, bf16* dx, int
 // lands at out[b][y][x + 3][0..3] = {R, G, B, 0} (bf16), columns [0,3) and [W+3, Wp) are zero (horizontal padding).
 __global__ void stem_pack_image_kernel(const float* __restrict__ img, long long img_bs, bf16* __restrict__ out, int B,
                                        int H, int W, int Wp) {
+  pdl_trigger(); pdl_wait();
   const float mean[3] = {0.485f, 0.456f, 0.406f};
   const float istd[3] = {1.f / 0.229f, 1.f / 0.224f, 1.f / 0.225f};
   const long long total = 1LL * B * H * Wp;

@@ -9,6 +9,7 @@ namespace act {
 // Also refreshes the bf16 shadow used as tensor-core operand.  mode 1: gradient identically zero (dead decoder
 // layers) -> m, v stay 0 and only the decoupled decay touches p.
 __global__ void adamw_kernel(AdamWArgs a, float bc1, float rsqrt_bc2) {
+  pdl_trigger(); pdl_wait();
   const long long n4 = a.n / 4;
   const float decay = 1.f - a.lr * a.wd;
   const float step_size = a.lr / bc1;
@@ -60,7 +61,7 @@ int adamw_step(const AdamWArgs& a, cudaStream_t st) {
   const double bc2 = 1.0 - std::pow(static_cast<double>(a.beta2), a.step);
   const long long n4 = a.n / 4;
   const int blocks = static_cast<int>(std::max<long long>(1, std::min<long long>((n4 + 255) / 256, 148 * 8)));
-  adamw_kernel<<<blocks, 256, 0, st>>>(a, static_cast<float>(bc1), static_cast<float>(1.0 / std::sqrt(bc2)));
+  ACT_CUDA(launch_pdl(adamw_kernel, dim3(blocks), dim3(256), 0, st, a, static_cast<float>(bc1), static_cast<float>(1.0 / std::sqrt(bc2))));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }

@@ -54,6 +54,7 @@ int pack_conv_weights(const float* w, const float* scale, bf16* wpk, bf16* wpkt,
 // 32(ci) x KK tile: coalesced fp32 reads of w[co][ci0..ci0+32][*] into shared memory, then 64-byte bf16 runs along ci
 // (wpk) and along co (wpkt).
 __global__ void __launch_bounds__(256) pack_conv_batched_kernel(const __grid_constant__ PackJobs jobs) {
+  pdl_trigger(); pdl_wait();
   __shared__ float tile[32][32 * 9 + 1];
   int b = blockIdx.x, j = 0;
   while (j + 1 < jobs.n && b >= jobs.job[j + 1].tile0) ++j;
@@ -92,7 +93,7 @@ int pack_conv_batched(PackJobs& jobs, cudaStream_t st) {
     jobs.job[i].tile0 = tiles;
     tiles += ((jobs.job[i].Cout + 31) / 32) * ((jobs.job[i].Cin + 31) / 32);
   }
-  pack_conv_batched_kernel<<<tiles, 256, 0, st>>>(jobs);
+  ACT_CUDA(launch_pdl(pack_conv_batched_kernel, dim3(tiles), dim3(256), 0, st, jobs));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
