@@ -149,6 +149,10 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_
   return d;
 }
 
+// Note (measured, tools/debug_conv3.py): a K-major 128B-swizzled operand may start at any 128-byte row of a larger
+// swizzled tile with this same plain descriptor -- the swizzle XOR is taken from the absolute smem address bits, and
+// setting the PTX "matrix base offset" field for such starts gives wrong results on B200.
+
 // Instruction descriptor for kind::f16 with bf16 A/B and fp32 D:
 //   [4,6) D fmt (1 = f32) | [7,10) A fmt (1 = bf16) | [10,13) B fmt | bit15 A major (1 = MN) | bit16 B major
 //   [17,23) N >> 3 | [24,29) M >> 4

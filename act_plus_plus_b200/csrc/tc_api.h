@@ -84,6 +84,9 @@ struct ConvLaunch {
   EpiDesc epi;                          // ldc/ldr/osz*/rsz* ignored (geometry comes from og / rg)
 };
 int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint = 0, int stages_hint = 0);
+// dense 3x3 / stride-1 tap sets: halo patch resident in shared memory (conv3_kernel.cuh); ACT_CONV3=0 disables it
+bool tc_conv3_applicable(const ConvLaunch& c);
+int tc_conv3(const ConvLaunch& c, cudaStream_t stream, int bn_hint = 0);
 
 struct WgradLaunch {
   PlaneDesc planes[4];                  // activation planes (tap.map selects)

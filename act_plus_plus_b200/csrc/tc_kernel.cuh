@@ -51,6 +51,7 @@ struct TcParams {
   // conv geometry
   int ntaps, cin_blocks;       // k-block kb -> tap kb / cin_blocks, channel block kb % cin_blocks
   int BW, BH, BNI;             // A box = {64, BW, BH, BNI} pixels (BW*BH*BNI <= 128)
+  int PW;                      // conv3 (halo-resident) mode: patch row pitch = BW + 2
   int tiles_w, tiles_h;        // tiles per image plane; m-tile index -> (nt, ht, wt)
   int NIMG;                    // images (for masking)
   int vH, vW;                  // valid tile-space extent (rows >= vH / cols >= vW are masked)
@@ -137,6 +138,116 @@ __device__ __forceinline__ void ldg32(const float* __restrict__ ptr, float (&dst
   for (int j = 0; j < 32; j += 4) {
     const float4 t = __ldg(reinterpret_cast<const float4*>(ptr + j));
     dst[j] = t.x; dst[j + 1] = t.y; dst[j + 2] = t.z; dst[j + 3] = t.w;
+  }
+}
+
+// Fused epilogue of one 32-column accumulator chunk of one row: alpha, per-column scale / bias, fp32 / bf16 residual,
+// ReLU, ReLU-mask against a saved activation, fp32 / bf16 / atomic output.  o_off / r_off = element offsets of the row.
+__device__ __forceinline__ void epi_store_chunk(const TcParams& p, const uint32_t (&v)[32], int gn0, long long o_off,
+                                                long long r_off) {
+  float f[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
+  const bool full = p.vec_ok && (gn0 + 32 <= p.N);
+  if (p.flags & EPI_SCALE) {
+    if (full) {
+      float sc[32];
+      ldg32(p.scale + gn0, sc);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] *= sc[j];
+    } else {
+      for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] *= __ldg(p.scale + gn0 + j);
+    }
+  }
+  if (p.flags & EPI_BIAS) {
+    if (full) {
+      float bi[32];
+      ldg32(p.bias + gn0, bi);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] += bi[j];
+    } else {
+      for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += __ldg(p.bias + gn0 + j);
+    }
+  }
+  if (p.flags & EPI_RES_F32) {
+    const float* rp = p.res_f32 + r_off + gn0;
+    if (full) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        const float4 u = *reinterpret_cast<const float4*>(rp + j);
+        f[j] += u.x; f[j + 1] += u.y; f[j + 2] += u.z; f[j + 3] += u.w;
+      }
+    } else {
+      for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += rp[j];
+    }
+  }
+  if (p.flags & EPI_RES_BF16) {
+    const __nv_bfloat16* rp = p.res_bf16 + r_off + gn0;
+    if (full) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 8) {
+        const uint4 u = *reinterpret_cast<const uint4*>(rp + j);
+        const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { const float2 x = __bfloat1622float2(h2[e]); f[j + 2 * e] += x.x; f[j + 2 * e + 1] += x.y; }
+      }
+    } else {
+      for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += __bfloat162float(rp[j]);
+    }
+  }
+  if (p.flags & EPI_RELU) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+  }
+  if (p.flags & EPI_MASK_POS) {
+    const __nv_bfloat16* ap = p.aux_bf16 + o_off + gn0;
+    if (full) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 8) {
+        const uint4 u = *reinterpret_cast<const uint4*>(ap + j);
+        const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 x = __bfloat1622float2(h2[e]);
+          if (!(x.x > 0.f)) f[j + 2 * e] = 0.f;
+          if (!(x.y > 0.f)) f[j + 2 * e + 1] = 0.f;
+        }
+      }
+    } else {
+      for (int j = 0; j < 32; ++j) if (gn0 + j < p.N && !(__bfloat162float(ap[j]) > 0.f)) f[j] = 0.f;
+    }
+  }
+  if (p.flags & EPI_OUT_F32) {
+    float* op = p.out_f32 + o_off + gn0;
+    if (p.flags & EPI_ATOMIC) {
+      if (full) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) red_add_v4(op + j, f[j], f[j + 1], f[j + 2], f[j + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) atomicAdd(op + j, f[j]);
+      }
+    } else if (full) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+    } else {
+      for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) op[j] = f[j];
+    }
+  }
+  if (p.flags & EPI_OUT_BF16) {
+    __nv_bfloat16* op = p.out_bf16 + o_off + gn0;
+    if (full) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 8) {
+        uint4 u;
+        __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) h2[e] = __floats2bfloat162_rn(f[j + 2 * e], f[j + 2 * e + 1]);
+        *reinterpret_cast<uint4*>(op + j) = u;
+      }
+    } else {
+      for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) op[j] = __float2bfloat16_rn(f[j]);
+    }
   }
 }
 
@@ -330,110 +441,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
             if (gn0 + j < p.Cout) atomicAdd(op + static_cast<long long>(j) * p.Cin, __uint_as_float(v[j]) * p.alpha);
           continue;
         }
-        float f[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
-        const bool full = p.vec_ok && (gn0 + 32 <= p.N);
-        if (p.flags & EPI_SCALE) {
-          if (full) {
-            float sc[32];
-            ldg32(p.scale + gn0, sc);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] *= sc[j];
-          } else {
-            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] *= __ldg(p.scale + gn0 + j);
-          }
-        }
-        if (p.flags & EPI_BIAS) {
-          if (full) {
-            float bi[32];
-            ldg32(p.bias + gn0, bi);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] += bi[j];
-          } else {
-            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += __ldg(p.bias + gn0 + j);
-          }
-        }
-        if (p.flags & EPI_RES_F32) {
-          const float* rp = p.res_f32 + r_off + gn0;
-          if (full) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const float4 u = *reinterpret_cast<const float4*>(rp + j);
-              f[j] += u.x; f[j + 1] += u.y; f[j + 2] += u.z; f[j + 3] += u.w;
-            }
-          } else {
-            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += rp[j];
-          }
-        }
-        if (p.flags & EPI_RES_BF16) {
-          const __nv_bfloat16* rp = p.res_bf16 + r_off + gn0;
-          if (full) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              const uint4 u = *reinterpret_cast<const uint4*>(rp + j);
-              const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
-#pragma unroll
-              for (int e = 0; e < 4; ++e) { const float2 x = __bfloat1622float2(h2[e]); f[j + 2 * e] += x.x; f[j + 2 * e + 1] += x.y; }
-            }
-          } else {
-            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += __bfloat162float(rp[j]);
-          }
-        }
-        if (p.flags & EPI_RELU) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-        }
-        if (p.flags & EPI_MASK_POS) {
-          const __nv_bfloat16* ap = p.aux_bf16 + o_off + gn0;
-          if (full) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              const uint4 u = *reinterpret_cast<const uint4*>(ap + j);
-              const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float2 x = __bfloat1622float2(h2[e]);
-                if (!(x.x > 0.f)) f[j + 2 * e] = 0.f;
-                if (!(x.y > 0.f)) f[j + 2 * e + 1] = 0.f;
-              }
-            }
-          } else {
-            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N && !(__bfloat162float(ap[j]) > 0.f)) f[j] = 0.f;
-          }
-        }
-        if (p.flags & EPI_OUT_F32) {
-          float* op = p.out_f32 + o_off + gn0;
-          if (p.flags & EPI_ATOMIC) {
-            if (full) {
-#pragma unroll
-              for (int j = 0; j < 32; j += 4) red_add_v4(op + j, f[j], f[j + 1], f[j + 2], f[j + 3]);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) atomicAdd(op + j, f[j]);
-            }
-          } else if (full) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
-          } else {
-            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) op[j] = f[j];
-          }
-        }
-        if (p.flags & EPI_OUT_BF16) {
-          __nv_bfloat16* op = p.out_bf16 + o_off + gn0;
-          if (full) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              uint4 u;
-              __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&u);
-#pragma unroll
-              for (int e = 0; e < 4; ++e) h2[e] = __floats2bfloat162_rn(f[j + 2 * e], f[j + 2 * e + 1]);
-              *reinterpret_cast<uint4*>(op + j) = u;
-            }
-          } else {
-            for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) op[j] = __float2bfloat16_rn(f[j]);
-          }
-        }
+        epi_store_chunk(p, v, gn0, o_off, r_off);
       }
     }
   }

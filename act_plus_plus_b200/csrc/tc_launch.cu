@@ -1,6 +1,7 @@
 // Host launchers for tc_kernel: tensor-map construction (driver entry point fetched at run time so the
 // library loads on machines without libcuda), tile selection, launch.
 #include "tc_api.h"
+#include "conv3_kernel.cuh"
 #include <mutex>
 #include <cstring>
 #include <algorithm>
@@ -294,6 +295,7 @@ static void pick_tile(int vW, int vH, int nimg, int mult, int max_ni, int* BW, i
 
 // --------------------------------------------------------------------------------------------- CONV
 int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint, int stages_hint) {
+  if (tc_conv3_applicable(c)) return tc_conv3(c, stream, bn_hint);
   ACT_CHECK(c.Cin % 64 == 0 && c.Cin >= 64, "Cin must be a multiple of 64");
   ACT_CHECK(c.ntaps >= 1 && c.ntaps <= 16 && c.nplanes >= 1 && c.nplanes <= 4, "bad tap table");
   if (check_epi(c.epi)) return -1;
@@ -326,6 +328,90 @@ int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint, int stages_hi
   if (bn == 64) return launch_inst<MODE_CONV, 0, 0, 64>(grid, st, stream, am, bm, p);
   if (bn == 128) return launch_inst<MODE_CONV, 0, 0, 128>(grid, st, stream, am, bm, p);
   return launch_inst<MODE_CONV, 0, 0, 256>(grid, st, stream, am, bm, p);
+}
+
+// --------------------------------------------------------------------------------------------- CONV3 (halo-resident)
+template <int BN>
+static int launch_conv3(long long total, cudaStream_t stream, const CUtensorMap& am, const CUtensorMap& bm, const TcParams& p) {
+  using Cfg = Conv3Cfg<BN>;
+  auto kern = conv3_kernel<BN>;
+  static bool configured = false;
+  if (!configured) {
+    ACT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    configured = true;
+  }
+  const unsigned ctas = static_cast<unsigned>(std::min<long long>(total, num_sms()));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
+  ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(192), static_cast<size_t>(Cfg::SMEM), stream, am, bm, p));
+  if (g_prof.on) { cudaEventRecord(e1, stream); g_prof.ev.push_back(e0); g_prof.ev.push_back(e1); g_prof.flops.push_back(g_next_flops); g_prof.label.push_back(g_next_label); }
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+bool tc_conv3_applicable(const ConvLaunch& c) {
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("ACT_CONV3"); on = (e && e[0] == '0') ? 0 : 1; }
+  if (!on || c.nplanes != 1 || c.ntaps < 1 || c.ntaps > 9 || c.Cin % 64 || c.Cout % 64) return false;
+  for (int i = 0; i < c.ntaps; ++i)
+    if (c.taps[i].map != 0 || c.taps[i].dh < -1 || c.taps[i].dh > 1 || c.taps[i].dw < -1 || c.taps[i].dw > 1) return false;
+  if (c.ntaps < 4) return false;                       // 1x1 / sparse tap sets gain nothing from the resident patch
+  const PlaneDesc& pl = c.planes[0];
+  return pl.W == c.vW && pl.H == c.vH && pl.N == c.NIMG;
+}
+
+int tc_conv3(const ConvLaunch& c, cudaStream_t stream, int bn_hint) {
+  ACT_CHECK(tc_conv3_applicable(c), "tc_conv3: not a dense 3x3 / stride-1 tap set");
+  if (check_epi(c.epi)) return -1;
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  // tile geometry: BH x BW outputs per 128-row accumulator, patch pitch PW = BW + 2 (<= 46 so every tap window fits)
+  double best = -1;
+  int BW = 1, BH = 1;
+  for (int bw = 2; bw <= std::min(c.vW, 44); ++bw) {
+    const int pw = bw + 2;
+    int bh = std::min(c.vH, 128 / pw);
+    while (bh > 1 && (bh + 2) * pw > 222) --bh;
+    if (bh < 1 || (bh + 2) * pw > 222) continue;
+    const long long tiles = 1LL * ((c.vW + bw - 1) / bw) * ((c.vH + bh - 1) / bh);
+    const double util = double(c.vW) * c.vH / (double(tiles) * 128.0) + 1e-4 * bw;
+    if (util > best) { best = util; BW = bw; BH = bh; }
+  }
+  p.BW = BW; p.BH = BH; p.PW = BW + 2; p.BNI = 1;
+  p.tiles_w = (c.vW + BW - 1) / BW; p.tiles_h = (c.vH + BH - 1) / BH;
+  p.NIMG = c.NIMG; p.vH = c.vH; p.vW = c.vW; p.og = c.og; p.rg = c.rg;
+  p.ntaps = c.ntaps; p.cin_blocks = c.Cin / 64; p.N = c.Cout; p.nz0 = 1; p.ksplit = 1;
+  for (int i = 0; i < c.ntaps; ++i) p.taps[i] = c.taps[i];
+  fill_epi(p, c.epi);
+  p.vec_ok = (c.og.ld % 8 == 0) && (c.rg.ld % 8 == 0 || !(c.epi.flags & (EPI_RES_F32 | EPI_RES_BF16))) &&
+             aligned16(c.epi.out_f32) && aligned16(c.epi.out_bf16) && aligned16(c.epi.res_f32) &&
+             aligned16(c.epi.res_bf16) && aligned16(c.epi.aux_bf16);
+  { static int dbg = -1; if (dbg < 0) { const char* e = getenv("ACT_TC_DEBUG"); dbg = e ? atoi(e) : 0; } p.debug = dbg; }
+  const long long mtiles = 1LL * p.tiles_w * p.tiles_h * c.NIMG;
+  int bn = bn_hint;
+  if (bn == 0) {
+    double bc = 1e30;
+    const int cands[3] = {64, 128, 256};
+    for (int cc : cands) {
+      if (c.Cout % cc) continue;
+      const long long tiles = mtiles * (c.Cout / cc);
+      const long long rounds = (tiles + num_sms() - 1) / num_sms();
+      const double cost = rounds * (p.cin_blocks * c.ntaps * 4 * (cc == 256 ? 75.0 : 56.0) + 1000.0 + 6.0 * cc);
+      if (cost <= bc * 1.0001) { bc = std::min(bc, cost); bn = cc; }
+    }
+  }
+  ACT_CHECK(bn == 64 || bn == 128 || bn == 256, "bn must be 64/128/256");
+  ACT_CHECK(c.Cout % bn == 0, "tc_conv3: Cout must be a multiple of the tile width");
+  p.gx = c.Cout / bn; p.gy = static_cast<int>(mtiles); p.gz = 1;
+  CUtensorMap am, bm;
+  if (plane_tmap(&am, c.planes[0], p.PW, BH + 2, 1)) return -1;
+  if (make_tmap_2d(&bm, c.wgt, c.wgt_ld, c.Cout, c.wgt_ld, bn)) return -1;
+  g_next_flops = 2.0 * c.vW * c.vH * c.NIMG * c.Cout * c.Cin * c.ntaps;
+  if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "conv3 %dx%dx%d Cin=%d Cout=%d taps=%d tile=%dx%d bn=%d grid=%dx%d", c.NIMG, c.vH, c.vW, c.Cin, c.Cout, c.ntaps, BH, BW, bn, p.gx, p.gy); g_next_label = buf; }
+  const long long total = 1LL * p.gx * p.gy;
+  if (bn == 64) return launch_conv3<64>(total, stream, am, bm, p);
+  if (bn == 128) return launch_conv3<128>(total, stream, am, bm, p);
+  return launch_conv3<256>(total, stream, am, bm, p);
 }
 
 // --------------------------------------------------------------------------------------------- WGRAD
