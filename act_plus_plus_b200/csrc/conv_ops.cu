@@ -122,7 +122,38 @@ int conv_wgrad_reserve(long long elems) {
   return 0;
 }
 
-// block = 32(co) x 32(ci) x KK tile of one job: T rows along ci read coalesced, dW written in contiguous ci*KK runs
+// block = 32(co) x 32(ci) x KK tile of one job: T rows along ci read coalesced, dW written in contiguous ci*KK runs.
+// KK is a template constant (0 = runtime value) so the index arithmetic is shifts and constant multiplies: with a
+// runtime divisor the kernel was instruction-bound (68 us for 11 M weights), not bandwidth-bound.
+template <int KKT>
+__device__ __forceinline__ void wgrad_fold_body(const FoldJob& jb, int b, float (*tile)[32 * 9 + 1]) {
+  const int Cout = jb.Cout, Cin = jb.Cin, KK = KKT ? KKT : jb.KK;
+  const int ci_tiles = (Cin + 31) / 32;
+  const int co0 = (b / ci_tiles) * 32, ci0 = (b % ci_tiles) * 32;
+  const int run = 32 * KK;
+  const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+  const bool ci_ok = ci0 + lane < Cin;
+  for (int t = 0; t < KK; ++t) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int co = wrp + 8 * c;
+      float v = 0.f;
+      if (ci_ok && co0 + co < Cout) v = __ldg(jb.T + (1LL * t * Cout + co0 + co) * Cin + ci0 + lane);
+      tile[co][lane * KK + t] = v;
+    }
+  }
+  __syncthreads();
+  const int valid = min(32, Cin - ci0) * KK;                  // floats of a co row that exist in dW
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const int co = wrp + 8 * c;
+    if (co0 + co >= Cout) continue;
+    const float a = jb.alpha * (jb.scale ? jb.scale[co0 + co] : 1.f);
+    float* drow = jb.dw + (1LL * (co0 + co) * Cin + ci0) * KK;
+    for (int o = lane; o < run; o += 32)
+      if (o < valid) drow[o] += a * tile[co][o];
+  }
+}
 __global__ void __launch_bounds__(256) wgrad_fold_kernel(const __grid_constant__ FoldJobs jobs) {
   pdl_trigger(); pdl_wait();
   __shared__ float tile[32][32 * 9 + 1];
@@ -130,22 +161,9 @@ __global__ void __launch_bounds__(256) wgrad_fold_kernel(const __grid_constant__
   while (j + 1 < jobs.n && b >= jobs.job[j + 1].tile0) ++j;
   const FoldJob& jb = jobs.job[j];
   b -= jb.tile0;
-  const int Cout = jb.Cout, Cin = jb.Cin, KK = jb.KK;
-  const int ci_tiles = (Cin + 31) / 32;
-  const int co0 = (b / ci_tiles) * 32, ci0 = (b % ci_tiles) * 32;
-  const int run = 32 * KK;
-  for (int idx = threadIdx.x; idx < 32 * run; idx += 256) {
-    const int ci = idx % 32, co = (idx / 32) % 32, t = idx / 1024;
-    float v = 0.f;
-    if (co0 + co < Cout && ci0 + ci < Cin) v = __ldg(jb.T + (1LL * t * Cout + co0 + co) * Cin + ci0 + ci);
-    tile[co][ci * KK + t] = v;
-  }
-  __syncthreads();
-  for (int idx = threadIdx.x; idx < 32 * run; idx += 256) {
-    const int co = idx / run, o = idx % run;
-    if (co0 + co < Cout && ci0 + o / KK < Cin)
-      jb.dw[(1LL * (co0 + co) * Cin + ci0) * KK + o] += jb.alpha * (jb.scale ? jb.scale[co0 + co] : 1.f) * tile[co][o];
-  }
+  if (jb.KK == 9) wgrad_fold_body<9>(jb, b, tile);
+  else if (jb.KK == 1) wgrad_fold_body<1>(jb, b, tile);
+  else wgrad_fold_body<0>(jb, b, tile);
 }
 int wgrad_fold_batched(FoldJobs& jobs, cudaStream_t stream) {
   ACT_CHECK(jobs.n >= 1 && jobs.n <= FoldJobs::MAX, "wgrad_fold_batched: 1..64 jobs");

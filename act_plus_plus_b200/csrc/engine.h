@@ -85,7 +85,7 @@ class Engine {
   int forward(int B, const float* qpos, const float* image, const float* actions, long long actions_bs,
               const uint8_t* is_pad, long long is_pad_bs, const float* eps, float* a_hat, float* is_pad_hat, float* mu,
               float* logvar, float* losses, cudaStream_t st);
-  int backward(int stage, float loss_grad, cudaStream_t st);      // stage: 0 = all, 1 = transformer, 2 = cvae, 3 = backbone
+  int backward(int stage, float loss_grad, cudaStream_t st);      // stage: 0 = all, 1 = transformer, 2 = cvae, 3 = backbone, 4 = cvae || backbone
   int zero_grad(cudaStream_t st);
   int adamw(int step, cudaStream_t st);
   const EngineConfig& cfg() const { return cfg_; }
@@ -140,6 +140,13 @@ class Engine {
   std::vector<void*> allocs_;
   long long ws_bytes_ = 0;
   int launches_ = 0;
+  // Independent sub-graphs (CVAE encoder vs. camera backbones, forward and backward) run on a side stream forked from /
+  // joined into the caller's stream with events; under stream capture this becomes two parallel branches of the graph.
+  cudaStream_t side_ = nullptr;
+  cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;
+  bool concurrent_ = true;                      // ACT_CONCURRENT=0 serialises everything on the caller's stream
+  int fork_side(cudaStream_t st);               // side_ waits for everything enqueued on st so far
+  int join_side(cudaStream_t st);               // st waits for everything enqueued on side_ so far
 
   // geometry
   int Hf_ = 0, Wf_ = 0, L_ = 0, Lp_ = 0, Lc_ = 0, Lcp_ = 0, nqp_ = 0;

@@ -364,11 +364,20 @@ int Engine::backward(int stage, float loss_grad, cudaStream_t st) {
   ACT_CHECK(cfg_.train && grads_ != nullptr, "engine has no training workspace / gradient buffer");
   ACT_CHECK(have_actions_ && cur_B_ > 0, "backward needs a preceding training forward (with actions)");
   if (stage == 0 || stage == 1) { if (transformer_bwd(loss_grad, st)) return -1; }
-  if (stage == 0 || stage == 2) { if (cvae_bwd(st)) return -1; }
-  if (stage == 0 || stage == 3) {
+  // After the transformer the CVAE-encoder branch (needs dz) and the backbone branch (needs d_feat) share no buffers:
+  // stage 0 / 4 run them as two parallel branches (side stream), stages 2 and 3 one at a time on the caller's stream.
+  const bool both = stage == 0 || stage == 4;
+  cudaStream_t sc = st;
+  if (both) {
+    if (fork_side(st)) return -1;
+    if (concurrent_) sc = side_;
+  }
+  if (both || stage == 2) { if (cvae_bwd(sc)) return -1; }
+  if (both || stage == 3) {
     for (int k = 0; k < cfg_.num_cameras; ++k)
       if (backbone_bwd(k, cur_B_, st)) return -1;
   }
+  if (sc != st && join_side(st)) return -1;
   return 0;
 }
 

@@ -392,9 +392,14 @@ int Engine::forward(int B, const float* qpos, const float* image, const float* a
   cur_B_ = B; have_actions_ = actions != nullptr;
   in_qpos_ = qpos; in_image_ = image; in_actions_ = actions; in_actions_bs_ = actions_bs; in_is_pad_ = is_pad; in_is_pad_bs_ = is_pad_bs;
   ACT_CUDA(cudaMemcpyAsync(pos_main_, P("additional_pos_embed.weight"), sizeof(float) * 2 * d, cudaMemcpyDeviceToDevice, st));
+  // The CVAE encoder (-> z -> latent token) and the camera backbones (-> image tokens) are independent until the main
+  // encoder reads src_: the CVAE branch runs on the side stream so its small launches fill the SMs the convs leave idle.
+  cudaStream_t sc = st;
   if (have_actions_) {
     ACT_CHECK(is_pad && eps, "training call needs is_pad and eps");
-    if (cvae_fwd(B, qpos, actions, actions_bs, is_pad, is_pad_bs, eps, st)) return -1;
+    if (fork_side(st)) return -1;
+    if (concurrent_) sc = side_;
+    if (cvae_fwd(B, qpos, actions, actions_bs, is_pad, is_pad_bs, eps, sc)) return -1;
   } else {
     ACT_CUDA(cudaMemsetAsync(z_, 0, sizeof(float) * B * Z, st));             // latent_sample = 0 (detr_vae.py:157)
   }
@@ -402,13 +407,14 @@ int Engine::forward(int B, const float* qpos, const float* image, const float* a
   g.I = B; g.J = d; g.R = Z; g.A = z_; g.ai = act::lin(Z); g.ar = act::lin(1);
   g.B = P("latent_out_proj.weight"); g.br = act::lin(1); g.bj = act::lin(Z); g.bias = P("latent_out_proj.bias");
   g.C = src_; g.ci = act::lin(1LL * L_ * d); g.cj = act::lin(1);
-  RUN(sgemm_generic(g, st));
+  RUN(sgemm_generic(g, sc));
   g = SgemmArgs(); g.I = B; g.J = d; g.R = S; g.A = qpos; g.ai = act::lin(S); g.ar = act::lin(1);
   g.B = P("input_proj_robot_state.weight"); g.br = act::lin(1); g.bj = act::lin(S); g.bias = P("input_proj_robot_state.bias");
   g.C = src_ + d; g.ci = act::lin(1LL * L_ * d); g.cj = act::lin(1);
   RUN(sgemm_generic(g, st));
   for (int k = 0; k < cfg_.num_cameras; ++k)
     if (backbone_fwd(k, B, image, st)) return -1;
+  if (sc != st && join_side(st)) return -1;
   RUN(add_pos_cast(src_, pos_main_, L_, enc_a_[0].xb, enc_a_[0].xpb, B * L_, d, st));
   const int nl = cfg_.enc_layers;
   for (int l = 0; l < nl; ++l) {

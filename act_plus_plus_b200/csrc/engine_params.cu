@@ -9,6 +9,27 @@ Engine::Engine(const EngineConfig& cfg) : cfg_(cfg) {}
 
 Engine::~Engine() {
   for (void* p : allocs_) cudaFree(p);
+  if (ev_fork_) cudaEventDestroy(ev_fork_);
+  if (ev_join_) cudaEventDestroy(ev_join_);
+  if (side_) cudaStreamDestroy(side_);
+}
+
+int Engine::fork_side(cudaStream_t st) {
+  if (!side_) {
+    const char* env = getenv("ACT_CONCURRENT");
+    concurrent_ = !(env && env[0] == '0');
+    ACT_CUDA(cudaStreamCreateWithFlags(&side_, cudaStreamNonBlocking));
+    ACT_CUDA(cudaEventCreateWithFlags(&ev_fork_, cudaEventDisableTiming));
+    ACT_CUDA(cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming));
+  }
+  ACT_CUDA(cudaEventRecord(ev_fork_, st));
+  ACT_CUDA(cudaStreamWaitEvent(side_, ev_fork_, 0));
+  return 0;
+}
+int Engine::join_side(cudaStream_t st) {
+  ACT_CUDA(cudaEventRecord(ev_join_, side_));
+  ACT_CUDA(cudaStreamWaitEvent(st, ev_join_, 0));
+  return 0;
 }
 
 template <typename T>

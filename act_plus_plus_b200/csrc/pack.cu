@@ -52,7 +52,46 @@ int pack_conv_weights(const float* w, const float* scale, bf16* wpk, bf16* wpkt,
 
 // Batched re-pack of every conv of a backbone in ONE launch (runs after each AdamW step).  A block owns a 32(co) x
 // 32(ci) x KK tile: coalesced fp32 reads of w[co][ci0..ci0+32][*] into shared memory, then 64-byte bf16 runs along ci
-// (wpk) and along co (wpkt).
+// (wpk) and along co (wpkt).  KK is a template constant: with a runtime divisor in the index arithmetic this kernel was
+// instruction-bound (110 us for 11 M weights).
+template <int KK>
+__device__ __forceinline__ void pack_conv_body(const PackJob& jb, int b, float (*tile)[32 * 9 + 1]) {
+  const int ci_tiles = (jb.Cin + 31) / 32;
+  const int co0 = (b / ci_tiles) * 32, ci0 = (b % ci_tiles) * 32;
+  constexpr int run = 32 * KK;                               // floats per co row of the tile (contiguous in w)
+  const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+  const int valid = min(32, jb.Cin - ci0) * KK;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const int co = wrp + 8 * c;
+    const bool ok = co0 + co < jb.Cout;
+    const float* wrow = jb.w + (1LL * (co0 + co) * jb.Cin + ci0) * KK;
+#pragma unroll
+    for (int o = lane; o < run; o += 32) tile[co][o] = (ok && o < valid) ? __ldg(wrow + o) : 0.f;
+  }
+  __syncthreads();
+  const bool ci_ok = ci0 + lane < jb.Cin;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {                              // wpk[co][t*Cin + ci]: ci = lane fastest
+    const int co = wrp + 8 * c;
+    if (co0 + co >= jb.Cout || !ci_ok) continue;
+    bf16* orow = jb.wpk + (1LL * (co0 + co) * KK) * jb.Cin + ci0 + lane;
+#pragma unroll
+    for (int t = 0; t < KK; ++t) orow[1LL * t * jb.Cin] = __float2bfloat16_rn(tile[co][lane * KK + t]);
+  }
+  if (jb.wpkt) {                                             // wpkt[ci][t*Cout + co]: co = lane fastest
+    const bool co_ok = co0 + lane < jb.Cout;
+    const float sc = (jb.scale && co_ok) ? jb.scale[co0 + lane] : 1.f;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int ci = wrp + 8 * c;
+      if (ci0 + ci >= jb.Cin || !co_ok) continue;
+      bf16* orow = jb.wpkt + (1LL * (ci0 + ci) * KK) * jb.Cout + co0 + lane;
+#pragma unroll
+      for (int t = 0; t < KK; ++t) orow[1LL * t * jb.Cout] = __float2bfloat16_rn(tile[lane][ci * KK + t] * sc);
+    }
+  }
+}
 __global__ void __launch_bounds__(256) pack_conv_batched_kernel(const __grid_constant__ PackJobs jobs) {
   pdl_trigger(); pdl_wait();
   __shared__ float tile[32][32 * 9 + 1];
@@ -60,30 +99,8 @@ __global__ void __launch_bounds__(256) pack_conv_batched_kernel(const __grid_con
   while (j + 1 < jobs.n && b >= jobs.job[j + 1].tile0) ++j;
   const PackJob& jb = jobs.job[j];
   b -= jb.tile0;
-  const int ci_tiles = (jb.Cin + 31) / 32;
-  const int co0 = (b / ci_tiles) * 32, ci0 = (b % ci_tiles) * 32;
-  const int KK = jb.KK, run = 32 * KK;                      // floats per co row of the tile (contiguous in w)
-  for (int idx = threadIdx.x; idx < 32 * run; idx += 256) {
-    const int co = idx / run, o = idx % run;
-    float v = 0.f;
-    if (co0 + co < jb.Cout && ci0 + o / KK < jb.Cin) v = jb.w[(1LL * (co0 + co) * jb.Cin + ci0) * KK + o];
-    tile[co][o] = v;
-  }
-  __syncthreads();
-  for (int idx = threadIdx.x; idx < 32 * run; idx += 256) {  // wpk[co][t*Cin + ci]: ci fastest
-    const int ci = idx % 32, t = (idx / 32) % KK, co = idx / (32 * KK);
-    if (co0 + co < jb.Cout && ci0 + ci < jb.Cin)
-      jb.wpk[(1LL * (co0 + co) * KK + t) * jb.Cin + ci0 + ci] = __float2bfloat16_rn(tile[co][ci * KK + t]);
-  }
-  if (jb.wpkt) {
-    for (int idx = threadIdx.x; idx < 32 * run; idx += 256) {  // wpkt[ci][t*Cout + co]: co fastest
-      const int co = idx % 32, t = (idx / 32) % KK, ci = idx / (32 * KK);
-      if (co0 + co < jb.Cout && ci0 + ci < jb.Cin) {
-        const float sc = jb.scale ? jb.scale[co0 + co] : 1.f;
-        jb.wpkt[(1LL * (ci0 + ci) * KK + t) * jb.Cout + co0 + co] = __float2bfloat16_rn(tile[co][ci * KK + t] * sc);
-      }
-    }
-  }
+  if (jb.KK == 9) pack_conv_body<9>(jb, b, tile);
+  else pack_conv_body<1>(jb, b, tile);
 }
 int pack_conv_batched(PackJobs& jobs, cudaStream_t st) {
   ACT_CHECK(jobs.n >= 1 && jobs.n <= PackJobs::MAX, "pack_conv_batched: 1..64 jobs");

@@ -2,6 +2,8 @@
 (batch sharded across ranks, gradients averaged with NCCL over NVLink while later backward stages still run)."""
 from __future__ import annotations
 
+import os
+
 import torch
 
 from .dp import GradReducer
@@ -13,10 +15,15 @@ def backward_data_parallel(eng: ActEngine, group, loss_grad: float = 1.0, bucket
     its own stream, ordered after the compute stream at enqueue time), so the transfer of the transformer gradients
     overlaps the CVAE-encoder and backbone backward.  Regions are contiguous slices of the flat gradient buffer."""
     red = GradReducer(eng.flat_grads, group, bucket_elems)
-    for stage, region in ((1, R_MAIN), (2, R_CVAE), (3, R_BACKBONE)):
+    # stage 4 = CVAE-encoder and backbone backward as two concurrent branches (ACT_DP_STAGES=123 keeps them serial,
+    # which starts the CVAE region's all-reduce earlier at the price of the lost overlap)
+    plan = (((1, (R_MAIN,)), (2, (R_CVAE,)), (3, (R_BACKBONE,))) if os.environ.get("ACT_DP_STAGES", "14") == "123"
+            else ((1, (R_MAIN,)), (4, (R_CVAE, R_BACKBONE))))
+    for stage, regions in plan:
         eng.backward(stage, loss_grad)
-        off, n = eng.region(region)
-        red.reduce(off, n)
+        for region in regions:
+            off, n = eng.region(region)
+            red.reduce(off, n)
     red.wait()
 
 

@@ -144,7 +144,8 @@ int act_engine_forward(act_engine* e, int B, const float* qpos, const float* ima
                        int64_t actions_bs, const uint8_t* is_pad, int64_t is_pad_bs, const float* eps, float* a_hat,
                        float* is_pad_hat, float* mu, float* logvar, float* losses, void* stream);
 /* gradients of loss_grad * loss into the bound gradient buffer.  stage 0 = everything; 1 = heads + transformer,
- * 2 = CVAE encoder, 3 = backbones (run 1,2,3 in order to overlap the gradient all-reduce of finished regions). */
+ * 2 = CVAE encoder, 3 = backbones, 4 = 2 and 3 as two concurrent branches (an internal side stream forked from and
+ * joined into `stream`).  Run 1 then 4 (or 1,2,3) to overlap the gradient all-reduce of finished regions. */
 int act_engine_backward(act_engine* e, int stage, float loss_grad, void* stream);
 int act_engine_zero_grad(act_engine* e, void* stream);
 int act_engine_adamw_step(act_engine* e, int step, void* stream);
