@@ -147,6 +147,19 @@ class Engine {
   bool concurrent_ = true;                      // ACT_CONCURRENT=0 serialises everything on the caller's stream
   int fork_side(cudaStream_t st);               // side_ waits for everything enqueued on st so far
   int join_side(cudaStream_t st);               // st waits for everything enqueued on side_ so far
+  // Weight/bias gradients are leaves of the backward graph (nothing reads them before the optimiser), so they are
+  // issued on a per-branch weight-gradient stream that trails the dX chain and fills the SMs its small grids leave idle.
+  // Their dY operands come from a bump arena (gy_alloc) instead of reused scratch, so the dX chain never has to wait
+  // for a weight-gradient read before overwriting a buffer.
+  cudaStream_t wg_[2] = {nullptr, nullptr};     // [0] trails the caller's stream, [1] trails side_
+  cudaEvent_t wg_ev_[2] = {nullptr, nullptr}, wg_done_[2] = {nullptr, nullptr};
+  bool wg_used_[2] = {false, false};
+  int ensure_streams();
+  cudaStream_t wg_fork(cudaStream_t st);        // returns the stream to launch the weight gradient on (st if serial)
+  int wg_join(cudaStream_t st);                 // st waits for every weight-gradient launch issued so far
+  bf16* gy_arena_ = nullptr;
+  long long gy_cap_ = 0, gy_off_ = 0, gy_lim_ = 0, gy_cvae_base_ = 0;
+  bf16* gy_alloc(long long elems);
 
   // geometry
   int Hf_ = 0, Wf_ = 0, L_ = 0, Lp_ = 0, Lc_ = 0, Lcp_ = 0, nqp_ = 0;

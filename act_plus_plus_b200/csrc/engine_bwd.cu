@@ -71,8 +71,9 @@ int Engine::linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cuda
   int bn = 64, ks = 1;
   plan_splitk(w.N, w.K, M, &bn, &ks);
   ++launches_;
-  if (tc_gemm(w.N, w.K, M, 1, 1, A, B, e, ks, st, bn)) return -1;
-  if (w.gb) RUN(colsum_bf16(dY, w.N, M, w.N, w.gb, st));
+  cudaStream_t wg = wg_fork(st);                       // dY (from the arena) is final on st at this point
+  if (tc_gemm(w.N, w.K, M, 1, 1, A, B, e, ks, wg, bn)) return -1;
+  if (w.gb) RUN(colsum_bf16(dY, w.N, M, w.N, w.gb, wg));
   return 0;
 }
 
@@ -122,20 +123,23 @@ int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K
 int Engine::enc_layer_bwd(const EncW& w, EncActs& a, const float* x_in, const float* dx2, const float* dx2b, float* dx_out,
                           float* gxp_out, int L, int B, cudaStream_t st) {
   (void)x_in;
-  const int M = B * L, d = cfg_.hidden_dim;
-  RUN(ln_bwd(dx2, dx2b, a.t2, a.mean2, a.rstd2, w.n2.g, gA_, gb1_, w.n2.gg, w.n2.gb, M, d, st));
-  if (linear_dwb(gb1_, M, w.l2, a.hh, st)) return -1;
-  if (linear_dx(gb1_, M, w.l2, 0, nullptr, a.hh, nullptr, gbhh_, st)) return -1;
-  if (linear_dwb(gbhh_, M, w.l1, a.x1b, st)) return -1;
-  if (linear_dx(gbhh_, M, w.l1, 0, gA_, nullptr, gB_, nullptr, st)) return -1;
-  RUN(ln_bwd(gB_, nullptr, a.t1, a.mean1, a.rstd1, w.n1.g, gA_, gb1_, w.n1.gg, w.n1.gb, M, d, st));
-  if (linear_dwb(gb1_, M, w.sa.o, a.o, st)) return -1;
-  if (linear_dx(gb1_, M, w.sa.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
-  if (attn_bwd(gb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gbqk_, 2 * d, gbqk_ + d, 2 * d, gbv_, d, B, L, L, st)) return -1;
-  if (linear_dwb(gbqk_, M, w.sa.qk, a.xpb, st)) return -1;
-  if (linear_dwb(gbv_, M, w.sa.v, a.xb, st)) return -1;
-  if (linear_dx(gbqk_, M, w.sa.qk, 0, nullptr, nullptr, gxp_out, nullptr, st)) return -1;
-  if (linear_dx(gbv_, M, w.sa.v, 0, gA_, nullptr, dx_out, nullptr, st)) return -1;
+  const int M = B * L, d = cfg_.hidden_dim, ff = cfg_.dim_ff;
+  bf16 *g1 = gy_alloc(1LL * M * d), *ghh = gy_alloc(1LL * M * ff), *g1b = gy_alloc(1LL * M * d);
+  bf16 *gqk = gy_alloc(2LL * M * d), *gv = gy_alloc(1LL * M * d);
+  if (!g1 || !ghh || !g1b || !gqk || !gv) return -1;
+  RUN(ln_bwd(dx2, dx2b, a.t2, a.mean2, a.rstd2, w.n2.g, gA_, g1, w.n2.gg, w.n2.gb, M, d, st));
+  if (linear_dwb(g1, M, w.l2, a.hh, st)) return -1;
+  if (linear_dx(g1, M, w.l2, 0, nullptr, a.hh, nullptr, ghh, st)) return -1;
+  if (linear_dwb(ghh, M, w.l1, a.x1b, st)) return -1;
+  if (linear_dx(ghh, M, w.l1, 0, gA_, nullptr, gB_, nullptr, st)) return -1;
+  RUN(ln_bwd(gB_, nullptr, a.t1, a.mean1, a.rstd1, w.n1.g, gA_, g1b, w.n1.gg, w.n1.gb, M, d, st));
+  if (linear_dwb(g1b, M, w.sa.o, a.o, st)) return -1;
+  if (linear_dx(g1b, M, w.sa.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
+  if (attn_bwd(gb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gqk, 2 * d, gqk + d, 2 * d, gv, d, B, L, L, st)) return -1;
+  if (linear_dwb(gqk, M, w.sa.qk, a.xpb, st)) return -1;
+  if (linear_dwb(gv, M, w.sa.v, a.xb, st)) return -1;
+  if (linear_dx(gqk, M, w.sa.qk, 0, nullptr, nullptr, gxp_out, nullptr, st)) return -1;
+  if (linear_dx(gv, M, w.sa.v, 0, gA_, nullptr, dx_out, nullptr, st)) return -1;
   return 0;
 }
 
@@ -159,24 +163,30 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
   g = SgemmArgs(); g.I = Md; g.J = d; g.R = A; g.A = d_a_hat_; g.ai = act::lin(A); g.ar = act::lin(1);
   g.B = P("action_head.weight"); g.br = act::lin(d); g.bj = act::lin(1); g.C = d_hs_; g.ci = act::lin(d); g.cj = act::lin(1);
   RUN(sgemm_generic(g, st));
-  // shared final norm, norm3, FFN
+  // shared final norm, norm3, FFN  (every dY that a deferred weight gradient reads lives in the arena)
+  gy_off_ = 0; gy_lim_ = gy_cvae_base_;
+  const int ff = cfg_.dim_ff;
+  bf16 *g3 = gy_alloc(1LL * Md * d), *ghh = gy_alloc(1LL * Md * ff), *g2 = gy_alloc(1LL * Md * d), *gq = gy_alloc(1LL * Md * d);
+  bf16 *gk = gy_alloc(1LL * Me * d), *gcv = gy_alloc(1LL * Me * d), *g1 = gy_alloc(1LL * Md * d), *gqk = gy_alloc(2LL * Md * d);
+  bf16 *gv = gy_alloc(1LL * Md * d);
+  if (!g3 || !ghh || !g2 || !gq || !gk || !gcv || !g1 || !gqk || !gv) return -1;
   RUN(ln_bwd(d_hs_, nullptr, a.y3, hs_mean_, hs_rstd_, dec_norm_.g, gA_, nullptr, dec_norm_.gg, dec_norm_.gb, Md, d, st));
-  RUN(ln_bwd(gA_, nullptr, a.t3, a.mean3, a.rstd3, w.n3.g, gB_, gb1_, w.n3.gg, w.n3.gb, Md, d, st));
-  if (linear_dwb(gb1_, Md, w.l2, a.hh, st)) return -1;
-  if (linear_dx(gb1_, Md, w.l2, 0, nullptr, a.hh, nullptr, gbhh_, st)) return -1;
-  if (linear_dwb(gbhh_, Md, w.l1, a.y2b, st)) return -1;
-  if (linear_dx(gbhh_, Md, w.l1, 0, gB_, nullptr, gA_, nullptr, st)) return -1;
+  RUN(ln_bwd(gA_, nullptr, a.t3, a.mean3, a.rstd3, w.n3.g, gB_, g3, w.n3.gg, w.n3.gb, Md, d, st));
+  if (linear_dwb(g3, Md, w.l2, a.hh, st)) return -1;
+  if (linear_dx(g3, Md, w.l2, 0, nullptr, a.hh, nullptr, ghh, st)) return -1;
+  if (linear_dwb(ghh, Md, w.l1, a.y2b, st)) return -1;
+  if (linear_dx(ghh, Md, w.l1, 0, gB_, nullptr, gA_, nullptr, st)) return -1;
   // norm2, cross-attention
-  RUN(ln_bwd(gA_, nullptr, a.t2, a.mean2, a.rstd2, w.n2.g, gB_, gb1_, w.n2.gg, w.n2.gb, Md, d, st));
-  if (linear_dwb(gb1_, Md, w.ca.o, a.co, st)) return -1;
-  if (linear_dx(gb1_, Md, w.ca.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
-  if (attn_bwd(gb2_, a.q, d, a.k, d, a.cv, d, a.cP, gbqk_, d, gbk_, d, gbv_, d, B, nq, L_, st)) return -1;
-  if (linear_dwb(gbqk_, Md, w.ca.q, a.y1pb, st)) return -1;
-  if (linear_dx(gbqk_, Md, w.ca.q, 0, nullptr, nullptr, gE_, nullptr, st)) return -1;          // wrt y1 + query_pos
-  if (linear_dwb(gbk_, Me, w.ca.k, mem_pb_, st)) return -1;
-  if (linear_dx(gbk_, Me, w.ca.k, 0, nullptr, nullptr, gMemPos_, nullptr, st)) return -1;      // wrt memory + pos
-  if (linear_dwb(gbv_, Me, w.ca.v, mem_b_, st)) return -1;
-  if (linear_dx(gbv_, Me, w.ca.v, 0, nullptr, nullptr, gMem_, nullptr, st)) return -1;         // wrt memory
+  RUN(ln_bwd(gA_, nullptr, a.t2, a.mean2, a.rstd2, w.n2.g, gB_, g2, w.n2.gg, w.n2.gb, Md, d, st));
+  if (linear_dwb(g2, Md, w.ca.o, a.co, st)) return -1;
+  if (linear_dx(g2, Md, w.ca.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
+  if (attn_bwd(gb2_, a.q, d, a.k, d, a.cv, d, a.cP, gq, d, gk, d, gcv, d, B, nq, L_, st)) return -1;
+  if (linear_dwb(gq, Md, w.ca.q, a.y1pb, st)) return -1;
+  if (linear_dx(gq, Md, w.ca.q, 0, nullptr, nullptr, gE_, nullptr, st)) return -1;          // wrt y1 + query_pos
+  if (linear_dwb(gk, Me, w.ca.k, mem_pb_, st)) return -1;
+  if (linear_dx(gk, Me, w.ca.k, 0, nullptr, nullptr, gMemPos_, nullptr, st)) return -1;      // wrt memory + pos
+  if (linear_dwb(gcv, Me, w.ca.v, mem_b_, st)) return -1;
+  if (linear_dx(gcv, Me, w.ca.v, 0, nullptr, nullptr, gMem_, nullptr, st)) return -1;         // wrt memory
   auto reduce_batch = [&](const float* src, long long batch_stride, int n, float* dst) {       // dst[j] += sum_b src[b*bs + j]
     SgemmArgs r;
     r.I = 1; r.J = n; r.R = B; r.A = one_; r.ai = act::lin(0); r.ar = act::lin(0);
@@ -189,13 +199,13 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
   if (reduce_batch(gMemPos_, 1LL * L_ * d, 2 * d, g_addpos)) return -1;
   if (reduce_batch(gE_, 1LL * nq * d, nq * d, g_query)) return -1;
   // norm1 (input gradient = dt2 + query branch), self-attention over the queries
-  RUN(ln_bwd(gB_, gE_, a.t1, a.mean1, a.rstd1, w.n1.g, gA_, gb1_, w.n1.gg, w.n1.gb, Md, d, st));
-  if (linear_dwb(gb1_, Md, w.sa.o, a.o, st)) return -1;
-  if (linear_dx(gb1_, Md, w.sa.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
-  if (attn_bwd(gb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gbqk_, 2 * d, gbqk_ + d, 2 * d, gbv_, d, B, nq, nq, st)) return -1;
-  if (linear_dwb(gbqk_, Md, w.sa.qk, a.xpb, st)) return -1;
-  if (linear_dwb(gbv_, Md, w.sa.v, a.xb, st)) return -1;
-  if (linear_dx(gbqk_, Md, w.sa.qk, 0, nullptr, nullptr, gE_, nullptr, st)) return -1;
+  RUN(ln_bwd(gB_, gE_, a.t1, a.mean1, a.rstd1, w.n1.g, gA_, g1, w.n1.gg, w.n1.gb, Md, d, st));
+  if (linear_dwb(g1, Md, w.sa.o, a.o, st)) return -1;
+  if (linear_dx(g1, Md, w.sa.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
+  if (attn_bwd(gb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gqk, 2 * d, gqk + d, 2 * d, gv, d, B, nq, nq, st)) return -1;
+  if (linear_dwb(gqk, Md, w.sa.qk, a.xpb, st)) return -1;
+  if (linear_dwb(gv, Md, w.sa.v, a.xb, st)) return -1;
+  if (linear_dx(gqk, Md, w.sa.qk, 0, nullptr, nullptr, gE_, nullptr, st)) return -1;
   if (reduce_batch(gE_, 1LL * nq * d, nq * d, g_query)) return -1;
   // main encoder, last layer first
   const float* dx2 = gMem_;
@@ -224,13 +234,15 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
   const int Mf = B * Hf_ * Wf_;
   for (int k = 0; k < cfg_.num_cameras; ++k) {
     const long long total = 1LL * Mf * (d / 4);
+    bf16* gtok = gy_alloc(1LL * Mf * d);
+    if (!gtok) return -1;
     gather_tokens_kernel<<<static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 8)), 256, 0, st>>>(
-        d_src_, gb2_, B, L_, Hf_, Wf_, cfg_.num_cameras, k, d / 4);
+        d_src_, gtok, B, L_, Hf_, Wf_, cfg_.num_cameras, k, d / 4);
     ++launches_;
     ACT_CUDA(cudaGetLastError());
     const bf16* feat = cam_a_[k].blk[7].y;
-    if (linear_dwb(gb2_, Mf, input_proj_, feat, st)) return -1;
-    if (linear_dx(gb2_, Mf, input_proj_, 0, nullptr, feat, nullptr, d_feat_ + 1LL * k * cfg_.batch_max * Hf_ * Wf_ * 512, st)) return -1;
+    if (linear_dwb(gtok, Mf, input_proj_, feat, st)) return -1;
+    if (linear_dx(gtok, Mf, input_proj_, 0, nullptr, feat, nullptr, d_feat_ + 1LL * k * cfg_.batch_max * Hf_ * Wf_ * 512, st)) return -1;
   }
   return 0;
 }
@@ -240,6 +252,7 @@ int Engine::cvae_bwd(cudaStream_t st) {
   const int B = cur_B_, d = cfg_.hidden_dim, nq = cfg_.num_queries, A = cfg_.action_dim, Z = cfg_.latent_dim, S = cfg_.state_dim;
   const int Mc = B * Lc_, nl = cfg_.enc_layers;
   const long long ts = 1LL * Lc_ * d;
+  gy_off_ = gy_cvae_base_; gy_lim_ = gy_cap_;
   RUN(reparam_bwd(dz_, eps_, logvar_, d_mu_, d_logvar_, d_info_, B, Z, st));
   SgemmArgs g;
   const float* cls_out = cvae_a_[nl - 1].x2;
@@ -378,6 +391,7 @@ int Engine::backward(int stage, float loss_grad, cudaStream_t st) {
       if (backbone_bwd(k, cur_B_, st)) return -1;
   }
   if (sc != st && join_side(st)) return -1;
+  if (wg_join(st)) return -1;
   return 0;
 }
 

@@ -119,6 +119,12 @@ int Engine::alloc_workspace() {
     gMem_ = A_(float, Me * d); gMemPos_ = A_(float, Me * d);
     gb1_ = A_(bf16, Mmax * d); gb2_ = A_(bf16, Mmax * d); gbqk_ = A_(bf16, Mmax * 2 * d); gbhh_ = A_(bf16, Mmax * ff);
     gbv_ = A_(bf16, Mmax * d); gbk_ = A_(bf16, Mmax * d);
+    {   // dY arena: every dY that feeds a deferred weight gradient (5 per encoder layer, 10 in the decoder layer, 1 input_proj)
+      const long long per_row = 3LL * d + 2 * d + ff;                 // gb1 x2, gbv, gbqk, gbhh
+      gy_cap_ = cfg_.enc_layers * (Me + Mc) * (per_row + 512) + (Md * (per_row + 4 * d) + 2 * Me * d) + 1LL * Bm * Hf_ * Wf_ * d * cfg_.num_cameras + 64 * 256;
+      gy_arena_ = A_(bf16, gy_cap_);
+      gy_cvae_base_ = gy_cap_ - (cfg_.enc_layers * Mc * (per_row + 512) + 16 * 256);
+    }
     d_src_ = A_(float, Me * d); d_tokC_ = A_(float, Mc * d);
     const long long cmax = 1LL * Bm * fh_[1] * fw_[1] * 64;        // largest NHWC activation (conv1 output)
     for (int i = 0; i < 4; ++i) { cg_[i] = A_(bf16, i == 0 ? cmax : cmax / 4); }

@@ -12,19 +12,58 @@ Engine::~Engine() {
   if (ev_fork_) cudaEventDestroy(ev_fork_);
   if (ev_join_) cudaEventDestroy(ev_join_);
   if (side_) cudaStreamDestroy(side_);
+  for (int i = 0; i < 2; ++i) {
+    if (wg_ev_[i]) cudaEventDestroy(wg_ev_[i]);
+    if (wg_done_[i]) cudaEventDestroy(wg_done_[i]);
+    if (wg_[i]) cudaStreamDestroy(wg_[i]);
+  }
 }
 
-int Engine::fork_side(cudaStream_t st) {
-  if (!side_) {
-    const char* env = getenv("ACT_CONCURRENT");
-    concurrent_ = !(env && env[0] == '0');
-    ACT_CUDA(cudaStreamCreateWithFlags(&side_, cudaStreamNonBlocking));
-    ACT_CUDA(cudaEventCreateWithFlags(&ev_fork_, cudaEventDisableTiming));
-    ACT_CUDA(cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming));
+int Engine::ensure_streams() {
+  if (side_) return 0;
+  const char* env = getenv("ACT_CONCURRENT");
+  concurrent_ = !(env && env[0] == '0');
+  ACT_CUDA(cudaStreamCreateWithFlags(&side_, cudaStreamNonBlocking));
+  ACT_CUDA(cudaEventCreateWithFlags(&ev_fork_, cudaEventDisableTiming));
+  ACT_CUDA(cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming));
+  for (int i = 0; i < 2; ++i) {
+    ACT_CUDA(cudaStreamCreateWithFlags(&wg_[i], cudaStreamNonBlocking));
+    ACT_CUDA(cudaEventCreateWithFlags(&wg_ev_[i], cudaEventDisableTiming));
+    ACT_CUDA(cudaEventCreateWithFlags(&wg_done_[i], cudaEventDisableTiming));
   }
+  return 0;
+}
+int Engine::fork_side(cudaStream_t st) {
+  if (ensure_streams()) return -1;
   ACT_CUDA(cudaEventRecord(ev_fork_, st));
   ACT_CUDA(cudaStreamWaitEvent(side_, ev_fork_, 0));
   return 0;
+}
+cudaStream_t Engine::wg_fork(cudaStream_t st) {
+  if (ensure_streams() || !concurrent_) return st;
+  const int b = (st == side_) ? 1 : 0;
+  if (cudaEventRecord(wg_ev_[b], st) != cudaSuccess || cudaStreamWaitEvent(wg_[b], wg_ev_[b], 0) != cudaSuccess) {
+    set_error("weight-gradient stream fork failed");
+    return st;
+  }
+  wg_used_[b] = true;
+  return wg_[b];
+}
+int Engine::wg_join(cudaStream_t st) {
+  for (int b = 0; b < 2; ++b) {
+    if (!wg_used_[b]) continue;
+    ACT_CUDA(cudaEventRecord(wg_done_[b], wg_[b]));
+    ACT_CUDA(cudaStreamWaitEvent(st, wg_done_[b], 0));
+    wg_used_[b] = false;
+  }
+  return 0;
+}
+bf16* Engine::gy_alloc(long long elems) {
+  elems = (elems + 127) & ~127LL;
+  if (gy_off_ + elems > gy_lim_) { set_error("backward dY arena overflow"); return nullptr; }
+  bf16* p = gy_arena_ + gy_off_;
+  gy_off_ += elems;
+  return p;
 }
 int Engine::join_side(cudaStream_t st) {
   ACT_CUDA(cudaEventRecord(ev_join_, side_));
