@@ -160,6 +160,9 @@ class Engine {
   bf16* gy_arena_ = nullptr;
   long long gy_cap_ = 0, gy_off_ = 0, gy_lim_ = 0, gy_cvae_base_ = 0;
   bf16* gy_alloc(long long elems);
+  bf16* cgy_arena_ = nullptr;                   // same idea for the backbone's activation gradients (conv wgrad operands)
+  long long cgy_cap_ = 0, cgy_off_ = 0;
+  bf16* cgy_alloc(long long elems);
 
   // geometry
   int Hf_ = 0, Wf_ = 0, L_ = 0, Lp_ = 0, Lc_ = 0, Lcp_ = 0, nqp_ = 0;

@@ -301,9 +301,10 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
   CamW& cw = cam_w_[cam];
   CamActs& ca = cam_a_[cam];
   const bf16* g = d_feat_ + 1LL * cam * cfg_.batch_max * Hf_ * Wf_ * 512;
-  bf16* bufs[3] = {cg_[1], cg_[2], cg_[3]};
-  // conv weight gradients accumulate in staged layout (line-coalesced reductions) and are folded into dW by ONE launch
-  ACT_CUDA(cudaMemsetAsync(wstage_, 0, sizeof(float) * wstage_n_, st));
+  // conv weight gradients accumulate in staged layout (line-coalesced reductions) and are folded into dW by ONE launch;
+  // all of it runs on the weight-gradient stream, reading activation gradients that live in the conv-gradient arena
+  cudaStream_t wg = wg_fork(st);
+  ACT_CUDA(cudaMemsetAsync(wstage_, 0, sizeof(float) * wstage_n_, wg));
   FoldJobs folds;
   long long woff = 0;
   auto wgrad = [&](const ConvShape& cs, const bf16* xin, const bf16* dy, const ConvW& cw2) -> int {
@@ -313,9 +314,9 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
     woff += n;
     folds.job[folds.n++] = FoldJob{T, cw2.scale, cw2.gw, 1.f, cs.Cout, cs.Cin, cs.KH * cs.KH, 0};
     ++launches_;
-    return conv_wgrad_staged(cs, xin, dy, T, st);
+    wg = wg_fork(st);                                // dy is final on st here
+    return conv_wgrad_staged(cs, xin, dy, T, wg);
   };
-  int gi = -1;                                       // index in bufs holding g (-1: d_feat_)
   for (int i = 7; i >= 0; --i) {
     BlockW& bw = cw.blk[i];
     BlockActs& ba = ca.blk[i];
@@ -324,11 +325,9 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
     const int st1 = bw.c1.stride;
     const int Hc = (st1 == 2) ? fh_[1 + s] : Ho, Wc = (st1 == 2) ? fw_[1 + s] : Wo;
     const bf16* x_in = (i == 0) ? ca.p1 : ca.blk[i - 1].y;
-    const int ga_i = (gi + 1 + 3) % 3;
-    bf16* ga = bufs[ga_i];
-    int dx_i = (ga_i + 1) % 3;
-    if (dx_i == gi) dx_i = (dx_i + 1) % 3;
-    bf16* dx = bufs[dx_i];
+    bf16* ga = cgy_alloc(1LL * B * Ho * Wo * bw.c1.Cout);
+    bf16* dx = cgy_alloc(1LL * B * Hc * Wc * bw.c1.Cin);
+    if (!ga || !dx) return -1;
     ConvShape s2{B, Ho, Wo, bw.c2.Cin, bw.c2.Cout, 3, 1, 1};
     ConvShape s1{B, Hc, Wc, bw.c1.Cin, bw.c1.Cout, 3, st1, 1};
     if (wgrad(s2, ba.a, g, bw.c2)) return -1;
@@ -351,23 +350,26 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
       e1.flags |= EPI_RES_BF16; e1.res_bf16 = g;
       RUN(conv_dgrad(s1, ga, bw.c1.wpkt, e1, nullptr, st));
     }
-    g = dx; gi = dx_i;
+    g = dx;
   }
-  RUN(wgrad_fold_batched(folds, st));
-  // stem: max-pool backward (+ReLU mask), then dW1 = scale * dy1^T im2col(normalised image)
+  RUN(wgrad_fold_batched(folds, wg));
+  // stem: max-pool backward (+ReLU mask), then dW1 = scale * dy1^T (row windows of the normalised image)
   const int H1 = fh_[1], W1 = fw_[1];
-  RUN(maxpool_bwd(g, ca.pidx, ca.y1, cg_[0], B, H1, W1, 64, st));
-  // dW1 over the same row-window operand the forward read (ca.xp is still resident): tmp[co][kw*4+c][kh]
-  ACT_CUDA(cudaMemsetAsync(conv1_tmp_, 0, sizeof(float) * 64 * 64 * 7, st));
+  bf16* gpool = cgy_alloc(1LL * B * H1 * W1 * 64);
+  if (!gpool) return -1;
+  RUN(maxpool_bwd(g, ca.pidx, ca.y1, gpool, B, H1, W1, 64, st));
+  wg = wg_fork(st);
+  // dW1 over the same row-window operand the forward read (ca.xp is still resident): tmp[kh][co][kw*4+c]
+  ACT_CUDA(cudaMemsetAsync(conv1_tmp_, 0, sizeof(float) * 64 * 64 * 7, wg));
   {
     WgradLaunch w;
     if (stem_launch(cam, B, nullptr, &w)) return -1;
-    w.dy.ptr = cg_[0]; w.dy.C = 64; w.dy.W = W1; w.dy.H = H1; w.dy.N = B;
+    w.dy.ptr = gpool; w.dy.C = 64; w.dy.W = W1; w.dy.H = H1; w.dy.N = B;
     w.dy.sW = 64; w.dy.sH = 64LL * W1; w.dy.sN = 64LL * W1 * H1;
     w.dw = conv1_tmp_; w.alpha = 1.f; w.scale = nullptr;
-    RUN(tc_wgrad(w, st));
+    RUN(tc_wgrad(w, wg));
   }
-  conv1_grad_fold_kernel<<<(64 * 147 + 255) / 256, 256, 0, st>>>(conv1_tmp_, cw.stem.scale, cw.stem.gw);
+  conv1_grad_fold_kernel<<<(64 * 147 + 255) / 256, 256, 0, wg>>>(conv1_tmp_, cw.stem.scale, cw.stem.gw);
   ++launches_;
   ACT_CUDA(cudaGetLastError());
   return 0;
@@ -387,6 +389,7 @@ int Engine::backward(int stage, float loss_grad, cudaStream_t st) {
   }
   if (both || stage == 2) { if (cvae_bwd(sc)) return -1; }
   if (both || stage == 3) {
+    cgy_off_ = 0;
     for (int k = 0; k < cfg_.num_cameras; ++k)
       if (backbone_bwd(k, cur_B_, st)) return -1;
   }

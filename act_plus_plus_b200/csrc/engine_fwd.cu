@@ -129,6 +129,16 @@ int Engine::alloc_workspace() {
     const long long cmax = 1LL * Bm * fh_[1] * fw_[1] * 64;        // largest NHWC activation (conv1 output)
     for (int i = 0; i < 4; ++i) { cg_[i] = A_(bf16, i == 0 ? cmax : cmax / 4); }
     d_feat_ = A_(bf16, 1LL * cfg_.num_cameras * Bm * Hf_ * Wf_ * 512);
+    {   // conv-gradient arena: per residual block the c2 input gradient and the block input gradient, + the pool gradient
+      long long n = 1LL * Bm * fh_[1] * fw_[1] * 64 + 128;
+      for (int i = 0; i < 8; ++i) {
+        const int s4 = i / 2, Cout = 64 << s4, strided = (i % 2 == 0 && s4 > 0);
+        const int Cin = strided ? Cout / 2 : Cout;
+        n += 1LL * Bm * fh_[2 + s4] * fw_[2 + s4] * Cout + 1LL * Bm * fh_[strided ? 1 + s4 : 2 + s4] * fw_[strided ? 1 + s4 : 2 + s4] * Cin + 256;
+      }
+      cgy_cap_ = n * cfg_.num_cameras;
+      cgy_arena_ = A_(bf16, cgy_cap_);
+    }
     conv1_tmp_ = A_(float, 64 * 64 * 7);
     {
       static const int ci_[4] = {64, 64, 128, 256}, co_[4] = {64, 128, 256, 512};

@@ -58,6 +58,13 @@ int Engine::wg_join(cudaStream_t st) {
   }
   return 0;
 }
+bf16* Engine::cgy_alloc(long long elems) {
+  elems = (elems + 127) & ~127LL;
+  if (cgy_off_ + elems > cgy_cap_) { set_error("backward conv-gradient arena overflow"); return nullptr; }
+  bf16* p = cgy_arena_ + cgy_off_;
+  cgy_off_ += elems;
+  return p;
+}
 bf16* Engine::gy_alloc(long long elems) {
   elems = (elems + 127) & ~127LL;
   if (gy_off_ + elems > gy_lim_) { set_error("backward dY arena overflow"); return nullptr; }
