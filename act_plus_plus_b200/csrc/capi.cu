@@ -164,6 +164,10 @@ extern "C" int act_engine_forward(act_engine* e, int B, const float* qpos, const
 }
 extern "C" int act_engine_backward(act_engine* e, int stage, float loss_grad, void* stream) { return e->eng->backward(stage, loss_grad, ST(stream)); }
 extern "C" int act_engine_zero_grad(act_engine* e, void* stream) { return e->eng->zero_grad(ST(stream)); }
+extern "C" int act_engine_zero_grad_async(act_engine* e, void* stream) { return e->eng->zero_grad(ST(stream), true); }
+extern "C" int act_engine_backward_and_step(act_engine* e, int step, float loss_grad, void* stream) {
+  return e->eng->backward_and_step(step, loss_grad, ST(stream));
+}
 extern "C" int act_engine_adamw_step(act_engine* e, int step, void* stream) { return e->eng->adamw(step, ST(stream)); }
 extern "C" int act_engine_set_lr(act_engine* e, float lr, float lr_backbone) { e->eng->set_lr(lr, lr_backbone); return 0; }
 extern "C" int act_engine_launches(act_engine* e, int reset) { const int n = e->eng->launches(); if (reset) e->eng->reset_launches(); return n; }

@@ -86,8 +86,12 @@ class Engine {
               const uint8_t* is_pad, long long is_pad_bs, const float* eps, float* a_hat, float* is_pad_hat, float* mu,
               float* logvar, float* losses, cudaStream_t st);
   int backward(int stage, float loss_grad, cudaStream_t st);      // stage: 0 = all, 1 = transformer, 2 = cvae, 3 = backbone, 4 = cvae || backbone
-  int zero_grad(cudaStream_t st);
+  int zero_grad(cudaStream_t st, bool async = false);
   int adamw(int step, cudaStream_t st);
+  int adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm = 0);
+  // backward(0) + adamw() with the optimiser of each parameter region trailing that region's last weight gradient, so
+  // the HBM-bound AdamW of the transformer / CVAE regions overlaps the tensor-bound backbone backward
+  int backward_and_step(int step, float loss_grad, cudaStream_t st);
   const EngineConfig& cfg() const { return cfg_; }
   long long workspace_bytes() const { return ws_bytes_; }
   int launches() const { return launches_; }
@@ -145,17 +149,21 @@ class Engine {
   cudaStream_t side_ = nullptr;
   cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;
   bool concurrent_ = true;                      // ACT_CONCURRENT=0 serialises everything on the caller's stream
+  int sm_reserve_ = 0;                          // ACT_SM_RESERVE: SMs the backbone launches leave to the concurrent CVAE branch
   int fork_side(cudaStream_t st);               // side_ waits for everything enqueued on st so far
   int join_side(cudaStream_t st);               // st waits for everything enqueued on side_ so far
   // Weight/bias gradients are leaves of the backward graph (nothing reads them before the optimiser), so they are
   // issued on a per-branch weight-gradient stream that trails the dX chain and fills the SMs its small grids leave idle.
   // Their dY operands come from a bump arena (gy_alloc) instead of reused scratch, so the dX chain never has to wait
   // for a weight-gradient read before overwriting a buffer.
-  cudaStream_t wg_[2] = {nullptr, nullptr};     // [0] trails the caller's stream, [1] trails side_
-  cudaEvent_t wg_ev_[2] = {nullptr, nullptr}, wg_done_[2] = {nullptr, nullptr};
-  bool wg_used_[2] = {false, false};
+  static constexpr int NWG = 3;                 // weight gradients of different layers are independent: round-robin
+  cudaStream_t wg_[2][NWG + 1] = {};            // [0][*] trail the caller's stream, [1][*] trail side_; lane NWG = optimiser
+  cudaEvent_t wg_ev_[2] = {nullptr, nullptr}, wg_done_[2][NWG + 1] = {}, ev_stage_ = nullptr;
+  bool wg_used_[2][NWG + 1] = {};
+  int wg_rr_[2] = {0, 0};
   int ensure_streams();
-  cudaStream_t wg_fork(cudaStream_t st);        // returns the stream to launch the weight gradient on (st if serial)
+  cudaStream_t wg_fork(cudaStream_t st, int lane = -1);   // stream to launch a weight gradient on (st itself if serial)
+  cudaStream_t wg_gather(cudaStream_t st, int lane = 0);  // that lane of st's branch, ordered after st and every other lane
   int wg_join(cudaStream_t st);                 // st waits for every weight-gradient launch issued so far
   bf16* gy_arena_ = nullptr;
   long long gy_cap_ = 0, gy_off_ = 0, gy_lim_ = 0, gy_cvae_base_ = 0;

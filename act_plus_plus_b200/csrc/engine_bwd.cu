@@ -284,8 +284,9 @@ int Engine::cvae_bwd(cudaStream_t st) {
   g = SgemmArgs(); g.I = 1; g.J = d; g.R = B; g.A = one_; g.ai = act::lin(0); g.ar = act::lin(0);
   g.B = d_tokC_ + d; g.br = act::lin(ts); g.bj = act::lin(1); g.C = G("encoder_joint_proj.bias"); g.ci = act::lin(0); g.cj = act::lin(1); g.accumulate = 1;
   RUN(sgemm_generic(g, st));
-  g = SgemmArgs(); g.I = d; g.J = A; g.R = B * nq; g.A = d_tokC_ + 2 * d; g.ai = act::lin(1); g.ar = batched(nq, ts, d);
-  g.B = in_actions_; g.br = batched(nq, in_actions_bs_, A); g.bj = act::lin(1); g.C = G("encoder_action_proj.weight"); g.ci = act::lin(A); g.cj = act::lin(1); g.accumulate = 1;
+  // dW[c][a] += sum_t dTok[t][c] * actions[t][a], issued transposed (rows = a, columns = c) so lanes run along c
+  g = SgemmArgs(); g.I = A; g.J = d; g.R = B * nq; g.A = in_actions_; g.ai = act::lin(1); g.ar = batched(nq, in_actions_bs_, A);
+  g.B = d_tokC_ + 2 * d; g.br = batched(nq, ts, d); g.bj = act::lin(1); g.C = G("encoder_action_proj.weight"); g.ci = act::lin(1); g.cj = act::lin(A); g.accumulate = 1;
   RUN(sgemm_generic(g, st));
   g = SgemmArgs(); g.I = 1; g.J = d; g.R = B * nq; g.A = one_; g.ai = act::lin(0); g.ar = act::lin(0);
   g.B = d_tokC_ + 2 * d; g.br = batched(nq, ts, d); g.bj = act::lin(1); g.C = G("encoder_action_proj.bias"); g.ci = act::lin(0); g.cj = act::lin(1); g.accumulate = 1;
@@ -303,8 +304,9 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
   const bf16* g = d_feat_ + 1LL * cam * cfg_.batch_max * Hf_ * Wf_ * 512;
   // conv weight gradients accumulate in staged layout (line-coalesced reductions) and are folded into dW by ONE launch;
   // all of it runs on the weight-gradient stream, reading activation gradients that live in the conv-gradient arena
-  cudaStream_t wg = wg_fork(st);
+  cudaStream_t wg = wg_fork(st, 0);
   ACT_CUDA(cudaMemsetAsync(wstage_, 0, sizeof(float) * wstage_n_, wg));
+  if (wg != st) ACT_CUDA(cudaEventRecord(ev_stage_, wg));
   FoldJobs folds;
   long long woff = 0;
   auto wgrad = [&](const ConvShape& cs, const bf16* xin, const bf16* dy, const ConvW& cw2) -> int {
@@ -315,6 +317,7 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
     folds.job[folds.n++] = FoldJob{T, cw2.scale, cw2.gw, 1.f, cs.Cout, cs.Cin, cs.KH * cs.KH, 0};
     ++launches_;
     wg = wg_fork(st);                                // dy is final on st here
+    if (wg != st) ACT_CUDA(cudaStreamWaitEvent(wg, ev_stage_, 0));   // staging buffer cleared
     return conv_wgrad_staged(cs, xin, dy, T, wg);
   };
   for (int i = 7; i >= 0; --i) {
@@ -352,6 +355,7 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
     }
     g = dx;
   }
+  wg = wg_gather(st);
   RUN(wgrad_fold_batched(folds, wg));
   // stem: max-pool backward (+ReLU mask), then dW1 = scale * dy1^T (row windows of the normalised image)
   const int H1 = fh_[1], W1 = fw_[1];
@@ -375,9 +379,40 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
   return 0;
 }
 
+int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st) {
+  ACT_CHECK(cfg_.train && grads_ != nullptr, "engine has no training workspace / gradient buffer");
+  ACT_CHECK(have_actions_ && cur_B_ > 0, "backward needs a preceding training forward (with actions)");
+  if (ensure_streams()) return -1;
+  if (!concurrent_) return backward(0, loss_grad, st) || adamw(step, st) ? -1 : 0;
+  if (wg_join(st)) return -1;                               // an asynchronous zero_grad
+  if (transformer_bwd(loss_grad, st)) return -1;
+  if (fork_side(st)) return -1;
+  if (cvae_bwd(side_)) return -1;
+  {   // MAIN / DEAD regions: every gradient and every read of these weights is ordered before this point of lane 0
+    cudaStream_t wg = wg_gather(st, NWG);
+    if (adamw_region(R_MAIN, step, wg, 3) || adamw_region(R_DEAD, step, wg, 3)) return -1;
+  }
+  {   // CVAE region trails the CVAE branch's weight gradients
+    cudaStream_t wg = wg_gather(side_, NWG);
+    if (adamw_region(R_CVAE, step, wg, 6)) return -1;
+  }
+  cgy_off_ = 0;
+  tc_set_sm_reserve(sm_reserve_);
+  for (int k = 0; k < cfg_.num_cameras; ++k)
+    if (backbone_bwd(k, cur_B_, st)) { tc_set_sm_reserve(0); return -1; }
+  tc_set_sm_reserve(0);
+  {   // BACKBONE region: trails the batched fold and the stem weight gradient, not the (longer) CVAE branch
+    cudaStream_t wg = wg_gather(st, NWG);
+    if (adamw_region(R_BACKBONE, step, wg, 3)) return -1;
+  }
+  if (join_side(st)) return -1;
+  return wg_join(st);
+}
+
 int Engine::backward(int stage, float loss_grad, cudaStream_t st) {
   ACT_CHECK(cfg_.train && grads_ != nullptr, "engine has no training workspace / gradient buffer");
   ACT_CHECK(have_actions_ && cur_B_ > 0, "backward needs a preceding training forward (with actions)");
+  if (wg_join(st)) return -1;                               // an asynchronous zero_grad
   if (stage == 0 || stage == 1) { if (transformer_bwd(loss_grad, st)) return -1; }
   // After the transformer the CVAE-encoder branch (needs dz) and the backbone branch (needs d_feat) share no buffers:
   // stage 0 / 4 run them as two parallel branches (side stream), stages 2 and 3 one at a time on the caller's stream.

@@ -428,8 +428,10 @@ int Engine::forward(int B, const float* qpos, const float* image, const float* a
   g.B = P("input_proj_robot_state.weight"); g.br = act::lin(1); g.bj = act::lin(S); g.bias = P("input_proj_robot_state.bias");
   g.C = src_ + d; g.ci = act::lin(1LL * L_ * d); g.cj = act::lin(1);
   RUN(sgemm_generic(g, st));
+  if (sc != st) tc_set_sm_reserve(sm_reserve_);
   for (int k = 0; k < cfg_.num_cameras; ++k)
-    if (backbone_fwd(k, B, image, st)) return -1;
+    if (backbone_fwd(k, B, image, st)) { tc_set_sm_reserve(0); return -1; }
+  tc_set_sm_reserve(0);
   if (sc != st && join_side(st)) return -1;
   RUN(add_pos_cast(src_, pos_main_, L_, enc_a_[0].xb, enc_a_[0].xpb, B * L_, d, st));
   const int nl = cfg_.enc_layers;

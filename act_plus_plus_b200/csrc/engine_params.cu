@@ -12,10 +12,13 @@ Engine::~Engine() {
   if (ev_fork_) cudaEventDestroy(ev_fork_);
   if (ev_join_) cudaEventDestroy(ev_join_);
   if (side_) cudaStreamDestroy(side_);
-  for (int i = 0; i < 2; ++i) {
-    if (wg_ev_[i]) cudaEventDestroy(wg_ev_[i]);
-    if (wg_done_[i]) cudaEventDestroy(wg_done_[i]);
-    if (wg_[i]) cudaStreamDestroy(wg_[i]);
+  if (ev_stage_) cudaEventDestroy(ev_stage_);
+  for (int b = 0; b < 2; ++b) {
+    if (wg_ev_[b]) cudaEventDestroy(wg_ev_[b]);
+    for (int i = 0; i <= NWG; ++i) {
+      if (wg_done_[b][i]) cudaEventDestroy(wg_done_[b][i]);
+      if (wg_[b][i]) cudaStreamDestroy(wg_[b][i]);
+    }
   }
 }
 
@@ -23,13 +26,22 @@ int Engine::ensure_streams() {
   if (side_) return 0;
   const char* env = getenv("ACT_CONCURRENT");
   concurrent_ = !(env && env[0] == '0');
-  ACT_CUDA(cudaStreamCreateWithFlags(&side_, cudaStreamNonBlocking));
+  if (const char* r = getenv("ACT_SM_RESERVE")) sm_reserve_ = atoi(r);
+  int prio_lo = 0, prio_hi = 0;
+  ACT_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+  const char* pe = getenv("ACT_SIDE_PRIO");
+  // ACT_SIDE_PRIO=1 gives the CVAE branch (a long chain of small kernels) SM slots ahead of the backbone branch; measured
+  // neutral-to-worse (the persistent conv kernels then wait for their late CTAs), so the default is equal priority
+  ACT_CUDA(cudaStreamCreateWithPriority(&side_, cudaStreamNonBlocking, (pe && pe[0] == '1') ? prio_hi : prio_lo));
   ACT_CUDA(cudaEventCreateWithFlags(&ev_fork_, cudaEventDisableTiming));
   ACT_CUDA(cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming));
-  for (int i = 0; i < 2; ++i) {
-    ACT_CUDA(cudaStreamCreateWithFlags(&wg_[i], cudaStreamNonBlocking));
-    ACT_CUDA(cudaEventCreateWithFlags(&wg_ev_[i], cudaEventDisableTiming));
-    ACT_CUDA(cudaEventCreateWithFlags(&wg_done_[i], cudaEventDisableTiming));
+  ACT_CUDA(cudaEventCreateWithFlags(&ev_stage_, cudaEventDisableTiming));
+  for (int b = 0; b < 2; ++b) {
+    ACT_CUDA(cudaEventCreateWithFlags(&wg_ev_[b], cudaEventDisableTiming));
+    for (int i = 0; i <= NWG; ++i) {
+      ACT_CUDA(cudaStreamCreateWithFlags(&wg_[b][i], cudaStreamNonBlocking));
+      ACT_CUDA(cudaEventCreateWithFlags(&wg_done_[b][i], cudaEventDisableTiming));
+    }
   }
   return 0;
 }
@@ -39,23 +51,35 @@ int Engine::fork_side(cudaStream_t st) {
   ACT_CUDA(cudaStreamWaitEvent(side_, ev_fork_, 0));
   return 0;
 }
-cudaStream_t Engine::wg_fork(cudaStream_t st) {
+cudaStream_t Engine::wg_fork(cudaStream_t st, int lane) {
   if (ensure_streams() || !concurrent_) return st;
   const int b = (st == side_) ? 1 : 0;
-  if (cudaEventRecord(wg_ev_[b], st) != cudaSuccess || cudaStreamWaitEvent(wg_[b], wg_ev_[b], 0) != cudaSuccess) {
+  const int i = lane >= 0 ? lane : (wg_rr_[b]++ % NWG);
+  if (cudaEventRecord(wg_ev_[b], st) != cudaSuccess || cudaStreamWaitEvent(wg_[b][i], wg_ev_[b], 0) != cudaSuccess) {
     set_error("weight-gradient stream fork failed");
     return st;
   }
-  wg_used_[b] = true;
-  return wg_[b];
+  wg_used_[b][i] = true;
+  return wg_[b][i];
+}
+cudaStream_t Engine::wg_gather(cudaStream_t st, int lane) {
+  if (ensure_streams() || !concurrent_) return st;
+  const int b = (st == side_) ? 1 : 0;
+  for (int i = 0; i <= NWG; ++i) {
+    if (i == lane || !wg_used_[b][i]) continue;
+    if (cudaEventRecord(wg_done_[b][i], wg_[b][i]) != cudaSuccess || cudaStreamWaitEvent(wg_[b][lane], wg_done_[b][i], 0) != cudaSuccess)
+      set_error("weight-gradient stream gather failed");
+  }
+  return wg_fork(st, lane);
 }
 int Engine::wg_join(cudaStream_t st) {
-  for (int b = 0; b < 2; ++b) {
-    if (!wg_used_[b]) continue;
-    ACT_CUDA(cudaEventRecord(wg_done_[b], wg_[b]));
-    ACT_CUDA(cudaStreamWaitEvent(st, wg_done_[b], 0));
-    wg_used_[b] = false;
-  }
+  for (int b = 0; b < 2; ++b)
+    for (int i = 0; i <= NWG; ++i) {
+      if (!wg_used_[b][i]) continue;
+      ACT_CUDA(cudaEventRecord(wg_done_[b][i], wg_[b][i]));
+      ACT_CUDA(cudaStreamWaitEvent(st, wg_done_[b][i], 0));
+      wg_used_[b][i] = false;
+    }
   return 0;
 }
 bf16* Engine::cgy_alloc(long long elems) {
@@ -291,28 +315,27 @@ int Engine::refresh_shadows(cudaStream_t st) {
   return 0;
 }
 
-int Engine::zero_grad(cudaStream_t st) {
+int Engine::zero_grad(cudaStream_t st, bool async) {
   ACT_CHECK(grads_ != nullptr, "no gradient buffer bound");
   const long long n = region_off_[R_DEAD];     // MAIN | CVAE | BACKBONE are contiguous and first
-  ACT_CUDA(cudaMemsetAsync(grads_, 0, n * sizeof(float), st));
+  // async: the clear runs on the weight-gradient stream beside the forward pass; backward()/adamw() join it
+  cudaStream_t s = async ? wg_fork(st) : st;
+  ACT_CUDA(cudaMemsetAsync(grads_, 0, n * sizeof(float), s));
   return 0;
 }
 
-int Engine::adamw(int step, cudaStream_t st) {
+int Engine::adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm) {
   ACT_CHECK(params_ && grads_ && m_ && v_, "optimizer state not bound");
-  auto run = [&](int r, float lr, int mode, bool shadow) {
-    AdamWArgs a;
-    const long long o = region_off_[r];
-    a.p = params_ + o; a.g = grads_ + o; a.m = m_ + o; a.v = v_ + o; a.shadow = shadow ? shadow_ + o : nullptr;
-    a.n = region_n_[r]; a.lr = lr; a.beta1 = cfg_.beta1; a.beta2 = cfg_.beta2; a.eps = cfg_.adam_eps; a.wd = cfg_.weight_decay;
-    a.step = step; a.mode = mode;
-    ++launches_;
-    return adamw_step(a, st);
-  };
-  if (run(R_MAIN, cfg_.lr, 0, true)) return -1;
-  if (have_actions_ || true) { if (run(R_CVAE, cfg_.lr, 0, true)) return -1; }
-  if (run(R_BACKBONE, cfg_.lr_backbone, 0, false)) return -1;
-  if (run(R_DEAD, cfg_.lr, 1, cfg_.faithful_decoder != 0)) return -1;
+  AdamWArgs a;
+  const long long o = region_off_[r];
+  const bool shadow = r == R_MAIN || r == R_CVAE || (r == R_DEAD && cfg_.faithful_decoder != 0);
+  a.p = params_ + o; a.g = grads_ + o; a.m = m_ + o; a.v = v_ + o; a.shadow = shadow ? shadow_ + o : nullptr;
+  a.n = region_n_[r]; a.lr = r == R_BACKBONE ? cfg_.lr_backbone : cfg_.lr; a.beta1 = cfg_.beta1; a.beta2 = cfg_.beta2;
+  a.eps = cfg_.adam_eps; a.wd = cfg_.weight_decay; a.step = step; a.mode = r == R_DEAD ? 1 : 0;
+  a.background = blocks_per_sm;
+  ++launches_;
+  if (adamw_step(a, st)) return -1;
+  if (r != R_BACKBONE) return 0;
   // packed conv operands (transposed / scaled layouts) are rebuilt from the fp32 masters, one launch per camera
   for (int k = 0; k < cfg_.num_cameras; ++k) {
     CamW& c = cam_w_[k];
@@ -330,6 +353,14 @@ int Engine::adamw(int step, cudaStream_t st) {
     if (pack_conv_batched(jobs, st)) return -1;
     ++launches_;
   }
+  return 0;
+}
+
+int Engine::adamw(int step, cudaStream_t st) {
+  if (wg_join(st)) return -1;
+  const int order[4] = {R_MAIN, R_CVAE, R_BACKBONE, R_DEAD};
+  for (int r : order)
+    if (adamw_region(r, step, st)) return -1;
   return 0;
 }
 

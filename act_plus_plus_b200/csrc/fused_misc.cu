@@ -51,8 +51,73 @@ __global__ void __launch_bounds__(256) sgemm_generic_kernel(SgemmArgs a) {
     else *c = v;
   }
 }
+// Short reductions (R <= 64, e.g. the 14/16-wide input projections and d_hs = d_a W): one thread per output, lanes
+// along j, the A row is a warp broadcast.  The block shape of the generic kernel would leave 7/8 of its threads idle.
+__global__ void __launch_bounds__(256) sgemm_short_kernel(SgemmArgs a) {
+  pdl_trigger(); pdl_wait();
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  const int i = blockIdx.y;
+  if (j >= a.J) return;
+  const float* Ai = a.A + ioff(a.ai, i);
+  const float* Bj = a.B + ioff(a.bj, j);
+  const long long sa = a.ar.s, sb = a.br.s;
+  float acc = 0.f;
+#pragma unroll 4
+  for (int r = 0; r < a.R; ++r) acc += __ldg(Ai + r * sa) * __ldg(Bj + r * sb);
+  acc *= a.alpha;
+  if (a.bias) acc += a.bias[j];
+  float* c = a.C + ioff(a.ci, i) + ioff(a.cj, j);
+  if (a.accumulate) atomicAdd(c, acc);
+  else *c = acc;
+}
+// Long reductions with both operands contiguous along r and few output columns (action / is_pad heads, latent_proj):
+// one warp per (output row, group of 4 columns), lanes along r (coalesced); 4 independent dot products keep enough
+// loads in flight to cover the L2 latency.
+__global__ void __launch_bounds__(256) sgemm_rowdot_kernel(SgemmArgs a) {
+  pdl_trigger(); pdl_wait();
+  const int lane = threadIdx.x & 31;
+  const int jg = (a.J + 3) / 4;
+  const int w = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (w >= a.I * jg) return;
+  const int i = w / jg, j0 = (w % jg) * 4;
+  const float* Ai = a.A + ioff(a.ai, i);
+  const float* Bj[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) Bj[q] = a.B + ioff(a.bj, min(j0 + q, a.J - 1));
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int r = lane; r < a.R; r += 32) {
+    const float av = __ldg(Ai + r);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) acc[q] += av * __ldg(Bj[q] + r);
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], o);
+  }
+  if (lane < 4 && j0 + lane < a.J) {
+    const int j = j0 + lane;
+    float v = (lane == 0 ? acc[0] : lane == 1 ? acc[1] : lane == 2 ? acc[2] : acc[3]) * a.alpha;
+    if (a.bias) v += a.bias[j];
+    float* c = a.C + ioff(a.ci, i) + ioff(a.cj, j);
+    if (a.accumulate) atomicAdd(c, v);
+    else *c = v;
+  }
+}
 int sgemm_generic(const SgemmArgs& a, cudaStream_t st) {
   if (a.I <= 0 || a.J <= 0) return 0;
+  ACT_CHECK(a.I <= 65535, "sgemm_generic: too many rows");
+  const bool flat = a.ar.rpb >= a.R && a.br.rpb >= a.R;
+  if (flat && a.R <= 64 && a.J >= 128) {
+    ACT_CUDA(launch_pdl(sgemm_short_kernel, dim3((a.J + 255) / 256, a.I), dim3(256), 0, st, a));
+    ACT_CUDA(cudaGetLastError());
+    return 0;
+  }
+  if (flat && a.ar.s == 1 && a.br.s == 1 && a.J <= 64 && a.R >= 128) {
+    ACT_CUDA(launch_pdl(sgemm_rowdot_kernel, dim3((a.I * ((a.J + 3) / 4) + 7) / 8), dim3(256), 0, st, a));
+    ACT_CUDA(cudaGetLastError());
+    return 0;
+  }
   const int jb = (a.J + 31) / 32;
   int split = 1;
   if (a.accumulate && a.R > 64) {
@@ -61,7 +126,6 @@ int sgemm_generic(const SgemmArgs& a, cudaStream_t st) {
     split = static_cast<int>(std::max<long long>(1, std::min<long long>((a.R + 31) / 32, (2 * 148 + blocks - 1) / blocks)));
   }
   dim3 grid(jb, a.I, split);
-  ACT_CHECK(a.I <= 65535, "sgemm_generic: too many rows");
   ACT_CUDA(launch_pdl(sgemm_generic_kernel, grid, dim3(32, 8), 0, st, a));
   ACT_CUDA(cudaGetLastError());
   return 0;

@@ -61,6 +61,7 @@ struct AdamWArgs {
   float lr, beta1, beta2, eps, wd;
   int step;          // 1-based
   int mode;          // 0 = full AdamW, 1 = weight decay only (gradient identically zero)
+  int background = 0;   // n > 0: launch n blocks per SM (n x 256 threads) so concurrently running tensor-core CTAs still find a slot
 };
 int adamw_step(const AdamWArgs& a, cudaStream_t st);
 int temporal_agg_step(float* ring, const float* chunks, const int* t, double* out, int E, int nq, int A, double k,

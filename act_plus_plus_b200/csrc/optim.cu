@@ -60,7 +60,7 @@ int adamw_step(const AdamWArgs& a, cudaStream_t st) {
   const double bc1 = 1.0 - std::pow(static_cast<double>(a.beta1), a.step);
   const double bc2 = 1.0 - std::pow(static_cast<double>(a.beta2), a.step);
   const long long n4 = a.n / 4;
-  const int blocks = static_cast<int>(std::max<long long>(1, std::min<long long>((n4 + 255) / 256, 148 * 8)));
+  const int blocks = static_cast<int>(std::max<long long>(1, std::min<long long>((n4 + 255) / 256, 148 * (a.background > 0 ? std::min(a.background, 8) : 8))));
   ACT_CUDA(launch_pdl(adamw_kernel, dim3(blocks), dim3(256), 0, st, a, static_cast<float>(bc1), static_cast<float>(1.0 / std::sqrt(bc2))));
   ACT_CUDA(cudaGetLastError());
   return 0;

@@ -86,6 +86,7 @@ struct ConvLaunch {
 int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint = 0, int stages_hint = 0);
 // dense 3x3 / stride-1 tap sets: halo patch resident in shared memory (conv3_kernel.cuh); ACT_CONV3=0 disables it
 bool tc_conv3_applicable(const ConvLaunch& c);
+void tc_set_sm_reserve(int n);   // persistent launches that follow leave n SMs free for a concurrent branch
 int tc_conv3(const ConvLaunch& c, cudaStream_t stream, int bn_hint = 0);
 
 struct WgradLaunch {

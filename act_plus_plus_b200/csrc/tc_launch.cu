@@ -125,6 +125,10 @@ int tc_profile_end(double* total_ms, double* total_flops, int* launches, double*
   return 0;
 }
 
+static int g_sm_reserve = 0;
+static int oversub() { static int k = 0; if (!k) { const char* e = getenv("ACT_TC_OVERSUB"); k = e ? std::max(1, atoi(e)) : 1; } return k; }
+// SMs left free by the persistent launches that follow (a concurrent latency-bound branch runs there); 0 = use all.
+void tc_set_sm_reserve(int n) { g_sm_reserve = n < 0 ? 0 : n; }
 static int num_sms() {
   static int n = 0;
   if (n == 0) {
@@ -132,7 +136,7 @@ static int num_sms() {
     if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) n = v;
     else n = 148;
   }
-  return n;
+  return std::max(n / 2, n - g_sm_reserve);
 }
 
 // Persistent launch: `tiles` = logical tile grid (x fastest); the kernel runs min(#tiles, #SMs) CTAs, one per SM
@@ -158,7 +162,7 @@ static int launch_inst(dim3 tiles, int stages, cudaStream_t stream, const CUtens
   p.gx = static_cast<int>(tiles.x); p.gy = static_cast<int>(tiles.y); p.gz = static_cast<int>(tiles.z);
   const long long total = 1LL * tiles.x * tiles.y * tiles.z;
   ACT_CHECK(total > 0 && total < (1LL << 30), "bad tile grid");
-  const unsigned ctas = static_cast<unsigned>(std::min<long long>(total, num_sms()));
+  const unsigned ctas = static_cast<unsigned>(std::min<long long>(total, 1LL * oversub() * num_sms()));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
   ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(Cfg::THREADS), static_cast<size_t>(smem), stream, am[0], am[1], am[2], am[3], bm, p, stages));
@@ -340,7 +344,7 @@ static int launch_conv3(long long total, cudaStream_t stream, const CUtensorMap&
     ACT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
     configured = true;
   }
-  const unsigned ctas = static_cast<unsigned>(std::min<long long>(total, num_sms()));
+  const unsigned ctas = static_cast<unsigned>(std::min<long long>(total, 1LL * oversub() * num_sms()));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
   ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(192), static_cast<size_t>(Cfg::SMEM), stream, am, bm, p));

@@ -190,8 +190,20 @@ class ActEngine:
     def backward(self, stage: int = 0, loss_grad: float = 1.0):
         check(self.lib.act_engine_backward(self._h, stage, float(loss_grad), _stream()), "act_engine_backward")
 
-    def zero_grad(self):
-        check(self.lib.act_engine_zero_grad(self._h, _stream()), "act_engine_zero_grad")
+    def zero_grad(self, overlap_forward: bool = False):
+        """overlap_forward: clear the gradients beside the next forward (the next backward / optimiser call waits)."""
+        if overlap_forward:
+            check(self.lib.act_engine_zero_grad_async(self._h, _stream()), "act_engine_zero_grad_async")
+        else:
+            check(self.lib.act_engine_zero_grad(self._h, _stream()), "act_engine_zero_grad")
+
+    def backward_and_step(self, loss_grad: float = 1.0):
+        """loss.backward(); optimizer.step() as one call: each region's AdamW overlaps the remaining backward."""
+        self._shared["step"] += 1
+        check(self.lib.act_engine_backward_and_step(self._h, self._shared["step"], float(loss_grad), _stream()),
+              "act_engine_backward_and_step")
+        self._shared["version"] += 1
+        self._synced_version = self._shared["version"]
 
     def adamw_step(self):
         self._shared["step"] += 1

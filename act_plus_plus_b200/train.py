@@ -29,11 +29,11 @@ def backward_data_parallel(eng: ActEngine, group, loss_grad: float = 1.0, bucket
 
 def train_step(eng: ActEngine, qpos, image, actions, is_pad, eps=None, dp_group=None) -> torch.Tensor:
     """Returns the device tensor [l1, kl, loss] of this rank's shard."""
-    eng.zero_grad()
+    eng.zero_grad(overlap_forward=True)
     out = eng.forward(qpos, image, actions, is_pad, eps)
     if dp_group is None:
-        eng.backward(0, 1.0)
+        eng.backward_and_step(1.0)
     else:
         backward_data_parallel(eng, dp_group, 1.0)
-    eng.adamw_step()
+        eng.adamw_step()
     return out["losses"]

@@ -224,7 +224,7 @@ def run_ours(args):
         try:
             for k in stat:
                 stat[k].copy_(devb[0][k])
-            s = torch.cuda.Stream()
+            s = torch.cuda.Stream(priority=int(os.environ.get('ACT_STREAM_PRIO', '-1')))
             s.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(s):
                 step_direct(stat)

@@ -148,6 +148,13 @@ int act_engine_forward(act_engine* e, int B, const float* qpos, const float* ima
  * joined into `stream`).  Run 1 then 4 (or 1,2,3) to overlap the gradient all-reduce of finished regions. */
 int act_engine_backward(act_engine* e, int stage, float loss_grad, void* stream);
 int act_engine_zero_grad(act_engine* e, void* stream);
+/* same, but the clear runs beside the following forward on an internal stream; the next act_engine_backward /
+ * act_engine_backward_and_step / act_engine_adamw_step on this engine waits for it. */
+int act_engine_zero_grad_async(act_engine* e, void* stream);
+/* loss.backward() + optimizer.step() (imitate_episodes.py:603-607) as one call: act_engine_backward(e, 0, ...) followed
+ * by act_engine_adamw_step(e, step, ...), with each parameter region's AdamW launched as soon as that region's
+ * gradients are final so it overlaps the remaining backward.  Single-process only (no gradient all-reduce in between). */
+int act_engine_backward_and_step(act_engine* e, int step, float loss_grad, void* stream);
 int act_engine_adamw_step(act_engine* e, int step, void* stream);
 int act_engine_set_lr(act_engine* e, float lr, float lr_backbone);
 int act_engine_launches(act_engine* e, int reset);

@@ -110,3 +110,35 @@ def test_backward_matches_reference_autograd(case):
     assert np.median(samp_rel) < 3e-2 and np.median(norm_rel) < 2e-2, (case, "median", float(np.median(samp_rel)))
     assert norm_rel.max() < 0.06, (case, max(rows, key=lambda r: r[3]))
     assert samp_rel.max() < (0.1 if case.startswith("full") else 0.45), (case, rows[0])
+
+
+def test_overlapped_step_equals_serial_step():
+    """train_step (async zero_grad, CVAE || backbone branches, weight gradients and per-region AdamW on trailing
+    streams) must give the same parameters as the plain call sequence zero_grad -> forward -> backward(1,2,3) -> adamw
+    on one stream.  Differences come only from fp32 atomic accumulation order."""
+    from act_plus_plus_b200.train import train_step
+    _, _, sd, cb, eng_a = _setup("small_k1")
+    _, _, _, _, eng_b = _setup("small_k1")
+    for eng in (eng_a, eng_b):
+        eng.set_lr(1e-3, 1e-3)          # large enough that a wrong / missing update is far outside the tolerance
+    eps = torch.randn((cb["qpos"].shape[0], 32), device="cuda", generator=torch.Generator(device="cuda").manual_seed(5))
+    for _ in range(3):
+        la = train_step(eng_a, cb["qpos"], cb["image"], cb["actions"], cb["is_pad"], eps).clone()
+        eng_b.zero_grad()
+        lb = eng_b.forward(cb["qpos"], cb["image"], cb["actions"], cb["is_pad"], eps)["losses"].clone()
+        for stage in (1, 2, 3):
+            eng_b.backward(stage, 1.0)
+        eng_b.adamw_step()
+    torch.cuda.synchronize()
+    assert torch.allclose(la, lb, rtol=2e-3, atol=1e-5), (la, lb)
+    from act_plus_plus_b200.engine import R_BACKBONE, R_CVAE, R_MAIN
+    pa, pb, p0 = eng_a.flat_params, eng_b.flat_params, _setup("small_k1")[4].flat_params
+    for name, r in (("main", R_MAIN), ("cvae", R_CVAE), ("backbone", R_BACKBONE)):
+        off, n = eng_b.region(r)
+        da = (pa[off:off + n] - pb[off:off + n]).abs()
+        moved = (pb[off:off + n] - p0[off:off + n]).abs().mean().item()
+        # Adam normalises every update to ~lr, so a skipped / doubled / stale-gradient region update moves the mean by
+        # ~1e-3 per step; elements whose true gradient is zero (e.g. key biases) may flip sign on rounding noise.
+        assert moved > 5e-4, f"{name}: parameters did not move ({moved})"
+        assert da.mean().item() <= 0.02 * moved, f"{name}: mean |overlapped - serial| = {da.mean().item()} vs moved {moved}"
+        assert (da > 0.5 * moved).float().mean().item() < 5e-3, f"{name}: too many diverging elements"
