@@ -37,3 +37,49 @@ def train_step(eng: ActEngine, qpos, image, actions, is_pad, eps=None, dp_group=
         backward_data_parallel(eng, dp_group, 1.0)
         eng.adamw_step()
     return out["losses"]
+
+
+class InputPrefetcher:
+    """Double-buffered host->device staging for the training loop (the role of the DataLoader's pinned-memory prefetch in
+    imitate_episodes.py:596-601): `submit(host_batch)` enqueues the H2D copy of a pinned batch on a copy stream,
+    `next()` hands the oldest submitted batch to the current stream.  Submitting batch i+1 before consuming batch i lets
+    its transfer run under step i's kernels.  A slot is reused only after the step that read it has been enqueued
+    (event recorded by `next()` for the previous occupant and waited for by the copy stream)."""
+
+    def __init__(self, example: dict, device, depth: int = 2):
+        self.device = torch.device(device)
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        self.slots = [{k: torch.empty(v.shape, dtype=v.dtype, device=self.device) for k, v in example.items()}
+                      for _ in range(depth)]
+        self.ready = [torch.cuda.Event() for _ in range(depth)]
+        self.free = [None] * depth
+        self.head = self.tail = 0
+        self.depth = depth
+
+    def submit(self, host_batch: dict):
+        assert self.tail - self.head < self.depth, "prefetch queue full: call next() first"
+        s = self.tail % self.depth
+        with torch.cuda.stream(self.copy_stream):
+            if self.free[s] is not None:
+                self.copy_stream.wait_event(self.free[s])
+            for k, v in host_batch.items():
+                self.slots[s][k].copy_(v, non_blocking=True)
+            self.ready[s].record(self.copy_stream)
+        self.tail += 1
+
+    def next(self) -> dict:
+        """The returned tensors are valid until `depth` more batches have been submitted; consume them on the current
+        stream (e.g. copy into the step's static inputs) before calling submit() again for this slot."""
+        assert self.head < self.tail, "nothing submitted"
+        s = self.head % self.depth
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(self.ready[s])
+        self.head += 1
+        return self.slots[s]
+
+    def consumed(self):
+        """Mark the most recently returned batch as read by everything enqueued so far on the current stream."""
+        s = (self.head - 1) % self.depth
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self.free[s] = ev

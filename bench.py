@@ -276,16 +276,22 @@ def run_ours(args):
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
     loss_host = 0.0
+    from act_plus_plus_b200.train import InputPrefetcher
+    pf = InputPrefetcher(host[0], dev, depth=2)
+    pf.submit(host[0])
     for i in range(args.steps):
-        hb = host[i % NB]
+        if i + 1 < args.steps:
+            pf.submit(host[(i + 1) % NB])                            # H2D of the next step's inputs runs under this step
+        db = pf.next()
         if graph is not None:
             for k in stat:
-                stat[k].copy_(hb[k], non_blocking=True)
+                stat[k].copy_(db[k], non_blocking=True)
+            pf.consumed()
             graph.replay()
             ls = g_losses
         else:
-            db = {k: v.to(dev, non_blocking=True) for k, v in hb.items()}
             ls = step_direct(db)
+            pf.consumed()
         loss_host = float(ls[2].item())                              # device->host read of the step's loss
     f1.record()
     barrier()

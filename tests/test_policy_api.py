@@ -130,3 +130,21 @@ def test_batched_rollout_matches_reference_ensemble_lines():
         for e in range(E):
             ref = oracles[e].step(t, chunks[e][None])[0] * stats["action_std"].double() + stats["action_mean"].double()
             assert torch.allclose(out[e].cpu(), ref, rtol=1e-12, atol=1e-12), (t, e)
+
+
+def test_input_prefetcher_delivers_batches_in_order():
+    from act_plus_plus_b200.train import InputPrefetcher
+    host = [dict(x=torch.full((1 << 20,), float(i)).pin_memory(), y=torch.arange(8).add(i).pin_memory()) for i in range(5)]
+    pf = InputPrefetcher(host[0], "cuda", depth=2)
+    pf.submit(host[0])
+    seen = []
+    for i in range(5):
+        if i + 1 < 5:
+            pf.submit(host[i + 1])
+        b = pf.next()
+        seen.append((b["x"].sum().item() / (1 << 20), b["y"].clone()))     # consume on the current stream
+        pf.consumed()
+    torch.cuda.synchronize()
+    for i, (x, y) in enumerate(seen):
+        assert x == float(i)
+        assert torch.equal(y.cpu(), torch.arange(8) + i)
