@@ -211,6 +211,18 @@ class ActEngine:
         self._shared["version"] += 1
         self._synced_version = self._shared["version"]     # the fused step refreshed this engine's own shadows
 
+    def begin_optimizer_step(self) -> int:
+        """Advance the shared step counter; the per-region updates of this optimiser step all use the returned value."""
+        self._shared["step"] += 1
+        return self._shared["step"]
+
+    def adamw_region(self, step: int, region: int, blocks_per_sm: int = 0):
+        check(self.lib.act_engine_adamw_region(self._h, step, region, blocks_per_sm, _stream()), "act_engine_adamw_region")
+
+    def end_optimizer_step(self):
+        self._shared["version"] += 1
+        self._synced_version = self._shared["version"]
+
     def set_lr(self, lr: float, lr_backbone: float):
         check(self.lib.act_engine_set_lr(self._h, lr, lr_backbone), "act_engine_set_lr")
 

@@ -7,7 +7,7 @@ import os
 import torch
 
 from .dp import GradReducer
-from .engine import R_BACKBONE, R_CVAE, R_MAIN, ActEngine
+from .engine import R_BACKBONE, R_CVAE, R_DEAD, R_MAIN, ActEngine
 
 
 def backward_data_parallel(eng: ActEngine, group, loss_grad: float = 1.0, bucket_elems: int = 0):
@@ -27,12 +27,50 @@ def backward_data_parallel(eng: ActEngine, group, loss_grad: float = 1.0, bucket
     red.wait()
 
 
+def backward_and_step_data_parallel(eng: ActEngine, group, loss_grad: float = 1.0, bucket_elems: int = 0):
+    """Data-parallel loss.backward() + optimizer.step(): backward stage 1 (heads + transformer) -> all-reduce of that
+    region -> its AdamW on a side stream as soon as the reduction lands, all of it under backward stage 4 (CVAE encoder
+    || backbones); the two remaining regions are reduced and updated after stage 4."""
+    cur = torch.cuda.current_stream()
+    side = _side_stream(eng)
+    step = eng.begin_optimizer_step()
+    red_main = GradReducer(eng.flat_grads, group, bucket_elems)
+    eng.backward(1, loss_grad)
+    red_main.reduce(*eng.region(R_MAIN))
+    side.wait_stream(cur)                       # every read of the main-region weights (stage 1) is ordered before
+    with torch.cuda.stream(side):
+        red_main.wait()
+        eng.adamw_region(step, R_MAIN, 3)
+        eng.adamw_region(step, R_DEAD, 3)
+    eng.backward(4, loss_grad)
+    red = GradReducer(eng.flat_grads, group, bucket_elems)
+    for region in (R_CVAE, R_BACKBONE):
+        red.reduce(*eng.region(region))
+    red.wait()
+    eng.adamw_region(step, R_CVAE)
+    eng.adamw_region(step, R_BACKBONE)
+    cur.wait_stream(side)
+    eng.end_optimizer_step()
+
+
+_SIDE_STREAMS = {}
+
+
+def _side_stream(eng: ActEngine) -> "torch.cuda.Stream":
+    key = (id(eng), torch.cuda.current_device())
+    if key not in _SIDE_STREAMS:
+        _SIDE_STREAMS[key] = torch.cuda.Stream()
+    return _SIDE_STREAMS[key]
+
+
 def train_step(eng: ActEngine, qpos, image, actions, is_pad, eps=None, dp_group=None) -> torch.Tensor:
     """Returns the device tensor [l1, kl, loss] of this rank's shard."""
     eng.zero_grad(overlap_forward=True)
     out = eng.forward(qpos, image, actions, is_pad, eps)
     if dp_group is None:
         eng.backward_and_step(1.0)
+    elif os.environ.get("ACT_DP_OVERLAP_OPT", "1") == "1":
+        backward_and_step_data_parallel(eng, dp_group, 1.0)
     else:
         backward_data_parallel(eng, dp_group, 1.0)
         eng.adamw_step()

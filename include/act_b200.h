@@ -155,6 +155,10 @@ int act_engine_zero_grad_async(act_engine* e, void* stream);
  * by act_engine_adamw_step(e, step, ...), with each parameter region's AdamW launched as soon as that region's
  * gradients are final so it overlaps the remaining backward.  Single-process only (no gradient all-reduce in between). */
 int act_engine_backward_and_step(act_engine* e, int step, float loss_grad, void* stream);
+/* AdamW of one parameter region (index as in act_engine_region; the backbone region also re-packs the conv operands).
+ * blocks_per_sm > 0 limits the launch to that many 256-thread blocks per SM so it can run beside tensor-core kernels.
+ * The data-parallel host loop uses it to update a region as soon as its gradient all-reduce has finished. */
+int act_engine_adamw_region(act_engine* e, int step, int region, int blocks_per_sm, void* stream);
 int act_engine_adamw_step(act_engine* e, int step, void* stream);
 int act_engine_set_lr(act_engine* e, float lr, float lr_backbone);
 int act_engine_launches(act_engine* e, int reset);
