@@ -106,7 +106,7 @@ class Engine {
                 bf16* out_bf16, cudaStream_t st);
   int linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cudaStream_t st);
   int attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv, const uint8_t* mask,
-               bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st);
+               bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st, bool v_on_aux = false);
   int attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv,
                const bf16* P, bf16* dQ, long long lddq, bf16* dK, long long lddk, bf16* dV, long long lddv, int B, int Lq,
                int Lk, cudaStream_t st);
@@ -165,6 +165,12 @@ class Engine {
   cudaStream_t wg_fork(cudaStream_t st, int lane = -1);   // stream to launch a weight gradient on (st itself if serial)
   cudaStream_t wg_gather(cudaStream_t st, int lane = 0);  // that lane of st's branch, ordered after st and every other lane
   int wg_join(cudaStream_t st);                 // st waits for every weight-gradient launch issued so far
+  // One auxiliary lane per branch for independent kernels inside a layer (V projection beside QK projection -> QK^T ->
+  // softmax; dV / dK beside the dP -> softmax-backward -> dQ chain; dx(v) beside dx(qk)).
+  cudaStream_t aux_[2] = {nullptr, nullptr};
+  cudaEvent_t aux_ev_[2] = {nullptr, nullptr}, aux_done_[2] = {nullptr, nullptr};
+  cudaStream_t aux_fork(cudaStream_t st);       // aux lane of st's branch, ordered after everything enqueued on st so far
+  int aux_join(cudaStream_t st);                // st waits for the aux lane
   bf16* gy_arena_ = nullptr;
   long long gy_cap_ = 0, gy_off_ = 0, gy_lim_ = 0, gy_cvae_base_ = 0;
   bf16* gy_alloc(long long elems);

@@ -82,13 +82,15 @@ int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K
                      int Lq, int Lk, cudaStream_t st) {
   const int h = cfg_.nheads, hd = 64, Lkp = roundup(Lk, 8);
   const long long ph = 1LL * Lq * Lkp, pb = 1LL * h * Lq * Lkp;
+  // dV and dK only feed the projections' gradients: they run on the aux lane beside dP -> softmax backward -> dQ
+  cudaStream_t ax = aux_fork(st);
   {  // dV[j,d] = sum_i P[i,j] dO[i,d]
     MatDesc a, b; EpiDesc e;
     a.ptr = P; a.mn_major = 1; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
     b.ptr = dO; b.mn_major = 1; b.ld = 512; b.sz0 = hd; b.sz1 = 1LL * Lq * 512;
     e.flags = EPI_OUT_BF16; e.out_bf16 = dV; e.ldc = lddv; e.osz0 = hd; e.osz1 = Lk * lddv;
     ++launches_;
-    if (tc_gemm(Lk, hd, Lq, h, B, a, b, e, 1, st)) return -1;
+    if (tc_gemm(Lk, hd, Lq, h, B, a, b, e, 1, ax)) return -1;
   }
   {  // dP[i,j] = sum_d dO[i,d] V[j,d]
     MatDesc a, b; EpiDesc e;
@@ -99,6 +101,15 @@ int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K
     if (tc_gemm(Lq, Lk, hd, h, B, a, b, e, 1, st)) return -1;
   }
   RUN(softmax_bwd(P, Sbuf_, dSbuf_, B * h * Lq, Lk, Lkp, 0.125f, st));
+  if (ax != st) ax = aux_fork(st);                   // dS is final
+  {  // dK[j,d] = sum_i dS[i,j] Q[i,d]
+    MatDesc a, b; EpiDesc e;
+    a.ptr = dSbuf_; a.mn_major = 1; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
+    b.ptr = Q; b.mn_major = 1; b.ld = ldq; b.sz0 = hd; b.sz1 = Lq * ldq;
+    e.flags = EPI_OUT_BF16; e.out_bf16 = dK; e.ldc = lddk; e.osz0 = hd; e.osz1 = Lk * lddk;
+    ++launches_;
+    if (tc_gemm(Lk, hd, Lq, h, B, a, b, e, 1, ax)) return -1;
+  }
   {  // dQ[i,d] = sum_j dS[i,j] K[j,d]
     MatDesc a, b; EpiDesc e;
     a.ptr = dSbuf_; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
@@ -107,14 +118,7 @@ int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K
     ++launches_;
     if (tc_gemm(Lq, hd, Lk, h, B, a, b, e, 1, st)) return -1;
   }
-  {  // dK[j,d] = sum_i dS[i,j] Q[i,d]
-    MatDesc a, b; EpiDesc e;
-    a.ptr = dSbuf_; a.mn_major = 1; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
-    b.ptr = Q; b.mn_major = 1; b.ld = ldq; b.sz0 = hd; b.sz1 = Lq * ldq;
-    e.flags = EPI_OUT_BF16; e.out_bf16 = dK; e.ldc = lddk; e.osz0 = hd; e.osz1 = Lk * lddk;
-    ++launches_;
-    if (tc_gemm(Lk, hd, Lq, h, B, a, b, e, 1, st)) return -1;
-  }
+  if (ax != st && aux_join(st)) return -1;
   return 0;
 }
 
@@ -138,8 +142,10 @@ int Engine::enc_layer_bwd(const EncW& w, EncActs& a, const float* x_in, const fl
   if (attn_bwd(gb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gqk, 2 * d, gqk + d, 2 * d, gv, d, B, L, L, st)) return -1;
   if (linear_dwb(gqk, M, w.sa.qk, a.xpb, st)) return -1;
   if (linear_dwb(gv, M, w.sa.v, a.xb, st)) return -1;
+  cudaStream_t ax = aux_fork(st);                    // the two input gradients are independent
+  if (linear_dx(gv, M, w.sa.v, 0, gA_, nullptr, dx_out, nullptr, ax)) return -1;
   if (linear_dx(gqk, M, w.sa.qk, 0, nullptr, nullptr, gxp_out, nullptr, st)) return -1;
-  if (linear_dx(gv, M, w.sa.v, 0, gA_, nullptr, dx_out, nullptr, st)) return -1;
+  if (ax != st && aux_join(st)) return -1;
   return 0;
 }
 

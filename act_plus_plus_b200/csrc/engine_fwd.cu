@@ -191,7 +191,7 @@ int Engine::linear(const bf16* X, int M, const LinW& w, uint32_t flags, const fl
 
 // softmax(Q K^T / sqrt(64) + mask) V per (batch, head); Q/K/V are strided head views of projection buffers.
 int Engine::attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv,
-                     const uint8_t* mask, bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st) {
+                     const uint8_t* mask, bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st, bool v_on_aux) {
   const int h = cfg_.nheads, hd = 64, Lkp = roundup(Lk, 8);
   MatDesc a, b;
   EpiDesc e;
@@ -202,6 +202,7 @@ int Engine::attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk,
   ++launches_;
   if (tc_gemm(Lq, Lk, hd, h, B, a, b, e, 1, st)) return -1;
   RUN(softmax_fwd(Sbuf_, mask, P, B * h * Lq, Lk, Lkp, h * Lq, st));
+  if (v_on_aux && aux_join(st)) return -1;           // V was projected on the aux lane
   MatDesc pa, vb;
   EpiDesc eo;
   pa.ptr = P; pa.ld = Lkp; pa.sz0 = 1LL * Lq * Lkp; pa.sz1 = 1LL * h * Lq * Lkp;
@@ -217,9 +218,10 @@ int Engine::enc_layer_fwd(const EncW& w, EncActs& a, const float* x, const float
                           const uint8_t* mask, int B, bool emit_next, bf16* next_xb, bf16* next_xpb, cudaStream_t st) {
   (void)pos;
   const int M = B * L, d = cfg_.hidden_dim;
+  cudaStream_t ax = aux_fork(st);                    // V projection beside QK projection -> QK^T -> softmax
+  if (linear(a.xb, M, w.sa.v, 0, nullptr, nullptr, a.v, nullptr, ax)) return -1;
   if (linear(a.xpb, M, w.sa.qk, 0, nullptr, nullptr, a.qk, nullptr, st)) return -1;
-  if (linear(a.xb, M, w.sa.v, 0, nullptr, nullptr, a.v, nullptr, st)) return -1;
-  if (attn_fwd(a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, mask, a.P, a.o, B, L, L, st)) return -1;
+  if (attn_fwd(a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, mask, a.P, a.o, B, L, L, st, ax != st)) return -1;
   if (linear(a.o, M, w.sa.o, 0, x, a.t1, nullptr, nullptr, st)) return -1;
   RUN(ln_fwd(a.t1, w.n1.g, w.n1.b, nullptr, 1, a.x1, a.x1b, nullptr, a.mean1, a.rstd1, M, d, st));
   if (linear(a.x1b, M, w.l1, EPI_RELU, nullptr, nullptr, a.hh, nullptr, st)) return -1;

@@ -14,6 +14,11 @@ Engine::~Engine() {
   if (side_) cudaStreamDestroy(side_);
   if (ev_stage_) cudaEventDestroy(ev_stage_);
   for (int b = 0; b < 2; ++b) {
+    if (aux_ev_[b]) cudaEventDestroy(aux_ev_[b]);
+    if (aux_done_[b]) cudaEventDestroy(aux_done_[b]);
+    if (aux_[b]) cudaStreamDestroy(aux_[b]);
+  }
+  for (int b = 0; b < 2; ++b) {
     if (wg_ev_[b]) cudaEventDestroy(wg_ev_[b]);
     for (int i = 0; i <= NWG; ++i) {
       if (wg_done_[b][i]) cudaEventDestroy(wg_done_[b][i]);
@@ -37,6 +42,11 @@ int Engine::ensure_streams() {
   ACT_CUDA(cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming));
   ACT_CUDA(cudaEventCreateWithFlags(&ev_stage_, cudaEventDisableTiming));
   for (int b = 0; b < 2; ++b) {
+    ACT_CUDA(cudaStreamCreateWithFlags(&aux_[b], cudaStreamNonBlocking));
+    ACT_CUDA(cudaEventCreateWithFlags(&aux_ev_[b], cudaEventDisableTiming));
+    ACT_CUDA(cudaEventCreateWithFlags(&aux_done_[b], cudaEventDisableTiming));
+  }
+  for (int b = 0; b < 2; ++b) {
     ACT_CUDA(cudaEventCreateWithFlags(&wg_ev_[b], cudaEventDisableTiming));
     for (int i = 0; i <= NWG; ++i) {
       ACT_CUDA(cudaStreamCreateWithFlags(&wg_[b][i], cudaStreamNonBlocking));
@@ -49,6 +59,24 @@ int Engine::fork_side(cudaStream_t st) {
   if (ensure_streams()) return -1;
   ACT_CUDA(cudaEventRecord(ev_fork_, st));
   ACT_CUDA(cudaStreamWaitEvent(side_, ev_fork_, 0));
+  return 0;
+}
+cudaStream_t Engine::aux_fork(cudaStream_t st) {
+  static int aux_on = -1;
+  if (aux_on < 0) { const char* e = getenv("ACT_AUX"); aux_on = !(e && e[0] == '0'); }
+  if (ensure_streams() || !concurrent_ || !aux_on) return st;
+  const int b = (st == side_) ? 1 : 0;
+  if (cudaEventRecord(aux_ev_[b], st) != cudaSuccess || cudaStreamWaitEvent(aux_[b], aux_ev_[b], 0) != cudaSuccess) {
+    set_error("aux lane fork failed");
+    return st;
+  }
+  return aux_[b];
+}
+int Engine::aux_join(cudaStream_t st) {
+  if (!side_ || !concurrent_) return 0;
+  const int b = (st == side_) ? 1 : 0;
+  ACT_CUDA(cudaEventRecord(aux_done_[b], aux_[b]));
+  ACT_CUDA(cudaStreamWaitEvent(st, aux_done_[b], 0));
   return 0;
 }
 cudaStream_t Engine::wg_fork(cudaStream_t st, int lane) {
