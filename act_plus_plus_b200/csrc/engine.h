@@ -106,17 +106,18 @@ class Engine {
                 bf16* out_bf16, cudaStream_t st);
   int linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cudaStream_t st);
   int attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv, const uint8_t* mask,
-               bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st, bool v_on_aux = false);
+               bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st, bool v_on_aux = false, float* S = nullptr);
   int attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv,
                const bf16* P, bf16* dQ, long long lddq, bf16* dK, long long lddk, bf16* dV, long long lddv, int B, int Lq,
-               int Lk, cudaStream_t st);
+               int Lk, cudaStream_t st, float* S = nullptr, bf16* dS = nullptr, bool use_aux = true);
   int enc_layer_fwd(const EncW& w, EncActs& a, const float* x, const float* pos, const float* next_pos, int L,
                     const uint8_t* mask, int B, bool emit_next, bf16* next_xb, bf16* next_xpb, cudaStream_t st);
   int enc_layer_bwd(const EncW& w, EncActs& a, const float* x_in, const float* dx2, const float* dx2b, float* dx_out,
                     float* gxp_out, int L, int B, cudaStream_t st);
   int backbone_fwd(int cam, int B, const float* image, cudaStream_t st);
   int backbone_bwd(int cam, int B, cudaStream_t st);
-  int dec_layer_fwd(int B, cudaStream_t st);
+  int dec_self_fwd(int B, cudaStream_t st);     // query self-attention block: depends on weights only
+  int dec_cross_fwd(int B, cudaStream_t st);    // cross-attention + FFN + norms on the encoder memory
   int transformer_bwd(float loss_grad, cudaStream_t st);
   int cvae_fwd(int B, const float* qpos, const float* actions, long long actions_bs, const uint8_t* is_pad,
                long long is_pad_bs, const float* eps, cudaStream_t st);
@@ -167,10 +168,15 @@ class Engine {
   int wg_join(cudaStream_t st);                 // st waits for every weight-gradient launch issued so far
   // One auxiliary lane per branch for independent kernels inside a layer (V projection beside QK projection -> QK^T ->
   // softmax; dV / dK beside the dP -> softmax-backward -> dQ chain; dx(v) beside dx(qk)).
-  cudaStream_t aux_[2] = {nullptr, nullptr};
-  cudaEvent_t aux_ev_[2] = {nullptr, nullptr}, aux_done_[2] = {nullptr, nullptr};
-  cudaStream_t aux_fork(cudaStream_t st);       // aux lane of st's branch, ordered after everything enqueued on st so far
-  int aux_join(cudaStream_t st);                // st waits for the aux lane
+  // Lane 1 carries the decoder's query self-attention block (forward: weights only, so it runs beside the main encoder;
+  // backward: a leaf after the cross-attention backward, so it runs beside the encoder backward) on private scratch.
+  cudaStream_t aux_[2][2] = {};
+  cudaEvent_t aux_ev_[2][2] = {}, aux_done_[2][2] = {};
+  bool aux_used_[2][2] = {};
+  cudaStream_t aux_fork(cudaStream_t st, int lane = 0);   // aux lane of st's branch, ordered after everything on st so far
+  int aux_join(cudaStream_t st, int lane = 0);            // st waits for that aux lane
+  float *Sbuf2_ = nullptr, *dgA_ = nullptr, *dgB_ = nullptr, *dgE_ = nullptr;
+  bf16 *dSbuf2_ = nullptr, *dgb2_ = nullptr;
   bf16* gy_arena_ = nullptr;
   long long gy_cap_ = 0, gy_off_ = 0, gy_lim_ = 0, gy_cvae_base_ = 0;
   bf16* gy_alloc(long long elems);

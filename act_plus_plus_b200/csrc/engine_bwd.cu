@@ -79,11 +79,13 @@ int Engine::linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cuda
 
 int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv,
                      const bf16* P, bf16* dQ, long long lddq, bf16* dK, long long lddk, bf16* dV, long long lddv, int B,
-                     int Lq, int Lk, cudaStream_t st) {
+                     int Lq, int Lk, cudaStream_t st, float* S, bf16* dS, bool use_aux) {
+  if (!S) S = Sbuf_;
+  if (!dS) dS = dSbuf_;
   const int h = cfg_.nheads, hd = 64, Lkp = roundup(Lk, 8);
   const long long ph = 1LL * Lq * Lkp, pb = 1LL * h * Lq * Lkp;
   // dV and dK only feed the projections' gradients: they run on the aux lane beside dP -> softmax backward -> dQ
-  cudaStream_t ax = aux_fork(st);
+  cudaStream_t ax = use_aux ? aux_fork(st) : st;
   {  // dV[j,d] = sum_i P[i,j] dO[i,d]
     MatDesc a, b; EpiDesc e;
     a.ptr = P; a.mn_major = 1; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
@@ -96,15 +98,15 @@ int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K
     MatDesc a, b; EpiDesc e;
     a.ptr = dO; a.ld = 512; a.sz0 = hd; a.sz1 = 1LL * Lq * 512;
     b.ptr = V; b.ld = ldv; b.sz0 = hd; b.sz1 = Lk * ldv;
-    e.flags = EPI_OUT_F32; e.out_f32 = Sbuf_; e.ldc = Lkp; e.osz0 = ph; e.osz1 = pb;
+    e.flags = EPI_OUT_F32; e.out_f32 = S; e.ldc = Lkp; e.osz0 = ph; e.osz1 = pb;
     ++launches_;
     if (tc_gemm(Lq, Lk, hd, h, B, a, b, e, 1, st)) return -1;
   }
-  RUN(softmax_bwd(P, Sbuf_, dSbuf_, B * h * Lq, Lk, Lkp, 0.125f, st));
+  RUN(softmax_bwd(P, S, dS, B * h * Lq, Lk, Lkp, 0.125f, st));
   if (ax != st) ax = aux_fork(st);                   // dS is final
   {  // dK[j,d] = sum_i dS[i,j] Q[i,d]
     MatDesc a, b; EpiDesc e;
-    a.ptr = dSbuf_; a.mn_major = 1; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
+    a.ptr = dS; a.mn_major = 1; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
     b.ptr = Q; b.mn_major = 1; b.ld = ldq; b.sz0 = hd; b.sz1 = Lq * ldq;
     e.flags = EPI_OUT_BF16; e.out_bf16 = dK; e.ldc = lddk; e.osz0 = hd; e.osz1 = Lk * lddk;
     ++launches_;
@@ -112,7 +114,7 @@ int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K
   }
   {  // dQ[i,d] = sum_j dS[i,j] K[j,d]
     MatDesc a, b; EpiDesc e;
-    a.ptr = dSbuf_; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
+    a.ptr = dS; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
     b.ptr = K; b.mn_major = 1; b.ld = ldk; b.sz0 = hd; b.sz1 = Lk * ldk;
     e.flags = EPI_OUT_BF16; e.out_bf16 = dQ; e.ldc = lddq; e.osz0 = hd; e.osz1 = Lq * lddq;
     ++launches_;
@@ -182,37 +184,45 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
   if (linear_dx(g3, Md, w.l2, 0, nullptr, a.hh, nullptr, ghh, st)) return -1;
   if (linear_dwb(ghh, Md, w.l1, a.y2b, st)) return -1;
   if (linear_dx(ghh, Md, w.l1, 0, gB_, nullptr, gA_, nullptr, st)) return -1;
-  // norm2, cross-attention
-  RUN(ln_bwd(gA_, nullptr, a.t2, a.mean2, a.rstd2, w.n2.g, gB_, g2, w.n2.gg, w.n2.gb, Md, d, st));
+  // norm2, cross-attention.  dgB_ (wrt y1) and dgE_ (wrt y1 + query_pos) are private to the decoder: the query
+  // self-attention backward below consumes them on lane 1 while this stream goes on with the encoder layers.
+  RUN(ln_bwd(gA_, nullptr, a.t2, a.mean2, a.rstd2, w.n2.g, dgB_, g2, w.n2.gg, w.n2.gb, Md, d, st));
   if (linear_dwb(g2, Md, w.ca.o, a.co, st)) return -1;
   if (linear_dx(g2, Md, w.ca.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
   if (attn_bwd(gb2_, a.q, d, a.k, d, a.cv, d, a.cP, gq, d, gk, d, gcv, d, B, nq, L_, st)) return -1;
   if (linear_dwb(gq, Md, w.ca.q, a.y1pb, st)) return -1;
-  if (linear_dx(gq, Md, w.ca.q, 0, nullptr, nullptr, gE_, nullptr, st)) return -1;          // wrt y1 + query_pos
+  if (linear_dx(gq, Md, w.ca.q, 0, nullptr, nullptr, dgE_, nullptr, st)) return -1;          // wrt y1 + query_pos
   if (linear_dwb(gk, Me, w.ca.k, mem_pb_, st)) return -1;
-  if (linear_dx(gk, Me, w.ca.k, 0, nullptr, nullptr, gMemPos_, nullptr, st)) return -1;      // wrt memory + pos
   if (linear_dwb(gcv, Me, w.ca.v, mem_b_, st)) return -1;
-  if (linear_dx(gcv, Me, w.ca.v, 0, nullptr, nullptr, gMem_, nullptr, st)) return -1;         // wrt memory
-  auto reduce_batch = [&](const float* src, long long batch_stride, int n, float* dst) {       // dst[j] += sum_b src[b*bs + j]
+  float* g_addpos = G("additional_pos_embed.weight");
+  float* g_query = G("query_embed.weight");
+  auto reduce_batch_on = [&](cudaStream_t s2, const float* src, long long batch_stride, int n, float* dst) {   // dst[j] += sum_b src[b*bs + j]
     SgemmArgs r;
     r.I = 1; r.J = n; r.R = B; r.A = one_; r.ai = act::lin(0); r.ar = act::lin(0);
     r.B = src; r.br = act::lin(batch_stride); r.bj = act::lin(1); r.C = dst; r.ci = act::lin(0); r.cj = act::lin(1); r.accumulate = 1;
     ++launches_;
-    return sgemm_generic(r, st);
+    return sgemm_generic(r, s2);
   };
-  float* g_addpos = G("additional_pos_embed.weight");
-  float* g_query = G("query_embed.weight");
+  auto reduce_batch = [&](const float* src, long long batch_stride, int n, float* dst) { return reduce_batch_on(st, src, batch_stride, n, dst); };
+  {   // query self-attention block: a leaf of the backward graph (its only consumers are weight / query_embed gradients)
+    cudaStream_t dl = aux_fork(st, 1);
+    if (reduce_batch_on(dl, dgE_, 1LL * nq * d, nq * d, g_query)) return -1;
+    RUN(ln_bwd(dgB_, dgE_, a.t1, a.mean1, a.rstd1, w.n1.g, dgA_, g1, w.n1.gg, w.n1.gb, Md, d, dl));
+    if (linear_dwb(g1, Md, w.sa.o, a.o, dl)) return -1;
+    if (linear_dx(g1, Md, w.sa.o, 0, nullptr, nullptr, nullptr, dgb2_, dl)) return -1;
+    if (attn_bwd(dgb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gqk, 2 * d, gqk + d, 2 * d, gv, d, B, nq, nq, dl, Sbuf2_, dSbuf2_, false)) return -1;
+    if (linear_dwb(gqk, Md, w.sa.qk, a.xpb, dl)) return -1;
+    if (linear_dwb(gv, Md, w.sa.v, a.xb, dl)) return -1;
+    if (linear_dx(gqk, Md, w.sa.qk, 0, nullptr, nullptr, dgE_, nullptr, dl)) return -1;
+    if (reduce_batch_on(dl, dgE_, 1LL * nq * d, nq * d, g_query)) return -1;
+  }
+  {   // memory gradients: the two cross-attention input projections are independent
+    cudaStream_t ax = aux_fork(st);
+    if (linear_dx(gcv, Me, w.ca.v, 0, nullptr, nullptr, gMem_, nullptr, ax)) return -1;         // wrt memory
+    if (linear_dx(gk, Me, w.ca.k, 0, nullptr, nullptr, gMemPos_, nullptr, st)) return -1;       // wrt memory + pos
+    if (ax != st && aux_join(st)) return -1;
+  }
   if (reduce_batch(gMemPos_, 1LL * L_ * d, 2 * d, g_addpos)) return -1;
-  if (reduce_batch(gE_, 1LL * nq * d, nq * d, g_query)) return -1;
-  // norm1 (input gradient = dt2 + query branch), self-attention over the queries
-  RUN(ln_bwd(gB_, gE_, a.t1, a.mean1, a.rstd1, w.n1.g, gA_, g1, w.n1.gg, w.n1.gb, Md, d, st));
-  if (linear_dwb(g1, Md, w.sa.o, a.o, st)) return -1;
-  if (linear_dx(g1, Md, w.sa.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
-  if (attn_bwd(gb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gqk, 2 * d, gqk + d, 2 * d, gv, d, B, nq, nq, st)) return -1;
-  if (linear_dwb(gqk, Md, w.sa.qk, a.xpb, st)) return -1;
-  if (linear_dwb(gv, Md, w.sa.v, a.xb, st)) return -1;
-  if (linear_dx(gqk, Md, w.sa.qk, 0, nullptr, nullptr, gE_, nullptr, st)) return -1;
-  if (reduce_batch(gE_, 1LL * nq * d, nq * d, g_query)) return -1;
   // main encoder, last layer first
   const float* dx2 = gMem_;
   const float* dx2b = gMemPos_;
@@ -250,7 +260,7 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
     if (linear_dwb(gtok, Mf, input_proj_, feat, st)) return -1;
     if (linear_dx(gtok, Mf, input_proj_, 0, nullptr, feat, nullptr, d_feat_ + 1LL * k * cfg_.batch_max * Hf_ * Wf_ * 512, st)) return -1;
   }
-  return 0;
+  return aux_join(st, 1);                            // the decoder self-attention backward (lane 1)
 }
 
 // Reverse of cvae_fwd: reparametrisation + KL, latent_proj, the 4 masked encoder layers, the token projections.

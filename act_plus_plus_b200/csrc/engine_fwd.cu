@@ -106,12 +106,15 @@ int Engine::alloc_workspace() {
   maskC_ = A_(uint8_t, Mc);
   const long long smax = 1LL * Bm * h * std::max(1LL * L_ * Lp_, 1LL * Lc_ * Lcp_);
   Sbuf_ = A_(float, smax);
+  Sbuf2_ = A_(float, 1LL * Bm * h * nq * nqp_);       // decoder self-attention scores (runs beside the encoder)
   latent_info_ = A_(float, 1LL * Bm * 2 * cfg_.latent_dim); mu_ = A_(float, 1LL * Bm * cfg_.latent_dim);
   logvar_ = A_(float, 1LL * Bm * cfg_.latent_dim); z_ = A_(float, 1LL * Bm * cfg_.latent_dim); eps_ = A_(float, 1LL * Bm * cfg_.latent_dim);
   hs_ = A_(float, Md * d); hs_mean_ = A_(float, Md); hs_rstd_ = A_(float, Md);
   a_hat_ = A_(float, Md * cfg_.action_dim); is_pad_hat_ = A_(float, Md); losses_ = A_(float, 8);
   if (cfg_.train) {
     dSbuf_ = A_(bf16, smax);
+    dSbuf2_ = A_(bf16, 1LL * Bm * h * nq * nqp_);
+    dgA_ = A_(float, Md * d); dgB_ = A_(float, Md * d); dgE_ = A_(float, Md * d); dgb2_ = A_(bf16, Md * d);
     d_a_hat_ = A_(float, Md * cfg_.action_dim); d_mu_ = A_(float, 1LL * Bm * cfg_.latent_dim);
     d_logvar_ = A_(float, 1LL * Bm * cfg_.latent_dim); d_hs_ = A_(float, Md * d); dz_ = A_(float, 1LL * Bm * cfg_.latent_dim);
     d_info_ = A_(float, 1LL * Bm * 2 * cfg_.latent_dim);
@@ -191,17 +194,18 @@ int Engine::linear(const bf16* X, int M, const LinW& w, uint32_t flags, const fl
 
 // softmax(Q K^T / sqrt(64) + mask) V per (batch, head); Q/K/V are strided head views of projection buffers.
 int Engine::attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv,
-                     const uint8_t* mask, bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st, bool v_on_aux) {
+                     const uint8_t* mask, bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st, bool v_on_aux, float* S) {
+  if (!S) S = Sbuf_;
   const int h = cfg_.nheads, hd = 64, Lkp = roundup(Lk, 8);
   MatDesc a, b;
   EpiDesc e;
   a.ptr = Q; a.ld = ldq; a.sz0 = hd; a.sz1 = Lq * ldq;
   b.ptr = K; b.ld = ldk; b.sz0 = hd; b.sz1 = Lk * ldk;
-  e.flags = EPI_OUT_F32; e.alpha = 0.125f; e.out_f32 = Sbuf_;
+  e.flags = EPI_OUT_F32; e.alpha = 0.125f; e.out_f32 = S;
   e.ldc = Lkp; e.osz0 = 1LL * Lq * Lkp; e.osz1 = 1LL * h * Lq * Lkp;
   ++launches_;
   if (tc_gemm(Lq, Lk, hd, h, B, a, b, e, 1, st)) return -1;
-  RUN(softmax_fwd(Sbuf_, mask, P, B * h * Lq, Lk, Lkp, h * Lq, st));
+  RUN(softmax_fwd(S, mask, P, B * h * Lq, Lk, Lkp, h * Lq, st));
   if (v_on_aux && aux_join(st)) return -1;           // V was projected on the aux lane
   MatDesc pa, vb;
   EpiDesc eo;
@@ -374,21 +378,28 @@ int Engine::backbone_fwd(int cam, int B, const float* image, cudaStream_t st) {
 
 // Decoder layer 0 (transformer.py:274-295) + the shared final norm (transformer.py:171-181); only index [0] of the
 // stacked intermediates is consumed downstream (detr_vae.py:245).
-int Engine::dec_layer_fwd(int B, cudaStream_t st) {
-  const int d = cfg_.hidden_dim, nq = cfg_.num_queries, Md = B * nq, Me = B * L_;
+int Engine::dec_self_fwd(int B, cudaStream_t st) {
+  const int d = cfg_.hidden_dim, nq = cfg_.num_queries, Md = B * nq;
   const DecW& w = dec_w_[0];
   DecActs& a = dec_a_;
   const float* qpos_embed = P("query_embed.weight");
   RUN(add_pos_cast(tgt0_, qpos_embed, nq, a.xb, a.xpb, Md, d, st));            // tgt = 0 (transformer.py:109)
   if (linear(a.xpb, Md, w.sa.qk, 0, nullptr, nullptr, a.qk, nullptr, st)) return -1;
   if (linear(a.xb, Md, w.sa.v, 0, nullptr, nullptr, a.v, nullptr, st)) return -1;
-  if (attn_fwd(a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, nullptr, a.P, a.o, B, nq, nq, st)) return -1;
+  if (attn_fwd(a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, nullptr, a.P, a.o, B, nq, nq, st, false, Sbuf2_)) return -1;
   if (linear(a.o, Md, w.sa.o, 0, tgt0_, a.t1, nullptr, nullptr, st)) return -1;
   RUN(ln_fwd(a.t1, w.n1.g, w.n1.b, qpos_embed, nq, a.y1, nullptr, a.y1pb, a.mean1, a.rstd1, Md, d, st));
   if (linear(a.y1pb, Md, w.ca.q, 0, nullptr, nullptr, a.q, nullptr, st)) return -1;
+  return 0;
+}
+int Engine::dec_cross_fwd(int B, cudaStream_t st) {
+  const int d = cfg_.hidden_dim, nq = cfg_.num_queries, Md = B * nq, Me = B * L_;
+  const DecW& w = dec_w_[0];
+  DecActs& a = dec_a_;
+  cudaStream_t ax = aux_fork(st);
+  if (linear(mem_b_, Me, w.ca.v, 0, nullptr, nullptr, a.cv, nullptr, ax)) return -1;
   if (linear(mem_pb_, Me, w.ca.k, 0, nullptr, nullptr, a.k, nullptr, st)) return -1;
-  if (linear(mem_b_, Me, w.ca.v, 0, nullptr, nullptr, a.cv, nullptr, st)) return -1;
-  if (attn_fwd(a.q, d, a.k, d, a.cv, d, nullptr, a.cP, a.co, B, nq, L_, st)) return -1;
+  if (attn_fwd(a.q, d, a.k, d, a.cv, d, nullptr, a.cP, a.co, B, nq, L_, st, ax != st)) return -1;
   if (linear(a.co, Md, w.ca.o, 0, a.y1, a.t2, nullptr, nullptr, st)) return -1;
   RUN(ln_fwd(a.t2, w.n2.g, w.n2.b, nullptr, 1, a.y2, a.y2b, nullptr, a.mean2, a.rstd2, Md, d, st));
   if (linear(a.y2b, Md, w.l1, EPI_RELU, nullptr, nullptr, a.hh, nullptr, st)) return -1;
@@ -436,6 +447,9 @@ int Engine::forward(int B, const float* qpos, const float* image, const float* a
   tc_set_sm_reserve(0);
   if (sc != st && join_side(st)) return -1;
   RUN(add_pos_cast(src_, pos_main_, L_, enc_a_[0].xb, enc_a_[0].xpb, B * L_, d, st));
+  // the decoder's query self-attention block reads weights only: lane 1 runs it beside the main encoder
+  cudaStream_t dl = aux_fork(st, 1);
+  if (dl != st && dec_self_fwd(B, dl)) return -1;
   const int nl = cfg_.enc_layers;
   for (int l = 0; l < nl; ++l) {
     const float* x = l == 0 ? src_ : enc_a_[l - 1].x2;
@@ -443,7 +457,9 @@ int Engine::forward(int B, const float* qpos, const float* image, const float* a
     if (enc_layer_fwd(enc_w_[l], enc_a_[l], x, pos_main_, pos_main_, L_, nullptr, B, true, more ? enc_a_[l + 1].xb : mem_b_,
                       more ? enc_a_[l + 1].xpb : mem_pb_, st)) return -1;
   }
-  if (dec_layer_fwd(B, st)) return -1;
+  if (dl == st) { if (dec_self_fwd(B, st)) return -1; }
+  else if (aux_join(st, 1)) return -1;
+  if (dec_cross_fwd(B, st)) return -1;
   const int Md = B * nq;
   g = SgemmArgs(); g.I = Md; g.J = A; g.R = d; g.A = hs_; g.ai = act::lin(d); g.ar = act::lin(1);
   g.B = P("action_head.weight"); g.br = act::lin(1); g.bj = act::lin(d); g.bias = P("action_head.bias");

@@ -13,11 +13,12 @@ Engine::~Engine() {
   if (ev_join_) cudaEventDestroy(ev_join_);
   if (side_) cudaStreamDestroy(side_);
   if (ev_stage_) cudaEventDestroy(ev_stage_);
-  for (int b = 0; b < 2; ++b) {
-    if (aux_ev_[b]) cudaEventDestroy(aux_ev_[b]);
-    if (aux_done_[b]) cudaEventDestroy(aux_done_[b]);
-    if (aux_[b]) cudaStreamDestroy(aux_[b]);
-  }
+  for (int b = 0; b < 2; ++b)
+    for (int l = 0; l < 2; ++l) {
+      if (aux_ev_[b][l]) cudaEventDestroy(aux_ev_[b][l]);
+      if (aux_done_[b][l]) cudaEventDestroy(aux_done_[b][l]);
+      if (aux_[b][l]) cudaStreamDestroy(aux_[b][l]);
+    }
   for (int b = 0; b < 2; ++b) {
     if (wg_ev_[b]) cudaEventDestroy(wg_ev_[b]);
     for (int i = 0; i <= NWG; ++i) {
@@ -41,11 +42,12 @@ int Engine::ensure_streams() {
   ACT_CUDA(cudaEventCreateWithFlags(&ev_fork_, cudaEventDisableTiming));
   ACT_CUDA(cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming));
   ACT_CUDA(cudaEventCreateWithFlags(&ev_stage_, cudaEventDisableTiming));
-  for (int b = 0; b < 2; ++b) {
-    ACT_CUDA(cudaStreamCreateWithFlags(&aux_[b], cudaStreamNonBlocking));
-    ACT_CUDA(cudaEventCreateWithFlags(&aux_ev_[b], cudaEventDisableTiming));
-    ACT_CUDA(cudaEventCreateWithFlags(&aux_done_[b], cudaEventDisableTiming));
-  }
+  for (int b = 0; b < 2; ++b)
+    for (int l = 0; l < 2; ++l) {
+      ACT_CUDA(cudaStreamCreateWithFlags(&aux_[b][l], cudaStreamNonBlocking));
+      ACT_CUDA(cudaEventCreateWithFlags(&aux_ev_[b][l], cudaEventDisableTiming));
+      ACT_CUDA(cudaEventCreateWithFlags(&aux_done_[b][l], cudaEventDisableTiming));
+    }
   for (int b = 0; b < 2; ++b) {
     ACT_CUDA(cudaEventCreateWithFlags(&wg_ev_[b], cudaEventDisableTiming));
     for (int i = 0; i <= NWG; ++i) {
@@ -61,22 +63,25 @@ int Engine::fork_side(cudaStream_t st) {
   ACT_CUDA(cudaStreamWaitEvent(side_, ev_fork_, 0));
   return 0;
 }
-cudaStream_t Engine::aux_fork(cudaStream_t st) {
+cudaStream_t Engine::aux_fork(cudaStream_t st, int lane) {
   static int aux_on = -1;
   if (aux_on < 0) { const char* e = getenv("ACT_AUX"); aux_on = !(e && e[0] == '0'); }
   if (ensure_streams() || !concurrent_ || !aux_on) return st;
   const int b = (st == side_) ? 1 : 0;
-  if (cudaEventRecord(aux_ev_[b], st) != cudaSuccess || cudaStreamWaitEvent(aux_[b], aux_ev_[b], 0) != cudaSuccess) {
+  if (cudaEventRecord(aux_ev_[b][lane], st) != cudaSuccess || cudaStreamWaitEvent(aux_[b][lane], aux_ev_[b][lane], 0) != cudaSuccess) {
     set_error("aux lane fork failed");
     return st;
   }
-  return aux_[b];
+  aux_used_[b][lane] = true;
+  return aux_[b][lane];
 }
-int Engine::aux_join(cudaStream_t st) {
+int Engine::aux_join(cudaStream_t st, int lane) {
   if (!side_ || !concurrent_) return 0;
   const int b = (st == side_) ? 1 : 0;
-  ACT_CUDA(cudaEventRecord(aux_done_[b], aux_[b]));
-  ACT_CUDA(cudaStreamWaitEvent(st, aux_done_[b], 0));
+  if (!aux_used_[b][lane]) return 0;
+  aux_used_[b][lane] = false;
+  ACT_CUDA(cudaEventRecord(aux_done_[b][lane], aux_[b][lane]));
+  ACT_CUDA(cudaStreamWaitEvent(st, aux_done_[b][lane], 0));
   return 0;
 }
 cudaStream_t Engine::wg_fork(cudaStream_t st, int lane) {
