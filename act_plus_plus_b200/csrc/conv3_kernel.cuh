@@ -26,7 +26,7 @@ struct Conv3Cfg {
 };
 
 template <int BN>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(320, 1)
 conv3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ CUtensorMap bmap,
              const __grid_constant__ TcParams p) {
   using Cfg = Conv3Cfg<BN>;
@@ -50,7 +50,7 @@ conv3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ C
     prefetch_tmap(&bmap);
     for (int s = 0; s < Cfg::NP; ++s) { mbar_init(&pfull[s], 1); mbar_init(&pempty[s], 1); }
     for (int s = 0; s < Cfg::NW; ++s) { mbar_init(&wfull[s], 1); mbar_init(&wempty[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 4); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 8); }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
@@ -124,8 +124,9 @@ conv3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ C
       }
     }
   } else {
-    // ============================================================== epilogue warps (2..5)
+    // ============================================================== epilogue warps (2..9): two per TMEM lane quadrant
     const int q = warp & 3;
+    const int cbeg = ((warp - 2) >> 2) * (BN / 2), cend = cbeg + BN / 2;
     const int r = q * 32 + lane;                       // accumulator row = patch-linear output position
     const int ph = r / p.PW, pw = r % p.PW;
     uint32_t lt = 0;
@@ -142,12 +143,12 @@ conv3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ C
       tc_fence_after();
       const uint32_t tmem_acc = tmem_base + acc * BN + (static_cast<uint32_t>(q * 32) << 16);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = cbeg; c0 < cend; c0 += 32) {
         uint32_t v[32];
         __syncwarp();
         tmem_ld_32x32(tmem_acc + c0, v);
         tmem_ld_wait();
-        if (c0 + 32 >= BN) {
+        if (c0 + 32 >= cend) {
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty[acc]);

@@ -96,6 +96,7 @@ class Engine {
   long long workspace_bytes() const { return ws_bytes_; }
   int launches() const { return launches_; }
   void reset_launches() { launches_ = 0; }
+  int set_concurrent(bool on) { if (ensure_streams()) return -1; concurrent_ = on; return 0; }
   void set_lr(float lr, float lr_backbone) { cfg_.lr = lr; cfg_.lr_backbone = lr_backbone; }
 
  private:

@@ -86,7 +86,7 @@ struct TcCfg {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int ACC_COLS = BN;                                   // one accumulator buffer
   static constexpr int TMEM_COLS = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;
-  static constexpr int THREADS = 192;
+  static constexpr int THREADS = 320;      // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue (two per TMEM lane quadrant)
   static constexpr int MAX_STAGES = 8;
 };
 
@@ -252,7 +252,7 @@ __device__ __forceinline__ void epi_store_chunk(const TcParams& p, const uint32_
 }
 
 template <int MODE, int A_MN, int B_MN, int BN>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(320, 1)
 tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUtensorMap amap1,
           const __grid_constant__ CUtensorMap amap2, const __grid_constant__ CUtensorMap amap3,
           const __grid_constant__ CUtensorMap bmap, const __grid_constant__ TcParams p, int num_stages) {
@@ -276,7 +276,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
     prefetch_tmap(&amap0);
     prefetch_tmap(&bmap);
     for (int s = 0; s < num_stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 4); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 8); }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
@@ -375,7 +375,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
           } else {
 #pragma unroll
             for (int k = 0; k < 4; ++k, ad += (A_MN ? 128 : 2), bd += (B_MN ? 128 : 2))
-              umma_bf16(tmem_d, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+              umma_bf16((p.debug & 4) ? tmem_base + (k & 1) * Cfg::ACC_COLS : tmem_d, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
           umma_commit(&empty_bar[s]);          // frees this smem stage when the MMAs above retire
         }
@@ -383,9 +383,12 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
       }
     }
   } else {
-    // ============================================================== epilogue warps (2..5)
+    // ============================================================== epilogue warps (2..9)
+    // Two warps per TMEM lane quadrant, each draining half of the tile's columns: for the single-round launches that
+    // dominate the step the epilogue is exposed latency, so its width matters more than its instruction count.
     const int q = warp & 3;                  // TMEM lane quadrant this warp may access
     const int r = q * 32 + lane;             // accumulator row handled by this thread
+    const int cbeg = ((warp - 2) >> 2) * (BN / 2), cend = cbeg + BN / 2;
     uint32_t lt = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
       const TileCoord c = decode_tile<MODE, BN>(p, t);
@@ -420,12 +423,12 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
       const uint32_t tmem_acc = tmem_base + acc * Cfg::ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
 
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = cbeg; c0 < cend; c0 += 32) {
         uint32_t v[32];
         __syncwarp();
         tmem_ld_32x32(tmem_acc + c0, v);
         tmem_ld_wait();
-        if (c0 + 32 >= BN) {                   // last chunk is in registers: hand the accumulator back to the MMA warp
+        if (c0 + 32 >= cend) {                 // last chunk is in registers: hand the accumulator back to the MMA warp
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty_bar[acc]);

@@ -347,7 +347,7 @@ static int launch_conv3(long long total, cudaStream_t stream, const CUtensorMap&
   const unsigned ctas = static_cast<unsigned>(std::min<long long>(total, 1LL * oversub() * num_sms()));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
-  ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(192), static_cast<size_t>(Cfg::SMEM), stream, am, bm, p));
+  ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(320), static_cast<size_t>(Cfg::SMEM), stream, am, bm, p));
   if (g_prof.on) { cudaEventRecord(e1, stream); g_prof.ev.push_back(e0); g_prof.ev.push_back(e1); g_prof.flops.push_back(g_next_flops); g_prof.label.push_back(g_next_label); }
   ACT_CUDA(cudaGetLastError());
   return 0;

@@ -223,6 +223,10 @@ class ActEngine:
         self._shared["version"] += 1
         self._synced_version = self._shared["version"]
 
+    def set_concurrent(self, on: bool):
+        """False: all launches in program order on the caller's stream (for per-kernel timing); call between steps."""
+        check(self.lib.act_engine_set_concurrent(self._h, 1 if on else 0), "act_engine_set_concurrent")
+
     def set_lr(self, lr: float, lr_backbone: float):
         check(self.lib.act_engine_set_lr(self._h, lr, lr_backbone), "act_engine_set_lr")
 

@@ -159,6 +159,9 @@ int act_engine_backward_and_step(act_engine* e, int step, float loss_grad, void*
  * blocks_per_sm > 0 limits the launch to that many 256-thread blocks per SM so it can run beside tensor-core kernels.
  * The data-parallel host loop uses it to update a region as soon as its gradient all-reduce has finished. */
 int act_engine_adamw_region(act_engine* e, int step, int region, int blocks_per_sm, void* stream);
+/* on = 0: every launch of this engine goes to the caller's stream in program order (no internal branches); used to time
+ * kernels one at a time.  Call only between steps (never between zero_grad_async / forward / backward of one step). */
+int act_engine_set_concurrent(act_engine* e, int on);
 int act_engine_adamw_step(act_engine* e, int step, void* stream);
 int act_engine_set_lr(act_engine* e, float lr, float lr_backbone);
 int act_engine_launches(act_engine* e, int reset);

@@ -43,7 +43,7 @@ GEMMS = [  # name, M, N, K, a_mn, b_mn, ksplit
     ("dw_ffn1", 3200, 512, 2416, 1, 1, 2), ("dw_ffn2", 512, 3200, 2416, 1, 1, 3), ("dw_attn", 512, 512, 2416, 1, 1, 10),
     ("stem_gemm", 614400, 64, 192, 0, 0, 1), ("big", 8192, 8192, 8192, 0, 0, 1),
 ]
-ATTN = [("enc_qkT", 302, 302, 64, 64, 0, 0), ("enc_pv", 302, 64, 304, 64, 0, 1), ("cvae_qkT", 102, 102, 64, 64, 0, 0)]
+ATTN = [("enc_qkT", 302, 304, 64, 64, 0, 0), ("enc_pv", 302, 64, 304, 64, 0, 1), ("cvae_qkT", 102, 104, 64, 64, 0, 0)]
 CONVS = [(8, 120, 160, 64, 64, 3, 1), (8, 60, 80, 128, 128, 3, 1), (8, 30, 40, 256, 256, 3, 1), (8, 15, 20, 512, 512, 3, 1),
          (8, 120, 160, 64, 128, 3, 2), (8, 60, 80, 128, 256, 3, 2)]
 
