@@ -173,6 +173,7 @@ extern "C" int act_engine_adamw_region(act_engine* e, int step, int region, int 
   if (region < 0 || region >= R_COUNT) { set_error("act_engine_adamw_region: bad region"); return -1; }
   return e->eng->adamw_region(region, step, ST(stream), blocks_per_sm);
 }
+extern "C" int act_engine_set_image_format(act_engine* e, int fmt) { return e->eng->set_image_format(fmt); }
 extern "C" int act_engine_set_concurrent(act_engine* e, int on) { return e->eng->set_concurrent(on != 0); }
 extern "C" int act_engine_set_lr(act_engine* e, float lr, float lr_backbone) { e->eng->set_lr(lr, lr_backbone); return 0; }
 extern "C" int act_engine_launches(act_engine* e, int reset) { const int n = e->eng->launches(); if (reset) e->eng->reset_launches(); return n; }

@@ -96,6 +96,9 @@ class Engine {
   long long workspace_bytes() const { return ws_bytes_; }
   int launches() const { return launches_; }
   void reset_launches() { launches_ = 0; }
+  // 0: image is float32 [B, K, 3, H, W] in [0, 1] (policy.py:264 signature); 1: uint8 [B, K, H, W, 3] (dataset frames)
+  int set_image_format(int fmt) { if (fmt != 0 && fmt != 1) { set_error("image format must be 0 (f32 CHW) or 1 (u8 HWC)"); return -1; } image_fmt_ = fmt; return 0; }
+  int image_fmt_ = 0;
   int set_concurrent(bool on) { if (ensure_streams()) return -1; concurrent_ = on; return 0; }
   void set_lr(float lr, float lr_backbone) { cfg_.lr = lr; cfg_.lr_backbone = lr_backbone; }
 

@@ -327,8 +327,13 @@ int Engine::backbone_fwd(int cam, int B, const float* image, cudaStream_t st) {
   const int K = cfg_.num_cameras, H = fh_[0], W = fw_[0], d = cfg_.hidden_dim;
   CamW& cw = cam_w_[cam];
   CamActs& ca = cam_a_[cam];
-  const float* img = image + 1LL * cam * 3 * H * W;
-  RUN(stem_pack_image(img, 1LL * K * 3 * H * W, ca.xp, B, H, W, Wp_, st));
+  if (image_fmt_ == 1) {
+    const uint8_t* img8 = reinterpret_cast<const uint8_t*>(image) + 1LL * cam * H * W * 3;
+    RUN(stem_pack_image_u8(img8, 1LL * K * H * W * 3, ca.xp, B, H, W, Wp_, st));
+  } else {
+    const float* img = image + 1LL * cam * 3 * H * W;
+    RUN(stem_pack_image(img, 1LL * K * 3 * H * W, ca.xp, B, H, W, Wp_, st));
+  }
   {
     ConvLaunch c;
     if (stem_launch(cam, B, &c, nullptr)) return -1;

@@ -366,6 +366,37 @@ __global__ void stem_pack_image_kernel(const float* __restrict__ img, long long 
     reinterpret_cast<uint2*>(out)[i] = o;
   }
 }
+// Same for the dataset's native layout (utils.py:133-158 keeps uint8 HWC frames and divides by 255 on the host): pixel
+// (y, x) of camera `cam` is img[b][cam][y][x][0..3) uint8; x/255 is formed in fp32 exactly like `image_data / 255.0`.
+__global__ void stem_pack_image_u8_kernel(const uint8_t* __restrict__ img, long long img_bs, bf16* __restrict__ out,
+                                          int B, int H, int W, int Wp) {
+  pdl_trigger(); pdl_wait();
+  const float mean[3] = {0.485f, 0.456f, 0.406f};
+  const float istd[3] = {1.f / 0.229f, 1.f / 0.224f, 1.f / 0.225f};
+  const long long total = 1LL * B * H * Wp;
+  for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
+    const int xp = static_cast<int>(i % Wp);
+    const long long r = i / Wp;
+    const int y = static_cast<int>(r % H), b = static_cast<int>(r / H);
+    const int x = xp - 3;
+    float v[3] = {0.f, 0.f, 0.f};
+    if (x >= 0 && x < W) {
+      const uint8_t* px = img + b * img_bs + (1LL * y * W + x) * 3;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[c] = (static_cast<float>(__ldg(px + c)) / 255.0f - mean[c]) * istd[c];
+    }
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], 0.f);
+    uint2 o;
+    o.x = *reinterpret_cast<uint32_t*>(&lo); o.y = *reinterpret_cast<uint32_t*>(&hi);
+    reinterpret_cast<uint2*>(out)[i] = o;
+  }
+}
+int stem_pack_image_u8(const uint8_t* img_cam, long long img_bs, bf16* out, int B, int H, int W, int Wp, cudaStream_t st) {
+  const long long total = 1LL * B * H * Wp;
+  stem_pack_image_u8_kernel<<<static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16)), 256, 0, st>>>(img_cam, img_bs, out, B, H, W, Wp);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
 int stem_pack_image(const float* img_cam, long long img_bs, bf16* out, int B, int H, int W, int Wp, cudaStream_t st) {
   const long long total = 1LL * B * H * Wp;
   stem_pack_image_kernel<<<static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16)), 256, 0, st>>>(img_cam, img_bs, out, B, H, W, Wp);

@@ -52,6 +52,7 @@ int maxpool_fwd(const bf16* x, bf16* y, uint8_t* idx, int N, int H, int W, int C
 int maxpool_bwd(const bf16* dy, const uint8_t* idx, const bf16* x, bf16* dx, int N, int H, int W, int C, cudaStream_t st);
 // image fp32 [B,3,H,W] (batch stride img_bs) -> ImageNet-normalised NHWC4 bf16 [B][H][Wp][4], 3 zero pixels left pad
 int stem_pack_image(const float* img_cam, long long img_bs, bf16* out, int B, int H, int W, int Wp, cudaStream_t st);
+int stem_pack_image_u8(const uint8_t* img_cam, long long img_bs, bf16* out, int B, int H, int W, int Wp, cudaStream_t st);
 int im2col_conv1(const float* img_cam, long long img_bs, bf16* out, int B, int H, int W, int KP, cudaStream_t st);
 
 // ---- optim.cu

@@ -148,8 +148,17 @@ class ActEngine:
         B = qpos.shape[0]
         assert qpos.is_cuda and image.is_cuda, "inputs must be CUDA tensors"
         qpos = qpos.contiguous().float()
-        image = image.contiguous().float()
-        assert image.shape == (B, c.num_cameras, 3, c.img_h, c.img_w), f"image shape {tuple(image.shape)}"
+        if image.dtype == torch.uint8:             # dataset-native frames [B, K, H, W, 3]: /255 + normalise fused on device
+            image = image.contiguous()
+            assert image.shape == (B, c.num_cameras, c.img_h, c.img_w, 3), f"uint8 image shape {tuple(image.shape)}"
+            fmt = 1
+        else:
+            image = image.contiguous().float()
+            assert image.shape == (B, c.num_cameras, 3, c.img_h, c.img_w), f"image shape {tuple(image.shape)}"
+            fmt = 0
+        if fmt != getattr(self, "_image_fmt", 0):
+            check(self.lib.act_engine_set_image_format(self._h, fmt), "act_engine_set_image_format")
+            self._image_fmt = fmt
         assert qpos.shape[1] == c.state_dim
         out = dict(a_hat=torch.empty((B, c.num_queries, c.action_dim), dtype=torch.float32, device=self.device))
         iph = torch.empty((B, c.num_queries, 1), dtype=torch.float32, device=self.device) if want_is_pad_hat else None

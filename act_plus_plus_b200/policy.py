@@ -153,7 +153,11 @@ class DETRVAE(nn.Module):
         return eng
 
     def _engine_for(self, qpos, image, train: bool) -> ActEngine:
-        B, H, W = int(qpos.shape[0]), int(image.shape[-2]), int(image.shape[-1])
+        B = int(qpos.shape[0])
+        if image.dtype == torch.uint8:                 # dataset-native frames [B, K, H, W, 3]
+            H, W = int(image.shape[2]), int(image.shape[3])
+        else:
+            H, W = int(image.shape[-2]), int(image.shape[-1])
         key = (H, W, bool(train))
         eng = self._engines.get(key)
         if eng is None or eng.cfg.batch_max < B:

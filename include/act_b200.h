@@ -162,6 +162,11 @@ int act_engine_adamw_region(act_engine* e, int step, int region, int blocks_per_
 /* on = 0: every launch of this engine goes to the caller's stream in program order (no internal branches); used to time
  * kernels one at a time.  Call only between steps (never between zero_grad_async / forward / backward of one step). */
 int act_engine_set_concurrent(act_engine* e, int on);
+/* Layout of the `image` argument of the following act_engine_forward calls: 0 = float32 [B, K, 3, H, W] in [0, 1] (the
+ * reference call signature, policy.py:264); 1 = uint8 [B, K, H, W, 3], the dataset's native frames (utils.py:133-158
+ * divides by 255 and permutes on the host) -- the /255, the ImageNet normalisation and the layout change are fused into
+ * the stem's image pack, and the host->device copy shrinks 4x. */
+int act_engine_set_image_format(act_engine* e, int fmt);
 int act_engine_adamw_step(act_engine* e, int step, void* stream);
 int act_engine_set_lr(act_engine* e, float lr, float lr_backbone);
 int act_engine_launches(act_engine* e, int reset);

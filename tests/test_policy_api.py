@@ -148,3 +148,69 @@ def test_input_prefetcher_delivers_batches_in_order():
     for i, (x, y) in enumerate(seen):
         assert x == float(i)
         assert torch.equal(y.cpu(), torch.arange(8) + i)
+
+
+def test_uint8_hwc_ingest_equals_float_path():
+    """Dataset-native uint8 [B,K,H,W,3] frames (utils.py:133-158) through the fused ingest == the reference-side
+    `einsum('k h w c -> k c h w') / 255.0` float path, bit for bit (same fp32 division, same bf16 packing)."""
+    from act_plus_plus_b200.engine import ActEngine
+    from act_plus_plus_b200.policy import _init_like_reference
+    B, K, H, W = 2, 1, 96, 128
+    g = torch.Generator(device="cpu").manual_seed(11)
+    u8 = torch.randint(0, 256, (B, K, H, W, 3), generator=g, dtype=torch.uint8)
+    f32 = (u8.permute(0, 1, 4, 2, 3).float() / 255.0).contiguous()
+    qpos = torch.randn((B, 14), generator=g)
+    eng = ActEngine(batch_max=B, num_cameras=K, img_h=H, img_w=W, train=False)
+    _init_like_reference(eng, seed=2)
+    a = eng.forward(qpos.cuda(), f32.cuda())["a_hat"].clone()
+    b = eng.forward(qpos.cuda(), u8.cuda())["a_hat"].clone()
+    c = eng.forward(qpos.cuda(), f32.cuda())["a_hat"].clone()       # switching back works too
+    torch.cuda.synchronize()
+    assert torch.equal(a, b) and torch.equal(a, c)
+    assert a.abs().max().item() > 0
+
+
+def test_checkpoint_file_round_trip(tmp_path):
+    """imitate_episodes.py:614-619 saves `policy.serialize()` with torch.save and :168-177 restores it with
+    `policy.deserialize(torch.load(...))`: a checkpoint written by one policy object must reproduce the same actions in
+    a fresh one, keep the reference's key names, and the optimiser state (which the reference never saves) round-trips."""
+    from act_plus_plus_b200.policy import ACTPolicy
+    gold, cfg, sd, batch, K = _load_case("small_k1")
+    pol = ACTPolicy(_policy_config(K))
+    pol.deserialize({"model." + k: v for k, v in sd.items()})
+    pol.cuda(); pol.train()
+    opt = pol.configure_optimizers()
+    for _ in range(2):
+        opt.zero_grad()
+        pol(batch["qpos"], batch["image"], batch["actions"], batch["is_pad"])["loss"].backward()
+        opt.step()
+    pol.eval()
+    with torch.inference_mode():
+        a_ref = pol(batch["qpos"], batch["image"]).clone()
+    ck = tmp_path / "policy_last.ckpt"
+    torch.save(pol.serialize(), ck)
+    torch.save(opt.state_dict(), tmp_path / "optim.ckpt")
+    loaded = torch.load(ck, map_location="cpu")
+    assert set(loaded) == {"model." + k for k in sd}, "checkpoint keys must be the reference's state_dict names"
+    pol2 = ACTPolicy(_policy_config(K))
+    st = pol2.deserialize(loaded)
+    assert not st.missing_keys and not st.unexpected_keys
+    pol2.cuda(); pol2.eval()
+    with torch.inference_mode():
+        a2 = pol2(batch["qpos"], batch["image"]).clone()
+    assert torch.equal(a_ref, a2)
+    # optimiser state: continue training from the restored moments == continue in the original object
+    opt2 = pol2.configure_optimizers()
+    opt2.load_state_dict(torch.load(tmp_path / "optim.ckpt", map_location="cpu"))
+    eps = torch.randn((batch["qpos"].shape[0], 32), device="cuda")
+    outs = []
+    for p, o in ((pol, opt), (pol2, opt2)):
+        p.train()
+        eng = p.model._engine_for(batch["qpos"], batch["image"], True)
+        eng.zero_grad()
+        eng.forward(batch["qpos"], batch["image"], batch["actions"][:, :100], batch["is_pad"][:, :100], eps)
+        eng.backward(0, 1.0)
+        o.step()
+        outs.append(p.serialize()["model.action_head.weight"].clone())
+    torch.cuda.synchronize()
+    assert torch.allclose(outs[0], outs[1], rtol=0, atol=2e-6)

@@ -1,0 +1,57 @@
+"""2-rank data-parallel parity: two DP steps on shards of 8 must equal two single-process steps on the full batch of 16
+(gradient averaging of equal shards == full-batch mean).  Launch with torchrun --nproc-per-node 2."""
+import os
+import sys
+import torch
+import torch.distributed as dist
+sys.path.insert(0, ".")
+from act_plus_plus_b200.engine import ActEngine, R_BACKBONE, R_CVAE, R_MAIN
+from act_plus_plus_b200.policy import _init_like_reference
+from act_plus_plus_b200.train import train_step
+
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+Bs, H, W = 4, 96, 128
+B = Bs * world
+g = torch.Generator(device="cpu").manual_seed(7)
+full = dict(image=torch.rand((B, 1, 3, H, W), generator=g), qpos=torch.randn((B, 14), generator=g),
+            actions=torch.randn((B, 100, 16), generator=g), is_pad=(torch.arange(100)[None].repeat(B, 1) >= 70),
+            eps=torch.randn((B, 32), generator=g))
+full = {k: v.cuda() for k, v in full.items()}
+mine = {k: v[rank * Bs:(rank + 1) * Bs].contiguous() for k, v in full.items()}
+eng = ActEngine(batch_max=Bs, img_h=H, img_w=W, train=True)
+_init_like_reference(eng, seed=3)
+eng.set_lr(1e-3, 1e-3)
+for _ in range(2):
+    train_step(eng, mine["qpos"], mine["image"], mine["actions"], mine["is_pad"], mine["eps"], dist.group.WORLD)
+torch.cuda.synchronize()
+ok = True
+if rank == 0:
+    ref = ActEngine(batch_max=B, img_h=H, img_w=W, train=True)
+    _init_like_reference(ref, seed=3)
+    p0 = ref.flat_params.clone()
+    ref.set_lr(1e-3, 1e-3)
+    for _ in range(2):
+        train_step(ref, full["qpos"], full["image"], full["actions"], full["is_pad"], full["eps"])
+    torch.cuda.synchronize()
+    for name, r in (("main", R_MAIN), ("cvae", R_CVAE), ("backbone", R_BACKBONE)):
+        off, n = ref.region(r)
+        d = (eng.flat_params[off:off + n] - ref.flat_params[off:off + n]).abs()
+        moved = (ref.flat_params[off:off + n] - p0[off:off + n]).abs().mean().item()
+        frac = (d > 0.5 * moved).float().mean().item()
+        good = moved > 2e-4 and d.mean().item() <= 0.05 * moved and frac < 2e-2
+        ok &= good
+        print(f"dp_check {name}: moved {moved:.3e} mean|dp-full| {d.mean().item():.3e} diverging {frac:.2e} {'OK' if good else 'FAIL'}")
+t = torch.tensor([1.0 if ok else 0.0], device="cuda")
+dist.broadcast(t, 0)
+# all ranks must hold identical parameters after the averaged update
+chk = eng.flat_params.double().sum().reshape(1)
+lst = [torch.zeros_like(chk) for _ in range(world)]
+dist.all_gather(lst, chk)
+same = all(torch.equal(lst[0], x) for x in lst)
+if rank == 0:
+    print("dp_check replicas identical:", same)
+torch.cuda.synchronize()
+sys.stdout.flush()
+os._exit(0 if (t.item() == 1.0 and same) else 1)
