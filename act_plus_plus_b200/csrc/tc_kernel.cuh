@@ -74,6 +74,7 @@ struct TcParams {
   long long ldc, ldr;                   // GEMM: row strides of out / residual
   long long osz0, osz1, rsz0, rsz1;     // GEMM: batch strides of out / residual
   int vec_ok;                           // all epilogue pointers / strides allow 16-byte vector access
+  int vec32_ok;                         // ... and the outputs allow 32-byte (sector-wide) stores
   int debug;                            // experiment switches (ACT_TC_DEBUG): 1 = skip epilogue math+stores, 2 = skip TMA loads
 };
 
@@ -227,6 +228,11 @@ __device__ __forceinline__ void epi_store_chunk(const TcParams& p, const uint32_
 #pragma unroll
         for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) atomicAdd(op + j, f[j]);
       }
+    } else if (full && p.vec32_ok) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 8)
+        st_global_v8(op + j, __float_as_uint(f[j]), __float_as_uint(f[j + 1]), __float_as_uint(f[j + 2]), __float_as_uint(f[j + 3]),
+                     __float_as_uint(f[j + 4]), __float_as_uint(f[j + 5]), __float_as_uint(f[j + 6]), __float_as_uint(f[j + 7]));
     } else if (full) {
 #pragma unroll
       for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
@@ -236,7 +242,16 @@ __device__ __forceinline__ void epi_store_chunk(const TcParams& p, const uint32_
   }
   if (p.flags & EPI_OUT_BF16) {
     __nv_bfloat16* op = p.out_bf16 + o_off + gn0;
-    if (full) {
+    if (full && p.vec32_ok) {
+      uint32_t w[16];
+#pragma unroll
+      for (int e = 0; e < 16; ++e) {
+        const __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * e], f[2 * e + 1]);
+        w[e] = *reinterpret_cast<const uint32_t*>(&h);
+      }
+      st_global_v8(op, w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7]);
+      st_global_v8(op + 16, w[8], w[9], w[10], w[11], w[12], w[13], w[14], w[15]);
+    } else if (full) {
 #pragma unroll
       for (int j = 0; j < 32; j += 8) {
         uint4 u;

@@ -216,6 +216,11 @@ void plan_splitk(int M, int N, int K, int* bn_out, int* ks_out) {
 }
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+static bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; }
+// NHWC outputs: every pixel offset is a multiple of og.ld (and of og.sn), so 32-byte stores need ld % 16 (bf16)
+static bool conv_out32(const ConvLaunch& c) {
+  return aligned32(c.epi.out_f32) && aligned32(c.epi.out_bf16) && c.og.ld % 16 == 0 && c.og.sn % 16 == 0;
+}
 
 static void fill_epi(TcParams& p, const EpiDesc& e) {
   p.flags = e.flags; p.alpha = e.alpha; p.bias = e.bias; p.scale = e.scale; p.res_f32 = e.res_f32;
@@ -256,6 +261,8 @@ int tc_gemm(int M, int N, int K, int nz0, int nz1, const MatDesc& A, const MatDe
              (epi.rsz0 % 8 == 0) && (epi.rsz1 % 8 == 0) && aligned16(epi.out_f32) && aligned16(epi.out_bf16) &&
              aligned16(epi.res_f32) && aligned16(epi.res_bf16) && aligned16(epi.aux_bf16);
   p.vec_ok = vec ? 1 : 0;
+  p.vec32_ok = vec && aligned32(epi.out_f32) && aligned32(epi.out_bf16) &&
+               (!epi.out_bf16 || (epi.ldc % 16 == 0 && epi.osz0 % 16 == 0 && epi.osz1 % 16 == 0));
   CUtensorMap am[4], bm;
   if (mat_tmap(&am[0], A, M, K, nz0, nz1, 128)) return -1;
   am[1] = am[2] = am[3] = am[0];
@@ -318,6 +325,7 @@ int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint, int stages_hi
   p.vec_ok = (c.og.ld % 8 == 0) && (c.rg.ld % 8 == 0 || !(c.epi.flags & (EPI_RES_F32 | EPI_RES_BF16))) &&
              aligned16(c.epi.out_f32) && aligned16(c.epi.out_bf16) && aligned16(c.epi.res_f32) &&
              aligned16(c.epi.res_bf16) && aligned16(c.epi.aux_bf16);
+  p.vec32_ok = p.vec_ok && conv_out32(c);
   const long long mtiles = 1LL * p.tiles_w * p.tiles_h * tiles_n;
   int bn = bn_hint;
   if (bn == 0) bn = pick_bn(c.Cout, mtiles, c.ntaps * (c.Cin / 64));
@@ -390,6 +398,7 @@ int tc_conv3(const ConvLaunch& c, cudaStream_t stream, int bn_hint) {
   p.vec_ok = (c.og.ld % 8 == 0) && (c.rg.ld % 8 == 0 || !(c.epi.flags & (EPI_RES_F32 | EPI_RES_BF16))) &&
              aligned16(c.epi.out_f32) && aligned16(c.epi.out_bf16) && aligned16(c.epi.res_f32) &&
              aligned16(c.epi.res_bf16) && aligned16(c.epi.aux_bf16);
+  p.vec32_ok = p.vec_ok && conv_out32(c);
   { static int dbg = -1; if (dbg < 0) { const char* e = getenv("ACT_TC_DEBUG"); dbg = e ? atoi(e) : 0; } p.debug = dbg; }
   const long long mtiles = 1LL * p.tiles_w * p.tiles_h * c.NIMG;
   int bn = bn_hint;
