@@ -105,9 +105,9 @@ class Engine {
  private:
   // ---- helpers (engine_fwd.cu / engine_bwd.cu)
   int linear(const bf16* X, int M, const LinW& w, uint32_t flags, const float* res_f32, float* out_f32, bf16* out_bf16,
-             const bf16* aux, cudaStream_t st);
+             const bf16* aux, cudaStream_t st, bool splitk = false);
   int linear_dx(const bf16* dY, int M, const LinW& w, uint32_t flags, const float* res_f32, const bf16* aux, float* out_f32,
-                bf16* out_bf16, cudaStream_t st);
+                bf16* out_bf16, cudaStream_t st, bool splitk = false);
   int linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cudaStream_t st);
   int attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv, const uint8_t* mask,
                bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st, bool v_on_aux = false, float* S = nullptr);
@@ -181,6 +181,18 @@ class Engine {
   int aux_join(cudaStream_t st, int lane = 0);            // st waits for that aux lane
   float *Sbuf2_ = nullptr, *dgA_ = nullptr, *dgB_ = nullptr, *dgE_ = nullptr;
   bf16 *dSbuf2_ = nullptr, *dgb2_ = nullptr;
+  // Long-K GEMMs with few output tiles (K = 3200: FFN down-projection forward, FFN up-projection data gradient) run
+  // split-K with fp32 reductions into PRE-ZEROED outputs (bias / residual are added by the first split only).  The
+  // zeroing happens on a weight-gradient lane at the start of forward / backward, long before the outputs are needed.
+  cudaEvent_t ev_zero_f_ = nullptr, ev_zero_b_ = nullptr;
+  bool zero_f_pending_ = false, zero_b_pending_ = false;
+  float* gz_arena_ = nullptr;                   // zeroed fp32 outputs of the backward split-K GEMMs (one slice per layer)
+  long long gz_cap_ = 0, gz_off_ = 0;
+  float* gz_alloc(long long elems);
+  long long gz_cvae_base_ = 0;
+  static bool splitk_on() { static int v = -1; if (v < 0) { const char* e = getenv("ACT_SPLITK"); v = !(e && e[0] == '0'); } return v != 0; }
+  int zero_backward_outputs(cudaStream_t st);
+  int zero_forward_outputs(cudaStream_t st, bool with_cvae);
   bf16* gy_arena_ = nullptr;
   long long gy_cap_ = 0, gy_off_ = 0, gy_lim_ = 0, gy_cvae_base_ = 0;
   bf16* gy_alloc(long long elems);

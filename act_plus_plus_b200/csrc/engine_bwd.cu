@@ -52,14 +52,19 @@ __global__ void conv1_grad_fold_kernel(const float* __restrict__ tmp, const floa
 
 // dX[M,K] = dY[M,N] * W[N,K]   (A = dY K-major, B = W read MN-major)
 int Engine::linear_dx(const bf16* dY, int M, const LinW& w, uint32_t flags, const float* res_f32, const bf16* aux,
-                      float* out_f32, bf16* out_bf16, cudaStream_t st) {
+                      float* out_f32, bf16* out_bf16, cudaStream_t st, bool splitk) {
   MatDesc A, B;
   A.ptr = dY; A.ld = w.N; B.ptr = w.w; B.mn_major = 1; B.ld = w.K;
   EpiDesc e;
   e.flags = flags | (out_f32 ? EPI_OUT_F32 : 0) | (out_bf16 ? EPI_OUT_BF16 : 0) | (res_f32 ? EPI_RES_F32 : 0) | (aux ? EPI_MASK_POS : 0);
   e.res_f32 = res_f32; e.out_f32 = out_f32; e.out_bf16 = out_bf16; e.aux_bf16 = aux; e.ldc = w.K; e.ldr = w.K;
+  int bn = 0, ks = 1;
+  if (splitk && splitk_on() && out_f32 && !out_bf16 && !aux && !(flags & EPI_RELU)) {   // caller pre-zeroed out_f32
+    plan_splitk(M, w.K, w.N, &bn, &ks);
+    if (ks > 1) e.flags |= EPI_ATOMIC; else bn = 0;
+  }
   ++launches_;
-  return tc_gemm(M, w.K, w.N, 1, 1, A, B, e, 1, st);
+  return tc_gemm(M, w.K, w.N, 1, 1, A, B, e, ks, st, bn);
 }
 
 // dW[N,K] += dY^T X ; db[N] += colsum(dY)
@@ -137,8 +142,11 @@ int Engine::enc_layer_bwd(const EncW& w, EncActs& a, const float* x_in, const fl
   if (linear_dwb(g1, M, w.l2, a.hh, st)) return -1;
   if (linear_dx(g1, M, w.l2, 0, nullptr, a.hh, nullptr, ghh, st)) return -1;
   if (linear_dwb(ghh, M, w.l1, a.x1b, st)) return -1;
-  if (linear_dx(ghh, M, w.l1, 0, gA_, nullptr, gB_, nullptr, st)) return -1;
-  RUN(ln_bwd(gB_, nullptr, a.t1, a.mean1, a.rstd1, w.n1.g, gA_, g1b, w.n1.gg, w.n1.gb, M, d, st));
+  float* gBz = splitk_on() ? gz_alloc(1LL * M * d) : gB_;        // zeroed slice: the K = 3200 data gradient runs split-K
+  if (!gBz) return -1;
+  if (zero_b_pending_) ACT_CUDA(cudaStreamWaitEvent(st, ev_zero_b_, 0));
+  if (linear_dx(ghh, M, w.l1, 0, gA_, nullptr, gBz, nullptr, st, true)) return -1;
+  RUN(ln_bwd(gBz, nullptr, a.t1, a.mean1, a.rstd1, w.n1.g, gA_, g1b, w.n1.gg, w.n1.gb, M, d, st));
   if (linear_dwb(g1b, M, w.sa.o, a.o, st)) return -1;
   if (linear_dx(g1b, M, w.sa.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
   if (attn_bwd(gb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gqk, 2 * d, gqk + d, 2 * d, gv, d, B, L, L, st)) return -1;
@@ -173,6 +181,7 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
   RUN(sgemm_generic(g, st));
   // shared final norm, norm3, FFN  (every dY that a deferred weight gradient reads lives in the arena)
   gy_off_ = 0; gy_lim_ = gy_cvae_base_;
+  gz_off_ = 0;
   const int ff = cfg_.dim_ff;
   bf16 *g3 = gy_alloc(1LL * Md * d), *ghh = gy_alloc(1LL * Md * ff), *g2 = gy_alloc(1LL * Md * d), *gq = gy_alloc(1LL * Md * d);
   bf16 *gk = gy_alloc(1LL * Me * d), *gcv = gy_alloc(1LL * Me * d), *g1 = gy_alloc(1LL * Md * d), *gqk = gy_alloc(2LL * Md * d);
@@ -183,10 +192,13 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
   if (linear_dwb(g3, Md, w.l2, a.hh, st)) return -1;
   if (linear_dx(g3, Md, w.l2, 0, nullptr, a.hh, nullptr, ghh, st)) return -1;
   if (linear_dwb(ghh, Md, w.l1, a.y2b, st)) return -1;
-  if (linear_dx(ghh, Md, w.l1, 0, gB_, nullptr, gA_, nullptr, st)) return -1;
+  float* gAz = splitk_on() ? gz_alloc(1LL * Md * d) : gA_;
+  if (!gAz) return -1;
+  if (zero_b_pending_) ACT_CUDA(cudaStreamWaitEvent(st, ev_zero_b_, 0));
+  if (linear_dx(ghh, Md, w.l1, 0, gB_, nullptr, gAz, nullptr, st, true)) return -1;
   // norm2, cross-attention.  dgB_ (wrt y1) and dgE_ (wrt y1 + query_pos) are private to the decoder: the query
   // self-attention backward below consumes them on lane 1 while this stream goes on with the encoder layers.
-  RUN(ln_bwd(gA_, nullptr, a.t2, a.mean2, a.rstd2, w.n2.g, dgB_, g2, w.n2.gg, w.n2.gb, Md, d, st));
+  RUN(ln_bwd(gAz, nullptr, a.t2, a.mean2, a.rstd2, w.n2.g, dgB_, g2, w.n2.gg, w.n2.gb, Md, d, st));
   if (linear_dwb(g2, Md, w.ca.o, a.co, st)) return -1;
   if (linear_dx(g2, Md, w.ca.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
   if (attn_bwd(gb2_, a.q, d, a.k, d, a.cv, d, a.cP, gq, d, gk, d, gcv, d, B, nq, L_, st)) return -1;
@@ -269,6 +281,7 @@ int Engine::cvae_bwd(cudaStream_t st) {
   const int Mc = B * Lc_, nl = cfg_.enc_layers;
   const long long ts = 1LL * Lc_ * d;
   gy_off_ = gy_cvae_base_; gy_lim_ = gy_cap_;
+  gz_off_ = gz_cvae_base_;
   RUN(reparam_bwd(dz_, eps_, logvar_, d_mu_, d_logvar_, d_info_, B, Z, st));
   SgemmArgs g;
   const float* cls_out = cvae_a_[nl - 1].x2;
@@ -401,6 +414,7 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st) {
   if (ensure_streams()) return -1;
   if (!concurrent_) return backward(0, loss_grad, st) || adamw(step, st) ? -1 : 0;
   if (wg_join(st)) return -1;                               // an asynchronous zero_grad
+  if (zero_backward_outputs(st)) return -1;
   if (transformer_bwd(loss_grad, st)) return -1;
   if (fork_side(st)) return -1;
   if (cvae_bwd(side_)) return -1;
@@ -429,6 +443,7 @@ int Engine::backward(int stage, float loss_grad, cudaStream_t st) {
   ACT_CHECK(cfg_.train && grads_ != nullptr, "engine has no training workspace / gradient buffer");
   ACT_CHECK(have_actions_ && cur_B_ > 0, "backward needs a preceding training forward (with actions)");
   if (wg_join(st)) return -1;                               // an asynchronous zero_grad
+  if (zero_backward_outputs(st)) return -1;
   if (stage == 0 || stage == 1) { if (transformer_bwd(loss_grad, st)) return -1; }
   // After the transformer the CVAE-encoder branch (needs dz) and the backbone branch (needs d_feat) share no buffers:
   // stage 0 / 4 run them as two parallel branches (side stream), stages 2 and 3 one at a time on the caller's stream.

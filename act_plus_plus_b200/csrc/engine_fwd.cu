@@ -126,6 +126,9 @@ int Engine::alloc_workspace() {
       const long long per_row = 3LL * d + 2 * d + ff;                 // gb1 x2, gbv, gbqk, gbhh
       gy_cap_ = cfg_.enc_layers * (Me + Mc) * (per_row + 512) + (Md * (per_row + 4 * d) + 2 * Me * d) + 1LL * Bm * Hf_ * Wf_ * d * cfg_.num_cameras + 64 * 256;
       gy_arena_ = A_(bf16, gy_cap_);
+      gz_cap_ = cfg_.enc_layers * (Me + Mc) * d + Md * d + 64 * 32;
+      gz_arena_ = A_(float, gz_cap_);
+      gz_cvae_base_ = gz_cap_ - (cfg_.enc_layers * Mc * d + 32 * 32);
       gy_cvae_base_ = gy_cap_ - (cfg_.enc_layers * Mc * (per_row + 512) + 16 * 256);
     }
     d_src_ = A_(float, Me * d); d_tokC_ = A_(float, Mc * d);
@@ -180,7 +183,7 @@ int Engine::alloc_workspace() {
 
 // --------------------------------------------------------------------------------------------- GEMM helpers
 int Engine::linear(const bf16* X, int M, const LinW& w, uint32_t flags, const float* res_f32, float* out_f32,
-                   bf16* out_bf16, const bf16* aux, cudaStream_t st) {
+                   bf16* out_bf16, const bf16* aux, cudaStream_t st, bool splitk) {
   MatDesc A, B;
   A.ptr = X; A.ld = w.K; B.ptr = w.w; B.ld = w.K;
   EpiDesc e;
@@ -188,8 +191,27 @@ int Engine::linear(const bf16* X, int M, const LinW& w, uint32_t flags, const fl
             (res_f32 ? EPI_RES_F32 : 0) | (aux ? EPI_MASK_POS : 0);
   e.bias = w.b; e.res_f32 = res_f32; e.out_f32 = out_f32; e.out_bf16 = out_bf16; e.aux_bf16 = aux;
   e.ldc = w.N; e.ldr = w.N;
+  int bn = 0, ks = 1;
+  if (splitk && splitk_on() && out_f32 && !out_bf16 && !aux && !(flags & EPI_RELU)) {   // caller pre-zeroed out_f32
+    plan_splitk(M, w.N, w.K, &bn, &ks);
+    if (ks > 1) e.flags |= EPI_ATOMIC; else bn = 0;
+  }
   ++launches_;
-  return tc_gemm(M, w.N, w.K, 1, 1, A, B, e, 1, st);
+  return tc_gemm(M, w.N, w.K, 1, 1, A, B, e, ks, st, bn);
+}
+
+// Zero the fp32 outputs of the forward split-K GEMMs (the FFN down-projections) on a weight-gradient lane.
+int Engine::zero_forward_outputs(cudaStream_t st, bool with_cvae) {
+  if (!splitk_on()) return 0;
+  cudaStream_t z = wg_fork(st, 1);
+  const int d = cfg_.hidden_dim;
+  const long long Me = 1LL * cur_B_ * L_, Mc = 1LL * cur_B_ * Lc_, Md = 1LL * cur_B_ * cfg_.num_queries;
+  for (auto& a : enc_a_) ACT_CUDA(cudaMemsetAsync(a.t2, 0, sizeof(float) * Me * d, z));
+  if (with_cvae) for (auto& a : cvae_a_) ACT_CUDA(cudaMemsetAsync(a.t2, 0, sizeof(float) * Mc * d, z));
+  ACT_CUDA(cudaMemsetAsync(dec_a_.t3, 0, sizeof(float) * Md * d, z));
+  zero_f_pending_ = z != st;
+  if (zero_f_pending_) ACT_CUDA(cudaEventRecord(ev_zero_f_, z));
+  return 0;
 }
 
 // softmax(Q K^T / sqrt(64) + mask) V per (batch, head); Q/K/V are strided head views of projection buffers.
@@ -229,7 +251,8 @@ int Engine::enc_layer_fwd(const EncW& w, EncActs& a, const float* x, const float
   if (linear(a.o, M, w.sa.o, 0, x, a.t1, nullptr, nullptr, st)) return -1;
   RUN(ln_fwd(a.t1, w.n1.g, w.n1.b, nullptr, 1, a.x1, a.x1b, nullptr, a.mean1, a.rstd1, M, d, st));
   if (linear(a.x1b, M, w.l1, EPI_RELU, nullptr, nullptr, a.hh, nullptr, st)) return -1;
-  if (linear(a.hh, M, w.l2, 0, a.x1, a.t2, nullptr, nullptr, st)) return -1;
+  if (zero_f_pending_) ACT_CUDA(cudaStreamWaitEvent(st, ev_zero_f_, 0));      // a.t2 was zeroed for the split-K reduction
+  if (linear(a.hh, M, w.l2, 0, a.x1, a.t2, nullptr, nullptr, st, true)) return -1;
   RUN(ln_fwd(a.t2, w.n2.g, w.n2.b, next_pos, L, a.x2, emit_next ? next_xb : nullptr, emit_next ? next_xpb : nullptr,
              a.mean2, a.rstd2, M, d, st));
   return 0;
@@ -408,7 +431,8 @@ int Engine::dec_cross_fwd(int B, cudaStream_t st) {
   if (linear(a.co, Md, w.ca.o, 0, a.y1, a.t2, nullptr, nullptr, st)) return -1;
   RUN(ln_fwd(a.t2, w.n2.g, w.n2.b, nullptr, 1, a.y2, a.y2b, nullptr, a.mean2, a.rstd2, Md, d, st));
   if (linear(a.y2b, Md, w.l1, EPI_RELU, nullptr, nullptr, a.hh, nullptr, st)) return -1;
-  if (linear(a.hh, Md, w.l2, 0, a.y2, a.t3, nullptr, nullptr, st)) return -1;
+  if (zero_f_pending_) ACT_CUDA(cudaStreamWaitEvent(st, ev_zero_f_, 0));
+  if (linear(a.hh, Md, w.l2, 0, a.y2, a.t3, nullptr, nullptr, st, true)) return -1;
   RUN(ln_fwd(a.t3, w.n3.g, w.n3.b, nullptr, 1, a.y3, nullptr, nullptr, a.mean3, a.rstd3, Md, d, st));
   RUN(ln_fwd(a.y3, dec_norm_.g, dec_norm_.b, nullptr, 1, hs_, nullptr, nullptr, hs_mean_, hs_rstd_, Md, d, st));
   return 0;
@@ -426,6 +450,7 @@ int Engine::forward(int B, const float* qpos, const float* image, const float* a
   cur_B_ = B; have_actions_ = actions != nullptr;
   in_qpos_ = qpos; in_image_ = image; in_actions_ = actions; in_actions_bs_ = actions_bs; in_is_pad_ = is_pad; in_is_pad_bs_ = is_pad_bs;
   ACT_CUDA(cudaMemcpyAsync(pos_main_, P("additional_pos_embed.weight"), sizeof(float) * 2 * d, cudaMemcpyDeviceToDevice, st));
+  if (ensure_streams() || zero_forward_outputs(st, have_actions_)) return -1;
   // The CVAE encoder (-> z -> latent token) and the camera backbones (-> image tokens) are independent until the main
   // encoder reads src_: the CVAE branch runs on the side stream so its small launches fill the SMs the convs leave idle.
   cudaStream_t sc = st;

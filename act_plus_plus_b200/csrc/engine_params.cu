@@ -13,6 +13,8 @@ Engine::~Engine() {
   if (ev_join_) cudaEventDestroy(ev_join_);
   if (side_) cudaStreamDestroy(side_);
   if (ev_stage_) cudaEventDestroy(ev_stage_);
+  if (ev_zero_f_) cudaEventDestroy(ev_zero_f_);
+  if (ev_zero_b_) cudaEventDestroy(ev_zero_b_);
   for (int b = 0; b < 2; ++b)
     for (int l = 0; l < 2; ++l) {
       if (aux_ev_[b][l]) cudaEventDestroy(aux_ev_[b][l]);
@@ -42,6 +44,8 @@ int Engine::ensure_streams() {
   ACT_CUDA(cudaEventCreateWithFlags(&ev_fork_, cudaEventDisableTiming));
   ACT_CUDA(cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming));
   ACT_CUDA(cudaEventCreateWithFlags(&ev_stage_, cudaEventDisableTiming));
+  ACT_CUDA(cudaEventCreateWithFlags(&ev_zero_f_, cudaEventDisableTiming));
+  ACT_CUDA(cudaEventCreateWithFlags(&ev_zero_b_, cudaEventDisableTiming));
   for (int b = 0; b < 2; ++b)
     for (int l = 0; l < 2; ++l) {
       ACT_CUDA(cudaStreamCreateWithFlags(&aux_[b][l], cudaStreamNonBlocking));
@@ -113,6 +117,21 @@ int Engine::wg_join(cudaStream_t st) {
       ACT_CUDA(cudaStreamWaitEvent(st, wg_done_[b][i], 0));
       wg_used_[b][i] = false;
     }
+  return 0;
+}
+float* Engine::gz_alloc(long long elems) {
+  elems = (elems + 31) & ~31LL;
+  if (gz_off_ + elems > gz_cap_) { set_error("backward split-K output arena overflow"); return nullptr; }
+  float* p = gz_arena_ + gz_off_;
+  gz_off_ += elems;
+  return p;
+}
+int Engine::zero_backward_outputs(cudaStream_t st) {
+  if (!splitk_on() || !gz_arena_) return 0;
+  cudaStream_t z = wg_fork(st, 1);
+  ACT_CUDA(cudaMemsetAsync(gz_arena_, 0, sizeof(float) * gz_cap_, z));
+  zero_b_pending_ = z != st;
+  if (zero_b_pending_) ACT_CUDA(cudaEventRecord(ev_zero_b_, z));
   return 0;
 }
 bf16* Engine::cgy_alloc(long long elems) {

@@ -144,8 +144,9 @@ __device__ __forceinline__ void ldg32(const float* __restrict__ ptr, float (&dst
 
 // Fused epilogue of one 32-column accumulator chunk of one row: alpha, per-column scale / bias, fp32 / bf16 residual,
 // ReLU, ReLU-mask against a saved activation, fp32 / bf16 / atomic output.  o_off / r_off = element offsets of the row.
+// `addends` = false for k-splits other than the first: bias and residual are added exactly once per output element.
 __device__ __forceinline__ void epi_store_chunk(const TcParams& p, const uint32_t (&v)[32], int gn0, long long o_off,
-                                                long long r_off) {
+                                                long long r_off, bool addends = true) {
   float f[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
@@ -160,7 +161,7 @@ __device__ __forceinline__ void epi_store_chunk(const TcParams& p, const uint32_
       for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] *= __ldg(p.scale + gn0 + j);
     }
   }
-  if (p.flags & EPI_BIAS) {
+  if ((p.flags & EPI_BIAS) && addends) {
     if (full) {
       float bi[32];
       ldg32(p.bias + gn0, bi);
@@ -170,7 +171,7 @@ __device__ __forceinline__ void epi_store_chunk(const TcParams& p, const uint32_
       for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += __ldg(p.bias + gn0 + j);
     }
   }
-  if (p.flags & EPI_RES_F32) {
+  if ((p.flags & EPI_RES_F32) && addends) {
     const float* rp = p.res_f32 + r_off + gn0;
     if (full) {
 #pragma unroll
@@ -182,7 +183,7 @@ __device__ __forceinline__ void epi_store_chunk(const TcParams& p, const uint32_
       for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += rp[j];
     }
   }
-  if (p.flags & EPI_RES_BF16) {
+  if ((p.flags & EPI_RES_BF16) && addends) {
     const __nv_bfloat16* rp = p.res_bf16 + r_off + gn0;
     if (full) {
 #pragma unroll
@@ -459,7 +460,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
             if (gn0 + j < p.Cout) atomicAdd(op + static_cast<long long>(j) * p.Cin, __uint_as_float(v[j]) * p.alpha);
           continue;
         }
-        epi_store_chunk(p, v, gn0, o_off, r_off);
+        epi_store_chunk(p, v, gn0, o_off, r_off, p.ksplit <= 1 || c.kb_begin == 0);
       }
     }
   }

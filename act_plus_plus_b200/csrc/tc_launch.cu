@@ -248,6 +248,7 @@ int tc_gemm(int M, int N, int K, int nz0, int nz1, const MatDesc& A, const MatDe
   if (check_epi(epi)) return -1;
   if (ksplit < 1) ksplit = 1;
   if (ksplit > 1) ACT_CHECK(epi.flags & EPI_ATOMIC, "split-K needs the atomic epilogue");
+  if (ksplit > 1) ACT_CHECK(!(epi.flags & (EPI_RELU | EPI_MASK_POS)), "split-K cannot apply a non-linear epilogue");
   const int nb = nz0 * nz1;
   const int mt = (M + 127) / 128;
   int bn = bn_hint;
