@@ -191,6 +191,8 @@ class Engine {
   float* gz_alloc(long long elems);
   long long gz_cvae_base_ = 0;
   static bool splitk_on() { static int v = -1; if (v < 0) { const char* e = getenv("ACT_SPLITK"); v = !(e && e[0] == '0'); } return v != 0; }
+  // the forward stays bit-reproducible by default (split-K reduction order is not); ACT_SPLITK_FWD=1 opts in
+  static bool splitk_fwd_on() { static int v = -1; if (v < 0) { const char* e = getenv("ACT_SPLITK_FWD"); v = (e && e[0] == '1'); } return v != 0 && splitk_on(); }
   int zero_backward_outputs(cudaStream_t st);
   int zero_forward_outputs(cudaStream_t st, bool with_cvae);
   bf16* gy_arena_ = nullptr;

@@ -192,7 +192,8 @@ int Engine::linear(const bf16* X, int M, const LinW& w, uint32_t flags, const fl
   e.bias = w.b; e.res_f32 = res_f32; e.out_f32 = out_f32; e.out_bf16 = out_bf16; e.aux_bf16 = aux;
   e.ldc = w.N; e.ldr = w.N;
   int bn = 0, ks = 1;
-  if (splitk && splitk_on() && out_f32 && !out_bf16 && !aux && !(flags & EPI_RELU)) {   // caller pre-zeroed out_f32
+  // opt-in, training calls only: the fp32 reduction order of a split-K launch is not reproducible
+  if (splitk && splitk_fwd_on() && have_actions_ && out_f32 && !out_bf16 && !aux && !(flags & EPI_RELU)) {   // caller pre-zeroed out_f32
     plan_splitk(M, w.N, w.K, &bn, &ks);
     if (ks > 1) e.flags |= EPI_ATOMIC; else bn = 0;
   }
@@ -202,7 +203,8 @@ int Engine::linear(const bf16* X, int M, const LinW& w, uint32_t flags, const fl
 
 // Zero the fp32 outputs of the forward split-K GEMMs (the FFN down-projections) on a weight-gradient lane.
 int Engine::zero_forward_outputs(cudaStream_t st, bool with_cvae) {
-  if (!splitk_on()) return 0;
+  zero_f_pending_ = false;
+  if (!splitk_fwd_on() || !have_actions_) return 0;
   cudaStream_t z = wg_fork(st, 1);
   const int d = cfg_.hidden_dim;
   const long long Me = 1LL * cur_B_ * L_, Mc = 1LL * cur_B_ * Lc_, Md = 1LL * cur_B_ * cfg_.num_queries;
