@@ -89,6 +89,9 @@ class Engine {
   int zero_grad(cudaStream_t st, bool async = false);
   int adamw(int step, cudaStream_t st);
   int adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm = 0);
+  int adamw_range(long long off, long long n, float lr, bool shadow, int step, cudaStream_t st, int blocks_per_sm);
+  int inline_opt_step_ = 0;                      // > 0 while backward_and_step runs: cvae_bwd updates each layer as soon as its gradients are final
+  long long cvae_layer_off_[16] = {0}, cvae_layer_n_[16] = {0};
   // backward(0) + adamw() with the optimiser of each parameter region trailing that region's last weight gradient, so
   // the HBM-bound AdamW of the transformer / CVAE regions overlaps the tensor-bound backbone backward
   int backward_and_step(int step, float loss_grad, cudaStream_t st);

@@ -301,6 +301,11 @@ int Engine::cvae_bwd(cudaStream_t st) {
   for (int l = nl - 1; l >= 0; --l) {
     if (enc_layer_bwd(cvae_w_[l], cvae_a_[l], nullptr, dx2, dx2b, gC_, gD_, Lc_, B, st)) return -1;
     dx2 = gC_; dx2b = gD_;
+    if (inline_opt_step_ > 0 && l < 16 && cvae_layer_n_[l] > 0) {
+      // this layer's gradients are final and nothing below reads its weights: update it under the remaining layers
+      cudaStream_t wg = wg_gather(st, NWG);
+      if (adamw_range(cvae_layer_off_[l], cvae_layer_n_[l], cfg_.lr, true, inline_opt_step_, wg, 3)) return -1;
+    }
   }
   RUN(add_out(gC_, gD_, d_tokC_, 1LL * Mc * d, st));
   // token 0: cls_embed ; token 1: encoder_joint_proj(qpos) ; tokens 2..: encoder_action_proj(actions)
@@ -417,14 +422,21 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st) {
   if (zero_backward_outputs(st)) return -1;
   if (transformer_bwd(loss_grad, st)) return -1;
   if (fork_side(st)) return -1;
-  if (cvae_bwd(side_)) return -1;
+  inline_opt_step_ = step;
+  const int cvae_rc = cvae_bwd(side_);
+  inline_opt_step_ = 0;
+  if (cvae_rc) return -1;
   {   // MAIN / DEAD regions: every gradient and every read of these weights is ordered before this point of lane 0
     cudaStream_t wg = wg_gather(st, NWG);
     if (adamw_region(R_MAIN, step, wg, 3) || adamw_region(R_DEAD, step, wg, 3)) return -1;
   }
-  {   // CVAE region trails the CVAE branch's weight gradients
+  {   // CVAE region: the encoder layers were updated inside cvae_bwd, the token projections / latent_proj follow here
     cudaStream_t wg = wg_gather(side_, NWG);
-    if (adamw_region(R_CVAE, step, wg, 6)) return -1;
+    const int nl = std::min(cfg_.enc_layers, 16);
+    const long long tail = cvae_layer_off_[nl - 1] + cvae_layer_n_[nl - 1];
+    const long long head_n = cvae_layer_off_[0] - region_off_[R_CVAE];
+    if (adamw_range(region_off_[R_CVAE], head_n, cfg_.lr, true, step, wg, 6)) return -1;
+    if (adamw_range(tail, region_off_[R_CVAE] + region_n_[R_CVAE] - tail, cfg_.lr, true, step, wg, 6)) return -1;
   }
   cgy_off_ = 0;
   tc_set_sm_reserve(sm_reserve_);

@@ -256,6 +256,16 @@ void Engine::build_tensor_table() {
     region_n_[r] = off - region_off_[r];
   }
   total_floats_ = off;
+  for (int l = 0; l < cfg_.enc_layers && l < 16; ++l) {     // contiguous span of CVAE-encoder layer l inside R_CVAE
+    const std::string pre = "encoder.layers." + std::to_string(l) + ".";
+    long long lo = -1, hi = -1;
+    for (auto& t : tensors_)
+      if (t.region == R_CVAE && t.name.compare(0, pre.size(), pre) == 0) {
+        if (lo < 0 || t.offset < lo) lo = t.offset;
+        hi = std::max(hi, t.offset + (t.numel + 7) / 8 * 8);
+      }
+    cvae_layer_off_[l] = lo; cvae_layer_n_[l] = hi - lo;
+  }
   for (size_t i = 0; i < tensors_.size(); ++i) index_[tensors_[i].name] = static_cast<int>(i);
 }
 
@@ -376,6 +386,16 @@ int Engine::zero_grad(cudaStream_t st, bool async) {
   return 0;
 }
 
+int Engine::adamw_range(long long off, long long n, float lr, bool shadow, int step, cudaStream_t st, int blocks_per_sm) {
+  ACT_CHECK(params_ && grads_ && m_ && v_, "optimizer state not bound");
+  if (n <= 0) return 0;
+  AdamWArgs a;
+  a.p = params_ + off; a.g = grads_ + off; a.m = m_ + off; a.v = v_ + off; a.shadow = shadow ? shadow_ + off : nullptr;
+  a.n = n; a.lr = lr; a.beta1 = cfg_.beta1; a.beta2 = cfg_.beta2; a.eps = cfg_.adam_eps; a.wd = cfg_.weight_decay;
+  a.step = step; a.mode = 0; a.background = blocks_per_sm;
+  ++launches_;
+  return adamw_step(a, st);
+}
 int Engine::adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm) {
   ACT_CHECK(params_ && grads_ && m_ && v_, "optimizer state not bound");
   AdamWArgs a;
