@@ -20,6 +20,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 B_PER_GPU, H, W, K_CAM, NQ, A_DIM, S_DIM, Z_DIM = 8, 480, 640, 1, 100, 16, 14, 32
+# mean DRAM bytes per tcgen05 launch of the step (ncu, profiles/r01_tc_dram_per_step.md): 2787.8 MB / 277 launches
+TC_DRAM_BYTES_PER_LAUNCH = 2787.8e6 / 277
 FLOP_PER_SAMPLE_TRAIN = 115.6e9        # live path (decoder layer 0 only), 3x forward
 ADAMW_BYTES = 83.9e6 * 28
 
@@ -272,27 +274,33 @@ def run_ours(args):
     ms = e0.elapsed_time(e1)
     # ---------------- end-to-end: pinned host inputs -> H2D -> step -> loss D2H, every step
     h2d = sum(v.numel() * v.element_size() for v in host[0].values())
+    from act_plus_plus_b200.train import InputPrefetcher
+    pf = InputPrefetcher(host[0], dev, depth=2)                      # staging buffers / copy stream: created once
+
+    def e2e_steps(n):
+        last = 0.0
+        pf.submit(host[0])
+        for i in range(n):
+            if i + 1 < n:
+                pf.submit(host[(i + 1) % NB])                        # H2D of the next step's inputs runs under this step
+            db = pf.next()
+            if graph is not None:
+                for k in stat:
+                    stat[k].copy_(db[k], non_blocking=True)
+                pf.consumed()
+                graph.replay()
+                ls = g_losses
+            else:
+                ls = step_direct(db)
+                pf.consumed()
+            last = float(ls[2].item())                               # device->host read of the step's loss
+        return last
+
+    e2e_steps(max(3, args.warmup))                                   # untimed warm-up of the host-driven loop
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
-    loss_host = 0.0
-    from act_plus_plus_b200.train import InputPrefetcher
-    pf = InputPrefetcher(host[0], dev, depth=2)
-    pf.submit(host[0])
-    for i in range(args.steps):
-        if i + 1 < args.steps:
-            pf.submit(host[(i + 1) % NB])                            # H2D of the next step's inputs runs under this step
-        db = pf.next()
-        if graph is not None:
-            for k in stat:
-                stat[k].copy_(db[k], non_blocking=True)
-            pf.consumed()
-            graph.replay()
-            ls = g_losses
-        else:
-            ls = step_direct(db)
-            pf.consumed()
-        loss_host = float(ls[2].item())                              # device->host read of the step's loss
+    loss_host = e2e_steps(args.steps)
     f1.record()
     barrier()
     ms_e2e = f0.elapsed_time(f1)
@@ -341,7 +349,9 @@ def run_ours(args):
                 e2e=dict(value=n_samples / (ms_e2e / 1e3), unit="samples/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=4),
                 gpu_launches=launches_per_step * args.steps,
                 roofline=dict(bound="tensor", achieved=tc_tflops, peak=peaks["tf_sust"], unit="TFLOP/s",
-                              frac=tc_tflops / peaks["tf_sust"], traffic=None, peak_source=peaks["src"] + " (sustained bf16)",
+                              frac=tc_tflops / peaks["tf_sust"], traffic=TC_DRAM_BYTES_PER_LAUNCH, peak_source=peaks["src"] + " (sustained bf16)",
+                              traffic_source="profiles/r01_tc_dram_per_step.md: ncu dram__bytes_read+write summed over the 277 tcgen05 launches "
+                                             "of one step (cold cache per launch) / 277",
                               kernel="tc_kernel<*> (all tcgen05 GEMM/conv/wgrad launches of one step)",
                               launches_per_step=nl.value // PSTEPS, tc_ms_per_step=tc_ms_step,
                               timing="CUDA events around every launch, serial direct-launch replay of the step "
