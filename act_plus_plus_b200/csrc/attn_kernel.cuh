@@ -1,0 +1,251 @@
+// Attention scores fused with their row-wise softmax (forward) or softmax backward, for head_dim 64 and up to 320 keys:
+//   FWD:  P  = softmax(scale * Q K^T + key_padding_mask)                      (transformer.py:194,254-255 via nn.MHA)
+//   BWD:  dS = scale * P o (dP - rowsum(dP o P)),   dP = dO V^T               (its autograd)
+// One CTA tile = 128 query rows x ALL keys of one (batch, head): the [128 x W] fp32 score tile lives in TMEM
+// (W = 128 or 320 columns), so the row reductions never leave the SM and the fp32 score matrix never touches HBM
+// (the unfused path writes S fp32, reads it back in a softmax kernel and writes P: 3 x the traffic and one more launch).
+// Warp roles as in tc_kernel: warp 0 TMA producer, warp 1 MMA issuer, warps 2-9 epilogue -- two warps per TMEM lane
+// quadrant, each owning half of the row's columns in registers; the two halves of a row exchange max / sum through
+// shared memory (named barrier over the 256 epilogue threads).
+#pragma once
+#include "tc_kernel.cuh"
+
+namespace act {
+
+struct AttnParams {
+  int Lq, Lk, Lkp;              // query rows, keys, padded row stride of P / dS (multiple of 8)
+  int heads, batch, qtiles;
+  float scale;
+  const uint8_t* mask;          // [batch, Lk] key padding mask (1 = masked) or null        (FWD)
+  const __nv_bfloat16* P;       // [batch, heads, Lq, Lkp] probabilities                    (BWD input)
+  __nv_bfloat16* out;           // P (FWD) or dS (BWD), same layout
+  int vec32;                    // rows of `out` are 32-byte aligned (Lkp % 16 == 0): whole-sector stores
+};
+
+template <int W>
+struct AttnCfg {
+  static constexpr int NMMA = W > 256 ? 2 : 1;          // tcgen05 N <= 256: 320 keys = 2 x 160
+  static constexpr int NPER = W / NMMA;
+  static constexpr int A_BYTES = 128 * 128;             // 128 rows x 64 bf16
+  static constexpr int B_BYTES = W * 128;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = 2;
+  static constexpr int TMEM_COLS = W <= 128 ? 128 : 512;
+  static constexpr int NC = W / 64;                     // 32-column chunks per epilogue warp (half a row)
+  static constexpr int SMEM = 1024 + STAGES * STAGE_BYTES + 2 * 2 * 128 * 4 + 4 * 8 + 16;
+};
+
+template <int W, int BWD>
+__global__ void __launch_bounds__(256, 1)
+attn_scores_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ CUtensorMap bmap,
+                   const __grid_constant__ AttnParams p) {
+  using Cfg = AttnCfg<W>;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  float* xch = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);      // [2 passes][2 halves][128 rows]
+  uint64_t* full = reinterpret_cast<uint64_t*>(xch + 2 * 2 * 128);
+  uint64_t* tfull = full + Cfg::STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull + 1);
+
+  // Eight warps, all of them epilogue (two per TMEM lane quadrant; 10 warps would cap the kernel at 168 registers per
+  // thread -- three warps on one SM sub-partition -- and spill the 160-column row half).  Thread 0 is also the TMA
+  // producer and the MMA issuer: one tile is a single 64-deep k-block (8 MMAs), and with a [128 x 320] fp32 tile the
+  // TMEM holds one accumulator, so MMA(i+1) can only start once tile i is in registers anyway.
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool leader = threadIdx.x == 0;
+  const int total_tiles = p.qtiles * p.heads * p.batch;
+  constexpr uint32_t idesc = make_idesc_bf16(128, Cfg::NPER, 0, 0);
+
+  pdl_trigger();
+  if (leader) {
+    prefetch_tmap(&amap);
+    prefetch_tmap(&bmap);
+    for (int s = 0; s < Cfg::STAGES; ++s) mbar_init(&full[s], 1);
+    mbar_init(tfull, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) { __syncwarp(); tmem_alloc(tmem_slot, Cfg::TMEM_COLS); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+
+  auto load_tile = [&](int t, int s) {                     // leader only
+    const int qt = t % p.qtiles, hd = (t / p.qtiles) % p.heads, b = t / (p.qtiles * p.heads);
+    mbar_expect_tx(&full[s], Cfg::STAGE_BYTES);
+    uint8_t* st = smem + s * Cfg::STAGE_BYTES;
+    tma_load_4d(st, &amap, &full[s], 0, qt * 128, hd, b);                          // rows >= Lq are zero-filled
+#pragma unroll
+    for (int h = 0; h < Cfg::NMMA; ++h)                                              // keys >= Lk are zero-filled
+      tma_load_4d(st + Cfg::A_BYTES + h * Cfg::NPER * 128, &bmap, &full[s], 0, h * Cfg::NPER, hd, b);
+  };
+  auto mma_tile = [&](uint32_t i) {                        // leader only: tile i of this CTA sits in stage i % STAGES
+    const int s = i % Cfg::STAGES;
+    mbar_wait(&full[s], (i / Cfg::STAGES) & 1);
+    tc_fence_after();
+    const uint32_t a0 = smem_u32(smem) + s * Cfg::STAGE_BYTES;
+#pragma unroll
+    for (int h = 0; h < Cfg::NMMA; ++h) {
+      uint64_t ad = make_smem_desc(a0, 16, 1024);
+      uint64_t bd = make_smem_desc(a0 + Cfg::A_BYTES + h * Cfg::NPER * 128, 16, 1024);
+#pragma unroll
+      for (int k = 0; k < 4; ++k, ad += 2, bd += 2) umma_bf16(tmem_base + h * Cfg::NPER, ad, bd, idesc, k > 0 ? 1u : 0u);
+    }
+    umma_commit(tfull);
+  };
+  if (leader && static_cast<int>(blockIdx.x) < total_tiles) {
+    load_tile(blockIdx.x, 0);
+    if (static_cast<int>(blockIdx.x + gridDim.x) < total_tiles) load_tile(blockIdx.x + gridDim.x, 1);
+    mma_tile(0);
+  }
+  __syncwarp();
+
+  {
+    const int q = warp & 3, half = warp >> 2;
+    const int r = q * 32 + lane;
+    const int cbeg = half * (W / 2);
+    uint32_t it = 0;
+    // leader, once every warp holds tile `it` in registers: refill the stage tile `it` used, then issue tile it+1
+    auto next_tile = [&](int t, uint32_t i) {
+      const int t1 = t + gridDim.x, t2 = t + 2 * gridDim.x;
+      if (t1 >= total_tiles) return;
+      tc_fence_after();
+      if (t2 < total_tiles) load_tile(t2, i % Cfg::STAGES);
+      mma_tile(i + 1);
+    };
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      const int qt = t % p.qtiles, hd = (t / p.qtiles) % p.heads, b = t / (p.qtiles * p.heads);
+      const int gm = qt * 128 + r;
+      const bool row_ok = gm < p.Lq;
+      const long long row_off = ((static_cast<long long>(b) * p.heads + hd) * p.Lq + (row_ok ? gm : 0)) * p.Lkp;
+      mbar_wait(tfull, it & 1);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + cbeg;
+      float v[Cfg::NC][32];
+#pragma unroll
+      for (int c = 0; c < Cfg::NC; ++c) {
+        uint32_t u[32];
+        tmem_ld_32x32(tacc + c * 32, u);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[c][j] = __uint_as_float(u[j]);
+      }
+      tc_fence_before();                                    // the barrier below also tells the leader TMEM is drained
+
+      float* x0 = xch + (half * 128 + r);                   // my slot / my partner's slot, pass 0
+      float* y0 = xch + ((half ^ 1) * 128 + r);
+      if (!BWD) {
+        const uint8_t* mrow = p.mask ? p.mask + static_cast<long long>(b) * p.Lk : nullptr;
+        float mx = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < Cfg::NC; ++c)
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int col = cbeg + c * 32 + j;
+            const bool dead = col >= p.Lk || (mrow && __ldg(mrow + min(col, p.Lk - 1)));
+            v[c][j] = dead ? -INFINITY : v[c][j] * p.scale;
+            mx = fmaxf(mx, v[c][j]);
+          }
+        *x0 = mx;
+        __syncthreads();
+        if (leader) next_tile(t, it);
+        __syncwarp();
+        mx = fmaxf(mx, *y0);
+        if (mx == -INFINITY) mx = 0.f;
+        float sum = 0.f;
+#pragma unroll
+        for (int c = 0; c < Cfg::NC; ++c)
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { v[c][j] = __expf(v[c][j] - mx); sum += v[c][j]; }
+        x0[256] = sum;
+        __syncthreads();
+        sum += y0[256];
+        const float inv = sum > 0.f ? 1.f / sum : 0.f;
+#pragma unroll
+        for (int c = 0; c < Cfg::NC; ++c)
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[c][j] *= inv;
+      } else {
+        // pass 1: dot = sum_j P_j dP_j over the whole row
+        const __nv_bfloat16* prow = p.P + row_off;
+        float dot = 0.f;
+#pragma unroll
+        for (int c = 0; c < Cfg::NC; ++c) {
+          const int col0 = cbeg + c * 32;
+          if (row_ok && col0 < p.Lk) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              if (col0 + j >= p.Lkp) break;
+              const uint4 w = __ldg(reinterpret_cast<const uint4*>(prow + col0 + j));
+              const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&w);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float2 f = __bfloat1622float2(h2[e]);
+                if (col0 + j + 2 * e < p.Lk) dot += f.x * v[c][j + 2 * e];
+                if (col0 + j + 2 * e + 1 < p.Lk) dot += f.y * v[c][j + 2 * e + 1];
+              }
+            }
+          }
+        }
+        *x0 = dot;
+        __syncthreads();
+        if (leader) next_tile(t, it);
+        __syncwarp();
+        dot += *y0;
+        // pass 2: dS = scale * P * (dP - dot); P is re-read (L1 / L2 hit)
+#pragma unroll
+        for (int c = 0; c < Cfg::NC; ++c) {
+          const int col0 = cbeg + c * 32;
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            float pv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (row_ok && col0 + j < p.Lkp && col0 < p.Lk) {
+              const uint4 w = __ldg(reinterpret_cast<const uint4*>(prow + col0 + j));
+              const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&w);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) { const float2 f = __bfloat1622float2(h2[e]); pv[2 * e] = f.x; pv[2 * e + 1] = f.y; }
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[c][j + e] = (col0 + j + e < p.Lk) ? p.scale * pv[e] * (v[c][j + e] - dot) : 0.f;
+          }
+        }
+        __syncthreads();      // keep the two exchange passes of consecutive tiles apart
+      }
+      // store bf16, pad columns [Lk, Lkp) as zeros (FWD: exp(-inf) = 0 already)
+      if (row_ok) {
+        __nv_bfloat16* orow = p.out + row_off;
+#pragma unroll
+        for (int c = 0; c < Cfg::NC; ++c) {
+          const int col0 = cbeg + c * 32;
+          if (col0 >= p.Lkp) continue;
+          uint32_t w[16];
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            const __nv_bfloat162 h = __floats2bfloat162_rn(v[c][2 * e], v[c][2 * e + 1]);
+            w[e] = *reinterpret_cast<const uint32_t*>(&h);
+          }
+          if (p.vec32 && col0 + 32 <= p.Lkp) {
+            st_global_v8(orow + col0, w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7]);
+            st_global_v8(orow + col0 + 16, w[8], w[9], w[10], w[11], w[12], w[13], w[14], w[15]);
+          } else {
+#pragma unroll
+            for (int e = 0; e < 4; ++e)                       // Lkp is a multiple of 8: whole 16-byte pieces
+              if (col0 + e * 8 < p.Lkp)
+                *reinterpret_cast<uint4*>(orow + col0 + e * 8) = make_uint4(w[4 * e], w[4 * e + 1], w[4 * e + 2], w[4 * e + 3]);
+          }
+        }
+      }
+      if (!BWD) __syncthreads();  // exchange slots are reused by the next tile
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+}  // namespace act

@@ -74,6 +74,14 @@ extern "C" int act_softmax_fwd(const float* S, const uint8_t* mask, void* P, int
 extern "C" int act_softmax_bwd(const void* P, const float* dP, void* dS, int R, int L, int Lp, float scale, void* stream) {
   return softmax_bwd(BF(P), dP, BFM(dS), R, L, Lp, scale, ST(stream));
 }
+extern "C" int act_attn_scores(int bwd, const void* A, int64_t lda, int64_t a_sz0, int64_t a_sz1, const void* Bm, int64_t ldb,
+                               int64_t b_sz0, int64_t b_sz1, int Lq, int Lk, int Lkp, int heads, int batch, float scale,
+                               const uint8_t* mask, const void* P, void* out, void* stream) {
+  MatDesc a, b;
+  a.ptr = BF(A); a.ld = lda; a.sz0 = a_sz0; a.sz1 = a_sz1;
+  b.ptr = BF(Bm); b.ld = ldb; b.sz0 = b_sz0; b.sz1 = b_sz1;
+  return tc_attn_scores(bwd, a, b, Lq, Lk, Lkp, heads, batch, scale, mask, BF(P), BFM(out), ST(stream));
+}
 extern "C" int act_colsum_bf16(const void* X, int64_t ld, int M, int N, float* out, void* stream) {
   return colsum_bf16(BF(X), ld, M, N, out, ST(stream));
 }

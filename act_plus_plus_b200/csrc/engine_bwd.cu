@@ -99,15 +99,20 @@ int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K
     ++launches_;
     if (tc_gemm(Lk, hd, Lq, h, B, a, b, e, 1, ax)) return -1;
   }
-  {  // dP[i,j] = sum_d dO[i,d] V[j,d]
+  {  // dP[i,j] = sum_d dO[i,d] V[j,d], then dS = scale * P o (dP - rowsum(dP o P))
     MatDesc a, b; EpiDesc e;
     a.ptr = dO; a.ld = 512; a.sz0 = hd; a.sz1 = 1LL * Lq * 512;
     b.ptr = V; b.ld = ldv; b.sz0 = hd; b.sz1 = Lk * ldv;
-    e.flags = EPI_OUT_F32; e.out_f32 = S; e.ldc = Lkp; e.osz0 = ph; e.osz1 = pb;
-    ++launches_;
-    if (tc_gemm(Lq, Lk, hd, h, B, a, b, e, 1, st)) return -1;
+    if (tc_attn_scores_applicable(Lk, Lkp)) {
+      ++launches_;
+      if (tc_attn_scores(1, a, b, Lq, Lk, Lkp, h, B, 0.125f, nullptr, P, dS, st)) return -1;
+    } else {
+      e.flags = EPI_OUT_F32; e.out_f32 = S; e.ldc = Lkp; e.osz0 = ph; e.osz1 = pb;
+      ++launches_;
+      if (tc_gemm(Lq, Lk, hd, h, B, a, b, e, 1, st)) return -1;
+      RUN(softmax_bwd(P, S, dS, B * h * Lq, Lk, Lkp, 0.125f, st));
+    }
   }
-  RUN(softmax_bwd(P, S, dS, B * h * Lq, Lk, Lkp, 0.125f, st));
   if (ax != st) ax = aux_fork(st);                   // dS is final
   {  // dK[j,d] = sum_i dS[i,j] Q[i,d]
     MatDesc a, b; EpiDesc e;

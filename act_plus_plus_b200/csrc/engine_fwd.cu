@@ -225,11 +225,17 @@ int Engine::attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk,
   EpiDesc e;
   a.ptr = Q; a.ld = ldq; a.sz0 = hd; a.sz1 = Lq * ldq;
   b.ptr = K; b.ld = ldk; b.sz0 = hd; b.sz1 = Lk * ldk;
-  e.flags = EPI_OUT_F32; e.alpha = 0.125f; e.out_f32 = S;
-  e.ldc = Lkp; e.osz0 = 1LL * Lq * Lkp; e.osz1 = 1LL * h * Lq * Lkp;
-  ++launches_;
-  if (tc_gemm(Lq, Lk, hd, h, B, a, b, e, 1, st)) return -1;
-  RUN(softmax_fwd(S, mask, P, B * h * Lq, Lk, Lkp, h * Lq, st));
+  if (tc_attn_scores_applicable(Lk, Lkp)) {
+    // scores + mask + softmax in one kernel: the fp32 score tile stays in TMEM (csrc/attn_kernel.cuh)
+    ++launches_;
+    if (tc_attn_scores(0, a, b, Lq, Lk, Lkp, h, B, 0.125f, mask, nullptr, P, st)) return -1;
+  } else {
+    e.flags = EPI_OUT_F32; e.alpha = 0.125f; e.out_f32 = S;
+    e.ldc = Lkp; e.osz0 = 1LL * Lq * Lkp; e.osz1 = 1LL * h * Lq * Lkp;
+    ++launches_;
+    if (tc_gemm(Lq, Lk, hd, h, B, a, b, e, 1, st)) return -1;
+    RUN(softmax_fwd(S, mask, P, B * h * Lq, Lk, Lkp, h * Lq, st));
+  }
   if (v_on_aux && aux_join(st)) return -1;           // V was projected on the aux lane
   MatDesc pa, vb;
   EpiDesc eo;

@@ -86,7 +86,12 @@ struct ConvLaunch {
 int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint = 0, int stages_hint = 0);
 // dense 3x3 / stride-1 tap sets: halo patch resident in shared memory (conv3_kernel.cuh); ACT_CONV3=0 disables it
 bool tc_conv3_applicable(const ConvLaunch& c);
-void tc_set_sm_reserve(int n);   // persistent launches that follow leave n SMs free for a concurrent branch
+void tc_set_sm_reserve(int n);
+// Attention scores fused with softmax (bwd = 0) / softmax backward (bwd = 1) for head_dim 64 and Lk <= 320 keys.
+bool tc_attn_scores_applicable(int Lk, int Lkp);
+int tc_attn_scores(int bwd, const MatDesc& A, const MatDesc& B, int Lq, int Lk, int Lkp, int heads, int batch, float scale,
+                   const uint8_t* mask, const bf16* P, bf16* out, cudaStream_t stream);
+   // persistent launches that follow leave n SMs free for a concurrent branch
 int tc_conv3(const ConvLaunch& c, cudaStream_t stream, int bn_hint = 0);
 
 struct WgradLaunch {

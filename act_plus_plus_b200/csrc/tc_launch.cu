@@ -2,6 +2,7 @@
 // library loads on machines without libcuda), tile selection, launch.
 #include "tc_api.h"
 #include "conv3_kernel.cuh"
+#include "attn_kernel.cuh"
 #include <mutex>
 #include <cstring>
 #include <algorithm>
@@ -474,4 +475,53 @@ int tc_wgrad(const WgradLaunch& w, cudaStream_t stream) {
   return launch_inst<MODE_WGRAD, 1, 1, 128>(grid, 0, stream, am, bm, p);
 }
 
+}  // namespace act
+
+namespace act {
+// --------------------------------------------------------------------------------------------- fused attention scores
+template <int W, int BWD>
+static int launch_attn(const CUtensorMap& am, const CUtensorMap& bm, const AttnParams& p, int tiles, cudaStream_t stream) {
+  using Cfg = AttnCfg<W>;
+  auto kern = attn_scores_kernel<W, BWD>;
+  static bool configured = false;
+  if (!configured) {
+    ACT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    configured = true;
+  }
+  const unsigned ctas = static_cast<unsigned>(std::min(tiles, num_sms()));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
+  ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(256), static_cast<size_t>(Cfg::SMEM), stream, am, bm, p));
+  if (g_prof.on) { cudaEventRecord(e1, stream); g_prof.ev.push_back(e0); g_prof.ev.push_back(e1); g_prof.flops.push_back(g_next_flops); g_prof.label.push_back(g_next_label); }
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+bool tc_attn_scores_applicable(int Lk, int Lkp) {
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("ACT_FUSED_ATTN"); on = !(e && e[0] == '0'); }
+  return on && Lk >= 1 && Lk <= 320 && Lkp % 8 == 0 && Lkp >= Lk;
+}
+
+// FWD: out = softmax(scale * A B^T + mask) with A = Q [Lq x 64], B = K [Lk x 64] per (head, batch)
+// BWD: out = scale * P o (dP - rowsum(dP o P)), dP = A B^T with A = dO, B = V
+int tc_attn_scores(int bwd, const MatDesc& A, const MatDesc& B, int Lq, int Lk, int Lkp, int heads, int batch, float scale,
+                   const uint8_t* mask, const bf16* P, bf16* out, cudaStream_t stream) {
+  ACT_CHECK(tc_attn_scores_applicable(Lk, Lkp), "fused attention scores need Lk <= 320 and a padded stride % 8 == 0");
+  ACT_CHECK(!A.mn_major && !B.mn_major && out && (!bwd || P), "fused attention scores: bad operands");
+  ACT_CHECK((reinterpret_cast<uintptr_t>(out) & 31) == 0 && (!P || (reinterpret_cast<uintptr_t>(P) & 15) == 0), "fused attention scores: unaligned P / dS");
+  const int W = Lk <= 128 ? 128 : 320;
+  AttnParams p;
+  memset(&p, 0, sizeof(p));
+  p.Lq = Lq; p.Lk = Lk; p.Lkp = Lkp; p.heads = heads; p.batch = batch; p.qtiles = (Lq + 127) / 128; p.scale = scale;
+  p.mask = mask; p.P = P; p.out = out; p.vec32 = (Lkp % 16 == 0) ? 1 : 0;
+  CUtensorMap am, bm;
+  if (mat_tmap(&am, A, Lq, 64, heads, batch, 128)) return -1;
+  if (mat_tmap(&bm, B, Lk, 64, heads, batch, W == 128 ? 128 : 160)) return -1;
+  const int tiles = p.qtiles * heads * batch;
+  g_next_flops = 2.0 * Lq * Lk * 64 * heads * batch;
+  if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "attn_%s Lq=%d Lk=%d z=%d W=%d", bwd ? "dS" : "P", Lq, Lk, heads * batch, W); g_next_label = buf; }
+  if (W == 128) return bwd ? launch_attn<128, 1>(am, bm, p, tiles, stream) : launch_attn<128, 0>(am, bm, p, tiles, stream);
+  return bwd ? launch_attn<320, 1>(am, bm, p, tiles, stream) : launch_attn<320, 0>(am, bm, p, tiles, stream);
+}
 }  // namespace act

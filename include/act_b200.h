@@ -80,6 +80,15 @@ int act_add_pos_cast(const float* x, const float* pos, int L, void* x_bf16, void
 int act_softmax_fwd(const float* S, const uint8_t* key_padding_mask, void* P, int R, int L, int Lp, int rows_per_batch,
                     void* stream);
 int act_softmax_bwd(const void* P, const float* dP, void* dS, int R, int L, int Lp, float scale, void* stream);
+/* Attention scores fused with softmax / softmax backward (head_dim 64, Lk <= 320; nn.MultiheadAttention's
+ * softmax(q k^T / 8 + key_padding_mask) `transformer.py:194,254-255` and its autograd):
+ *   bwd = 0: out[b,h,i,:] = softmax_j(scale * sum_d A[b,h,i,d] B[b,h,j,d] + mask[b,j])      (A = Q, B = K)
+ *   bwd = 1: out = scale * P o (dP - rowsum(dP o P)),  dP[b,h,i,j] = sum_d A[b,h,i,d] B[b,h,j,d]   (A = dO, B = V)
+ * A / B are bf16 row views (row stride ld*, head stride *_sz0, batch stride *_sz1, in elements); P / out are bf16
+ * [batch, heads, Lq, Lkp], columns [Lk, Lkp) are written 0; mask is uint8 [batch, Lk] or NULL. */
+int act_attn_scores(int bwd, const void* A, int64_t lda, int64_t a_sz0, int64_t a_sz1, const void* B, int64_t ldb, int64_t b_sz0,
+                    int64_t b_sz1, int Lq, int Lk, int Lkp, int heads, int batch, float scale, const uint8_t* key_padding_mask,
+                    const void* P, void* out, void* stream);
 int act_colsum_bf16(const void* X, int64_t ld, int M, int N, float* out_accum, void* stream);
 /* fp32 mini-GEMM for the K<=32 / N<=64 projections (detr_vae.py:57-63,81-97) and their gradients:
  * C(i,j) (+)= alpha*sum_r A(i,r)B(r,j) (+bias[j]); each index maps as (idx/rpb)*bs + (idx%rpb)*s (maps = 3 int64). */

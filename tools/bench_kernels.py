@@ -153,3 +153,33 @@ def bench_floor():
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "floor":
     bench_floor()
+
+
+def bench_attn():
+    """Fused scores+softmax kernel vs the unfused pair (tc_gemm fp32 scores + softmax kernel) and torch SDPA-free math."""
+    import ctypes as C
+    lib = ops._lib.lib()
+    st = lambda: torch.cuda.current_stream().cuda_stream
+    for (B, h, Lq, Lk) in ((8, 8, 302, 302), (8, 8, 102, 102), (8, 8, 100, 302), (8, 8, 100, 100)):
+        d = 512
+        Lkp = (Lk + 7) // 8 * 8
+        qk = torch.randn(B, Lq, 2 * d, device="cuda").bfloat16()
+        kk = torch.randn(B, Lk, 2 * d, device="cuda").bfloat16()
+        P = torch.zeros(B, h, Lq, Lkp, device="cuda", dtype=torch.bfloat16)
+        S = torch.zeros(B, h, Lq, Lkp, device="cuda", dtype=torch.float32)
+
+        def fused():
+            ops.check(lib.act_attn_scores(0, qk.data_ptr(), 2 * d, 64, Lq * 2 * d, kk.data_ptr() + d * 2, 2 * d, 64, Lk * 2 * d, Lq, Lk, Lkp,
+                                          h, B, C.c_float(0.125), None, None, P.data_ptr(), st()), "attn_scores")
+
+        epi = ops.make_epilogue(out_f32=S, ldc=Lkp, osz0=Lq * Lkp, osz1=h * Lq * Lkp, alpha=0.125)
+
+        def unfused():
+            ops.tc_gemm_raw(Lq, Lk, 64, h, B, qk, 0, 2 * d, 64, Lq * 2 * d, kk[:, :, d:], 0, 2 * d, 64, Lk * 2 * d, epi, 1, 0, 0)
+            ops.check(lib.act_softmax_fwd(S.data_ptr(), None, P.data_ptr(), B * h * Lq, Lk, Lkp, h * Lq, st()), "softmax")
+        tf, tu = graph_time(fused), graph_time(unfused)
+        print(json.dumps(dict(kind="attn_scores", B=B, h=h, Lq=Lq, Lk=Lk, fused_us=round(tf, 2), unfused_us=round(tu, 2))), flush=True)
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "attn":
+    bench_attn()
