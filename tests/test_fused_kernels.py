@@ -232,3 +232,44 @@ def test_temporal_agg_bit_exact_vs_reference_lines():
         for e in range(E):
             err = ((out[e] - ref).abs() / (ref.abs() + 1e-300)).max().item()
             assert err < 1e-12, (t, e, err)
+
+
+@pytest.mark.parametrize("B,h,Lq,Lk,masked", [(2, 8, 302, 302, False), (2, 8, 102, 102, True), (3, 8, 100, 302, False),
+                                              (1, 8, 100, 100, False), (2, 8, 130, 320, True)])
+def test_attn_scores_fused_matches_torch(B, h, Lq, Lk, masked):
+    """act_attn_scores: softmax(q k^T / 8 + key_padding_mask) and its backward with the score tile kept in TMEM, against
+    plain fp32 torch on the same bf16 operands (nn.MultiheadAttention math, transformer.py:194,254-255)."""
+    torch.manual_seed(3)
+    d, hd = h * 64, 64
+    Lkp = (Lk + 7) // 8 * 8
+    q = (torch.randn(B, Lq, d, device="cuda") * 0.7).bfloat16()
+    k = (torch.randn(B, Lk, d, device="cuda") * 0.7).bfloat16()
+    mask = None
+    if masked:
+        mask = torch.zeros(B, Lk, dtype=torch.uint8, device="cuda")
+        mask[:, Lk - 17:] = 1
+        mask[0, 5] = 1
+    P = torch.full((B, h, Lq, Lkp), 7.0, device="cuda", dtype=torch.bfloat16)
+    ck(L().act_attn_scores(0, p(q), d, hd, Lq * d, p(k), d, hd, Lk * d, Lq, Lk, Lkp, h, B, C.c_float(0.125),
+                           p(mask) if mask is not None else None, None, p(P), st()))
+    qf = q.float().view(B, Lq, h, hd).transpose(1, 2)
+    kf = k.float().view(B, Lk, h, hd).transpose(1, 2)
+    S = qf @ kf.transpose(2, 3) * 0.125
+    if mask is not None:
+        S = S.masked_fill(mask.bool()[:, None, None, :], float("-inf"))
+    ref = torch.softmax(S, dim=-1)
+    torch.cuda.synchronize()
+    assert (P[..., :Lk].float() - ref).abs().max().item() <= 4e-3
+    assert (P[..., Lk:].float() == 0).all()
+    # backward: dS = scale * P o (dP - rowsum(dP o P)), dP = dO V^T, with the kernel's own bf16 P
+    dO = torch.randn(B, Lq, d, device="cuda").bfloat16()
+    v = torch.randn(B, Lk, d, device="cuda").bfloat16()
+    dS = torch.full((B, h, Lq, Lkp), 7.0, device="cuda", dtype=torch.bfloat16)
+    ck(L().act_attn_scores(1, p(dO), d, hd, Lq * d, p(v), d, hd, Lk * d, Lq, Lk, Lkp, h, B, C.c_float(0.125), None, p(P), p(dS), st()))
+    dP = dO.float().view(B, Lq, h, hd).transpose(1, 2) @ v.float().view(B, Lk, h, hd).transpose(1, 2).transpose(2, 3)
+    Pf = P[..., :Lk].float()
+    ref_dS = 0.125 * Pf * (dP - (dP * Pf).sum(-1, keepdim=True))
+    torch.cuda.synchronize()
+    err = (dS[..., :Lk].float() - ref_dS).abs().max().item()
+    assert err <= 2e-2 * max(1.0, ref_dS.abs().max().item()), err
+    assert (dS[..., Lk:].float() == 0).all()
