@@ -137,27 +137,40 @@ attn_scores_kernel(const __grid_constant__ CUtensorMap amap, const __grid_consta
       float* y0 = xch + ((half ^ 1) * 128 + r);
       if (!BWD) {
         const uint8_t* mrow = p.mask ? p.mask + static_cast<long long>(b) * p.Lk : nullptr;
-        float mx = -INFINITY;
+        // eight independent partial maxima / sums: with two warps per scheduler a single 160-long dependent chain of
+        // FMNMX / FADD is pure latency (ncu: 18 % issue-active before this change)
+        float m8[8];
 #pragma unroll
-        for (int c = 0; c < Cfg::NC; ++c)
+        for (int e = 0; e < 8; ++e) m8[e] = -INFINITY;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int col = cbeg + c * 32 + j;
-            const bool dead = col >= p.Lk || (mrow && __ldg(mrow + min(col, p.Lk - 1)));
-            v[c][j] = dead ? -INFINITY : v[c][j] * p.scale;
-            mx = fmaxf(mx, v[c][j]);
+        for (int c = 0; c < Cfg::NC; ++c) {
+          const int col0 = cbeg + c * 32;
+          if (!mrow && col0 + 32 <= p.Lk) {                   // chunk entirely inside the row, no mask: scale only
+#pragma unroll
+            for (int j = 0; j < 32; ++j) { v[c][j] *= p.scale; m8[j & 7] = fmaxf(m8[j & 7], v[c][j]); }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int col = col0 + j;
+              const bool dead = col >= p.Lk || (mrow && __ldg(mrow + min(col, p.Lk - 1)));
+              v[c][j] = dead ? -INFINITY : v[c][j] * p.scale;
+              m8[j & 7] = fmaxf(m8[j & 7], v[c][j]);
+            }
           }
+        }
+        float mx = fmaxf(fmaxf(fmaxf(m8[0], m8[1]), fmaxf(m8[2], m8[3])), fmaxf(fmaxf(m8[4], m8[5]), fmaxf(m8[6], m8[7])));
         *x0 = mx;
         __syncthreads();
         if (leader) next_tile(t, it);
         __syncwarp();
         mx = fmaxf(mx, *y0);
         if (mx == -INFINITY) mx = 0.f;
-        float sum = 0.f;
+        float s8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
         for (int c = 0; c < Cfg::NC; ++c)
 #pragma unroll
-          for (int j = 0; j < 32; ++j) { v[c][j] = __expf(v[c][j] - mx); sum += v[c][j]; }
+          for (int j = 0; j < 32; ++j) { v[c][j] = __expf(v[c][j] - mx); s8[j & 7] += v[c][j]; }
+        float sum = ((s8[0] + s8[1]) + (s8[2] + s8[3])) + ((s8[4] + s8[5]) + (s8[6] + s8[7]));
         x0[256] = sum;
         __syncthreads();
         sum += y0[256];
@@ -169,7 +182,7 @@ attn_scores_kernel(const __grid_constant__ CUtensorMap amap, const __grid_consta
       } else {
         // pass 1: dot = sum_j P_j dP_j over the whole row
         const __nv_bfloat16* prow = p.P + row_off;
-        float dot = 0.f;
+        float d4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
         for (int c = 0; c < Cfg::NC; ++c) {
           const int col0 = cbeg + c * 32;
@@ -182,12 +195,13 @@ attn_scores_kernel(const __grid_constant__ CUtensorMap amap, const __grid_consta
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
                 const float2 f = __bfloat1622float2(h2[e]);
-                if (col0 + j + 2 * e < p.Lk) dot += f.x * v[c][j + 2 * e];
-                if (col0 + j + 2 * e + 1 < p.Lk) dot += f.y * v[c][j + 2 * e + 1];
+                if (col0 + j + 2 * e < p.Lk) d4[e] += f.x * v[c][j + 2 * e];
+                if (col0 + j + 2 * e + 1 < p.Lk) d4[e] += f.y * v[c][j + 2 * e + 1];
               }
             }
           }
         }
+        float dot = (d4[0] + d4[1]) + (d4[2] + d4[3]);
         *x0 = dot;
         __syncthreads();
         if (leader) next_tile(t, it);
