@@ -176,6 +176,11 @@ extern "C" int act_engine_zero_grad_async(act_engine* e, void* stream) { return 
 extern "C" int act_engine_backward_and_step(act_engine* e, int step, float loss_grad, void* stream) {
   return e->eng->backward_and_step(step, loss_grad, ST(stream));
 }
+extern "C" int act_engine_backward_and_step_dp(act_engine* e, int step, float loss_grad, void* stream,
+                                               act_grads_ready_fn grads_ready, void* user) {
+  if (!grads_ready) { set_error("act_engine_backward_and_step_dp: null callback"); return -1; }
+  return e->eng->backward_and_step(step, loss_grad, ST(stream), grads_ready, user);
+}
 extern "C" int act_engine_adamw_step(act_engine* e, int step, void* stream) { return e->eng->adamw(step, ST(stream)); }
 extern "C" int act_engine_adamw_region(act_engine* e, int step, int region, int blocks_per_sm, void* stream) {
   if (region < 0 || region >= R_COUNT) { set_error("act_engine_adamw_region: bad region"); return -1; }

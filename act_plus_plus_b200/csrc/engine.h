@@ -70,6 +70,8 @@ struct CamActs {
   BlockActs blk[8];
 };
 
+typedef int (*GradsReadyFn)(void* user, long long offset, long long count, void* stream);
+
 class Engine {
  public:
   explicit Engine(const EngineConfig& cfg);
@@ -90,11 +92,21 @@ class Engine {
   int adamw(int step, cudaStream_t st);
   int adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm = 0);
   int adamw_range(long long off, long long n, float lr, bool shadow, int step, cudaStream_t st, int blocks_per_sm);
+  GradsReadyFn grads_cb_ = nullptr;
+  void* grads_cb_user_ = nullptr;
+  int grads_ready(long long off, long long n, cudaStream_t st);
+  int backbone_bwd_and_step(cudaStream_t st);
+  int opt_step_ = 0, dp_bb_slot_ = 0;
+  bool dp_bb_pending_ = false;
+  cudaStream_t dp_main_st_ = nullptr;
   int inline_opt_step_ = 0;                      // > 0 while backward_and_step runs: cvae_bwd updates each layer as soon as its gradients are final
   long long cvae_layer_off_[16] = {0}, cvae_layer_n_[16] = {0};
   // backward(0) + adamw() with the optimiser of each parameter region trailing that region's last weight gradient, so
   // the HBM-bound AdamW of the transformer / CVAE regions overlaps the tensor-bound backbone backward
-  int backward_and_step(int step, float loss_grad, cudaStream_t st);
+  // grads_ready: data-parallel hook.  Called on the host while the step is enqueued, once per contiguous range of the
+  // flat gradient buffer, with the stream on which that range is final; it must enqueue the cross-rank average of the
+  // range and order `stream` after it.  The range's AdamW follows on the same stream.
+  int backward_and_step(int step, float loss_grad, cudaStream_t st, GradsReadyFn cb = nullptr, void* cb_user = nullptr);
   const EngineConfig& cfg() const { return cfg_; }
   long long workspace_bytes() const { return ws_bytes_; }
   int launches() const { return launches_; }

@@ -304,11 +304,15 @@ int Engine::cvae_bwd(cudaStream_t st) {
   const float* dx2 = gC_;
   const float* dx2b = nullptr;
   for (int l = nl - 1; l >= 0; --l) {
+    // data-parallel step: collectives run in enqueue order, so the backbone branch (other stream) is enqueued at the
+    // point of this branch where its gradients become final -- after dp_bb_slot_ encoder layers
+    if (dp_bb_pending_ && nl - 1 - l == dp_bb_slot_ && backbone_bwd_and_step(dp_main_st_)) return -1;
     if (enc_layer_bwd(cvae_w_[l], cvae_a_[l], nullptr, dx2, dx2b, gC_, gD_, Lc_, B, st)) return -1;
     dx2 = gC_; dx2b = gD_;
     if (inline_opt_step_ > 0 && l < 16 && cvae_layer_n_[l] > 0) {
       // this layer's gradients are final and nothing below reads its weights: update it under the remaining layers
       cudaStream_t wg = wg_gather(st, NWG);
+      if (grads_ready(cvae_layer_off_[l], cvae_layer_n_[l], wg)) return -1;
       if (adamw_range(cvae_layer_off_[l], cvae_layer_n_[l], cfg_.lr, true, inline_opt_step_, wg, 3)) return -1;
     }
   }
@@ -418,39 +422,85 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
   return 0;
 }
 
-int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st) {
-  ACT_CHECK(cfg_.train && grads_ != nullptr, "engine has no training workspace / gradient buffer");
-  ACT_CHECK(have_actions_ && cur_B_ > 0, "backward needs a preceding training forward (with actions)");
-  if (ensure_streams()) return -1;
-  if (!concurrent_) return backward(0, loss_grad, st) || adamw(step, st) ? -1 : 0;
-  if (wg_join(st)) return -1;                               // an asynchronous zero_grad
-  if (zero_backward_outputs(st)) return -1;
-  if (transformer_bwd(loss_grad, st)) return -1;
-  if (fork_side(st)) return -1;
-  inline_opt_step_ = step;
-  const int cvae_rc = cvae_bwd(side_);
-  inline_opt_step_ = 0;
-  if (cvae_rc) return -1;
-  {   // MAIN / DEAD regions: every gradient and every read of these weights is ordered before this point of lane 0
-    cudaStream_t wg = wg_gather(st, NWG);
-    if (adamw_region(R_MAIN, step, wg, 3) || adamw_region(R_DEAD, step, wg, 3)) return -1;
-  }
-  {   // CVAE region: the encoder layers were updated inside cvae_bwd, the token projections / latent_proj follow here
-    cudaStream_t wg = wg_gather(side_, NWG);
-    const int nl = std::min(cfg_.enc_layers, 16);
-    const long long tail = cvae_layer_off_[nl - 1] + cvae_layer_n_[nl - 1];
-    const long long head_n = cvae_layer_off_[0] - region_off_[R_CVAE];
-    if (adamw_range(region_off_[R_CVAE], head_n, cfg_.lr, true, step, wg, 6)) return -1;
-    if (adamw_range(tail, region_off_[R_CVAE] + region_n_[R_CVAE] - tail, cfg_.lr, true, step, wg, 6)) return -1;
-  }
+int Engine::grads_ready(long long off, long long n, cudaStream_t st) {
+  if (!grads_cb_ || n <= 0) return 0;
+  if (grads_cb_(grads_cb_user_, off, n, st)) { set_error("gradient all-reduce callback failed"); return -1; }
+  return 0;
+}
+
+// Backbone backward of every camera on `st`, then (inside backward_and_step) that region's averaging hook and AdamW on
+// the optimiser lane: it trails the batched fold and the stem weight gradient, not the (longer) CVAE branch.
+int Engine::backbone_bwd_and_step(cudaStream_t st) {
+  dp_bb_pending_ = false;
   cgy_off_ = 0;
   tc_set_sm_reserve(sm_reserve_);
   for (int k = 0; k < cfg_.num_cameras; ++k)
     if (backbone_bwd(k, cur_B_, st)) { tc_set_sm_reserve(0); return -1; }
   tc_set_sm_reserve(0);
-  {   // BACKBONE region: trails the batched fold and the stem weight gradient, not the (longer) CVAE branch
+  cudaStream_t wg = wg_gather(st, NWG);
+  if (grads_ready(region_off_[R_BACKBONE], region_n_[R_BACKBONE], wg)) return -1;
+  return adamw_region(R_BACKBONE, opt_step_, wg, 3);
+}
+
+int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsReadyFn cb, void* cb_user) {
+  ACT_CHECK(cfg_.train && grads_ != nullptr, "engine has no training workspace / gradient buffer");
+  ACT_CHECK(have_actions_ && cur_B_ > 0, "backward needs a preceding training forward (with actions)");
+  if (ensure_streams()) return -1;
+  if (!concurrent_) {
+    if (backward(0, loss_grad, st)) return -1;
+    if (cb) {                                               // serial data-parallel step: one averaging call per region
+      for (int r : {R_MAIN, R_CVAE, R_BACKBONE})
+        if (region_n_[r] > 0 && cb(cb_user, region_off_[r], region_n_[r], st)) { set_error("gradient all-reduce callback failed"); return -1; }
+    }
+    return adamw(step, st);
+  }
+  struct Guard {                                            // the hook is only live inside this call
+    Engine* e;
+    ~Guard() { e->grads_cb_ = nullptr; e->grads_cb_user_ = nullptr; e->inline_opt_step_ = 0; e->dp_bb_pending_ = false; tc_set_sm_reserve(0); }
+  } guard{this};
+  grads_cb_ = cb; grads_cb_user_ = cb_user; opt_step_ = step;
+  if (wg_join(st)) return -1;                               // an asynchronous zero_grad
+  if (zero_backward_outputs(st)) return -1;
+  if (transformer_bwd(loss_grad, st)) return -1;
+  auto main_regions = [&]() -> int {
+    // MAIN / DEAD regions: every gradient and every read of these weights is ordered before this point of lane 0
     cudaStream_t wg = wg_gather(st, NWG);
-    if (adamw_region(R_BACKBONE, step, wg, 3)) return -1;
+    if (grads_ready(region_off_[R_MAIN], region_n_[R_MAIN], wg)) return -1;
+    return adamw_region(R_MAIN, step, wg, 3) || adamw_region(R_DEAD, step, wg, 3) ? -1 : 0;
+  };
+  // With the hook the collectives run in the order they are enqueued here, so the region that is final first goes first
+  if (cb && main_regions()) return -1;
+  if (fork_side(st)) return -1;
+  auto cvae_branch = [&]() -> int {
+    inline_opt_step_ = step;
+    const int rc = cvae_bwd(side_);
+    inline_opt_step_ = 0;
+    if (rc) return -1;
+    // CVAE region: the encoder layers were updated inside cvae_bwd, the token projections / latent_proj follow here
+    cudaStream_t wg = wg_gather(side_, NWG);
+    const int nl = std::min(cfg_.enc_layers, 16);
+    const long long tail = cvae_layer_off_[nl - 1] + cvae_layer_n_[nl - 1];
+    const long long head_n = cvae_layer_off_[0] - region_off_[R_CVAE];
+    const long long tail_n = region_off_[R_CVAE] + region_n_[R_CVAE] - tail;
+    if (grads_ready(region_off_[R_CVAE], head_n, wg) || grads_ready(tail, tail_n, wg)) return -1;
+    if (adamw_range(region_off_[R_CVAE], head_n, cfg_.lr, true, step, wg, 6)) return -1;
+    return adamw_range(tail, tail_n, cfg_.lr, true, step, wg, 6);
+  };
+  static int bb_slot = -2;
+  if (bb_slot == -2) { const char* e = getenv("ACT_DP_BB_SLOT"); bb_slot = e ? atoi(e) : -1; }
+  dp_main_st_ = st;
+  if (cb) {
+    // backbone gradients are final roughly when half of the CVAE-encoder layers are (measured: profiles/r01_dp_timeline.md)
+    dp_bb_slot_ = bb_slot >= 0 ? bb_slot : cfg_.enc_layers / 2;
+    dp_bb_pending_ = true;
+    if (cvae_branch()) return -1;
+    if (dp_bb_pending_ && backbone_bwd_and_step(st)) return -1;
+  } else {
+    // the MAIN update is enqueued after the CVAE branch here: its (long) AdamW then does not sit ahead of the CVAE
+    // branch's first kernels in the launch order
+    if (cvae_branch()) return -1;
+    if (main_regions()) return -1;
+    if (backbone_bwd_and_step(st)) return -1;
   }
   if (join_side(st)) return -1;
   return wg_join(st);

@@ -214,6 +214,31 @@ class ActEngine:
         self._shared["version"] += 1
         self._synced_version = self._shared["version"]
 
+    def backward_and_step_dp(self, grads_ready, loss_grad: float = 1.0):
+        """Data-parallel loss.backward(); optimizer.step(): `grads_ready(offset, count, stream_ptr)` is called while the
+        step is enqueued, once per contiguous range of `flat_grads` whose producers are enqueued on CUDA stream
+        `stream_ptr`; it must enqueue the cross-rank average of that range and order the stream after it.  The range's
+        AdamW follows behind it, so every collective overlaps the backward work still running on other streams."""
+        import ctypes as C
+        err = []
+
+        def _cb(_user, off, n, stream):
+            try:
+                grads_ready(int(off), int(n), int(stream or 0))
+                return 0
+            except Exception as ex:            # an exception must not unwind through the C frames
+                err.append(ex)
+                return -1
+
+        cb = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_longlong, C.c_longlong, C.c_void_p)(_cb)
+        self._shared["step"] += 1
+        rc = self.lib.act_engine_backward_and_step_dp(self._h, self._shared["step"], float(loss_grad), _stream(), cb, None)
+        if err:
+            raise err[0]
+        check(rc, "act_engine_backward_and_step_dp")
+        self._shared["version"] += 1
+        self._synced_version = self._shared["version"]
+
     def adamw_step(self):
         self._shared["step"] += 1
         check(self.lib.act_engine_adamw_step(self._h, self._shared["step"], _stream()), "act_engine_adamw_step")

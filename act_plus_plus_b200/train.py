@@ -53,6 +53,40 @@ def backward_and_step_data_parallel(eng: ActEngine, group, loss_grad: float = 1.
     eng.end_optimizer_step()
 
 
+def backward_and_step_hooked(eng: ActEngine, group, loss_grad: float = 1.0):
+    """Data-parallel loss.backward() + optimizer.step() through the engine's gradient-ready hook
+    (act_engine_backward_and_step_dp): the engine announces each contiguous gradient range on the internal stream where
+    it becomes final -- main region after the transformer backward, each CVAE-encoder layer as its backward ends, the
+    backbone region after its weight-gradient fold -- and this callback enqueues the NCCL average there.  Every range's
+    AdamW follows its own all-reduce on that stream, so collectives and updates run under the remaining backward
+    branches; only the last range's reduction is exposed."""
+    import torch.distributed as dist
+    flat = eng.flat_grads
+    world = dist.get_world_size(group)
+    native_avg = dist.get_backend(group) == "nccl"
+
+    def ready(off: int, n: int, stream_ptr: int):
+        s = _external_stream(stream_ptr, flat.device)
+        with torch.cuda.stream(s):
+            t = flat[off:off + n]
+            work = dist.all_reduce(t, op=dist.ReduceOp.AVG if native_avg else dist.ReduceOp.SUM, group=group, async_op=True)
+            work.wait()                          # orders `s` after the collective; does not block the host
+            if not native_avg:
+                t.mul_(1.0 / world)
+
+    eng.backward_and_step_dp(ready, loss_grad)
+
+
+_EXT_STREAMS = {}
+
+
+def _external_stream(ptr: int, device) -> "torch.cuda.Stream":
+    key = (ptr, device.index)
+    if key not in _EXT_STREAMS:
+        _EXT_STREAMS[key] = torch.cuda.ExternalStream(ptr, device=device) if ptr else torch.cuda.default_stream(device)
+    return _EXT_STREAMS[key]
+
+
 _SIDE_STREAMS = {}
 
 
@@ -69,6 +103,8 @@ def train_step(eng: ActEngine, qpos, image, actions, is_pad, eps=None, dp_group=
     out = eng.forward(qpos, image, actions, is_pad, eps)
     if dp_group is None:
         eng.backward_and_step(1.0)
+    elif os.environ.get("ACT_DP_HOOK", "1") == "1":
+        backward_and_step_hooked(eng, dp_group, 1.0)
     elif os.environ.get("ACT_DP_OVERLAP_OPT", "1") == "1":
         backward_and_step_data_parallel(eng, dp_group, 1.0)
     else:

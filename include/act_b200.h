@@ -164,6 +164,16 @@ int act_engine_zero_grad_async(act_engine* e, void* stream);
  * by act_engine_adamw_step(e, step, ...), with each parameter region's AdamW launched as soon as that region's
  * gradients are final so it overlaps the remaining backward.  Single-process only (no gradient all-reduce in between). */
 int act_engine_backward_and_step(act_engine* e, int step, float loss_grad, void* stream);
+/* Data-parallel form of the call above (new work: the reference trains on one GPU).  While the step is
+ * being enqueued the engine calls grads_ready(user, offset, count, s) once for every contiguous range of the flat
+ * fp32 gradient buffer (act_engine_grads) as soon as the kernels producing it are enqueued; `s` is the CUDA stream on
+ * which the range is final.  The callback must enqueue the cross-rank average of grads[offset, offset+count) ordered
+ * after `s` and make `s` wait for it (NCCL all-reduce + event wait), then return 0; the engine enqueues the range's
+ * AdamW on `s` right behind it.  The ranges cover the main, CVAE-encoder and backbone regions exactly once per step,
+ * in the same order on every rank, so each collective overlaps the backward work that is still running. */
+typedef int (*act_grads_ready_fn)(void* user, long long offset, long long count, void* stream);
+int act_engine_backward_and_step_dp(act_engine* e, int step, float loss_grad, void* stream,
+                                    act_grads_ready_fn grads_ready, void* user);
 /* AdamW of one parameter region (index as in act_engine_region; the backbone region also re-packs the conv operands).
  * blocks_per_sm > 0 limits the launch to that many 256-thread blocks per SM so it can run beside tensor-core kernels.
  * The data-parallel host loop uses it to update a region as soon as its gradient all-reduce has finished. */

@@ -11,6 +11,13 @@ from act_plus_plus_b200.policy import _init_like_reference
 from act_plus_plus_b200.train import train_step
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 8
+group, rank = None, 0
+if int(os.environ.get("WORLD_SIZE", "1")) > 1:          # under torchrun: data-parallel step, rank 0 writes the timeline
+    import torch.distributed as dist
+    rank = int(os.environ["RANK"])
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+    group = dist.group.WORLD
 eng = ActEngine(batch_max=B, train=True)
 _init_like_reference(eng, seed=0)
 g = torch.Generator(device="cuda").manual_seed(0)
@@ -19,7 +26,7 @@ qpos = torch.randn((B, 14), generator=g, device="cuda")
 actions = torch.randn((B, 100, 16), generator=g, device="cuda")
 is_pad = torch.arange(100, device="cuda")[None].repeat(B, 1) >= 60
 eps = torch.randn((B, 32), generator=g, device="cuda")
-fn = lambda: train_step(eng, qpos, image, actions, is_pad, eps)
+fn = lambda: train_step(eng, qpos, image, actions, is_pad, eps, group)
 for _ in range(3):
     fn()
 torch.cuda.synchronize()
@@ -39,6 +46,9 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     for _ in range(3):
         gr.replay()
     torch.cuda.synchronize()
+if rank != 0:
+    torch.cuda.synchronize()
+    os._exit(0)
 os.makedirs("gpurun_out", exist_ok=True)
 prof.export_chrome_trace("gpurun_out/trace_full.json")
 tr = json.load(open("gpurun_out/trace_full.json"))
@@ -52,3 +62,6 @@ out = [dict(name=e["name"][:90], stream=e["args"].get("stream"), ts=round(e["ts"
 json.dump(out, open("gpurun_out/timeline.json", "w"))
 os.remove("gpurun_out/trace_full.json")
 print("kernels", len(out), "span us", out[-1]["ts"] + out[-1]["dur"])
+sys.stdout.flush()
+if group is not None:
+    os._exit(0)
