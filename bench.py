@@ -36,6 +36,11 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-infer", action="store_true", help="skip the batched-inference / latency legs")
     ap.add_argument("--infer-envs", type=int, default=128, help="environments per GPU in the rollout leg (1024/8)")
+    ap.add_argument("--batch", type=int, default=8, help="per-GPU batch (default 8 = BASELINE configs[1]; 64/N for configs[2] "
+                    "at fixed global batch, 16 for configs[3])")
+    ap.add_argument("--cameras", type=int, default=1, help="cameras per sample (3 = BASELINE configs[3], Mobile-ALOHA)")
+    ap.add_argument("--eager-gpu", action="store_true", help="also time the reference algorithm (oracle port) as eager PyTorch "
+                    "on this GPU, fp32 and bf16 autocast: the practical bar of SURVEY.md 8(d), not a reference-published number")
     return ap.parse_args()
 
 
@@ -84,6 +89,19 @@ class ClockSampler:
         return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm))
 
 
+def workload_name(b, k):
+    if b == 8 and k == 1:
+        tag = "ACT sim_transfer_cube_scripted training step (fwd+loss+bwd+AdamW), per-GPU batch 8, 1 camera 480x640"
+        cfgs = "BASELINE configs[1]"
+    elif k == 1:
+        tag = f"ACT sim_insertion_scripted training step (fwd+loss+bwd+AdamW), per-GPU batch {b}, 1 camera 480x640"
+        cfgs = "BASELINE configs[2] shape, non-default --batch"
+    else:
+        tag = f"Mobile-ALOHA {k}-camera ACT training step (fwd+loss+bwd+AdamW), per-GPU batch {b}, {k} cameras 480x640"
+        cfgs = "BASELINE configs[3] shape, non-default --cameras/--batch"
+    return f"{tag}, qpos 14, chunk 100, hidden 512, ff 3200, enc 4/dec 7, kl_weight 10 ({cfgs})"
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -92,51 +110,126 @@ def measured_peaks():
     return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
 
 
-def cpu_train_sample(batch=2, threads=None):
-    """Reference algorithm on host cores (oracle port = torch CPU fp32 restatement of the reference modules):
-    one fwd + loss + backward + AdamW step on a bounded sample (batch `batch` of the same 480x640 workload)."""
-    import torch
-    from oracle import act_oracle as O
-    threads = threads or os.cpu_count()
-    torch.set_num_threads(threads)
-    cfg = O.make_cfg(num_cameras=K_CAM)
-    sd = O.init_state_dict(cfg, 0)
-    b = O.make_inputs(cfg, batch, H, W, 0)
-    names = O.trainable_names(cfg)
-    params = [torch.nn.Parameter(sd[n]) for n in names]
-    opt = torch.optim.AdamW(params, lr=1e-5, weight_decay=1e-4)
-    t0 = time.time()
-    leaf = dict(sd)
-    leaf.update({n: p for n, p in zip(names, params)})
-    opt.zero_grad()
-    out = O.policy_forward(leaf, cfg, b["qpos"], b["image"], b["actions"], b["is_pad"], b["eps"])
-    out["loss"].backward()
-    opt.step()
-    dt = time.time() - t0
-    return batch / dt, threads, f"1 optimisation step (fwd+loss+bwd+AdamW) at batch {batch} of the 480x640 1-camera workload, {dt:.1f} s"
+class CpuTrainer:
+    """Reference algorithm on host cores (oracle port = torch CPU fp32 restatement of the reference modules, validated
+    against the unmodified reference by oracle/make_golden.py): zero_grad + fwd + loss + backward + AdamW steps of the
+    same 480x640 workload, built once and stepped repeatedly."""
+
+    def __init__(self, threads=None):
+        import torch
+        from oracle import act_oracle as O
+        self.torch, self.O = torch, O
+        self.threads = threads or os.cpu_count()
+        torch.set_num_threads(self.threads)
+        self.cfg = O.make_cfg(num_cameras=K_CAM)
+        self.sd = O.init_state_dict(self.cfg, 0)
+        self.names = O.trainable_names(self.cfg)
+        self.params = [torch.nn.Parameter(self.sd[n]) for n in self.names]
+        self.opt = torch.optim.AdamW(self.params, lr=1e-5, weight_decay=1e-4)
+        self.leaf = dict(self.sd)
+        self.leaf.update({n: p for n, p in zip(self.names, self.params)})
+        self.inputs = {}
+
+    def step(self, batch):
+        """one optimisation step at `batch` samples; returns seconds"""
+        O = self.O
+        if batch not in self.inputs:
+            self.inputs[batch] = O.make_inputs(self.cfg, batch, H, W, 0)
+        b = self.inputs[batch]
+        t0 = time.perf_counter()
+        self.opt.zero_grad()
+        out = O.policy_forward(self.leaf, self.cfg, b["qpos"], b["image"], b["actions"], b["is_pad"], b["eps"])
+        out["loss"].backward()
+        self.opt.step()
+        return time.perf_counter() - t0
+
+    def pick_batch(self, steps, budget_s):
+        """warm up with one batch-2 step and pick the largest per-step batch (<= the workload's 8) whose `steps`
+        steps fit the time budget"""
+        dt2 = self.step(2)
+        for b in (8, 4, 2):
+            if dt2 * (b / 2.0) * steps <= budget_s:
+                return b
+        return 1
+
+
+def cpu_train_sample(target_s=12.0, max_steps=8):
+    """cpu_baseline leg: a bounded sample (about 10-30 s of CPU work) of the bench workload on all host threads."""
+    tr = CpuTrainer()
+    b = tr.pick_batch(2, target_s)
+    tr.step(b)                                           # untimed warm-up at the chosen batch
+    n, tot = 0, 0.0
+    while n < max_steps and (n < 2 or tot < target_s):
+        tot += tr.step(b)
+        n += 1
+    return b * n / tot, tr.threads, (f"{n} optimisation steps (zero_grad+fwd+loss+bwd+AdamW) at batch {b} of the 480x640 "
+                                     f"1-camera workload, {tot:.1f} s, torch {tr.torch.__version__} CPU fp32")
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path (oracle port), all host threads."""
+    """--impl reference: the reference's CPU implementation of the path (oracle port), all host threads.  Each timed
+    step is one optimisation step at the largest batch <= 8 for which `--steps` steps end within a few minutes."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import torch
-    vals = []
-    for _ in range(max(1, min(args.warmup, 1))):
-        cpu_train_sample(2)
-    for _ in range(max(1, args.steps if args.steps <= 3 else 3)):
-        v, threads, sample = cpu_train_sample(2)
-        vals.append(v)
-    value = sum(vals) / len(vals)
+    tr = CpuTrainer()
+    b = tr.pick_batch(args.steps + args.warmup, 150.0)
+    for _ in range(args.warmup):
+        tr.step(b)
+    tot = 0.0
+    for _ in range(args.steps):
+        tot += tr.step(b)
+    value = b * args.steps / tot
+    sample = (f"{args.steps} optimisation steps at batch {b} of the 480x640 1-camera workload, {tot:.1f} s, "
+              f"torch {torch.__version__} CPU fp32")
     line = dict(impl="reference", metric="ACT train samples/s", value=value, unit="samples/s", n_gpus=args.gpus,
-                steps=len(vals), warmup=1, ms_per_step=2.0 / value * 1e3, higher_is_better=True, scaling="weak",
-                vs_baseline=None, dtype="f32", data="synthetic",
-                config=dict(workload="ACT sim_transfer_cube_scripted train step, batch 8/GPU, 1 camera 480x640, chunk 100 "
-                            "(reference algorithm on host CPU, bounded sample: batch 2 per step)", torch=torch.__version__),
-                cpu_baseline=dict(value=value, unit="samples/s", cores=threads, kind="port", sample=sample),
+                steps=args.steps, warmup=args.warmup, ms_per_step=tot / args.steps * 1e3, higher_is_better=True,
+                scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
+                config=dict(workload="ACT sim_transfer_cube_scripted training step (fwd+loss+bwd+AdamW), per-GPU batch 8, "
+                            "1 camera 480x640, qpos 14, chunk 100, hidden 512, ff 3200, enc 4/dec 7, kl_weight 10 (BASELINE configs[1])",
+                            impl_note=f"reference algorithm on host CPU (oracle port), bounded sample: batch {b} per step",
+                            torch=torch.__version__),
+                cpu_baseline=dict(value=value, unit="samples/s", cores=tr.threads, kind="port", sample=sample),
                 e2e=dict(value=value, unit="samples/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
     print(json.dumps(line))
+
+
+def eager_gpu_leg(dev, batch, steps=5):
+    """--eager-gpu: the reference algorithm (oracle port, same torch ops as the reference modules) as eager PyTorch on this
+    GPU with torch defaults, fp32 and bf16 autocast.  A baseline leg only ("the practical bar"): nothing
+    of the product path runs here and the product never calls this."""
+    import torch
+    from oracle import act_oracle as O
+    cfg = O.make_cfg(num_cameras=K_CAM)
+    sd = {k: v.to(dev) for k, v in O.init_state_dict(cfg, 0).items()}
+    names = O.trainable_names(cfg)
+    params = [torch.nn.Parameter(sd[n]) for n in names]
+    opt = torch.optim.AdamW(params, lr=1e-5, weight_decay=1e-4)
+    leaf = dict(sd)
+    leaf.update({n: p for n, p in zip(names, params)})
+    b = {k: v.to(dev) for k, v in O.make_inputs(cfg, batch, H, W, 0).items()}
+    res = {}
+    for tag, autocast in (("fp32", False), ("bf16_autocast", True)):
+        def one():
+            opt.zero_grad()
+            with torch.device(dev), torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+                out = O.policy_forward(leaf, cfg, b["qpos"], b["image"], b["actions"], b["is_pad"], b["eps"])
+            out["loss"].backward()
+            opt.step()
+        for _ in range(3):
+            one()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            one()
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        res[tag] = dict(ms_per_step=ms, samples_per_s=batch / ms * 1e3)
+    res["note"] = (f"eager PyTorch {torch.__version__} (cuDNN/cuBLAS, torch default TF32 settings) running the reference's op "
+                   f"sequence incl. all 7 decoder layers at batch {batch}; not a reference-published number")
+    return res
 
 
 def infer_legs(eng, dev, envs, steps):
@@ -161,7 +254,7 @@ def infer_legs(eng, dev, envs, steps):
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
     out.update(envs_per_gpu=envs, ms_per_env_step_batch=ms, chunks_per_s=envs / ms * 1e3,
-               tflops=34.9e9 * envs / ms / 1e9, action_checksum=float(act.sum()))
+               tflops={1: 34.9e9, 3: 107.1e9}.get(K_CAM, 34.9e9 * K_CAM) * envs / ms / 1e9, action_checksum=float(act.sum()))
     del big, imgs
     one = ActEngine.sharing(eng, 1, H, W, False)
     img1 = torch.rand((1, K_CAM, 3, H, W), generator=g).to(dev)
@@ -186,6 +279,9 @@ def run_ours(args):
     from act_plus_plus_b200.train import train_step
     import ctypes as C
 
+    global B_PER_GPU, K_CAM, FLOP_PER_SAMPLE_TRAIN
+    B_PER_GPU, K_CAM = args.batch, args.cameras
+    FLOP_PER_SAMPLE_TRAIN = {1: 115.6e9, 3: 332.0e9}.get(K_CAM, 115.6e9 * K_CAM)      # SURVEY.md 8(d), live path
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -320,6 +416,12 @@ def run_ours(args):
         ev.record()
     torch.cuda.synchronize()
     ev_pair_ms = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(0, 200, 2))[50]   # median empty event pair
+    dump_path = os.path.join(ROOT, "gpurun_out", f"tc_launches_rank{rank}.csv")
+    try:
+        os.makedirs(os.path.dirname(dump_path), exist_ok=True)
+        lib.act_tc_profile_set_dump(dump_path.encode())
+    except Exception:
+        dump_path = None
     lib.act_tc_profile_begin()
     PSTEPS = 2
     for i in range(PSTEPS):
@@ -327,7 +429,19 @@ def run_ours(args):
     torch.cuda.synchronize()
     tot_ms, tot_fl, nl, mx = C.c_double(), C.c_double(), C.c_int(), C.c_double()
     _lib.check(lib.act_tc_profile_end(C.byref(tot_ms), C.byref(tot_fl), C.byref(nl), C.byref(mx)), "tc_profile_end")
+    lib.act_tc_profile_set_dump(b"")
     eng.set_concurrent(True)
+    by_class = {}
+    if dump_path and os.path.exists(dump_path):
+        import csv
+        for row in csv.DictReader(open(dump_path)):
+            c = row["label"].split(" ")[0]
+            d = by_class.setdefault(c, dict(launches=0, ms=0.0, gflop=0.0))
+            d["launches"] += 1; d["ms"] += float(row["ms"]); d["gflop"] += float(row["gflop"])
+        for d in by_class.values():
+            net = max(1e-9, d["ms"] - d["launches"] * ev_pair_ms)
+            d.update(launches=d["launches"] // PSTEPS, ms=d["ms"] / PSTEPS, gflop=d["gflop"] / PSTEPS,
+                     tflops=d["gflop"] / d["ms"], tflops_net_of_event_cost=d["gflop"] / net)
     if rank != 0:
         # a captured graph that contains NCCL kernels keeps the communicator busy on teardown: leave without it
         torch.cuda.synchronize()
@@ -341,15 +455,14 @@ def run_ours(args):
     line = dict(metric="ACT train samples/s", value=value, unit="samples/s", n_gpus=world, steps=args.steps,
                 warmup=args.warmup, ms_per_step=ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
                 dtype="bf16", data="synthetic",
-                config=dict(workload="ACT sim_transfer_cube_scripted training step (fwd+loss+bwd+AdamW), per-GPU batch 8, "
-                            "1 camera 480x640, qpos 14, chunk 100, hidden 512, ff 3200, enc 4/dec 7, kl_weight 10 (BASELINE configs[1])",
+                config=dict(workload=workload_name(B, K_CAM),
                             global_batch=B * world, parallelism=f"dp{world}", cuda_graph=graph is not None,
                             l2="4 rotating input batches; parameters+Adam state (1.3 GB) exceed the 126 MB L2 every step",
                             dropout="0 (reference validation path; see DESIGN.md)", last_loss=loss_host),
                 e2e=dict(value=n_samples / (ms_e2e / 1e3), unit="samples/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=4),
                 gpu_launches=launches_per_step * args.steps,
                 roofline=dict(bound="tensor", achieved=tc_tflops, peak=peaks["tf_sust"], unit="TFLOP/s",
-                              frac=tc_tflops / peaks["tf_sust"], traffic=TC_DRAM_BYTES_PER_LAUNCH, peak_source=peaks["src"] + " (sustained bf16)",
+                              frac=tc_tflops / peaks["tf_sust"], traffic=TC_DRAM_BYTES_PER_LAUNCH if (B == 8 and K_CAM == 1) else None, peak_source=peaks["src"] + " (sustained bf16)",
                               traffic_source="profiles/r01_tc_dram_per_step.md: ncu dram__bytes_read+write summed over the 277 tcgen05 launches "
                                              "of one step (cold cache per launch) / 277",
                               kernel="tc_kernel<*> (all tcgen05 GEMM/conv/wgrad launches of one step)",
@@ -358,7 +471,7 @@ def run_ours(args):
                                      "(ACT engine concurrency off); includes the event-pair cost below",
                               event_pair_us=ev_pair_ms * 1e3,
                               achieved_net_of_event_cost=(tot_fl.value / PSTEPS) / max(1e-9, (tc_ms_step - (nl.value // PSTEPS) * ev_pair_ms) / 1e3) / 1e12,
-                              tc_share_of_serial_step=None, longest_launch_ms=mx.value,
+                              by_kernel_class=by_class, longest_launch_ms=mx.value,
                               whole_step_tflops=FLOP_PER_SAMPLE_TRAIN * B / (ms / args.steps / 1e3) / 1e12),
                 clocks=clk)
     # ---------------- HBM-bound side of the step: the fused AdamW (+ bf16 shadow, + conv re-pack), timed alone
@@ -378,6 +491,11 @@ def run_ours(args):
                                     algorithmic_bytes=adam_bytes, peak_source=peaks["src"] + " (copy bandwidth)")
     except Exception as ex:
         line["roofline_hbm"] = dict(error=str(ex)[:200])
+    if args.eager_gpu:
+        try:
+            line["eager_gpu_baseline"] = eager_gpu_leg(dev, B)
+        except Exception as ex:
+            line["eager_gpu_baseline"] = dict(error=str(ex)[:300])
     if not args.no_infer:
         try:
             line["inference"] = infer_legs(eng, dev, args.infer_envs, max(3, min(args.steps, 10)))
@@ -385,7 +503,7 @@ def run_ours(args):
             line["inference"] = dict(error=str(ex)[:200])
     if not args.no_cpu_baseline and world == 1:
         try:
-            v, threads, sample = cpu_train_sample(2)
+            v, threads, sample = cpu_train_sample()
             line["cpu_baseline"] = dict(value=v, unit="samples/s", cores=threads, kind="port", sample=sample)
         except Exception as ex:
             line["cpu_baseline"] = dict(value=None, unit="samples/s", cores=os.cpu_count(), kind="port", sample=f"failed: {ex}")
