@@ -182,6 +182,27 @@ extern "C" int act_engine_backward_and_step_dp(act_engine* e, int step, float lo
   return e->eng->backward_and_step(step, loss_grad, ST(stream), grads_ready, user);
 }
 extern "C" int act_engine_adamw_step(act_engine* e, int step, void* stream) { return e->eng->adamw(step, ST(stream)); }
+extern "C" int act_engine_dp_local(act_engine* e, void** grads, void** params, void** shadow, void** signal) {
+  return e->eng->dp_local(grads, params, shadow, signal);
+}
+extern "C" int act_engine_dp_export(act_engine* e, void* blob, int capacity) { return e->eng->dp_export(blob, capacity); }
+extern "C" int act_engine_dp_connect(act_engine* e, int rank, int world, const void* blobs, int blob_bytes) {
+  return e->eng->dp_connect(rank, world, blobs, blob_bytes);
+}
+extern "C" int act_engine_dp_set_peers(act_engine* e, int rank, int world, void* const* grads, void* const* params,
+                                       void* const* shadow, void* const* signal) {
+  return e->eng->dp_set_peers(rank, world, grads, params, shadow, signal);
+}
+extern "C" int act_engine_backward_and_step_p2p(act_engine* e, int step, float loss_grad, void* stream) {
+  return e->eng->backward_and_step(step, loss_grad, ST(stream), nullptr, nullptr, true);
+}
+extern "C" int act_engine_dp_status(act_engine* e) { return e->eng->dp_status(); }
+extern "C" int act_engine_dp_preset_signal(act_engine* e, int peer_rank, unsigned int epoch) {
+  return e->eng->dp_preset_signal(peer_rank, epoch);
+}
+extern "C" int act_engine_dp_slices(act_engine* e, long long* offsets, long long* counts, int capacity) {
+  return e->eng->dp_slices(offsets, counts, capacity);
+}
 extern "C" int act_engine_adamw_region(act_engine* e, int step, int region, int blocks_per_sm, void* stream) {
   if (region < 0 || region >= R_COUNT) { set_error("act_engine_adamw_region: bad region"); return -1; }
   return e->eng->adamw_region(region, step, ST(stream), blocks_per_sm);

@@ -1,0 +1,162 @@
+// Data-parallel optimiser step fused with its gradient exchange over NVLink peer memory (the reference is
+// single-GPU: imitate_episodes.py:603-607 is loss.backward(); optimizer.step()).
+//
+// Every rank maps every other rank's flat gradient / parameter / bf16-shadow buffers (CUDA IPC, dp_export / dp_connect
+// in engine_params.cu).  For one contiguous gradient range the three steps "all-reduce the gradients, run AdamW on the
+// whole range, (implicitly) keep replicas identical" become ONE kernel per rank:
+//   rank r owns the r-th slice of the range; for each float4 of its slice it loads the gradient from all ranks (peer
+//   loads, fixed rank order -> run-to-run deterministic), averages, applies torch.optim.AdamW (detr/main.py:102-110)
+//   with its private exp_avg / exp_avg_sq slice, and stores the new fp32 parameter and bf16 shadow into EVERY rank's
+//   buffers (peer stores).  Reduce-scatter, optimiser and all-gather in one pass: each rank reads 4 B/param from each
+//   peer for 1/N of the range and writes 4+2 B/param to each peer, instead of a ring all-reduce (2x the gradient bytes
+//   through local HBM on top of NVLink) followed by a full-range AdamW pass (28 B/param of local HBM per rank).
+// Ordering between ranks is a flag barrier in peer memory (one slot per barrier site and rank, monotonically increasing
+// epochs kept on the device so a captured CUDA graph can replay it).
+#include "kernels.h"
+#include <cmath>
+
+namespace act {
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_relaxed_sys_v4(const float4* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// One warp.  Lane j < world: publish "rank `rank` reached site `site` for the e-th time" in rank j's signal block, then
+// wait until rank j has published the same in ours.  status[0] is set to 1 if a peer does not show up within
+// `timeout_ns` (the step's results are then meaningless, but the GPU is not left spinning for ever).
+__global__ void dp_barrier_kernel(DpPeers peers, uint32_t* __restrict__ epoch, uint32_t* __restrict__ status, int site,
+                                  unsigned long long timeout_ns) {
+  const int lane = threadIdx.x;
+  const uint32_t e = epoch[site] + 1;
+  __syncwarp();
+  __threadfence_system();                                    // everything this GPU wrote before the barrier
+  if (lane < peers.world) {
+    st_release_sys(peers.signal[lane] + site * DP_MAX_WORLD + peers.rank, e);
+    const uint32_t* mine = peers.signal[peers.rank] + site * DP_MAX_WORLD + lane;
+    const unsigned long long t0 = globaltimer_ns();
+    while (static_cast<int32_t>(ld_acquire_sys(mine) - e) < 0) {
+      __nanosleep(200);
+      if (globaltimer_ns() - t0 > timeout_ns) { status[0] = 1u; break; }
+    }
+  }
+  __syncwarp();
+  __threadfence_system();
+  if (lane == 0) epoch[site] = e;
+}
+
+int dp_barrier(const DpPeers& peers, uint32_t* epoch, uint32_t* status, int site, cudaStream_t st) {
+  ACT_CHECK(site >= 0 && site < DP_MAX_SITES, "dp_barrier: too many barrier sites in one step");
+  dp_barrier_kernel<<<1, 32, 0, st>>>(peers, epoch, status, site, 20ull * 1000ull * 1000ull * 1000ull);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Rank r's slice of n4 float4s: [r*n4/world, (r+1)*n4/world) with the remainder spread over the lowest ranks.
+__host__ __device__ inline void dp_slice(long long n4, int rank, int world, long long* lo, long long* hi) {
+  const long long base = n4 / world, rem = n4 % world;
+  *lo = rank * base + (rank < rem ? rank : rem);
+  *hi = *lo + base + (rank < rem ? 1 : 0);
+}
+
+template <int WORLD>
+__global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs a, long long off, float bc1, float rsqrt_bc2) {
+  // WORLD > 0: compile-time rank count (unrolled peer loads all in flight); WORLD == 0: run-time count
+  const int world = WORLD > 0 ? WORLD : peers.world;
+  const long long n4 = a.n / 4;
+  long long lo, hi;
+  dp_slice(n4, peers.rank, world, &lo, &hi);
+  const float decay = 1.f - a.lr * a.wd;
+  const float step_size = a.lr / bc1;
+  const float inv_world = 1.f / static_cast<float>(world);
+  const long long off4 = off / 4;                              // ranges are 16-byte aligned (checked on the host)
+  for (long long i = lo + blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * 1LL * blockDim.x) {
+    float4 gs[WORLD > 0 ? WORLD : DP_MAX_WORLD];
+#pragma unroll
+    for (int j = 0; j < (WORLD > 0 ? WORLD : DP_MAX_WORLD); ++j)
+      if (j < world) gs[j] = ld_relaxed_sys_v4(reinterpret_cast<const float4*>(peers.grads[j]) + off4 + i);
+    float4 g = gs[0];
+#pragma unroll
+    for (int j = 1; j < (WORLD > 0 ? WORLD : DP_MAX_WORLD); ++j)
+      if (j < world) { g.x += gs[j].x; g.y += gs[j].y; g.z += gs[j].z; g.w += gs[j].w; }
+    g.x *= inv_world; g.y *= inv_world; g.z *= inv_world; g.w *= inv_world;
+    float4 p = reinterpret_cast<const float4*>(a.p)[i];
+    float4 m = reinterpret_cast<float4*>(a.m)[i], v = reinterpret_cast<float4*>(a.v)[i];
+#define ADAM1(c)                                                      \
+    p.c *= decay;                                                     \
+    m.c = a.beta1 * m.c + (1.f - a.beta1) * g.c;                      \
+    v.c = a.beta2 * v.c + (1.f - a.beta2) * g.c * g.c;                \
+    p.c -= step_size * (m.c / (sqrtf(v.c) * rsqrt_bc2 + a.eps));
+    ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
+#undef ADAM1
+    reinterpret_cast<float4*>(a.m)[i] = m;
+    reinterpret_cast<float4*>(a.v)[i] = v;
+    uint2 o;
+    {
+      __nv_bfloat162 l2 = __floats2bfloat162_rn(p.x, p.y), h2 = __floats2bfloat162_rn(p.z, p.w);
+      o.x = *reinterpret_cast<uint32_t*>(&l2); o.y = *reinterpret_cast<uint32_t*>(&h2);
+    }
+#pragma unroll
+    for (int j = 0; j < (WORLD > 0 ? WORLD : DP_MAX_WORLD); ++j) {
+      if (j < world) {
+        reinterpret_cast<float4*>(peers.params[j])[off4 + i] = p;
+        if (a.shadow) reinterpret_cast<uint2*>(peers.shadow[j])[off4 + i] = o;
+      }
+    }
+  }
+  // tail (n % 4 elements): rank 0, first threads of block 0
+  if (peers.rank == 0 && blockIdx.x == 0 && threadIdx.x < (a.n & 3)) {
+    const long long i = n4 * 4 + threadIdx.x;
+    float g = 0.f;
+    for (int j = 0; j < world; ++j) g += peers.grads[j][off + i];
+    g *= inv_world;
+    float p = a.p[i] * decay;
+    const float m = a.beta1 * a.m[i] + (1.f - a.beta1) * g;
+    const float v = a.beta2 * a.v[i] + (1.f - a.beta2) * g * g;
+    a.m[i] = m; a.v[i] = v;
+    p -= step_size * (m / (sqrtf(v) * rsqrt_bc2 + a.eps));
+    for (int j = 0; j < world; ++j) {
+      peers.params[j][off + i] = p;
+      if (a.shadow) peers.shadow[j][off + i] = __float2bfloat16_rn(p);
+    }
+  }
+  __threadfence_system();                                      // peer stores are performed before the next barrier's flag
+}
+
+// a.p / a.m / a.v point at this rank's own buffers at the START of the range (offset `off` floats into the flat buffers);
+// a.g and a.shadow's value are ignored except that a.shadow != nullptr asks for the bf16 shadow to be written.
+int dp_adamw_step(const DpPeers& peers, const AdamWArgs& a, long long off, cudaStream_t st) {
+  if (a.n <= 0) return 0;
+  ACT_CHECK(peers.world >= 2 && peers.world <= DP_MAX_WORLD, "dp_adamw_step: peers not connected");
+  ACT_CHECK((off & 3) == 0 && (reinterpret_cast<uintptr_t>(a.p) & 15) == 0, "data-parallel AdamW range must be 16-byte aligned");
+  const double bc1 = 1.0 - std::pow(static_cast<double>(a.beta1), a.step);
+  const double bc2 = 1.0 - std::pow(static_cast<double>(a.beta2), a.step);
+  const long long n4 = a.n / 4, slice = (n4 + peers.world - 1) / peers.world;
+  const int per_sm = a.background > 0 ? std::min(a.background, 8) : 8;
+  const int blocks = static_cast<int>(std::max<long long>(1, std::min<long long>((slice + 255) / 256, 148LL * per_sm)));
+  const float f1 = static_cast<float>(bc1), f2 = static_cast<float>(1.0 / std::sqrt(bc2));
+  switch (peers.world) {
+    case 2: dp_adamw_kernel<2><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2); break;
+    case 4: dp_adamw_kernel<4><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2); break;
+    case 8: dp_adamw_kernel<8><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2); break;
+    default: dp_adamw_kernel<0><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2); break;
+  }
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace act

@@ -106,7 +106,26 @@ class Engine {
   // grads_ready: data-parallel hook.  Called on the host while the step is enqueued, once per contiguous range of the
   // flat gradient buffer, with the stream on which that range is final; it must enqueue the cross-rank average of the
   // range and order `stream` after it.  The range's AdamW follows on the same stream.
-  int backward_and_step(int step, float loss_grad, cudaStream_t st, GradsReadyFn cb = nullptr, void* cb_user = nullptr);
+  int backward_and_step(int step, float loss_grad, cudaStream_t st, GradsReadyFn cb = nullptr, void* cb_user = nullptr,
+                        bool p2p = false);
+  // ---- data-parallel step over NVLink peer memory (dp_p2p.cu): every rank maps the other ranks' flat gradient /
+  // parameter / bf16-shadow buffers and a block of barrier flags; backward_and_step(p2p = true) then replaces each
+  // "all-reduce the range, AdamW the range" pair by a flag barrier and ONE kernel that reduces this rank's slice of the
+  // range from all ranks, updates it and stores the new parameters into every rank.  All of it runs on one dedicated
+  // stream in a fixed order (same on every rank), so the spinning barrier kernels cannot wait on each other crosswise.
+  static constexpr int DP_BLOB_BYTES = 4 * 64 + 4 * 8 + 8;
+  int dp_local(void** grads, void** params, void** shadow, void** signal);      // this rank's four buffers (allocates the flags)
+  int dp_export(void* blob, int cap);                                             // CUDA-IPC handles of the four buffers
+  int dp_connect(int rank, int world, const void* blobs, int blob_bytes);         // map every peer's buffers
+  int dp_set_peers(int rank, int world, void* const* grads, void* const* params, void* const* shadow, void* const* signal);
+  int dp_preset_signal(int peer_rank, uint32_t epoch);
+  int dp_status();                                                                // 0 ok, 1 a barrier timed out (synchronises)
+  int dp_world() const { return peers_.world; }
+  int dp_slices(long long* off, long long* n, int cap) const {
+    const int k = static_cast<int>(dp_ranges_.size());
+    for (int i = 0; i < k && i < cap; ++i) { off[i] = dp_ranges_[i].first; n[i] = dp_ranges_[i].second; }
+    return k;
+  }
   const EngineConfig& cfg() const { return cfg_; }
   long long workspace_bytes() const { return ws_bytes_; }
   int launches() const { return launches_; }
@@ -161,6 +180,15 @@ class Engine {
   long long region_off_[R_COUNT] = {0}, region_n_[R_COUNT] = {0};
   float *params_ = nullptr, *grads_ = nullptr, *m_ = nullptr, *v_ = nullptr;
   bf16* shadow_ = nullptr;
+  DpPeers peers_;
+  uint32_t *dp_signal_ = nullptr, *dp_epoch_ = nullptr, *dp_status_ = nullptr;
+  cudaStream_t dp_stream_ = nullptr;
+  cudaEvent_t dp_ev_[DP_MAX_SITES] = {}, dp_done_ = nullptr;
+  int dp_site_ = 0;
+  bool dp_fused_ = false;                       // true while backward_and_step(p2p = true) is being enqueued
+  std::vector<void*> dp_opened_;
+  std::vector<std::pair<long long, long long>> dp_ranges_;   // ranges exchanged by the last p2p step
+  int dp_sync_point(cudaStream_t producer);     // dp_stream_ waits for `producer`, then a cross-rank flag barrier on dp_stream_
   std::vector<void*> allocs_;
   long long ws_bytes_ = 0;
   int launches_ = 0;

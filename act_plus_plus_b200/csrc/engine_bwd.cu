@@ -423,6 +423,7 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
 }
 
 int Engine::grads_ready(long long off, long long n, cudaStream_t st) {
+  if (dp_fused_) return n > 0 ? dp_sync_point(st) : 0;      // every rank's gradients of the range are final past this point
   if (!grads_cb_ || n <= 0) return 0;
   if (grads_cb_(grads_cb_user_, off, n, st)) { set_error("gradient all-reduce callback failed"); return -1; }
   return 0;
@@ -442,12 +443,30 @@ int Engine::backbone_bwd_and_step(cudaStream_t st) {
   return adamw_region(R_BACKBONE, opt_step_, wg, 3);
 }
 
-int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsReadyFn cb, void* cb_user) {
+int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsReadyFn cb, void* cb_user, bool p2p) {
   ACT_CHECK(cfg_.train && grads_ != nullptr, "engine has no training workspace / gradient buffer");
   ACT_CHECK(have_actions_ && cur_B_ > 0, "backward needs a preceding training forward (with actions)");
+  ACT_CHECK(!p2p || (peers_.world > 1 && dp_stream_ != nullptr), "peer-memory data-parallel step without connected peers");
+  ACT_CHECK(!(p2p && cb), "peer-memory data-parallel step and an all-reduce callback are exclusive");
   if (ensure_streams()) return -1;
+  // the peer-memory step ends with a barrier: every rank has finished reading this rank's gradients and writing its
+  // parameters before the caller's stream goes on (next zero_grad / forward)
+  auto p2p_finish = [&]() -> int {
+    if (dp_sync_point(st)) return -1;
+    ACT_CUDA(cudaEventRecord(dp_done_, dp_stream_));
+    ACT_CUDA(cudaStreamWaitEvent(st, dp_done_, 0));
+    return 0;
+  };
   if (!concurrent_) {
     if (backward(0, loss_grad, st)) return -1;
+    if (p2p) {
+      struct G0 { Engine* e; ~G0() { e->dp_fused_ = false; } } g0{this};
+      dp_fused_ = true; dp_site_ = 0; dp_ranges_.clear();
+      for (int r : {R_MAIN, R_CVAE, R_BACKBONE})
+        if (region_n_[r] > 0 && (grads_ready(region_off_[r], region_n_[r], st) || adamw_region(r, step, st))) return -1;
+      if (adamw_region(R_DEAD, step, st)) return -1;
+      return p2p_finish();
+    }
     if (cb) {                                               // serial data-parallel step: one averaging call per region
       for (int r : {R_MAIN, R_CVAE, R_BACKBONE})
         if (region_n_[r] > 0 && cb(cb_user, region_off_[r], region_n_[r], st)) { set_error("gradient all-reduce callback failed"); return -1; }
@@ -456,9 +475,11 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
   }
   struct Guard {                                            // the hook is only live inside this call
     Engine* e;
-    ~Guard() { e->grads_cb_ = nullptr; e->grads_cb_user_ = nullptr; e->inline_opt_step_ = 0; e->dp_bb_pending_ = false; tc_set_sm_reserve(0); }
+    ~Guard() { e->grads_cb_ = nullptr; e->grads_cb_user_ = nullptr; e->inline_opt_step_ = 0; e->dp_bb_pending_ = false; e->dp_fused_ = false; tc_set_sm_reserve(0); }
   } guard{this};
   grads_cb_ = cb; grads_cb_user_ = cb_user; opt_step_ = step;
+  dp_fused_ = p2p; dp_site_ = 0; if (p2p) dp_ranges_.clear();
+  const bool dp = cb != nullptr || p2p;                     // either way: ranges are exchanged in the order enqueued here
   if (wg_join(st)) return -1;                               // an asynchronous zero_grad
   if (zero_backward_outputs(st)) return -1;
   if (transformer_bwd(loss_grad, st)) return -1;
@@ -469,7 +490,7 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
     return adamw_region(R_MAIN, step, wg, 3) || adamw_region(R_DEAD, step, wg, 3) ? -1 : 0;
   };
   // With the hook the collectives run in the order they are enqueued here, so the region that is final first goes first
-  if (cb && main_regions()) return -1;
+  if (dp && main_regions()) return -1;
   if (fork_side(st)) return -1;
   auto cvae_branch = [&]() -> int {
     inline_opt_step_ = step;
@@ -489,7 +510,7 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
   static int bb_slot = -2;
   if (bb_slot == -2) { const char* e = getenv("ACT_DP_BB_SLOT"); bb_slot = e ? atoi(e) : -1; }
   dp_main_st_ = st;
-  if (cb) {
+  if (dp) {
     // backbone gradients are final roughly when half of the CVAE-encoder layers are (measured: profiles/r01_dp_timeline.md)
     dp_bb_slot_ = bb_slot >= 0 ? bb_slot : cfg_.enc_layers / 2;
     dp_bb_pending_ = true;
@@ -503,7 +524,8 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
     if (backbone_bwd_and_step(st)) return -1;
   }
   if (join_side(st)) return -1;
-  return wg_join(st);
+  if (wg_join(st)) return -1;
+  return p2p ? p2p_finish() : 0;
 }
 
 int Engine::backward(int stage, float loss_grad, cudaStream_t st) {

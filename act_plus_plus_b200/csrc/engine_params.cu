@@ -1,5 +1,6 @@
 // Engine: tensor table (reference state_dict names), flat layout by optimizer region, bf16 shadows, AdamW.
 #include "engine.h"
+#include <cuda.h>
 #include <cmath>
 #include <cstring>
 
@@ -8,6 +9,10 @@ namespace act {
 Engine::Engine(const EngineConfig& cfg) : cfg_(cfg) {}
 
 Engine::~Engine() {
+  for (void* p : dp_opened_) cudaIpcCloseMemHandle(p);
+  for (cudaEvent_t e : dp_ev_) if (e) cudaEventDestroy(e);
+  if (dp_done_) cudaEventDestroy(dp_done_);
+  if (dp_stream_) cudaStreamDestroy(dp_stream_);
   for (void* p : allocs_) cudaFree(p);
   if (ev_fork_) cudaEventDestroy(ev_fork_);
   if (ev_join_) cudaEventDestroy(ev_join_);
@@ -394,6 +399,7 @@ int Engine::adamw_range(long long off, long long n, float lr, bool shadow, int s
   a.n = n; a.lr = lr; a.beta1 = cfg_.beta1; a.beta2 = cfg_.beta2; a.eps = cfg_.adam_eps; a.wd = cfg_.weight_decay;
   a.step = step; a.mode = 0; a.background = blocks_per_sm;
   ++launches_;
+  if (dp_fused_) { dp_ranges_.emplace_back(off, n); return dp_adamw_step(peers_, a, off, dp_stream_); }   // reduce + update + broadcast over peer memory
   return adamw_step(a, st);
 }
 int Engine::adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm) {
@@ -406,7 +412,16 @@ int Engine::adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm) {
   a.eps = cfg_.adam_eps; a.wd = cfg_.weight_decay; a.step = step; a.mode = r == R_DEAD ? 1 : 0;
   a.background = blocks_per_sm;
   ++launches_;
-  if (adamw_step(a, st)) return -1;
+  if (dp_fused_ && r != R_DEAD) {
+    dp_ranges_.emplace_back(o, a.n);
+    if (dp_adamw_step(peers_, a, o, dp_stream_)) return -1;
+    if (r != R_BACKBONE) return 0;
+    // the conv operands are re-packed from the fp32 masters: every rank's slice of them must have landed here first
+    if (dp_sync_point(dp_stream_)) return -1;
+    st = dp_stream_;
+  } else if (adamw_step(a, st)) {
+    return -1;
+  }
   if (r != R_BACKBONE) return 0;
   // packed conv operands (transposed / scaled layouts) are rebuilt from the fp32 masters, one launch per camera
   for (int k = 0; k < cfg_.num_cameras; ++k) {
@@ -426,6 +441,134 @@ int Engine::adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm) {
     ++launches_;
   }
   return 0;
+}
+
+// ------------------------------------------------------------------------------------------ peer-memory data parallel
+int Engine::dp_local(void** grads, void** params, void** shadow, void** signal) {
+  ACT_CHECK(params_ && grads_ && shadow_, "dp: parameters / gradients not bound");
+  if (!dp_signal_) {
+    dp_signal_ = reinterpret_cast<uint32_t*>(alloc<float>(DP_MAX_SITES * DP_MAX_WORLD));      // own cudaMalloc, zeroed
+    dp_epoch_ = reinterpret_cast<uint32_t*>(alloc<float>(DP_MAX_SITES));
+    dp_status_ = reinterpret_cast<uint32_t*>(alloc<float>(4));
+    ACT_CHECK(dp_signal_ && dp_epoch_ && dp_status_, "dp: flag allocation failed");
+    ACT_CUDA(cudaDeviceSynchronize());                                                          // alloc's memset
+  }
+  *grads = grads_; *params = params_; *shadow = shadow_; *signal = dp_signal_;
+  return 0;
+}
+
+namespace {
+struct DpBlob { cudaIpcMemHandle_t h[4]; long long off[4]; int device; int pad; };
+static_assert(sizeof(DpBlob) == Engine::DP_BLOB_BYTES, "DpBlob layout");
+
+// base address of the allocation that contains p (cudaIpcGetMemHandle wants the base; torch sub-allocates)
+int alloc_base(const void* p, void** base) {
+  using Fn = CUresult (*)(CUdeviceptr*, size_t*, CUdeviceptr);
+  static Fn fn = nullptr;
+  if (!fn) {
+    void* q = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &q, cudaEnableDefault, &qr) != cudaSuccess || !q) {
+      set_error("cuMemGetAddressRange unavailable"); return -1;
+    }
+    fn = reinterpret_cast<Fn>(q);
+  }
+  CUdeviceptr b = 0; size_t sz = 0;
+  if (fn(&b, &sz, reinterpret_cast<CUdeviceptr>(p)) != CUDA_SUCCESS) { set_error("cuMemGetAddressRange failed"); return -1; }
+  *base = reinterpret_cast<void*>(b);
+  return 0;
+}
+}  // namespace
+
+int Engine::dp_export(void* blob, int cap) {
+  ACT_CHECK(cap >= DP_BLOB_BYTES, "dp_export: buffer too small");
+  void* ptr[4];
+  if (dp_local(&ptr[0], &ptr[1], &ptr[2], &ptr[3])) return -1;
+  DpBlob b;
+  memset(&b, 0, sizeof b);
+  ACT_CUDA(cudaGetDevice(&b.device));
+  for (int i = 0; i < 4; ++i) {
+    void* base = nullptr;
+    if (alloc_base(ptr[i], &base)) return -1;
+    ACT_CUDA(cudaIpcGetMemHandle(&b.h[i], base));
+    b.off[i] = static_cast<const char*>(ptr[i]) - static_cast<const char*>(base);
+  }
+  memcpy(blob, &b, sizeof b);
+  return DP_BLOB_BYTES;
+}
+
+int Engine::dp_connect(int rank, int world, const void* blobs, int blob_bytes) {
+  ACT_CHECK(blob_bytes == DP_BLOB_BYTES, "dp_connect: blob size mismatch");
+  ACT_CHECK(world >= 2 && world <= DP_MAX_WORLD && rank >= 0 && rank < world, "dp_connect: bad rank / world");
+  void* mine[4];
+  if (dp_local(&mine[0], &mine[1], &mine[2], &mine[3])) return -1;
+  void* tab[4][DP_MAX_WORLD] = {};
+  for (int j = 0; j < world; ++j) {
+    if (j == rank) { for (int i = 0; i < 4; ++i) tab[i][j] = mine[i]; continue; }
+    DpBlob b;
+    memcpy(&b, static_cast<const char*>(blobs) + 1LL * j * DP_BLOB_BYTES, sizeof b);
+    for (int i = 0; i < 4; ++i) {
+      void* base = nullptr;
+      cudaError_t e = cudaIpcOpenMemHandle(&base, b.h[i], cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) {
+        set_error(std::string("cudaIpcOpenMemHandle (rank ") + std::to_string(j) + "): " + cudaGetErrorString(e));
+        cudaGetLastError();
+        return -1;
+      }
+      dp_opened_.push_back(base);
+      tab[i][j] = static_cast<char*>(base) + b.off[i];
+    }
+  }
+  return dp_set_peers(rank, world, tab[0], tab[1], tab[2], tab[3]);
+}
+
+int Engine::dp_set_peers(int rank, int world, void* const* grads, void* const* params, void* const* shadow, void* const* signal) {
+  ACT_CHECK(world >= 2 && world <= DP_MAX_WORLD && rank >= 0 && rank < world, "dp_set_peers: bad rank / world");
+  void* mine[4];
+  if (dp_local(&mine[0], &mine[1], &mine[2], &mine[3])) return -1;
+  ACT_CHECK(grads[rank] == mine[0] && params[rank] == mine[1] && shadow[rank] == mine[2] && signal[rank] == mine[3],
+            "dp_set_peers: entry `rank` must be this engine's own buffers");
+  peers_ = DpPeers();
+  peers_.rank = rank; peers_.world = world;
+  for (int j = 0; j < world; ++j) {
+    ACT_CHECK(grads[j] && params[j] && shadow[j] && signal[j], "dp_set_peers: null peer pointer");
+    peers_.grads[j] = static_cast<float*>(grads[j]); peers_.params[j] = static_cast<float*>(params[j]);
+    peers_.shadow[j] = static_cast<bf16*>(shadow[j]); peers_.signal[j] = static_cast<uint32_t*>(signal[j]);
+  }
+  if (!dp_stream_) {
+    ACT_CUDA(cudaStreamCreateWithFlags(&dp_stream_, cudaStreamNonBlocking));
+    for (cudaEvent_t& e : dp_ev_) ACT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    ACT_CUDA(cudaEventCreateWithFlags(&dp_done_, cudaEventDisableTiming));
+  }
+  return 0;
+}
+
+int Engine::dp_sync_point(cudaStream_t producer) {
+  ACT_CHECK(peers_.world > 1 && dp_stream_, "dp: peers not connected");
+  ACT_CHECK(dp_site_ < DP_MAX_SITES, "dp: too many barrier sites in one step");
+  if (producer != dp_stream_) {
+    ACT_CUDA(cudaEventRecord(dp_ev_[dp_site_], producer));
+    ACT_CUDA(cudaStreamWaitEvent(dp_stream_, dp_ev_[dp_site_], 0));
+  }
+  ++launches_;
+  return dp_barrier(peers_, dp_epoch_, dp_status_, dp_site_++, dp_stream_);
+}
+
+int Engine::dp_preset_signal(int peer_rank, uint32_t epoch) {
+  ACT_CHECK(dp_signal_ != nullptr && peer_rank >= 0 && peer_rank < DP_MAX_WORLD, "dp_preset_signal: no flag block / bad rank");
+  std::vector<uint32_t> h(DP_MAX_SITES * DP_MAX_WORLD);
+  ACT_CUDA(cudaMemcpy(h.data(), dp_signal_, h.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  for (int s = 0; s < DP_MAX_SITES; ++s) h[s * DP_MAX_WORLD + peer_rank] = epoch;
+  ACT_CUDA(cudaMemcpy(dp_signal_, h.data(), h.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int Engine::dp_status() {
+  if (!dp_status_) return 0;
+  uint32_t s = 0;
+  ACT_CUDA(cudaMemcpy(&s, dp_status_, sizeof s, cudaMemcpyDeviceToHost));
+  if (s) set_error("data-parallel flag barrier timed out (a peer did not reach the same step)");
+  return static_cast<int>(s);
 }
 
 int Engine::adamw(int step, cudaStream_t st) {

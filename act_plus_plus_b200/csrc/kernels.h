@@ -65,6 +65,18 @@ struct AdamWArgs {
   int background = 0;   // n > 0: launch n blocks per SM (n x 256 threads) so concurrently running tensor-core CTAs still find a slot
 };
 int adamw_step(const AdamWArgs& a, cudaStream_t st);
+
+// ---- dp_p2p.cu: data-parallel AdamW fused with the gradient exchange over NVLink peer memory
+constexpr int DP_MAX_WORLD = 8, DP_MAX_SITES = 64;
+struct DpPeers {           // device pointers valid on THIS device: index `rank` is local memory, the others are CUDA-IPC mappings
+  int rank = 0, world = 1;
+  float* grads[DP_MAX_WORLD] = {nullptr};
+  float* params[DP_MAX_WORLD] = {nullptr};
+  bf16* shadow[DP_MAX_WORLD] = {nullptr};
+  uint32_t* signal[DP_MAX_WORLD] = {nullptr};     // [DP_MAX_SITES][DP_MAX_WORLD] epochs per rank
+};
+int dp_barrier(const DpPeers& peers, uint32_t* epoch, uint32_t* status, int site, cudaStream_t st);
+int dp_adamw_step(const DpPeers& peers, const AdamWArgs& a, long long off, cudaStream_t st);
 int temporal_agg_step(float* ring, const float* chunks, const int* t, double* out, int E, int nq, int A, double k,
                       cudaStream_t st);
 

@@ -22,6 +22,21 @@ def shard_range(n: int, rank: int, world: int) -> Tuple[int, int]:
     return start, start + base + (1 if rank < rem else 0)
 
 
+def owner_slices(count: int, world: int) -> List[Tuple[int, int, int]]:
+    """(rank, lo, hi): the floats [lo, hi) of a `count`-float range (relative to its start) that `rank` owns in the
+    peer-memory optimiser step (csrc/dp_p2p.cu::dp_slice: float4 granularity, remainder to the lowest ranks; the
+    count % 4 tail belongs to rank 0)."""
+    n4 = count // 4
+    out = []
+    for r in range(world):
+        lo4, hi4 = shard_range(n4, r, world)
+        if hi4 > lo4:
+            out.append((r, 4 * lo4, 4 * hi4))
+    if count % 4:
+        out.append((0, 4 * n4, count))
+    return out
+
+
 def split_buckets(offset: int, count: int, bucket_elems: int) -> List[Tuple[int, int]]:
     """Cut one contiguous region into buckets of at most `bucket_elems` elements (the last may be short)."""
     if bucket_elems <= 0 or count <= bucket_elems:

@@ -239,6 +239,77 @@ class ActEngine:
         self._shared["version"] += 1
         self._synced_version = self._shared["version"]
 
+    # ---- data-parallel step over NVLink peer memory (csrc/dp_p2p.cu; include/act_b200.h "act_engine_dp_*")
+    DP_BLOB_BYTES = 296
+
+    def dp_local_ptrs(self):
+        """(grads, params, shadow, signal) device addresses of this engine's exchange buffers."""
+        import ctypes as C
+        out = [C.c_void_p() for _ in range(4)]
+        check(self.lib.act_engine_dp_local(self._h, *[C.byref(o) for o in out]), "act_engine_dp_local")
+        return tuple(int(o.value) for o in out)
+
+    def dp_set_peers(self, rank: int, world: int, table):
+        """table: four sequences (grads, params, shadow, signal) of `world` device addresses valid on this device."""
+        import ctypes as C
+        arrs = [(C.c_void_p * world)(*[int(x) for x in col]) for col in table]
+        check(self.lib.act_engine_dp_set_peers(self._h, rank, world, *arrs), "act_engine_dp_set_peers")
+        self._dp_world, self._dp_rank = world, rank
+
+    def dp_connect(self, group=None):
+        """Exchange CUDA-IPC handles of the flat gradient / parameter / shadow buffers and the barrier flags with every
+        rank of `group` (one process per GPU on one node) and map the peers' buffers."""
+        import ctypes as C
+        import torch.distributed as dist
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        torch.cuda.synchronize(self.device)
+        blob = C.create_string_buffer(self.DP_BLOB_BYTES)
+        n = self.lib.act_engine_dp_export(self._h, blob, self.DP_BLOB_BYTES)
+        if n != self.DP_BLOB_BYTES:
+            check(-1, "act_engine_dp_export")
+        blobs = [None] * world
+        dist.all_gather_object(blobs, bytes(blob.raw), group=group)
+        joined = b"".join(blobs)
+        check(self.lib.act_engine_dp_connect(self._h, rank, world, joined, self.DP_BLOB_BYTES), "act_engine_dp_connect")
+        self._dp_world, self._dp_rank = world, rank
+        dist.barrier(group)                     # nobody starts a step before every rank has mapped every peer
+
+    @property
+    def dp_connected(self) -> bool:
+        return getattr(self, "_dp_world", 1) > 1
+
+    def backward_and_step_p2p(self, loss_grad: float = 1.0):
+        """Data-parallel loss.backward(); optimizer.step() with the gradient exchange fused into the optimiser kernel
+        over peer memory (act_engine_backward_and_step_p2p).  Every rank must call it for the same step."""
+        self._shared["step"] += 1
+        check(self.lib.act_engine_backward_and_step_p2p(self._h, self._shared["step"], float(loss_grad), _stream()),
+              "act_engine_backward_and_step_p2p")
+        self._shared["version"] += 1
+        self._synced_version = self._shared["version"]
+
+    def dp_status(self) -> int:
+        return int(self.lib.act_engine_dp_status(self._h))
+
+    def dp_slices(self):
+        """[(offset, count)] ranges of the flat buffers exchanged by the last p2p step."""
+        import ctypes as C
+        cap = 64
+        off, cnt = (C.c_longlong * cap)(), (C.c_longlong * cap)()
+        k = self.lib.act_engine_dp_slices(self._h, off, cnt, cap)
+        return [(int(off[i]), int(cnt[i])) for i in range(min(k, cap))]
+
+    def dp_gather_moments(self, group=None):
+        """Moments are sharded by the p2p step (rank r holds the current exp_avg / exp_avg_sq of its slices only): make
+        every rank's flat moment buffers complete again (before saving the optimiser state)."""
+        import torch.distributed as dist
+        from .dp import owner_slices
+        world = dist.get_world_size(group)
+        for off, n in self.dp_slices():
+            for r, lo, hi in owner_slices(n, world):
+                src = dist.get_global_rank(group, r) if group is not None else r
+                for buf in (self.exp_avg, self.exp_avg_sq):
+                    dist.broadcast(buf[off + lo:off + hi], src=src, group=group)
+
     def adamw_step(self):
         self._shared["step"] += 1
         check(self.lib.act_engine_adamw_step(self._h, self._shared["step"], _stream()), "act_engine_adamw_step")

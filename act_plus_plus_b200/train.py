@@ -103,6 +103,9 @@ def train_step(eng: ActEngine, qpos, image, actions, is_pad, eps=None, dp_group=
     out = eng.forward(qpos, image, actions, is_pad, eps)
     if dp_group is None:
         eng.backward_and_step(1.0)
+    elif eng.dp_connected:
+        # gradient exchange fused into the optimiser kernel over NVLink peer memory (eng.dp_connect(group) was called)
+        eng.backward_and_step_p2p(1.0)
     elif os.environ.get("ACT_DP_HOOK", "1") == "1":
         backward_and_step_hooked(eng, dp_group, 1.0)
     elif os.environ.get("ACT_DP_OVERLAP_OPT", "1") == "1":

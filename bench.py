@@ -296,6 +296,11 @@ def run_ours(args):
     # random-init weights of the reference architecture, identical on every rank
     from act_plus_plus_b200.policy import _init_like_reference
     _init_like_reference(eng, seed=0)
+    # ACT_DP_P2P=1: gradient exchange fused into the optimiser kernel over NVLink peer memory (csrc/dp_p2p.cu) instead of
+    # NCCL all-reduce + AdamW.  Opt-in until it has been confirmed at every N the driver's scaling run uses.
+    p2p = world > 1 and os.environ.get("ACT_DP_P2P", "0") == "1"
+    if p2p:
+        eng.dp_connect(group)
     g = torch.Generator(device="cpu").manual_seed(1234 + rank)
     NB = 4                                            # rotate input batches (4 x 29.5 MB images) so nothing is cached
     host = []
@@ -405,6 +410,8 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, ms_e2e = float(t[0]), float(t[1])
+    if p2p and eng.dp_status() != 0:
+        raise RuntimeError("peer-memory data-parallel step: a flag barrier timed out")
     # ---------------- roofline leg: CUDA-event time of every tcgen05 kernel over two more (direct-launch) steps
     lib = _lib.lib()
     torch.cuda.synchronize()
@@ -457,6 +464,8 @@ def run_ours(args):
                 dtype="bf16", data="synthetic",
                 config=dict(workload=workload_name(B, K_CAM),
                             global_batch=B * world, parallelism=f"dp{world}", cuda_graph=graph is not None,
+                            grad_exchange=("none" if world == 1 else "peer-memory reduce+AdamW+broadcast kernel (ACT_DP_P2P=1)"
+                                           if p2p else "NCCL all-reduce per range, overlapped with backward"),
                             l2="4 rotating input batches; parameters+Adam state (1.3 GB) exceed the 126 MB L2 every step",
                             dropout="0 (reference validation path; see DESIGN.md)", last_loss=loss_host),
                 e2e=dict(value=n_samples / (ms_e2e / 1e3), unit="samples/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=4),

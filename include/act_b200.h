@@ -174,6 +174,36 @@ int act_engine_backward_and_step(act_engine* e, int step, float loss_grad, void*
 typedef int (*act_grads_ready_fn)(void* user, long long offset, long long count, void* stream);
 int act_engine_backward_and_step_dp(act_engine* e, int step, float loss_grad, void* stream,
                                     act_grads_ready_fn grads_ready, void* user);
+/* Data-parallel step over NVLink peer memory (no NCCL on the data path).  Set-up, once per process:
+ *   act_engine_dp_export   writes ACT_DP_BLOB_BYTES of CUDA-IPC handles (flat gradients, flat parameters, bf16 shadow,
+ *                          barrier flags) of this rank; exchange the blobs between ranks by any means (the Python host
+ *                          uses torch.distributed.all_gather_object);
+ *   act_engine_dp_connect  maps every peer's buffers (blobs = world x ACT_DP_BLOB_BYTES, rank order);
+ *   act_engine_dp_set_peers is the same with raw device pointers that are already valid on this device (engines of one
+ *                          process; entry `rank` must be this engine's own buffers as returned by act_engine_dp_local).
+ * act_engine_backward_and_step_p2p then runs the step of act_engine_backward_and_step with every "all-reduce the range,
+ * AdamW the range" pair replaced by a flag barrier in peer memory and ONE kernel per rank that reduces its 1/world slice
+ * of the range from all ranks' gradient buffers, applies AdamW with its private moment slice and stores the new fp32
+ * parameters + bf16 shadow into every rank's buffers (reduce-scatter + optimiser + all-gather in one pass).  Moments
+ * are therefore sharded: rank r holds the current exp_avg / exp_avg_sq only for its slices (act_engine_dp_slices), and
+ * the local gradient buffer keeps this rank's un-averaged gradients.  Every rank must issue the same sequence of
+ * calls.  act_engine_dp_status returns 1 if a barrier timed out (a peer never arrived); it synchronises the device. */
+#define ACT_DP_BLOB_BYTES 296
+int act_engine_dp_local(act_engine* e, void** grads, void** params, void** shadow, void** signal);
+int act_engine_dp_export(act_engine* e, void* blob, int capacity);
+int act_engine_dp_connect(act_engine* e, int rank, int world, const void* blobs, int blob_bytes);
+int act_engine_dp_set_peers(act_engine* e, int rank, int world, void* const* grads, void* const* params,
+                            void* const* shadow, void* const* signal);
+int act_engine_backward_and_step_p2p(act_engine* e, int step, float loss_grad, void* stream);
+int act_engine_dp_status(act_engine* e);
+/* Marks peer `peer_rank` as having arrived at every barrier up to `epoch` (writes this engine's own flag block).  For
+ * single-process tests and dry runs in which a peer is a plain set of buffers rather than a running engine. */
+int act_engine_dp_preset_signal(act_engine* e, int peer_rank, unsigned int epoch);
+/* The [offset, offset+count) ranges (in floats of the flat buffers) that the last p2p step exchanged, in order; returns
+ * the number of ranges (at most `capacity` are written).  Rank r owns floats [4*lo, 4*hi) of a range with
+ * n4 = count/4, lo = r*(n4/world) + min(r, n4%world), hi = lo + n4/world + (r < n4%world); rank 0 also owns the
+ * count%4 tail. */
+int act_engine_dp_slices(act_engine* e, long long* offsets, long long* counts, int capacity);
 /* AdamW of one parameter region (index as in act_engine_region; the backbone region also re-packs the conv operands).
  * blocks_per_sm > 0 limits the launch to that many 256-thread blocks per SM so it can run beside tensor-core kernels.
  * The data-parallel host loop uses it to update a region as soon as its gradient all-reduce has finished. */

@@ -119,6 +119,26 @@ def _dp_worker(rank, world, port, out_dir):
 
 
 @pytest.mark.timeout(600)
+def test_owner_slices_partition_every_range():
+    """Ownership map of the peer-memory optimiser step (csrc/dp_p2p.cu::dp_slice): float4 granularity, disjoint, complete."""
+    from act_plus_plus_b200.dp import owner_slices
+    for count in (0, 3, 4, 5, 16, 1023, 4096 + 2, 10_000_001):
+        for world in (1, 2, 3, 4, 8):
+            sl = owner_slices(count, world)
+            cover = sorted((lo, hi) for _, lo, hi in sl)
+            pos = 0
+            for lo, hi in cover:
+                assert lo == pos and hi > lo
+                pos = hi
+            assert pos == count
+            sizes = [hi - lo for r, lo, hi in sl if hi <= 4 * (count // 4)]
+            if sizes:
+                assert max(sizes) - min(sizes) <= 4
+            assert all(lo % 4 == 0 for _, lo, _ in sl)
+            if count % 4:
+                assert sl[-1] == (0, 4 * (count // 4), count)
+
+
 def test_dp_gradient_average_equals_full_batch_gloo(tmp_path):
     """2 ranks x 1 sample, gradients averaged through GradReducer == gradients of the 2-sample batch on one rank
     (the loss is a per-rank mean over equal shards)."""

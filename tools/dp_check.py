@@ -23,10 +23,16 @@ mine = {k: v[rank * Bs:(rank + 1) * Bs].contiguous() for k, v in full.items()}
 eng = ActEngine(batch_max=Bs, img_h=H, img_w=W, train=True)
 _init_like_reference(eng, seed=3)
 eng.set_lr(1e-3, 1e-3)
+P2P = os.environ.get("ACT_DP_P2P", "0") == "1"
+if P2P:
+    eng.dp_connect(dist.group.WORLD)       # gradient exchange inside the optimiser kernel over peer memory (csrc/dp_p2p.cu)
 for _ in range(2):
     train_step(eng, mine["qpos"], mine["image"], mine["actions"], mine["is_pad"], mine["eps"], dist.group.WORLD)
 torch.cuda.synchronize()
 ok = True
+if P2P:
+    ok = eng.dp_status() == 0
+    print(f"dp_check p2p rank {rank}: barrier status {'OK' if ok else 'TIMEOUT'}, {len(eng.dp_slices())} ranges exchanged")
 if rank == 0:
     ref = ActEngine(batch_max=B, img_h=H, img_w=W, train=True)
     _init_like_reference(ref, seed=3)
@@ -50,6 +56,23 @@ chk = eng.flat_params.double().sum().reshape(1)
 lst = [torch.zeros_like(chk) for _ in range(world)]
 dist.all_gather(lst, chk)
 same = all(torch.equal(lst[0], x) for x in lst)
+if P2P:
+    # the bf16 shadows (tensor-core operands) must be identical too: compare a second forward's losses across ranks on
+    # the SAME inputs (rank 0's shard)
+    shard0 = {k: v[:Bs].contiguous() for k, v in full.items()}
+    l = eng.forward(shard0["qpos"], shard0["image"], shard0["actions"], shard0["is_pad"], shard0["eps"])["losses"].double().reshape(1, 3)
+    ll = [torch.zeros_like(l) for _ in range(world)]
+    dist.all_gather(ll, l)
+    same_fwd = all(torch.equal(ll[0], x) for x in ll)
+    same = same and same_fwd
+    if rank == 0:
+        print("dp_check p2p forward identical across ranks:", same_fwd)
+    # sharded moments -> complete on every rank
+    eng.dp_gather_moments(dist.group.WORLD)
+    mchk = eng.exp_avg.double().abs().sum().reshape(1)
+    ml = [torch.zeros_like(mchk) for _ in range(world)]
+    dist.all_gather(ml, mchk)
+    same = same and all(torch.equal(ml[0], x) for x in ml)
 if rank == 0:
     print("dp_check replicas identical:", same)
 torch.cuda.synchronize()
