@@ -89,7 +89,7 @@ def test_p2p_step_with_ghost_peer(rank, concurrent):
     assert torch.equal(ghost_shadow[own & sh], p1[own & sh].to(torch.bfloat16))
     assert bool((ghost_shadow[~(own & sh)] == 7.0).all())
     # moments: current only on the owned slices
-    assert float((eng.exp_avg[own] - m[own]).abs().max()) < 1e-7
+    assert torch.allclose(eng.exp_avg[own], m[own], rtol=1e-5, atol=1e-10)
     assert bool((eng.exp_avg[theirs] == 0).all())
     # a second step runs (epochs advance, ghost flags still satisfied) and keeps the loss finite
     eng.zero_grad()
