@@ -30,6 +30,13 @@ __device__ __forceinline__ float4 ld_relaxed_sys_v4(const float4* p) {
   asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
   return v;
 }
+// L2-only (".cg") load: the data was published by the owner's release store before the barrier this kernel is ordered
+// after, and L1 is bypassed, so no stale line can be hit.  (System-scope relaxed loads were measured 4-5x slower here.)
+__device__ __forceinline__ float4 ld_cg_v4(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -73,9 +80,12 @@ __host__ __device__ inline void dp_slice(long long n4, int rank, int world, long
   *hi = *lo + base + (rank < rem ? 1 : 0);
 }
 
-template <int WORLD>
-__global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs a, long long off, float bc1, float rsqrt_bc2) {
-  // WORLD > 0: compile-time rank count (unrolled peer loads all in flight); WORLD == 0: run-time count
+template <int WORLD, int U>
+__global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs a, long long off, float bc1, float rsqrt_bc2,
+                                                       int ld_sys) {
+  // WORLD > 0: compile-time rank count; WORLD == 0: run-time count.  U float4 chunks per thread and iteration: all
+  // U * world peer loads are issued before the first use (a remote load is ~2 us; bytes in flight set the NVLink rate).
+  constexpr int W = WORLD > 0 ? WORLD : DP_MAX_WORLD;
   const int world = WORLD > 0 ? WORLD : peers.world;
   const long long n4 = a.n / 4;
   long long lo, hi;
@@ -84,37 +94,58 @@ __global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs 
   const float step_size = a.lr / bc1;
   const float inv_world = 1.f / static_cast<float>(world);
   const long long off4 = off / 4;                              // ranges are 16-byte aligned (checked on the host)
-  for (long long i = lo + blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * 1LL * blockDim.x) {
-    float4 gs[WORLD > 0 ? WORLD : DP_MAX_WORLD];
+  const long long S = gridDim.x * 1LL * blockDim.x;
+  for (long long i0 = lo + blockIdx.x * 1LL * blockDim.x + threadIdx.x; i0 < hi; i0 += U * S) {
+    float4 gs[U][W];
 #pragma unroll
-    for (int j = 0; j < (WORLD > 0 ? WORLD : DP_MAX_WORLD); ++j)
-      if (j < world) gs[j] = ld_relaxed_sys_v4(reinterpret_cast<const float4*>(peers.grads[j]) + off4 + i);
-    float4 g = gs[0];
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * S;
 #pragma unroll
-    for (int j = 1; j < (WORLD > 0 ? WORLD : DP_MAX_WORLD); ++j)
-      if (j < world) { g.x += gs[j].x; g.y += gs[j].y; g.z += gs[j].z; g.w += gs[j].w; }
-    g.x *= inv_world; g.y *= inv_world; g.z *= inv_world; g.w *= inv_world;
-    float4 p = reinterpret_cast<const float4*>(a.p)[i];
-    float4 m = reinterpret_cast<float4*>(a.m)[i], v = reinterpret_cast<float4*>(a.v)[i];
-#define ADAM1(c)                                                      \
-    p.c *= decay;                                                     \
-    m.c = a.beta1 * m.c + (1.f - a.beta1) * g.c;                      \
-    v.c = a.beta2 * v.c + (1.f - a.beta2) * g.c * g.c;                \
-    p.c -= step_size * (m.c / (sqrtf(v.c) * rsqrt_bc2 + a.eps));
-    ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
-#undef ADAM1
-    reinterpret_cast<float4*>(a.m)[i] = m;
-    reinterpret_cast<float4*>(a.v)[i] = v;
-    uint2 o;
-    {
-      __nv_bfloat162 l2 = __floats2bfloat162_rn(p.x, p.y), h2 = __floats2bfloat162_rn(p.z, p.w);
-      o.x = *reinterpret_cast<uint32_t*>(&l2); o.y = *reinterpret_cast<uint32_t*>(&h2);
+      for (int j = 0; j < W; ++j)
+        if (j < world && i < hi) {
+          const float4* src = reinterpret_cast<const float4*>(peers.grads[j]) + off4 + i;
+          gs[u][j] = ld_sys ? ld_relaxed_sys_v4(src) : ld_cg_v4(src);
+        }
+    }
+    float4 p[U], m[U], v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * S;
+      if (i < hi) {
+        p[u] = reinterpret_cast<const float4*>(a.p)[i];
+        m[u] = reinterpret_cast<const float4*>(a.m)[i];
+        v[u] = reinterpret_cast<const float4*>(a.v)[i];
+      }
     }
 #pragma unroll
-    for (int j = 0; j < (WORLD > 0 ? WORLD : DP_MAX_WORLD); ++j) {
-      if (j < world) {
-        reinterpret_cast<float4*>(peers.params[j])[off4 + i] = p;
-        if (a.shadow) reinterpret_cast<uint2*>(peers.shadow[j])[off4 + i] = o;
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * S;
+      if (i >= hi) continue;
+      float4 g = gs[u][0];
+#pragma unroll
+      for (int j = 1; j < W; ++j)
+        if (j < world) { g.x += gs[u][j].x; g.y += gs[u][j].y; g.z += gs[u][j].z; g.w += gs[u][j].w; }
+      g.x *= inv_world; g.y *= inv_world; g.z *= inv_world; g.w *= inv_world;
+#define ADAM1(c)                                                            \
+      p[u].c *= decay;                                                      \
+      m[u].c = a.beta1 * m[u].c + (1.f - a.beta1) * g.c;                    \
+      v[u].c = a.beta2 * v[u].c + (1.f - a.beta2) * g.c * g.c;              \
+      p[u].c -= step_size * (m[u].c / (sqrtf(v[u].c) * rsqrt_bc2 + a.eps));
+      ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
+#undef ADAM1
+      reinterpret_cast<float4*>(a.m)[i] = m[u];
+      reinterpret_cast<float4*>(a.v)[i] = v[u];
+      uint2 o;
+      {
+        __nv_bfloat162 l2 = __floats2bfloat162_rn(p[u].x, p[u].y), h2 = __floats2bfloat162_rn(p[u].z, p[u].w);
+        o.x = *reinterpret_cast<uint32_t*>(&l2); o.y = *reinterpret_cast<uint32_t*>(&h2);
+      }
+#pragma unroll
+      for (int j = 0; j < W; ++j) {
+        if (j < world) {
+          reinterpret_cast<float4*>(peers.params[j])[off4 + i] = p[u];
+          if (a.shadow) reinterpret_cast<uint2*>(peers.shadow[j])[off4 + i] = o;
+        }
       }
     }
   }
@@ -134,7 +165,10 @@ __global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs 
       if (a.shadow) peers.shadow[j][off + i] = __float2bfloat16_rn(p);
     }
   }
-  __threadfence_system();                                      // peer stores are performed before the next barrier's flag
+  // Peer stores must be performed before the next barrier's flag.  One cumulative system fence per block after a block
+  // barrier (a fence in every thread was measured to serialise: ~3 us of NVLink round trip per warp, 110 us per launch).
+  __syncthreads();
+  if (threadIdx.x == 0) __threadfence_system();
 }
 
 // a.p / a.m / a.v point at this rank's own buffers at the START of the range (offset `off` floats into the flat buffers);
@@ -147,13 +181,16 @@ int dp_adamw_step(const DpPeers& peers, const AdamWArgs& a, long long off, cudaS
   const double bc2 = 1.0 - std::pow(static_cast<double>(a.beta2), a.step);
   const long long n4 = a.n / 4, slice = (n4 + peers.world - 1) / peers.world;
   const int per_sm = a.background > 0 ? std::min(a.background, 8) : 8;
-  const int blocks = static_cast<int>(std::max<long long>(1, std::min<long long>((slice + 255) / 256, 148LL * per_sm)));
+  const int unroll = peers.world == 2 ? 4 : peers.world == 4 ? 2 : 1;
+  const int blocks = static_cast<int>(std::max<long long>(1, std::min<long long>((slice + 256LL * unroll - 1) / (256LL * unroll), 148LL * per_sm)));
   const float f1 = static_cast<float>(bc1), f2 = static_cast<float>(1.0 / std::sqrt(bc2));
+  static int ld_sys = -1;
+  if (ld_sys < 0) { const char* e = getenv("ACT_DP_LD_SYS"); ld_sys = (e && e[0] == '1') ? 1 : 0; }
   switch (peers.world) {
-    case 2: dp_adamw_kernel<2><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2); break;
-    case 4: dp_adamw_kernel<4><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2); break;
-    case 8: dp_adamw_kernel<8><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2); break;
-    default: dp_adamw_kernel<0><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2); break;
+    case 2: dp_adamw_kernel<2, 4><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2, ld_sys); break;
+    case 4: dp_adamw_kernel<4, 2><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2, ld_sys); break;
+    case 8: dp_adamw_kernel<8, 1><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2, ld_sys); break;
+    default: dp_adamw_kernel<0, 1><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2, ld_sys); break;
   }
   ACT_CUDA(cudaGetLastError());
   return 0;

@@ -99,6 +99,7 @@ class Engine {
   int opt_step_ = 0, dp_bb_slot_ = 0;
   bool dp_bb_pending_ = false;
   cudaStream_t dp_main_st_ = nullptr;
+  int dp_inline_from_ = 0;                       // CVAE layers >= this index are updated inside cvae_bwd, the rest at its end
   int inline_opt_step_ = 0;                      // > 0 while backward_and_step runs: cvae_bwd updates each layer as soon as its gradients are final
   long long cvae_layer_off_[16] = {0}, cvae_layer_n_[16] = {0};
   // backward(0) + adamw() with the optimiser of each parameter region trailing that region's last weight gradient, so
@@ -182,9 +183,13 @@ class Engine {
   bf16* shadow_ = nullptr;
   DpPeers peers_;
   uint32_t *dp_signal_ = nullptr, *dp_epoch_ = nullptr, *dp_status_ = nullptr;
-  cudaStream_t dp_stream_ = nullptr;
+  cudaStream_t dp_stream_ = nullptr, dp_pack_stream_ = nullptr;
+  cudaEvent_t dp_pack_ev_ = nullptr, dp_pack_done_ = nullptr;
+  bool dp_pack_running_ = false;
   cudaEvent_t dp_ev_[DP_MAX_SITES] = {}, dp_done_ = nullptr;
   int dp_site_ = 0;
+  bool dp_pack_pending_ = false;                // backbone updated by the p2p step: re-pack after the closing barrier
+  int repack_conv_operands(cudaStream_t st);
   bool dp_fused_ = false;                       // true while backward_and_step(p2p = true) is being enqueued
   std::vector<void*> dp_opened_;
   std::vector<std::pair<long long, long long>> dp_ranges_;   // ranges exchanged by the last p2p step

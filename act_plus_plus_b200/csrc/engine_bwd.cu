@@ -309,7 +309,7 @@ int Engine::cvae_bwd(cudaStream_t st) {
     if (dp_bb_pending_ && nl - 1 - l == dp_bb_slot_ && backbone_bwd_and_step(dp_main_st_)) return -1;
     if (enc_layer_bwd(cvae_w_[l], cvae_a_[l], nullptr, dx2, dx2b, gC_, gD_, Lc_, B, st)) return -1;
     dx2 = gC_; dx2b = gD_;
-    if (inline_opt_step_ > 0 && l < 16 && cvae_layer_n_[l] > 0) {
+    if (inline_opt_step_ > 0 && l < 16 && l >= dp_inline_from_ && cvae_layer_n_[l] > 0) {
       // this layer's gradients are final and nothing below reads its weights: update it under the remaining layers
       cudaStream_t wg = wg_gather(st, NWG);
       if (grads_ready(cvae_layer_off_[l], cvae_layer_n_[l], wg)) return -1;
@@ -440,7 +440,7 @@ int Engine::backbone_bwd_and_step(cudaStream_t st) {
   tc_set_sm_reserve(0);
   cudaStream_t wg = wg_gather(st, NWG);
   if (grads_ready(region_off_[R_BACKBONE], region_n_[R_BACKBONE], wg)) return -1;
-  return adamw_region(R_BACKBONE, opt_step_, wg, 3);
+  return adamw_region(R_BACKBONE, opt_step_, wg, dp_fused_ ? 6 : 3);
 }
 
 int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsReadyFn cb, void* cb_user, bool p2p) {
@@ -452,9 +452,13 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
   // the peer-memory step ends with a barrier: every rank has finished reading this rank's gradients and writing its
   // parameters before the caller's stream goes on (next zero_grad / forward)
   auto p2p_finish = [&]() -> int {
-    if (dp_sync_point(st)) return -1;
+    if (dp_sync_point(st)) return -1;                      // (also starts a still-pending conv re-pack)
     ACT_CUDA(cudaEventRecord(dp_done_, dp_stream_));
     ACT_CUDA(cudaStreamWaitEvent(st, dp_done_, 0));
+    if (dp_pack_running_) {
+      dp_pack_running_ = false;
+      ACT_CUDA(cudaStreamWaitEvent(st, dp_pack_done_, 0));
+    }
     return 0;
   };
   if (!concurrent_) {
@@ -475,10 +479,15 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
   }
   struct Guard {                                            // the hook is only live inside this call
     Engine* e;
-    ~Guard() { e->grads_cb_ = nullptr; e->grads_cb_user_ = nullptr; e->inline_opt_step_ = 0; e->dp_bb_pending_ = false; e->dp_fused_ = false; tc_set_sm_reserve(0); }
+    ~Guard() { e->grads_cb_ = nullptr; e->grads_cb_user_ = nullptr; e->inline_opt_step_ = 0; e->dp_bb_pending_ = false; e->dp_fused_ = false; e->dp_inline_from_ = 0; tc_set_sm_reserve(0); }
   } guard{this};
   grads_cb_ = cb; grads_cb_user_ = cb_user; opt_step_ = step;
   dp_fused_ = p2p; dp_site_ = 0; if (p2p) dp_ranges_.clear();
+  static int inline_layers = -2;
+  if (inline_layers == -2) { const char* e = getenv("ACT_DP_INLINE_LAYERS"); inline_layers = e ? atoi(e) : -1; }
+  // peer-memory exchange: only the first `enc_layers / 2` CVAE layers of the backward (the highest-numbered ones) are
+  // exchanged one by one; the rest form one range at the end of the branch
+  dp_inline_from_ = p2p ? std::max(0, cfg_.enc_layers - (inline_layers >= 0 ? inline_layers : cfg_.enc_layers / 2)) : 0;
   const bool dp = cb != nullptr || p2p;                     // either way: ranges are exchanged in the order enqueued here
   if (wg_join(st)) return -1;                               // an asynchronous zero_grad
   if (zero_backward_outputs(st)) return -1;
@@ -501,11 +510,17 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
     cudaStream_t wg = wg_gather(side_, NWG);
     const int nl = std::min(cfg_.enc_layers, 16);
     const long long tail = cvae_layer_off_[nl - 1] + cvae_layer_n_[nl - 1];
-    const long long head_n = cvae_layer_off_[0] - region_off_[R_CVAE];
+    // layers below dp_inline_from_ were not updated inside cvae_bwd (peer-memory exchange: the last layers' ranges would
+    // only queue up behind each other on the serial exchange stream): they go with the head as ONE range
+    const int lf = std::min(dp_inline_from_, nl);
+    const long long head_end = lf > 0 ? cvae_layer_off_[lf - 1] + cvae_layer_n_[lf - 1] : cvae_layer_off_[0];
+    const long long head_n = head_end - region_off_[R_CVAE];
     const long long tail_n = region_off_[R_CVAE] + region_n_[R_CVAE] - tail;
-    if (grads_ready(region_off_[R_CVAE], head_n, wg) || grads_ready(tail, tail_n, wg)) return -1;
-    if (adamw_range(region_off_[R_CVAE], head_n, cfg_.lr, true, step, wg, 6)) return -1;
-    return adamw_range(tail, tail_n, cfg_.lr, true, step, wg, 6);
+    const int bps = p2p ? 8 : 6;                            // nothing left to run beside these: whole chip
+    if (grads_ready(region_off_[R_CVAE], head_n, wg)) return -1;
+    if (adamw_range(region_off_[R_CVAE], head_n, cfg_.lr, true, step, wg, bps)) return -1;
+    if ((!p2p || head_n <= 0) && grads_ready(tail, tail_n, wg)) return -1;   // (peer memory: the head's barrier covers the tail)
+    return adamw_range(tail, tail_n, cfg_.lr, true, step, wg, bps);
   };
   static int bb_slot = -2;
   if (bb_slot == -2) { const char* e = getenv("ACT_DP_BB_SLOT"); bb_slot = e ? atoi(e) : -1; }

@@ -12,6 +12,9 @@ Engine::~Engine() {
   for (void* p : dp_opened_) cudaIpcCloseMemHandle(p);
   for (cudaEvent_t e : dp_ev_) if (e) cudaEventDestroy(e);
   if (dp_done_) cudaEventDestroy(dp_done_);
+  if (dp_pack_ev_) cudaEventDestroy(dp_pack_ev_);
+  if (dp_pack_done_) cudaEventDestroy(dp_pack_done_);
+  if (dp_pack_stream_) cudaStreamDestroy(dp_pack_stream_);
   if (dp_stream_) cudaStreamDestroy(dp_stream_);
   for (void* p : allocs_) cudaFree(p);
   if (ev_fork_) cudaEventDestroy(ev_fork_);
@@ -415,14 +418,17 @@ int Engine::adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm) {
   if (dp_fused_ && r != R_DEAD) {
     dp_ranges_.emplace_back(o, a.n);
     if (dp_adamw_step(peers_, a, o, dp_stream_)) return -1;
-    if (r != R_BACKBONE) return 0;
-    // the conv operands are re-packed from the fp32 masters: every rank's slice of them must have landed here first
-    if (dp_sync_point(dp_stream_)) return -1;
-    st = dp_stream_;
-  } else if (adamw_step(a, st)) {
-    return -1;
+    // the conv operands are re-packed from the fp32 masters once every rank's slice of them has landed here: that is
+    // what the step's closing barrier guarantees, so the re-pack is deferred to it (repack_conv_operands)
+    if (r == R_BACKBONE) dp_pack_pending_ = true;
+    return 0;
   }
+  if (adamw_step(a, st)) return -1;
   if (r != R_BACKBONE) return 0;
+  return repack_conv_operands(st);
+}
+
+int Engine::repack_conv_operands(cudaStream_t st) {
   // packed conv operands (transposed / scaled layouts) are rebuilt from the fp32 masters, one launch per camera
   for (int k = 0; k < cfg_.num_cameras; ++k) {
     CamW& c = cam_w_[k];
@@ -537,6 +543,9 @@ int Engine::dp_set_peers(int rank, int world, void* const* grads, void* const* p
   }
   if (!dp_stream_) {
     ACT_CUDA(cudaStreamCreateWithFlags(&dp_stream_, cudaStreamNonBlocking));
+    ACT_CUDA(cudaStreamCreateWithFlags(&dp_pack_stream_, cudaStreamNonBlocking));
+    ACT_CUDA(cudaEventCreateWithFlags(&dp_pack_ev_, cudaEventDisableTiming));
+    ACT_CUDA(cudaEventCreateWithFlags(&dp_pack_done_, cudaEventDisableTiming));
     for (cudaEvent_t& e : dp_ev_) ACT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     ACT_CUDA(cudaEventCreateWithFlags(&dp_done_, cudaEventDisableTiming));
   }
@@ -551,7 +560,18 @@ int Engine::dp_sync_point(cudaStream_t producer) {
     ACT_CUDA(cudaStreamWaitEvent(dp_stream_, dp_ev_[dp_site_], 0));
   }
   ++launches_;
-  return dp_barrier(peers_, dp_epoch_, dp_status_, dp_site_++, dp_stream_);
+  if (dp_barrier(peers_, dp_epoch_, dp_status_, dp_site_++, dp_stream_)) return -1;
+  if (dp_pack_pending_) {
+    // every rank has passed this barrier, so every rank's backbone kernel (earlier on its exchange stream) has finished
+    // storing its slice here: rebuild the packed conv operands on a stream of their own, beside the remaining exchange
+    dp_pack_pending_ = false;
+    ACT_CUDA(cudaEventRecord(dp_pack_ev_, dp_stream_));
+    ACT_CUDA(cudaStreamWaitEvent(dp_pack_stream_, dp_pack_ev_, 0));
+    if (repack_conv_operands(dp_pack_stream_)) return -1;
+    ACT_CUDA(cudaEventRecord(dp_pack_done_, dp_pack_stream_));
+    dp_pack_running_ = true;
+  }
+  return 0;
 }
 
 int Engine::dp_preset_signal(int peer_rank, uint32_t epoch) {

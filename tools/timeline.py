@@ -20,6 +20,8 @@ if int(os.environ.get("WORLD_SIZE", "1")) > 1:          # under torchrun: data-p
     group = dist.group.WORLD
 eng = ActEngine(batch_max=B, train=True)
 _init_like_reference(eng, seed=0)
+if group is not None and os.environ.get("ACT_DP_P2P", "0") == "1":
+    eng.dp_connect(group)
 g = torch.Generator(device="cuda").manual_seed(0)
 image = torch.rand((B, 1, 3, 480, 640), generator=g, device="cuda")
 qpos = torch.randn((B, 14), generator=g, device="cuda")
