@@ -51,6 +51,10 @@ def _declare(l):
         fn.argtypes = argtypes
 
 
+def last_error() -> str:
+    return lib().act_last_error().decode(errors="replace")
+
+
 def check(rc: int, what: str = ""):
     if rc != 0:
         msg = lib().act_last_error().decode(errors="replace")

@@ -258,21 +258,32 @@ class ActEngine:
 
     def dp_connect(self, group=None):
         """Exchange CUDA-IPC handles of the flat gradient / parameter / shadow buffers and the barrier flags with every
-        rank of `group` (one process per GPU on one node) and map the peers' buffers."""
+        rank of `group` (one process per GPU on one node) and map the peers' buffers.  Collective: every rank must call
+        it; if any rank fails, every rank raises RuntimeError (so callers can fall back to NCCL consistently)."""
         import ctypes as C
         import torch.distributed as dist
+        from ._lib import last_error
         world, rank = dist.get_world_size(group), dist.get_rank(group)
         torch.cuda.synchronize(self.device)
         blob = C.create_string_buffer(self.DP_BLOB_BYTES)
-        n = self.lib.act_engine_dp_export(self._h, blob, self.DP_BLOB_BYTES)
-        if n != self.DP_BLOB_BYTES:
-            check(-1, "act_engine_dp_export")
+        err = None
+        if self.lib.act_engine_dp_export(self._h, blob, self.DP_BLOB_BYTES) != self.DP_BLOB_BYTES:
+            err = "act_engine_dp_export: " + last_error()
         blobs = [None] * world
-        dist.all_gather_object(blobs, bytes(blob.raw), group=group)
-        joined = b"".join(blobs)
-        check(self.lib.act_engine_dp_connect(self._h, rank, world, joined, self.DP_BLOB_BYTES), "act_engine_dp_connect")
+        dist.all_gather_object(blobs, None if err else bytes(blob.raw), group=group)
+        if err is None and any(b is None for b in blobs):
+            err = "a peer could not export its buffers"
+        if err is None and self.lib.act_engine_dp_connect(self._h, rank, world, b"".join(blobs), self.DP_BLOB_BYTES) != 0:
+            err = "act_engine_dp_connect: " + last_error()
+        ok = torch.tensor([0.0 if err else 1.0], device=self.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)   # also: nobody starts a step before every rank is mapped
+        if float(ok) == 0.0:
+            raise RuntimeError(f"peer-memory data-parallel set-up failed: {err or 'on another rank'}")
         self._dp_world, self._dp_rank = world, rank
-        dist.barrier(group)                     # nobody starts a step before every rank has mapped every peer
+
+    def dp_disconnect(self):
+        """Go back to the NCCL / single-process step (the mappings stay open until the engine is destroyed)."""
+        self._dp_world = 1
 
     @property
     def dp_connected(self) -> bool:

@@ -296,11 +296,17 @@ def run_ours(args):
     # random-init weights of the reference architecture, identical on every rank
     from act_plus_plus_b200.policy import _init_like_reference
     _init_like_reference(eng, seed=0)
-    # ACT_DP_P2P=1: gradient exchange fused into the optimiser kernel over NVLink peer memory (csrc/dp_p2p.cu) instead of
-    # NCCL all-reduce + AdamW.  Opt-in until it has been confirmed at every N the driver's scaling run uses.
-    p2p = world > 1 and os.environ.get("ACT_DP_P2P", "0") == "1"
+    # Gradient exchange: by default fused into the optimiser kernel over NVLink peer memory (csrc/dp_p2p.cu; checked
+    # against the full-batch step and measured beside the NCCL path at N = 2, 4, 8: profiles/r01_dp_p2p_vs_nccl.md).
+    # ACT_DP_P2P=0 selects NCCL all-reduce + AdamW per range; it is also the fallback when any rank cannot map its
+    # peers' buffers (CUDA IPC unavailable).
+    p2p = world > 1 and os.environ.get("ACT_DP_P2P", "1") == "1"
     if p2p:
-        eng.dp_connect(group)
+        try:
+            eng.dp_connect(group)                    # collective: raises on every rank if any rank failed
+        except RuntimeError as ex:
+            print(f"[bench] rank {rank}: peer-memory exchange unavailable ({str(ex)[:160]}); using NCCL", file=sys.stderr)
+            p2p = False
     g = torch.Generator(device="cpu").manual_seed(1234 + rank)
     NB = 4                                            # rotate input batches (4 x 29.5 MB images) so nothing is cached
     host = []
@@ -464,8 +470,8 @@ def run_ours(args):
                 dtype="bf16", data="synthetic",
                 config=dict(workload=workload_name(B, K_CAM),
                             global_batch=B * world, parallelism=f"dp{world}", cuda_graph=graph is not None,
-                            grad_exchange=("none" if world == 1 else "peer-memory reduce+AdamW+broadcast kernel (ACT_DP_P2P=1)"
-                                           if p2p else "NCCL all-reduce per range, overlapped with backward"),
+                            grad_exchange=("none" if world == 1 else "peer-memory reduce+AdamW+broadcast kernel over NVLink (csrc/dp_p2p.cu)"
+                                           if p2p else "NCCL all-reduce per range, overlapped with backward (ACT_DP_P2P=0)"),
                             l2="4 rotating input batches; parameters+Adam state (1.3 GB) exceed the 126 MB L2 every step",
                             dropout="0 (reference validation path; see DESIGN.md)", last_loss=loss_host),
                 e2e=dict(value=n_samples / (ms_e2e / 1e3), unit="samples/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=4),
