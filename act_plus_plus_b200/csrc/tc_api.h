@@ -82,6 +82,7 @@ struct ConvLaunch {
   int vW = 0, vH = 0, NIMG = 0;         // tile-space extent (one accumulator row per (n,h,w))
   PixGeom og{}, rg{};
   EpiDesc epi;                          // ldc/ldr/osz*/rsz* ignored (geometry comes from og / rg)
+  double algo_flops = 0.0;              // > 0: algorithmic FLOPs of this launch for the profile (operands with zero padding in K)
 };
 int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint = 0, int stages_hint = 0);
 // dense 3x3 / stride-1 tap sets: halo patch resident in shared memory (conv3_kernel.cuh); ACT_CONV3=0 disables it
@@ -105,6 +106,7 @@ struct WgradLaunch {
   float alpha = 1.f;
   const float* scale = nullptr;         // unused by the kernel (applied by the fold)
   int ksplit = 0;                       // 0 -> heuristic
+  double algo_flops = 0.0;              // > 0: algorithmic FLOPs of this launch for the profile
 };
 int tc_wgrad(const WgradLaunch& w, cudaStream_t stream);
 

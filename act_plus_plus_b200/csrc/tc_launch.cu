@@ -336,7 +336,7 @@ int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint, int stages_hi
     if (plane_tmap(&am[i], c.planes[std::min(i, c.nplanes - 1)], BW, BH, BNI)) return -1;
   if (make_tmap_2d(&bm, c.wgt, c.wgt_ld, c.Cout, c.wgt_ld, bn)) return -1;
   dim3 grid((c.Cout + bn - 1) / bn, static_cast<unsigned>(mtiles), 1);
-  g_next_flops = 2.0 * c.vW * c.vH * c.NIMG * c.Cout * c.Cin * c.ntaps;
+  g_next_flops = c.algo_flops > 0 ? c.algo_flops : 2.0 * c.vW * c.vH * c.NIMG * c.Cout * c.Cin * c.ntaps;
   if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "conv %dx%dx%d Cin=%d Cout=%d taps=%d box=%dx%dx%d bn=%d grid=%ux%u", c.NIMG, c.vH, c.vW, c.Cin, c.Cout, c.ntaps, BNI, BH, BW, bn, grid.x, grid.y); g_next_label = buf; }
   const int st = stages_hint;
   if (bn == 64) return launch_inst<MODE_CONV, 0, 0, 64>(grid, st, stream, am, bm, p);
@@ -421,7 +421,7 @@ int tc_conv3(const ConvLaunch& c, cudaStream_t stream, int bn_hint) {
   CUtensorMap am, bm;
   if (plane_tmap(&am, c.planes[0], p.PW, BH + 2, 1)) return -1;
   if (make_tmap_2d(&bm, c.wgt, c.wgt_ld, c.Cout, c.wgt_ld, bn)) return -1;
-  g_next_flops = 2.0 * c.vW * c.vH * c.NIMG * c.Cout * c.Cin * c.ntaps;
+  g_next_flops = c.algo_flops > 0 ? c.algo_flops : 2.0 * c.vW * c.vH * c.NIMG * c.Cout * c.Cin * c.ntaps;
   if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "conv3 %dx%dx%d Cin=%d Cout=%d taps=%d tile=%dx%d bn=%d grid=%dx%d", c.NIMG, c.vH, c.vW, c.Cin, c.Cout, c.ntaps, BH, BW, bn, p.gx, p.gy); g_next_label = buf; }
   const long long total = 1LL * p.gx * p.gy;
   if (bn == 64) return launch_conv3<64>(total, stream, am, bm, p);
@@ -469,7 +469,7 @@ int tc_wgrad(const WgradLaunch& w, cudaStream_t stream) {
     if (plane_tmap(&am[i], w.planes[std::min(i, w.nplanes - 1)], BW, BH, 1)) return -1;
   if (plane_tmap(&bm, w.dy, BW, BH, 1)) return -1;
   dim3 grid(xt, ygroups, ks);
-  g_next_flops = 2.0 * w.dy.W * w.dy.H * w.dy.N * w.Cout * w.Cin * w.ntaps;
+  g_next_flops = w.algo_flops > 0 ? w.algo_flops : 2.0 * w.dy.W * w.dy.H * w.dy.N * w.Cout * w.Cin * w.ntaps;
   if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "wgrad %dx%dx%d Cin=%d Cout=%d taps=%d box=%dx%d bn=%d ks=%d grid=%ux%ux%u", w.dy.N, w.dy.H, w.dy.W, w.Cin, w.Cout, w.ntaps, BH, BW, bn, ks, grid.x, grid.y, grid.z); g_next_label = buf; }
   if (bn == 64) return launch_inst<MODE_WGRAD, 1, 1, 64>(grid, 0, stream, am, bm, p);
   return launch_inst<MODE_WGRAD, 1, 1, 128>(grid, 0, stream, am, bm, p);
