@@ -270,12 +270,54 @@ __global__ void maxpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict_
     }
   }
 }
+// Inference form (no arg-max record): packed bf16x2 maxima, one thread = 8 channels of TWO horizontally adjacent
+// outputs (their windows share one column: 15 loads for 2 outputs instead of 18).
+__global__ void maxpool_fwd_noidx_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int N, int H, int W, int C,
+                                         int Ho, int Wo) {
+  pdl_trigger(); pdl_wait();
+  const int C8 = C / 8, Wo2 = (Wo + 1) / 2;
+  const long long total = 1LL * N * Ho * Wo2 * C8;
+  const __nv_bfloat162 ninf = __halves2bfloat162(__ushort_as_bfloat16(0xFF80), __ushort_as_bfloat16(0xFF80));
+  for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
+    const int c8 = static_cast<int>(i % C8);
+    long long r = i / C8;
+    const int ox = 2 * static_cast<int>(r % Wo2); r /= Wo2;
+    const int oy = static_cast<int>(r % Ho);
+    const int n = static_cast<int>(r / Ho);
+    __nv_bfloat162 a[4], b[4];                               // outputs ox and ox + 1
+#pragma unroll
+    for (int e = 0; e < 4; ++e) { a[e] = ninf; b[e] = ninf; }
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const int iy = 2 * oy + kh - 1;
+      if (iy < 0 || iy >= H) continue;
+      const bf16* row = x + ((1LL * n * H + iy) * W) * C + c8 * 8;
+#pragma unroll
+      for (int kw = 0; kw < 5; ++kw) {                       // columns 2*ox-1 .. 2*ox+3; column 2*ox+1 feeds both outputs
+        const int ix = 2 * ox + kw - 1;
+        if (ix < 0 || ix >= W) continue;
+        const uint4 v = *reinterpret_cast<const uint4*>(row + 1LL * ix * C);
+        const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          if (kw <= 2) a[e] = __hmax2(a[e], h2[e]);
+          if (kw >= 2) b[e] = __hmax2(b[e], h2[e]);
+        }
+      }
+    }
+    const long long ooff = ((1LL * n * Ho + oy) * Wo + ox) * C + c8 * 8;
+    *reinterpret_cast<uint4*>(y + ooff) = *reinterpret_cast<const uint4*>(a);
+    if (ox + 1 < Wo) *reinterpret_cast<uint4*>(y + ooff + C) = *reinterpret_cast<const uint4*>(b);
+  }
+}
+
 int maxpool_fwd(const bf16* x, bf16* y, uint8_t* idx, int N, int H, int W, int C, cudaStream_t st) {
   ACT_CHECK(C % 8 == 0, "maxpool needs C % 8 == 0");
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   const long long total = 1LL * N * Ho * Wo * (C / 8);
   const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
-  ACT_CUDA(launch_pdl(maxpool_fwd_kernel, dim3(blocks), dim3(256), 0, st, x, y, idx, N, H, W, C, Ho, Wo));
+  if (idx) ACT_CUDA(launch_pdl(maxpool_fwd_kernel, dim3(blocks), dim3(256), 0, st, x, y, idx, N, H, W, C, Ho, Wo));
+  else ACT_CUDA(launch_pdl(maxpool_fwd_noidx_kernel, dim3(blocks), dim3(256), 0, st, x, y, N, H, W, C, Ho, Wo));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }

@@ -178,6 +178,19 @@ def test_maxpool_fwd_bwd():
     assert bad < 2e-3, bad
 
 
+@pytest.mark.parametrize("shape", [(2, 48, 64, 64), (1, 30, 50, 64), (3, 17, 23, 128)])
+def test_maxpool_fwd_inference_form(shape):
+    """idx == NULL selects the inference kernel (packed bf16 maxima, two outputs per thread): bit-equal to torch, also
+    for odd sizes (odd output width: the second output of the last pair does not exist) and signed inputs."""
+    N, H, W, Cc = shape
+    Ho, Wo = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+    x = rnd(N, H, W, Cc, seed=3).bfloat16()
+    y = torch.full((N, Ho, Wo, Cc), 9.0, device="cuda", dtype=torch.bfloat16)
+    ck(L().act_maxpool_fwd(p(x), p(y), None, N, H, W, Cc, st()))
+    ref = F.max_pool2d(x.float().permute(0, 3, 1, 2), 3, 2, 1).permute(0, 2, 3, 1)
+    assert torch.equal(y.float(), ref)
+
+
 def test_im2col_conv1_matches_conv():
     B, K, H, W, KP = 2, 2, 64, 96, 192
     g = torch.Generator(device="cuda").manual_seed(0)
