@@ -46,6 +46,9 @@ struct ConvW {
   const float* bn[4] = {nullptr, nullptr, nullptr, nullptr};   // weight, bias, running_mean, running_var
   bf16* wpk = nullptr; bf16* wpkt = nullptr;                   // packed shadows (engine-owned)
   float* scale = nullptr; float* shift = nullptr;              // folded FrozenBN (engine-owned)
+  // 64 -> 64 channel 3x3/s1 convs only (ResNet layer1): paired operands [128][12*64] (conv_ops.cu::pair_launch) and the
+  // folded FrozenBN repeated to 128 entries
+  bf16* wpk2 = nullptr; bf16* wpkt2 = nullptr; float* scale2 = nullptr; float* shift2 = nullptr;
 };
 
 struct BlockW { ConvW c1, c2, ds; bool has_ds = false; };
@@ -190,6 +193,7 @@ class Engine {
   int dp_site_ = 0;
   bool dp_pack_pending_ = false;                // backbone updated by the p2p step: re-pack after the closing barrier
   int repack_conv_operands(cudaStream_t st);
+  int repack_pair_operands(int cam, cudaStream_t st);   // after the packed conv operands of that camera were rebuilt
   bool dp_fused_ = false;                       // true while backward_and_step(p2p = true) is being enqueued
   std::vector<void*> dp_opened_;
   std::vector<std::pair<long long, long long>> dp_ranges_;   // ranges exchanged by the last p2p step

@@ -379,7 +379,7 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
     if (wgrad(s2, ba.a, g, bw.c2)) return -1;
     {
       EpiDesc e; e.flags = EPI_OUT_BF16 | EPI_MASK_POS; e.out_bf16 = ga; e.aux_bf16 = ba.a;
-      RUN(conv_dgrad(s2, g, bw.c2.wpkt, e, nullptr, st));
+      RUN(conv_dgrad(s2, g, bw.c2.wpkt, e, nullptr, st, bw.c2.wpkt2));
     }
     if (wgrad(s1, x_in, ga, bw.c1)) return -1;
     EpiDesc e1; e1.flags = EPI_OUT_BF16; e1.out_bf16 = dx;
@@ -394,7 +394,7 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
       launches_ += 3;                                                // four parity-class launches
     } else {
       e1.flags |= EPI_RES_BF16; e1.res_bf16 = g;
-      RUN(conv_dgrad(s1, ga, bw.c1.wpkt, e1, nullptr, st));
+      RUN(conv_dgrad(s1, ga, bw.c1.wpkt, e1, nullptr, st, bw.c1.wpkt2));
     }
     g = dx;
   }

@@ -52,6 +52,12 @@ int Engine::alloc_workspace() {
         bw.c1.scale = A_(float, cout); bw.c1.shift = A_(float, cout);
         bw.c2.wpk = A_(bf16, 9LL * cout * cout); bw.c2.wpkt = A_(bf16, 9LL * cout * cout);
         bw.c2.scale = A_(float, cout); bw.c2.shift = A_(float, cout);
+        if (cin == 64 && cout == 64 && conv_pair_ok(ConvShape{1, 2, 2, 64, 64, 3, 1, 1})) {   // opt-in, see conv_pair_ok
+          for (ConvW* w : {&bw.c1, &bw.c2}) {
+            w->wpk2 = A_(bf16, 128 * 768); w->wpkt2 = A_(bf16, 128 * 768);
+            w->scale2 = A_(float, 128); w->shift2 = A_(float, 128);
+          }
+        }
         if (b == 0 && s > 0) {
           bw.ds.wpk = A_(bf16, 1LL * cin * cout); bw.ds.wpkt = A_(bf16, 1LL * cin * cout);
           bw.ds.scale = A_(float, cout); bw.ds.shift = A_(float, cout);
@@ -396,7 +402,9 @@ int Engine::backbone_fwd(int cam, int B, const float* image, cudaStream_t st) {
     ConvShape s1{B, Hc, Wc, bw.c1.Cin, bw.c1.Cout, 3, bw.c1.stride, 1};
     EpiDesc e1;
     e1.flags = EPI_SCALE | EPI_BIAS | EPI_RELU | EPI_OUT_BF16; e1.scale = bw.c1.scale; e1.bias = bw.c1.shift; e1.out_bf16 = ba.a;
-    RUN(conv_fwd(s1, x, bw.c1.wpk, e1, st));
+    const bf16* wp1 = (bw.c1.wpk2 && conv_pair_ok(s1)) ? bw.c1.wpk2 : nullptr;
+    if (wp1) { e1.scale = bw.c1.scale2; e1.bias = bw.c1.shift2; }
+    RUN(conv_fwd(s1, x, bw.c1.wpk, e1, st, wp1));
     const int Ho = conv_out_dim(Hc, 3, bw.c1.stride, 1), Wo = conv_out_dim(Wc, 3, bw.c1.stride, 1);
     const bf16* idt = x;
     if (bw.has_ds) {
@@ -410,7 +418,9 @@ int Engine::backbone_fwd(int cam, int B, const float* image, cudaStream_t st) {
     EpiDesc e2;
     e2.flags = EPI_SCALE | EPI_BIAS | EPI_RES_BF16 | EPI_RELU | EPI_OUT_BF16;
     e2.scale = bw.c2.scale; e2.bias = bw.c2.shift; e2.res_bf16 = idt; e2.out_bf16 = ba.y;
-    RUN(conv_fwd(s2, ba.a, bw.c2.wpk, e2, st));
+    const bf16* wp2 = (bw.c2.wpk2 && conv_pair_ok(s2)) ? bw.c2.wpk2 : nullptr;
+    if (wp2) { e2.scale = bw.c2.scale2; e2.bias = bw.c2.shift2; }
+    RUN(conv_fwd(s2, ba.a, bw.c2.wpk, e2, st, wp2));
     x = ba.y; Hc = Ho; Wc = Wo;
   }
   // input_proj: 1x1 conv 512 -> d with bias, fp32 rows (b, 2 + y*(Wf*K) + cam*Wf + x) of src_

@@ -346,7 +346,11 @@ void Engine::setup_views() {
         BlockW& bw = c.blk[s * 2 + b];
         const std::string q = p + kStages[s] + "." + std::to_string(b) + ".";
         const int cin = b == 0 ? kStageCin[s] : kStageCout[s], cout = kStageCout[s], st = b == 0 ? kStageStride[s] : 1;
-        auto carry = [&](ConvW& dst, ConvW src) { src.wpk = dst.wpk; src.wpkt = dst.wpkt; src.scale = dst.scale; src.shift = dst.shift; dst = src; };
+        auto carry = [&](ConvW& dst, ConvW src) {
+          src.wpk = dst.wpk; src.wpkt = dst.wpkt; src.scale = dst.scale; src.shift = dst.shift;
+          src.wpk2 = dst.wpk2; src.wpkt2 = dst.wpkt2; src.scale2 = dst.scale2; src.shift2 = dst.shift2;
+          dst = src;
+        };
         carry(bw.c1, convw(q + "conv1.weight", q + "bn1.", cin, cout, 3, st, 1));
         carry(bw.c2, convw(q + "conv2.weight", q + "bn2.", cout, cout, 3, 1, 1));
         bw.has_ds = (b == 0 && (st != 1 || cin != cout));
@@ -382,10 +386,36 @@ int Engine::refresh_shadows(cudaStream_t st) {
         if (!w) continue;
         if (bn_fold(w->bn[0], w->bn[1], w->bn[2], w->bn[3], w->scale, w->shift, w->Cout, st)) return -1;
         if (pack_conv_weights(w->w32, w->scale, w->wpk, w->wpkt, w->Cout, w->Cin, w->KH * w->KH, st)) return -1;
+        if (w->scale2) {
+          for (int h = 0; h < 2; ++h) {
+            ACT_CUDA(cudaMemcpyAsync(w->scale2 + 64 * h, w->scale, 64 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+            ACT_CUDA(cudaMemcpyAsync(w->shift2 + 64 * h, w->shift, 64 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+          }
+        }
+      }
+    }
+    if (repack_pair_operands(k, st)) return -1;
+  }
+  return 0;
+}
+
+// paired 64-channel operands (forward from wpk, data gradient from wpkt) of one camera, one launch
+int Engine::repack_pair_operands(int cam, cudaStream_t st) {
+  PairJobs jobs;
+  for (int i = 0; i < 8; ++i) {
+    BlockW& b = cam_w_[cam].blk[i];
+    for (ConvW* w : {&b.c1, &b.c2}) {
+      if (!w->wpk2) continue;
+      for (int dg = 0; dg < (cfg_.train ? 2 : 1); ++dg) {
+        PairJob& j = jobs.job[jobs.n++];
+        j.src = dg ? w->wpkt : w->wpk; j.dst = dg ? w->wpkt2 : w->wpk2;
+        conv_pair_slots(dg != 0, j.even_slot, j.odd_slot);
       }
     }
   }
-  return 0;
+  if (jobs.n == 0) return 0;
+  ++launches_;
+  return pack_pair_batched(jobs, st);
 }
 
 int Engine::zero_grad(cudaStream_t st, bool async) {
@@ -448,6 +478,7 @@ int Engine::repack_conv_operands(cudaStream_t st) {
     }
     if (pack_conv_batched(jobs, st)) return -1;
     ++launches_;
+    if (repack_pair_operands(k, st)) return -1;
   }
   return 0;
 }

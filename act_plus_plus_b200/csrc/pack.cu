@@ -130,6 +130,7 @@ int bn_fold(const float* w, const float* b, const float* rm, const float* rv, fl
   return 0;
 }
 
+
 }  // namespace act
 
 namespace act {
@@ -144,6 +145,7 @@ int pack_conv1_weights(const float* w, bf16* wpk, int KP, cudaStream_t st) {
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
+
 }  // namespace act
 
 namespace act {
@@ -160,6 +162,26 @@ __global__ void pack_stem_kernel(const float* __restrict__ w, bf16* __restrict__
 }
 int pack_stem_weights(const float* w, bf16* wpk, cudaStream_t st) {
   pack_stem_kernel<<<(128 * 448 + 255) / 256, 256, 0, st>>>(w, wpk);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Paired 3x3/s1 weights for 64-channel convs (conv_ops.cu::pair_launch): dst [128][12*64]; slot s' = (dh+1)*4 + (e+1),
+// e = input column offset relative to the EVEN output pixel of the pair.  Rows 0..63 (even pixel) take the source slot
+// even_slot[s'], rows 64..127 (odd pixel) take odd_slot[s'] (-1 = zero block).  src is a packed [64][9*64] operand.
+__global__ void pack_pair_kernel(PairJobs jobs) {
+  const PairJob& jb = jobs.job[blockIdx.y];
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 128 * 12 * 64 / 8) return;
+  const int e8 = i % 8, sp = (i / 8) % 12, row = i / 96;
+  const int slot = row < 64 ? jb.even_slot[sp] : jb.odd_slot[sp];
+  uint4 v = make_uint4(0u, 0u, 0u, 0u);
+  if (slot >= 0) v = *reinterpret_cast<const uint4*>(jb.src + (1LL * (row & 63) * 9 + slot) * 64 + e8 * 8);
+  *reinterpret_cast<uint4*>(jb.dst + (1LL * row * 12 + sp) * 64 + e8 * 8) = v;
+}
+int pack_pair_batched(const PairJobs& jobs, cudaStream_t st) {
+  if (jobs.n <= 0) return 0;
+  pack_pair_kernel<<<dim3((128 * 12 * 8 + 255) / 256, jobs.n), 256, 0, st>>>(jobs);
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
