@@ -76,11 +76,13 @@ conv3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ C
           mbar_wait(&pempty[ps], ((pit / Cfg::NP) & 1) ^ 1);
           mbar_expect_tx(&pfull[ps], patch_tx);
           tma_load_4d(smem + ps * Cfg::PATCH_BYTES, &amap, &pfull[ps], cb * 64, tw * p.BW - 1, th * p.BH - 1, tn);
-          for (int tap = 0; tap < p.ntaps; ++tap, ++wit) {
+          for (int tap = 0; tap < p.ntaps; ++tap) {
+            if ((p.skip_mask >> (tap * p.cin_blocks + cb)) & 1u) continue;     // structurally zero weight block
             const int ws = wit % Cfg::NW;
             mbar_wait(&wempty[ws], ((wit / Cfg::NW) & 1) ^ 1);
             mbar_expect_tx(&wfull[ws], Cfg::W_BYTES);
             tma_load_2d(wsm + ws * Cfg::W_BYTES, &bmap, &wfull[ws], (p.taps[tap].wslot * p.cin_blocks + cb) * 64, n0);
+            ++wit;
           }
         }
       }
@@ -102,7 +104,8 @@ conv3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ C
           mbar_wait(&pfull[ps], (pit / Cfg::NP) & 1);
           tc_fence_after();
           const uint32_t pa = sbase + ps * Cfg::PATCH_BYTES;
-          for (int tap = 0; tap < p.ntaps; ++tap, ++wit) {
+          for (int tap = 0; tap < p.ntaps; ++tap) {
+            if ((p.skip_mask >> (tap * p.cin_blocks + cb)) & 1u) continue;
             const int ws = wit % Cfg::NW;
             mbar_wait(&wfull[ws], (wit / Cfg::NW) & 1);
             tc_fence_after();
@@ -117,6 +120,7 @@ conv3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ C
               first = 0;
             }
             umma_commit(&wempty[ws]);
+            ++wit;
           }
           umma_commit(&pempty[ps]);
         }

@@ -51,51 +51,48 @@ static int input_taps(const ConvShape& s, const bf16* x, PlaneDesc* planes, int*
 
 // ---- two output pixels per GEMM row for 64 -> 64 channel 3x3/s1 convs (forward and data gradient).
 // An M=128 tcgen05.mma costs the same for N = 64 and N = 128, so these convs (ResNet layer1: the largest images of the
-// trunk) ran at half the tensor rate.  Row r of the paired GEMM is the pixel pair (2r, 2r+1); its K dimension is the 4
-// input columns e = -1..2 (relative to pixel 2r) x 3 rows x 64 channels = 12 slots instead of 9, and N = 128 = the even
-// pixel's 64 outputs followed by the odd pixel's: 48 MMAs per 256 outputs instead of 72.  Input columns come from the two
-// W-parity planes of the NHWC tensor (column 2r+e = plane e&1, index r + floor(e/2); TMA zero fill = padding), the
-// output / residual / mask tensors [N,H,W,64] are the same memory as [N,H,W/2,128].
+// trunk) ran at half the tensor rate.  View the NHWC-64 tensors as pixel PAIRS, [N,H,W/2,128]: the conv becomes a dense
+// 3x3/s1 conv with 128 -> 128 channels over pairs (so it runs on the halo-resident conv3_kernel unchanged) whose weight
+// has structurally zero blocks: the pair to the left contributes only its odd pixel, the pair to the right only its even
+// pixel.  Of the 9 taps x 2 channel blocks, 6 are zero and are skipped (ConvLaunch::skip_mask): 48 N=128 MMAs per 256
+// output pixels instead of 72 N=64 MMAs.
 bool conv_pair_ok(const ConvShape& s) {
   static int env = -1;
-  // Opt-in (ACT_CONV_PAIR=1): on the generic per-tap kernel the 12 tap boxes per tile make it L2->SM bound (0.39-0.44 ms
-  // per layer1 conv at 128 images against 0.30-0.33 ms for the halo-resident conv3_kernel at N = 64); the pairing only
-  // pays inside conv3_kernel (two W-parity halo patches), which is not written yet.
-  if (env < 0) { const char* e = getenv("ACT_CONV_PAIR"); env = (e && e[0] == '1') ? 1 : 0; }
+  if (env < 0) { const char* e = getenv("ACT_CONV_PAIR"); env = (e && e[0] == '0') ? 0 : 1; }
   return env && s.KH == 3 && s.stride == 1 && s.pad == 1 && s.Cin == 64 && s.Cout == 64 && s.W % 2 == 0;
 }
-// forward tap (kh,kw) reads column offset dw = kw - 1, row offset dh = kh - 1; dgrad tap reads dw = 1 - kw, dh = 1 - kh
-void conv_pair_slots(bool dgrad, int8_t even_slot[12], int8_t odd_slot[12]) {
+// forward tap (kh,kw) reads column offset dw = kw - 1, row offset dh = kh - 1; dgrad tap reads dw = 1 - kw, dh = 1 - kh.
+// Block sp = ((dh+1)*3 + (dwp+1))*2 + pi holds input pixel e = 2*dwp + pi relative to the pair's even pixel.
+void conv_pair_slots(bool dgrad, int8_t even_slot[18], int8_t odd_slot[18]) {
   for (int dh = -1; dh <= 1; ++dh)
-    for (int e = -1; e <= 2; ++e) {
-      const int sp = (dh + 1) * 4 + (e + 1);
-      auto slot = [&](int dw) -> int8_t {
-        if (dw < -1 || dw > 1) return -1;
-        const int kh = dgrad ? 1 - dh : dh + 1, kw = dgrad ? 1 - dw : dw + 1;
-        return static_cast<int8_t>(kh * 3 + kw);
-      };
-      even_slot[sp] = slot(e);
-      odd_slot[sp] = slot(e - 1);
-    }
+    for (int dwp = -1; dwp <= 1; ++dwp)
+      for (int pi = 0; pi < 2; ++pi) {
+        const int sp = ((dh + 1) * 3 + (dwp + 1)) * 2 + pi, e = 2 * dwp + pi;
+        auto slot = [&](int dw) -> int8_t {
+          if (dw < -1 || dw > 1) return -1;
+          const int kh = dgrad ? 1 - dh : dh + 1, kw = dgrad ? 1 - dw : dw + 1;
+          return static_cast<int8_t>(kh * 3 + kw);
+        };
+        even_slot[sp] = slot(e);
+        odd_slot[sp] = slot(e - 1);
+      }
 }
 static int pair_launch(const bf16* in, int N, int H, int W, const bf16* wpair, const EpiDesc& epi, cudaStream_t stream) {
   ConvLaunch c;
-  for (int pw = 0; pw < 2; ++pw) {
-    PlaneDesc& pl = c.planes[pw];
-    pl.ptr = in + pw * 64; pl.C = 64; pl.W = W / 2; pl.H = H; pl.N = N;
-    pl.sW = 128; pl.sH = 64LL * W; pl.sN = 64LL * W * H;
-  }
-  c.nplanes = 2;
+  full_plane(&c.planes[0], in, N, H, W / 2, 128);
+  c.nplanes = 1;
   int n = 0;
   for (int dh = -1; dh <= 1; ++dh)
-    for (int e = -1; e <= 2; ++e) {
+    for (int dwp = -1; dwp <= 1; ++dwp) {
       TapDesc t;
-      t.map = static_cast<int16_t>(pmod(e, 2)); t.dh = static_cast<int16_t>(dh); t.dw = static_cast<int16_t>(floordiv(e, 2));
-      t.wslot = static_cast<int16_t>((dh + 1) * 4 + (e + 1));
+      t.map = 0; t.dh = static_cast<int16_t>(dh); t.dw = static_cast<int16_t>(dwp); t.wslot = static_cast<int16_t>(n);
+      // left pair: only its odd pixel (channel block 1) is within reach; right pair: only its even pixel (block 0)
+      if (dwp == -1) c.skip_mask |= 1u << (n * 2 + 0);
+      if (dwp == +1) c.skip_mask |= 1u << (n * 2 + 1);
       c.taps[n++] = t;
     }
   c.ntaps = n;
-  c.Cin = 64; c.Cout = 128; c.wgt = wpair; c.wgt_ld = 12 * 64;
+  c.Cin = 128; c.Cout = 128; c.wgt = wpair; c.wgt_ld = 9 * 128;
   c.vW = W / 2; c.vH = H; c.NIMG = N;
   c.og = PixGeom{H, W / 2, 1, 1, 0, 0, 128};
   c.rg = c.og;

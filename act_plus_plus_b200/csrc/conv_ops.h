@@ -9,7 +9,7 @@ struct ConvShape {
 };
 
 int conv_out_dim(int in, int k, int stride, int pad);
-// wpair (optional, 64 -> 64 channel 3x3/s1 convs with an even width): the paired operand [128][12*64] built by
+// wpair (optional, 64 -> 64 channel 3x3/s1 convs with an even width): the paired operand [128][9*128] built by
 // pack_pair_batched with conv_pair_slots(); one GEMM row then produces two horizontally adjacent output pixels (N = 128
 // at the MMA count of 1.5 N=64 rows).  Per-channel epilogue vectors (scale / bias) must then hold 128 entries (64 + 64).
 int conv_fwd(const ConvShape& s, const bf16* x, const bf16* wpk, const EpiDesc& epi, cudaStream_t stream,
@@ -17,8 +17,8 @@ int conv_fwd(const ConvShape& s, const bf16* x, const bf16* wpk, const EpiDesc& 
 int conv_dgrad(const ConvShape& s, const bf16* dy, const bf16* wpkt, EpiDesc epi, const bf16* res_compact,
                cudaStream_t stream, const bf16* wpair = nullptr);
 bool conv_pair_ok(const ConvShape& s);
-// source slots (kh*3+kw of wpk for fwd, of wpkt for dgrad) of the 12 paired slots, for the even / odd pixel rows
-void conv_pair_slots(bool dgrad, int8_t even_slot[12], int8_t odd_slot[12]);
+// source slots (kh*3+kw of wpk for fwd, of wpkt for dgrad) of the 18 paired blocks (tap*2 + input pixel parity), for the even / odd pixel rows
+void conv_pair_slots(bool dgrad, int8_t even_slot[18], int8_t odd_slot[18]);
 int conv_wgrad_reserve(long long elems);     // staging buffer [KK][Cout][Cin] fp32 (allocate before any stream capture)
 struct FoldJob { const float* T; const float* scale; float* dw; float alpha; int Cout, Cin, KK, tile0; };
 struct FoldJobs { static constexpr int MAX = 64; int n = 0; FoldJob job[MAX]; };

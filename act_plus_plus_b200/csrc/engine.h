@@ -46,7 +46,7 @@ struct ConvW {
   const float* bn[4] = {nullptr, nullptr, nullptr, nullptr};   // weight, bias, running_mean, running_var
   bf16* wpk = nullptr; bf16* wpkt = nullptr;                   // packed shadows (engine-owned)
   float* scale = nullptr; float* shift = nullptr;              // folded FrozenBN (engine-owned)
-  // 64 -> 64 channel 3x3/s1 convs only (ResNet layer1): paired operands [128][12*64] (conv_ops.cu::pair_launch) and the
+  // 64 -> 64 channel 3x3/s1 convs only (ResNet layer1): paired operands [128][9*128] (conv_ops.cu::pair_launch) and the
   // folded FrozenBN repeated to 128 entries
   bf16* wpk2 = nullptr; bf16* wpkt2 = nullptr; float* scale2 = nullptr; float* shift2 = nullptr;
 };

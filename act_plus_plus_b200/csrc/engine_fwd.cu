@@ -52,9 +52,9 @@ int Engine::alloc_workspace() {
         bw.c1.scale = A_(float, cout); bw.c1.shift = A_(float, cout);
         bw.c2.wpk = A_(bf16, 9LL * cout * cout); bw.c2.wpkt = A_(bf16, 9LL * cout * cout);
         bw.c2.scale = A_(float, cout); bw.c2.shift = A_(float, cout);
-        if (cin == 64 && cout == 64 && conv_pair_ok(ConvShape{1, 2, 2, 64, 64, 3, 1, 1})) {   // opt-in, see conv_pair_ok
+        if (cin == 64 && cout == 64 && conv_pair_ok(ConvShape{1, 2, 2, 64, 64, 3, 1, 1})) {   // ACT_CONV_PAIR=0 disables
           for (ConvW* w : {&bw.c1, &bw.c2}) {
-            w->wpk2 = A_(bf16, 128 * 768); w->wpkt2 = A_(bf16, 128 * 768);
+            w->wpk2 = A_(bf16, 128 * 1152); w->wpkt2 = A_(bf16, 128 * 1152);
             w->scale2 = A_(float, 128); w->shift2 = A_(float, 128);
           }
         }

@@ -11,7 +11,7 @@ int pack_conv_weights(const float* w, const float* scale, bf16* wpk, bf16* wpkt,
 struct PackJob { const float* w; const float* scale; bf16* wpk; bf16* wpkt; int Cout, Cin, KK, tile0; };
 struct PackJobs { static constexpr int MAX = 64; int n = 0; PackJob job[MAX]; };
 int pack_conv_batched(PackJobs& jobs, cudaStream_t st);   // all jobs in one launch
-struct PairJob { const bf16* src; bf16* dst; int8_t even_slot[12]; int8_t odd_slot[12]; };
+struct PairJob { const bf16* src; bf16* dst; int8_t even_slot[18]; int8_t odd_slot[18]; };
 struct PairJobs { static constexpr int MAX = 24; int n = 0; PairJob job[MAX]; };
 int pack_pair_batched(const PairJobs& jobs, cudaStream_t st);   // paired 64-channel 3x3 operands, all jobs in one launch
 int bn_fold(const float* w, const float* b, const float* rm, const float* rv, float* scale, float* shift, int n, cudaStream_t st);

@@ -166,22 +166,23 @@ int pack_stem_weights(const float* w, bf16* wpk, cudaStream_t st) {
   return 0;
 }
 
-// Paired 3x3/s1 weights for 64-channel convs (conv_ops.cu::pair_launch): dst [128][12*64]; slot s' = (dh+1)*4 + (e+1),
-// e = input column offset relative to the EVEN output pixel of the pair.  Rows 0..63 (even pixel) take the source slot
-// even_slot[s'], rows 64..127 (odd pixel) take odd_slot[s'] (-1 = zero block).  src is a packed [64][9*64] operand.
+// Paired 3x3/s1 weights for 64-channel convs (conv_ops.cu::pair_launch): the conv over pixel PAIRS [N,H,W/2,128] has
+// Cin' = Cout' = 128; dst [128][9 taps * 128]; block sp = tap*2 + pi is the 64 input channels of pixel parity pi of the
+// pair at (dh, dwp).  Rows 0..63 (even output pixel) take source slot even_slot[sp] of the packed [64][9*64] operand,
+// rows 64..127 (odd output pixel) odd_slot[sp]; -1 = zero block.
 __global__ void pack_pair_kernel(PairJobs jobs) {
   const PairJob& jb = jobs.job[blockIdx.y];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= 128 * 12 * 64 / 8) return;
-  const int e8 = i % 8, sp = (i / 8) % 12, row = i / 96;
+  if (i >= 128 * 18 * 8) return;
+  const int e8 = i % 8, sp = (i / 8) % 18, row = i / 144;
   const int slot = row < 64 ? jb.even_slot[sp] : jb.odd_slot[sp];
   uint4 v = make_uint4(0u, 0u, 0u, 0u);
   if (slot >= 0) v = *reinterpret_cast<const uint4*>(jb.src + (1LL * (row & 63) * 9 + slot) * 64 + e8 * 8);
-  *reinterpret_cast<uint4*>(jb.dst + (1LL * row * 12 + sp) * 64 + e8 * 8) = v;
+  *reinterpret_cast<uint4*>(jb.dst + (1LL * row * 18 + sp) * 64 + e8 * 8) = v;
 }
 int pack_pair_batched(const PairJobs& jobs, cudaStream_t st) {
   if (jobs.n <= 0) return 0;
-  pack_pair_kernel<<<dim3((128 * 12 * 8 + 255) / 256, jobs.n), 256, 0, st>>>(jobs);
+  pack_pair_kernel<<<dim3((128 * 18 * 8 + 255) / 256, jobs.n), 256, 0, st>>>(jobs);
   ACT_CUDA(cudaGetLastError());
   return 0;
 }

@@ -83,6 +83,7 @@ struct ConvLaunch {
   PixGeom og{}, rg{};
   EpiDesc epi;                          // ldc/ldr/osz*/rsz* ignored (geometry comes from og / rg)
   double algo_flops = 0.0;              // > 0: algorithmic FLOPs of this launch for the profile (operands with zero padding in K)
+  uint32_t skip_mask = 0;               // dense 3x3 tap sets on conv3_kernel: bit (tap index * Cin/64 + channel block) = zero block
 };
 int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint = 0, int stages_hint = 0);
 // dense 3x3 / stride-1 tap sets: halo patch resident in shared memory (conv3_kernel.cuh); ACT_CONV3=0 disables it

@@ -47,6 +47,7 @@ struct TcParams {
   int num_k_blocks;            // GEMM/CONV: k-blocks of 64 per CTA. WGRAD: total pixel tiles
   int nz0;                     // batch index z = z0 + nz0*z1
   int ksplit;                  // split-K factor (gz = batches*ksplit); requires EPI_ATOMIC when > 1
+  uint32_t skip_mask;          // conv3_kernel: bit (tap * cin_blocks + cb) set -> that weight block is all zero, skip it
   int gx, gy, gz;              // tile grid: x = N tiles (fastest), y = M tiles / pixel tiles / wgrad row groups, z = batch*split
   // conv geometry
   int ntaps, cin_blocks;       // k-block kb -> tap kb / cin_blocks, channel block kb % cin_blocks

@@ -395,6 +395,8 @@ int tc_conv3(const ConvLaunch& c, cudaStream_t stream, int bn_hint) {
   p.tiles_w = (c.vW + BW - 1) / BW; p.tiles_h = (c.vH + BH - 1) / BH;
   p.NIMG = c.NIMG; p.vH = c.vH; p.vW = c.vW; p.og = c.og; p.rg = c.rg;
   p.ntaps = c.ntaps; p.cin_blocks = c.Cin / 64; p.N = c.Cout; p.nz0 = 1; p.ksplit = 1;
+  p.skip_mask = c.skip_mask;
+  ACT_CHECK(c.skip_mask == 0 || c.ntaps * (c.Cin / 64) <= 32, "tc_conv3: skip mask covers at most 32 weight blocks");
   for (int i = 0; i < c.ntaps; ++i) p.taps[i] = c.taps[i];
   fill_epi(p, c.epi);
   p.vec_ok = (c.og.ld % 8 == 0) && (c.rg.ld % 8 == 0 || !(c.epi.flags & (EPI_RES_F32 | EPI_RES_BF16))) &&

@@ -153,7 +153,7 @@ class CpuTrainer:
         return 1
 
 
-def cpu_train_sample(target_s=12.0, max_steps=8):
+def cpu_train_sample(target_s=12.0, max_steps=40):
     """cpu_baseline leg: a bounded sample (about 10-30 s of CPU work) of the bench workload on all host threads."""
     tr = CpuTrainer()
     b = tr.pick_batch(2, target_s)
