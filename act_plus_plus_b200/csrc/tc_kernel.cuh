@@ -47,6 +47,7 @@ struct TcParams {
   int num_k_blocks;            // GEMM/CONV: k-blocks of 64 per CTA. WGRAD: total pixel tiles
   int nz0;                     // batch index z = z0 + nz0*z1
   int ksplit;                  // split-K factor (gz = batches*ksplit); requires EPI_ATOMIC when > 1
+  int b_res;                   // MODE_CONV: 1 = the whole weight operand (num_k_blocks x [BN x 64]) is loaded ONCE per CTA and stays in smem
   uint32_t skip_mask;          // conv3_kernel: bit (tap * cin_blocks + cb) set -> that weight block is all zero, skip it
   int gx, gy, gz;              // tile grid: x = N tiles (fastest), y = M tiles / pixel tiles / wgrad row groups, z = batch*split
   // conv geometry
@@ -277,11 +278,19 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [stages * STAGE_BYTES] tiles (1024-aligned), then barriers
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + num_stages * Cfg::STAGE_BYTES);
+  // resident weights (MODE_CONV, p.b_res): stages hold the A tile only, the weight operand follows the ring and is
+  // loaded once per CTA -- a persistent CTA re-reads the same [Cout x K] weights for every tile otherwise, and for the
+  // stem that re-streaming was half of the L2->SM traffic that bounds it
+  const bool b_res = (MODE == MODE_CONV) && p.b_res != 0;
+  const uint32_t stage_bytes = b_res ? Cfg::A_BYTES : Cfg::STAGE_BYTES;
+  const uint32_t res_bytes = b_res ? static_cast<uint32_t>(p.num_k_blocks) * BN * 128u : 0u;
+  uint8_t* bres = smem + num_stages * stage_bytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(bres + res_bytes);
   uint64_t* empty_bar = full_bar + Cfg::MAX_STAGES;
   uint64_t* tfull_bar = empty_bar + Cfg::MAX_STAGES;      // [2] accumulator buffer complete (MMA -> epilogue)
   uint64_t* tempty_bar = tfull_bar + 2;                   // [2] accumulator buffer drained (epilogue -> MMA)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* bres_bar = tempty_bar + 2;                    // resident weights landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bres_bar + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -294,6 +303,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
     prefetch_tmap(&bmap);
     for (int s = 0; s < num_stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 8); }
+    mbar_init(bres_bar, 1);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
@@ -308,6 +318,13 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
     if (elect_one()) {
       const CUtensorMap* amaps[4] = {&amap0, &amap1, &amap2, &amap3};
       uint32_t it = 0;                                  // running k-block counter across tiles (ring position)
+      if (MODE == MODE_CONV && b_res) {
+        mbar_expect_tx(bres_bar, res_bytes);
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          const int tap = kb / p.cin_blocks, cb = kb % p.cin_blocks;
+          tma_load_2d(bres + static_cast<uint32_t>(kb) * BN * 128u, &bmap, bres_bar, (p.taps[tap].wslot * p.cin_blocks + cb) * 64, 0);
+        }
+      }
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const TileCoord c = decode_tile<MODE, BN>(p, t);
         for (int i = 0; i < c.nkb; ++i, ++it) {
@@ -315,7 +332,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
           const int s = it % num_stages;
           const uint32_t ph = (it / num_stages) & 1;
           mbar_wait(&empty_bar[s], ph ^ 1);
-          uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
+          uint8_t* sa = smem + s * stage_bytes;
           uint8_t* sb = sa + Cfg::A_BYTES;
           if (p.debug & 2) { mbar_arrive(&full_bar[s]); continue; }
           if (MODE == MODE_GEMM) {
@@ -339,9 +356,9 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
             const int tap = kb / p.cin_blocks, cb = kb % p.cin_blocks;
             const TapDesc td = p.taps[tap];
             const uint32_t a_bytes = p.BW * p.BH * p.BNI * 128;
-            mbar_expect_tx(&full_bar[s], a_bytes + BN * 128);
+            mbar_expect_tx(&full_bar[s], a_bytes + (b_res ? 0u : BN * 128u));
             tma_load_4d(sa, amaps[td.map], &full_bar[s], cb * 64, c.tw * p.BW + td.dw, c.th * p.BH + td.dh, c.tn * p.BNI);
-            tma_load_2d(sb, &bmap, &full_bar[s], (td.wslot * p.cin_blocks + cb) * 64, c.n0);
+            if (!b_res) tma_load_2d(sb, &bmap, &full_bar[s], (td.wslot * p.cin_blocks + cb) * 64, c.n0);
           } else {
             // WGRAD: kb = pixel tile index -> (n, ht, wt)
             int u = kb;
@@ -373,6 +390,8 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
       const uint64_t adesc0 = A_MN ? make_smem_desc(sbase, lbo, 1024) : make_smem_desc(sbase, 16, 1024);
       const uint64_t bdesc0 = B_MN ? make_smem_desc(sbase + Cfg::A_BYTES, lbo, 1024) : make_smem_desc(sbase + Cfg::A_BYTES, 16, 1024);
       uint32_t it = 0, lt = 0;
+      const uint64_t bres_desc0 = make_smem_desc(smem_u32(bres), 16, 1024);
+      if (MODE == MODE_CONV && b_res) { mbar_wait(bres_bar, 0); tc_fence_after(); }
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
         const TileCoord c = decode_tile<MODE, BN>(p, t);
         const uint32_t acc = lt & 1;
@@ -385,8 +404,9 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
           mbar_wait(&full_bar[s], ph);
           tc_fence_after();
           // descriptors differ from the stage-0 / k-0 ones only in the 14-bit start-address field (16-byte units)
-          const uint32_t soff = static_cast<uint32_t>(s * Cfg::STAGE_BYTES) >> 4;
+          const uint32_t soff = (static_cast<uint32_t>(s) * stage_bytes) >> 4;
           uint64_t ad = adesc0 + soff, bd = bdesc0 + soff;
+          if (MODE == MODE_CONV && b_res) bd = bres_desc0 + ((static_cast<uint32_t>(c.kb_begin + i) * BN * 128u) >> 4);
           if (MODE == MODE_WGRAD) {
             for (int k = 0; k < ksteps; ++k, ad += 128, bd += 128) umma_bf16(tmem_d, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
           } else {

@@ -148,12 +148,17 @@ static int launch_inst(dim3 tiles, int stages, cudaStream_t stream, const CUtens
   using Cfg = TcCfg<MODE, A_MN, B_MN, BN>;
   auto kern = tc_kernel<MODE, A_MN, B_MN, BN>;
   const int max_smem = 227 * 1024;
-  const int extra = 1024 + (2 * Cfg::MAX_STAGES + 4) * 8 + 16;
-  const int fit = std::min<int>(Cfg::MAX_STAGES, (200 * 1024) / Cfg::STAGE_BYTES);
+  const int extra = 1024 + (2 * Cfg::MAX_STAGES + 5) * 8 + 16;
+  // resident weights (MODE_CONV, p.b_res): the ring holds A tiles only and the weight operand sits behind it
+  const bool bres = MODE == MODE_CONV && p.b_res != 0;
+  const int stage_bytes = bres ? Cfg::A_BYTES : Cfg::STAGE_BYTES;
+  const int res_bytes = bres ? p.num_k_blocks * BN * 128 : 0;
+  const int fit = std::min<int>(Cfg::MAX_STAGES, (200 * 1024 - res_bytes) / stage_bytes);
   if (stages <= 0) stages = fit;
-  stages = std::max(2, std::min(stages, std::min<int>(Cfg::MAX_STAGES, (max_smem - extra) / Cfg::STAGE_BYTES)));
+  stages = std::max(2, std::min(stages, std::min<int>(Cfg::MAX_STAGES, (max_smem - extra - res_bytes) / stage_bytes)));
+  ACT_CHECK(stages * stage_bytes + res_bytes + extra <= max_smem, "resident weight operand does not fit in shared memory");
   // never let two persistent CTAs share an SM (they would serialise on the TMEM allocation)
-  const int smem = std::max(stages * Cfg::STAGE_BYTES + extra, 116 * 1024);
+  const int smem = std::max(stages * stage_bytes + res_bytes + extra, 116 * 1024);
   static bool configured = false;     // per instantiation
   if (!configured) {
     ACT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
@@ -336,8 +341,16 @@ int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint, int stages_hi
     if (plane_tmap(&am[i], c.planes[std::min(i, c.nplanes - 1)], BW, BH, BNI)) return -1;
   if (make_tmap_2d(&bm, c.wgt, c.wgt_ld, c.Cout, c.wgt_ld, bn)) return -1;
   dim3 grid((c.Cout + bn - 1) / bn, static_cast<unsigned>(mtiles), 1);
+  {
+    // Weights resident in shared memory when one N tile covers Cout, they fit beside >= 4 A stages, and every CTA walks
+    // enough tiles to amortise the up-front load (ACT_CONV_BRES=0 disables).
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("ACT_CONV_BRES"); on = (e && e[0] == '0') ? 0 : 1; }
+    const long long res = 1LL * p.num_k_blocks * bn * 128;
+    p.b_res = (on && grid.x == 1 && res <= 128 * 1024 && mtiles >= 4LL * num_sms()) ? 1 : 0;
+  }
   g_next_flops = c.algo_flops > 0 ? c.algo_flops : 2.0 * c.vW * c.vH * c.NIMG * c.Cout * c.Cin * c.ntaps;
-  if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "conv %dx%dx%d Cin=%d Cout=%d taps=%d box=%dx%dx%d bn=%d grid=%ux%u", c.NIMG, c.vH, c.vW, c.Cin, c.Cout, c.ntaps, BNI, BH, BW, bn, grid.x, grid.y); g_next_label = buf; }
+  if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "conv %dx%dx%d Cin=%d Cout=%d taps=%d box=%dx%dx%d bn=%d grid=%ux%u%s", c.NIMG, c.vH, c.vW, c.Cin, c.Cout, c.ntaps, BNI, BH, BW, bn, grid.x, grid.y, p.b_res ? " wres" : ""); g_next_label = buf; }
   const int st = stages_hint;
   if (bn == 64) return launch_inst<MODE_CONV, 0, 0, 64>(grid, st, stream, am, bm, p);
   if (bn == 128) return launch_inst<MODE_CONV, 0, 0, 128>(grid, st, stream, am, bm, p);
