@@ -42,7 +42,7 @@ int Engine::alloc_workspace() {
   // packed conv operands + folded BN
   for (int k = 0; k < cfg_.num_cameras; ++k) {
     CamW& c = cam_w_[k];
-    c.stem.wpk = A_(bf16, 128 * 448); c.stem.scale = A_(float, 128); c.stem.shift = A_(float, 128);   // paired layout, see pack_stem_kernel
+    c.stem.wpk = A_(bf16, 256 * 448); c.stem.scale = A_(float, 256); c.stem.shift = A_(float, 256);   // grouped layout, see pack_stem_kernel
     static const int cin_[4] = {64, 64, 128, 256}, cout_[4] = {64, 128, 256, 512};
     for (int s = 0; s < 4; ++s)
       for (int b = 0; b < 2; ++b) {
@@ -344,23 +344,21 @@ int Engine::stem_launch(int cam, int B, ConvLaunch* c, WgradLaunch* w) {
     taps[kh].dw = 0; taps[kh].wslot = static_cast<int16_t>(kh);
   }
   if (c) {
-    // Forward: one GEMM row = the 16-pixel window starting at an EVEN output pixel; N = 128 = that pixel's 64 channels
-    // followed by its right neighbour's (weights rows 64..127 are the filters shifted by 8 columns).  The output
-    // [B, Ho, Wo, 64] is the same memory as [B, Ho, Wo/2, 128].  Falls back to one pixel per row for odd widths.
-    static int pair_env = -1;
-    if (pair_env < 0) { const char* e = getenv("ACT_STEM_PAIR"); pair_env = (e && e[0] == '0') ? 0 : 1; }
-    const bool pair = pair_env && (Wo % 2 == 0);
+    // Forward: one GEMM row = the 16-pixel window starting at output pixel g*r and produces the g = 4 (or 2) adjacent
+    // output pixels whose taps all lie inside it; N = 64*g = their channels one after the other (weights rows 64*j.. are
+    // the filters shifted by 8*j columns).  The output [B, Ho, Wo, 64] is the same memory as [B, Ho, Wo/g, 64*g].
+    // The issuer sustains one M=128 MMA per ~55 ns whatever N <= 128 is and ~75 ns at N = 256 (section 4.1 of DESIGN.md),
+    // so wider N is the only way to fill the tensor pipe with a 64-channel output.  ACT_STEM_GROUP=1|2|4 overrides.
+    static int grp_env = -1;
+    if (grp_env < 0) { const char* e = getenv("ACT_STEM_GROUP"); grp_env = e ? atoi(e) : 2; }   // 4 is implemented (N = 256) but not yet measured on the GPU
+    int g = grp_env >= 4 ? 4 : grp_env >= 2 ? 2 : 1;
+    while (g > 1 && Wo % g) g /= 2;
     c->planes[0] = pl[0]; c->planes[1] = pl[1]; c->nplanes = 2; c->ntaps = 7;
     for (int i = 0; i < 7; ++i) c->taps[i] = taps[i];
     c->Cin = 64; c->wgt = cw.stem.wpk; c->wgt_ld = 448;
-    if (pair) {
-      for (int ph = 0; ph < 2; ++ph) { c->planes[ph].W = Wo / 2; c->planes[ph].sW = 16; }
-      c->Cout = 128; c->vW = Wo / 2; c->vH = Ho; c->NIMG = B;
-      c->og = PixGeom{Ho, Wo / 2, 1, 1, 0, 0, 128, 0};
-    } else {
-      c->Cout = 64; c->vW = Wo; c->vH = Ho; c->NIMG = B;
-      c->og = PixGeom{Ho, Wo, 1, 1, 0, 0, 64, 0};
-    }
+    for (int ph = 0; ph < 2; ++ph) { c->planes[ph].W = Wo / g; c->planes[ph].sW = 8 * g; }
+    c->Cout = 64 * g; c->vW = Wo / g; c->vH = Ho; c->NIMG = B;
+    c->og = PixGeom{Ho, Wo / g, 1, 1, 0, 0, 64 * g, 0};
     c->rg = c->og;
     c->algo_flops = 2.0 * B * Ho * Wo * 64 * 147;           // 7x7x3 taps; the K-slabs are zero-padded to 7x64
   }

@@ -375,9 +375,11 @@ int Engine::refresh_shadows(cudaStream_t st) {
   for (int k = 0; k < cfg_.num_cameras; ++k) {
     CamW& c = cam_w_[k];
     if (bn_fold(c.stem.bn[0], c.stem.bn[1], c.stem.bn[2], c.stem.bn[3], c.stem.scale, c.stem.shift, 64, st)) return -1;
-    // entries 64..127 repeat 0..63: the paired stem GEMM has N = 128 (two output pixels per row)
-    ACT_CUDA(cudaMemcpyAsync(c.stem.scale + 64, c.stem.scale, 64 * sizeof(float), cudaMemcpyDeviceToDevice, st));
-    ACT_CUDA(cudaMemcpyAsync(c.stem.shift + 64, c.stem.shift, 64 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    // entries 64*j.. repeat 0..63: the grouped stem GEMM has N = 64*g (g output pixels per row)
+    for (int j = 1; j < 4; ++j) {
+      ACT_CUDA(cudaMemcpyAsync(c.stem.scale + 64 * j, c.stem.scale, 64 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+      ACT_CUDA(cudaMemcpyAsync(c.stem.shift + 64 * j, c.stem.shift, 64 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    }
     if (pack_stem_weights(c.stem.w32, c.stem.wpk, st)) return -1;
     for (int i = 0; i < 8; ++i) {
       BlockW& b = c.blk[i];

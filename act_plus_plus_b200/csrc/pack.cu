@@ -151,17 +151,17 @@ int pack_conv1_weights(const float* w, bf16* wpk, int KP, cudaStream_t st) {
 namespace act {
 // Stem (7x7/s2, 3 -> 64) weights for the implicit-GEMM formulation: one k-block per kernel row kh, 64 columns =
 // 16 pixels x 4 channels of the padded NHWC4 image window; column kw*4 + c holds w[co][c][kh][kw] (kw < 7, c < 3).
-// Rows 64..127 hold the same filters shifted right by one output pixel (2 input pixels = 8 columns): with them one
-// GEMM row produces TWO horizontally adjacent output pixels (N = 128 instead of 64 at the same MMA count, since an
-// M=128 tcgen05.mma costs the same for N = 64 and N = 128), reading the window that starts at the even pixel.
+// Rows 64*j .. 64*j+63 (j = 1, 2, 3) hold the same filters shifted right by j output pixels (2j input pixels = 8j
+// columns; the last real column is 24 + 27 = 51 < 64): with them one GEMM row produces up to FOUR horizontally adjacent
+// output pixels (N = 256 instead of 64 at the same MMA count per row), reading the window that starts at the first one.
 __global__ void pack_stem_kernel(const float* __restrict__ w, bf16* __restrict__ wpk) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= 128 * 448) return;
-  const int row = i / 448, co = row & 63, kh = (i % 448) / 64, e = i % 64, kw = (e >> 2) - (row >= 64 ? 2 : 0), c = e & 3;
+  if (i >= 256 * 448) return;
+  const int row = i / 448, co = row & 63, kh = (i % 448) / 64, e = i % 64, kw = (e >> 2) - 2 * (row >> 6), c = e & 3;
   wpk[i] = __float2bfloat16_rn((kw >= 0 && kw < 7 && c < 3) ? w[((co * 3 + c) * 7 + kh) * 7 + kw] : 0.f);
 }
 int pack_stem_weights(const float* w, bf16* wpk, cudaStream_t st) {
-  pack_stem_kernel<<<(128 * 448 + 255) / 256, 256, 0, st>>>(w, wpk);
+  pack_stem_kernel<<<(256 * 448 + 255) / 256, 256, 0, st>>>(w, wpk);
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
