@@ -350,7 +350,7 @@ int Engine::stem_launch(int cam, int B, ConvLaunch* c, WgradLaunch* w) {
     // The issuer sustains one M=128 MMA per ~55 ns whatever N <= 128 is and ~75 ns at N = 256 (section 4.1 of DESIGN.md),
     // so wider N is the only way to fill the tensor pipe with a 64-channel output.  ACT_STEM_GROUP=1|2|4 overrides.
     static int grp_env = -1;
-    if (grp_env < 0) { const char* e = getenv("ACT_STEM_GROUP"); grp_env = e ? atoi(e) : 2; }   // 4 is implemented (N = 256) but not yet measured on the GPU
+    if (grp_env < 0) { const char* e = getenv("ACT_STEM_GROUP"); grp_env = e ? atoi(e) : 4; }
     int g = grp_env >= 4 ? 4 : grp_env >= 2 ? 2 : 1;
     while (g > 1 && Wo % g) g /= 2;
     c->planes[0] = pl[0]; c->planes[1] = pl[1]; c->nplanes = 2; c->ntaps = 7;
