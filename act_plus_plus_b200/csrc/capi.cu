@@ -113,12 +113,11 @@ extern "C" int act_maxpool_fwd(const void* x, void* y, uint8_t* idx, int N, int 
 extern "C" int act_maxpool_bwd(const void* dy, const uint8_t* idx, const void* x, void* dx, int N, int H, int W, int C, void* stream) {
   return maxpool_bwd(BF(dy), idx, BF(x), BFM(dx), N, H, W, C, ST(stream));
 }
-extern "C" int act_im2col_conv1(const float* image, int64_t img_bs, void* out, int B, int H, int W, int KP, void* stream) {
-  return im2col_conv1(image, img_bs, BFM(out), B, H, W, KP, ST(stream));
-}
 extern "C" int act_adamw_step(float* p, const float* g, float* m, float* v, void* shadow, int64_t n, float lr, float b1,
                               float b2, float eps, float wd, int step, int mode, void* stream) {
-  AdamWArgs a{p, g, m, v, BFM(shadow), n, lr, b1, b2, eps, wd, step, mode};
+  AdamWArgs a;
+  a.p = p; a.g = g; a.m = m; a.v = v; a.shadow = BFM(shadow); a.n = n; a.lr = lr; a.beta1 = b1; a.beta2 = b2; a.eps = eps;
+  a.wd = wd; a.step = step; a.mode = mode;
   return adamw_step(a, ST(stream));
 }
 extern "C" int act_temporal_agg_step(float* ring, const float* chunks, const int* t, double* out, int E, int nq, int A,
@@ -136,7 +135,7 @@ extern "C" int act_engine_create(const act_engine_config* c, act_engine** out) {
   k.dec_layers = c->dec_layers; k.num_queries = c->num_queries; k.state_dim = c->state_dim; k.action_dim = c->action_dim;
   k.latent_dim = c->latent_dim; k.kl_weight = c->kl_weight; k.lr = c->lr; k.lr_backbone = c->lr_backbone;
   k.weight_decay = c->weight_decay; k.beta1 = c->beta1; k.beta2 = c->beta2; k.adam_eps = c->adam_eps;
-  k.faithful_decoder = c->faithful_decoder; k.train = c->train;
+  k.no_encoder = c->no_encoder; k.train = c->train;
   Engine* e = new Engine(k);
   if (e->init() != 0) { delete e; return -1; }
   *out = new act_engine{e};
@@ -205,12 +204,43 @@ extern "C" int act_engine_dp_slices(act_engine* e, long long* offsets, long long
 }
 extern "C" int act_engine_adamw_region(act_engine* e, int step, int region, int blocks_per_sm, void* stream) {
   if (region < 0 || region >= R_COUNT) { set_error("act_engine_adamw_region: bad region"); return -1; }
+  if (step <= 0) { set_error("act_engine_adamw_region: step must be >= 1"); return -1; }
+  if (e->eng->begin_opt_step(step, ST(stream))) return -1;      // idempotent: every region of one step sets the same value
   return e->eng->adamw_region(region, step, ST(stream), blocks_per_sm);
 }
 extern "C" int act_engine_set_image_format(act_engine* e, int fmt) { return e->eng->set_image_format(fmt); }
 extern "C" int act_engine_set_concurrent(act_engine* e, int on) { return e->eng->set_concurrent(on != 0); }
 extern "C" int act_engine_set_lr(act_engine* e, float lr, float lr_backbone) { e->eng->set_lr(lr, lr_backbone); return 0; }
+extern "C" int act_engine_set_dropout(act_engine* e, float p, uint64_t seed) { return e->eng->set_dropout(p, seed); }
+extern "C" int act_engine_dropout_state(act_engine* e, float* p, uint64_t* seed, uint32_t* step) {
+  unsigned long long s = 0;
+  const int rc = e->eng->dropout_state(p, &s, step);
+  if (seed) *seed = s;
+  return rc;
+}
+extern "C" int act_dropout_mask(uint64_t seed, uint32_t site, uint32_t step, float p, int64_t n, uint8_t* out, void* stream) {
+  return dropout_mask(seed, site, step, p, n, out, ST(stream));
+}
+extern "C" int act_engine_set_loss_grad(act_engine* e, const float* gvec3) { e->eng->set_loss_grad(gvec3); return 0; }
+extern "C" int act_engine_join_lanes(act_engine* e, void* stream) { return e->eng->join_lanes(ST(stream)); }
 extern "C" int act_engine_launches(act_engine* e, int reset) { const int n = e->eng->launches(); if (reset) e->eng->reset_launches(); return n; }
+
+extern "C" int act_engine_debug_buffer(act_engine* e, const char* name, void* dst, int64_t capacity, int64_t* numel,
+                                       int* dtype, void* stream) {
+  long long n = 0;
+  void* src = nullptr;
+  int dt = 0;
+  if (e->eng->debug_buffer(name, &src, &n, &dt)) return -1;
+  if (numel) *numel = n;
+  if (dtype) *dtype = dt;
+  if (!dst) return 0;
+  const long long bytes = n * (dt == 0 ? 4 : 2);
+  if (capacity < bytes) { set_error("act_engine_debug_buffer: destination too small"); return -1; }
+  if (cudaMemcpyAsync(dst, src, static_cast<size_t>(bytes), cudaMemcpyDeviceToDevice, ST(stream)) != cudaSuccess) {
+    set_error("act_engine_debug_buffer: copy failed"); return -1;
+  }
+  return 0;
+}
 
 extern "C" int act_tc_profile_begin(void) { tc_profile_begin(); return 0; }
 extern "C" int act_tc_profile_end(double* total_ms, double* total_flops, int* launches, double* max_ms) {

@@ -65,24 +65,23 @@ conv3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ C
   if (warp == 0) {
     // ============================================================== TMA producer
     if (elect_one()) {
-      uint32_t pit = 0, wit = 0;
+      uint32_t ps = 0, pph = 0, ws = 0, wph = 0;          // ring positions / phases (no div/mod in the loops)
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const int n0 = (t % p.gx) * BN;
         int u = t / p.gx;
         const int tw = u % p.tiles_w; u /= p.tiles_w;
         const int th = u % p.tiles_h, tn = u / p.tiles_h;
-        for (int cb = 0; cb < p.cin_blocks; ++cb, ++pit) {
-          const int ps = pit % Cfg::NP;
-          mbar_wait(&pempty[ps], ((pit / Cfg::NP) & 1) ^ 1);
+        for (int cb = 0; cb < p.cin_blocks; ++cb) {
+          mbar_wait(&pempty[ps], pph ^ 1);
           mbar_expect_tx(&pfull[ps], patch_tx);
           tma_load_4d(smem + ps * Cfg::PATCH_BYTES, &amap, &pfull[ps], cb * 64, tw * p.BW - 1, th * p.BH - 1, tn);
+          if (++ps == Cfg::NP) { ps = 0; pph ^= 1; }
           for (int tap = 0; tap < p.ntaps; ++tap) {
             if ((p.skip_mask >> (tap * p.cin_blocks + cb)) & 1u) continue;     // structurally zero weight block
-            const int ws = wit % Cfg::NW;
-            mbar_wait(&wempty[ws], ((wit / Cfg::NW) & 1) ^ 1);
+            mbar_wait(&wempty[ws], wph ^ 1);
             mbar_expect_tx(&wfull[ws], Cfg::W_BYTES);
             tma_load_2d(wsm + ws * Cfg::W_BYTES, &bmap, &wfull[ws], (p.taps[tap].wslot * p.cin_blocks + cb) * 64, n0);
-            ++wit;
+            if (++ws == Cfg::NW) { ws = 0; wph ^= 1; }
           }
         }
       }
@@ -92,37 +91,38 @@ conv3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ C
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16(128, BN, 0, 0);
       const uint32_t sbase = smem_u32(smem), wbase = smem_u32(wsm);
-      uint32_t pit = 0, wit = 0, lt = 0;
+      uint32_t ps = 0, pph = 0, ws = 0, wph = 0, lt = 0;
+      const uint64_t adesc0 = make_smem_desc(sbase, 16, 1024), bdesc0 = make_smem_desc(wbase, 16, 1024);
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
         const uint32_t acc = lt & 1;
         mbar_wait(&tempty[acc], ((lt >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
         uint32_t first = 1;
-        for (int cb = 0; cb < p.cin_blocks; ++cb, ++pit) {
-          const int ps = pit % Cfg::NP;
-          mbar_wait(&pfull[ps], (pit / Cfg::NP) & 1);
+        for (int cb = 0; cb < p.cin_blocks; ++cb) {
+          mbar_wait(&pfull[ps], pph);
           tc_fence_after();
-          const uint32_t pa = sbase + ps * Cfg::PATCH_BYTES;
+          const uint64_t pdesc = adesc0 + ps * (Cfg::PATCH_BYTES >> 4);
           for (int tap = 0; tap < p.ntaps; ++tap) {
             if ((p.skip_mask >> (tap * p.cin_blocks + cb)) & 1u) continue;
-            const int ws = wit % Cfg::NW;
-            mbar_wait(&wfull[ws], (wit / Cfg::NW) & 1);
+            mbar_wait(&wfull[ws], wph);
             tc_fence_after();
             const int off = (p.taps[tap].dh + 1) * p.PW + (p.taps[tap].dw + 1);       // patch row of accumulator row 0
             // row-shifted view of the patch: plain descriptor, no base-offset field -- measured on B200 the 128B swizzle
-            // is a function of the absolute shared-memory address bits, so TMA's placement and the MMA read agree
-            uint64_t ad = make_smem_desc(pa + static_cast<uint32_t>(off) * 128u, 16, 1024);
-            uint64_t bd = make_smem_desc(wbase + ws * Cfg::W_BYTES, 16, 1024);
+            // is a function of the absolute shared-memory address bits, so TMA's placement and the MMA read agree.
+            // Descriptors differ from the stage-0 ones only in the start-address field (16-byte units, never carries out).
+            uint64_t ad = pdesc + static_cast<uint32_t>(off) * 8u;
+            uint64_t bd = bdesc0 + ws * (Cfg::W_BYTES >> 4);
 #pragma unroll
             for (int k = 0; k < 4; ++k, ad += 2, bd += 2) {
               umma_bf16(tmem_d, ad, bd, idesc, first ? 0u : 1u);
               first = 0;
             }
             umma_commit(&wempty[ws]);
-            ++wit;
+            if (++ws == Cfg::NW) { ws = 0; wph ^= 1; }
           }
           umma_commit(&pempty[ps]);
+          if (++ps == Cfg::NP) { ps = 0; pph ^= 1; }
         }
         umma_commit(&tfull[acc]);
       }

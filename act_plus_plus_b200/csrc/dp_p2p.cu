@@ -50,6 +50,9 @@ __global__ void dp_barrier_kernel(DpPeers peers, uint32_t* __restrict__ epoch, u
                                   unsigned long long timeout_ns) {
   const int lane = threadIdx.x;
   const uint32_t e = epoch[site] + 1;
+  // an earlier barrier of this step timed out: do not wait again (the exchange kernels that follow skip their work,
+  // so no replica is overwritten with gradients a peer never finished); the host raises when it polls the status
+  if (status[0] != 0u) { if (lane == 0) epoch[site] = e; return; }
   __syncwarp();
   __threadfence_system();                                    // everything this GPU wrote before the barrier
   if (lane < peers.world) {
@@ -81,8 +84,11 @@ __host__ __device__ inline void dp_slice(long long n4, int rank, int world, long
 }
 
 template <int WORLD, int U>
-__global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs a, long long off, float bc1, float rsqrt_bc2,
+__global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs a, long long off, float bc1_host, float rs_host,
                                                        int ld_sys) {
+  if (a.abort_flag != nullptr && *a.abort_flag != 0u) return;    // a barrier of this step failed: leave every replica as it is
+  float bc1, rsqrt_bc2;
+  adam_bias(a, bc1_host, rs_host, &bc1, &rsqrt_bc2);
   // WORLD > 0: compile-time rank count; WORLD == 0: run-time count.  U float4 chunks per thread and iteration: all
   // U * world peer loads are issued before the first use (a remote load is ~2 us; bytes in flight set the NVLink rate).
   constexpr int W = WORLD > 0 ? WORLD : DP_MAX_WORLD;

@@ -18,7 +18,7 @@ struct EngineConfig {
   int num_queries = 100, state_dim = 14, action_dim = 16, latent_dim = 32;
   float kl_weight = 10.f;
   float lr = 1e-5f, lr_backbone = 1e-5f, weight_decay = 1e-4f, beta1 = 0.9f, beta2 = 0.999f, adam_eps = 1e-8f;
-  int faithful_decoder = 0;   // 1: also execute decoder layers 1.. (dead work in the reference, detr_vae.py:245)
+  int no_encoder = 0;         // 1: encoder=None variant (detr_vae.py:109-112): latent 0, kl 0, no `encoder.*` tensors
   int train = 1;              // 0: inference-only engine (no backward workspace)
 };
 
@@ -56,10 +56,12 @@ struct CamW { ConvW stem; BlockW blk[8]; };
 
 struct EncActs {       // saved activations of one post-norm encoder layer over M = B*L rows
   bf16 *xb = nullptr, *xpb = nullptr, *qk = nullptr, *v = nullptr, *P = nullptr, *o = nullptr, *x1b = nullptr, *hh = nullptr;
+  bf16* P2 = nullptr;    // dropout(P), the operand of P.V in train mode (P itself feeds the softmax backward)
   float *t1 = nullptr, *mean1 = nullptr, *rstd1 = nullptr, *x1 = nullptr, *t2 = nullptr, *mean2 = nullptr, *rstd2 = nullptr, *x2 = nullptr;
 };
 struct DecActs {
   bf16 *xb = nullptr, *xpb = nullptr, *qk = nullptr, *v = nullptr, *P = nullptr, *o = nullptr;     // self-attention
+  bf16 *P2 = nullptr, *cP2 = nullptr;                                                               // dropped attention weights
   float *t1 = nullptr, *mean1 = nullptr, *rstd1 = nullptr, *y1 = nullptr; bf16* y1pb = nullptr;
   bf16 *q = nullptr, *k = nullptr, *cv = nullptr, *cP = nullptr, *co = nullptr;                     // cross-attention
   float *t2 = nullptr, *mean2 = nullptr, *rstd2 = nullptr, *y2 = nullptr; bf16* y2b = nullptr;
@@ -92,7 +94,7 @@ class Engine {
               float* logvar, float* losses, cudaStream_t st);
   int backward(int stage, float loss_grad, cudaStream_t st);      // stage: 0 = all, 1 = transformer, 2 = cvae, 3 = backbone, 4 = cvae || backbone
   int zero_grad(cudaStream_t st, bool async = false);
-  int adamw(int step, cudaStream_t st);
+  int adamw(int step, cudaStream_t st, bool begin = true);
   int adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm = 0);
   int adamw_range(long long off, long long n, float lr, bool shadow, int step, cudaStream_t st, int blocks_per_sm);
   GradsReadyFn grads_cb_ = nullptr;
@@ -133,29 +135,48 @@ class Engine {
   const EngineConfig& cfg() const { return cfg_; }
   long long workspace_bytes() const { return ws_bytes_; }
   int launches() const { return launches_; }
+  int debug_buffer(const char* name, void** ptr, long long* numel, int* dtype);
+  int* opt_step_dev_ = nullptr;                 // device copy of the optimiser step (AdamW bias corrections read it)
+  // step > 0: the device counter is set to it; step == 0: the counter is incremented (CUDA-graph replays advance)
+  int begin_opt_step(int step, cudaStream_t st);
+  // Train-mode dropout (transformer.py:194,197,202-203,219-222,254-266,284-293; detr/main.py:45).  p = 0 turns it off
+  // (the reference's .eval()).  Masks are Philox functions of (seed, site, step, element) regenerated in the backward;
+  // the step counter lives on the device and is bumped by every training forward (CUDA-graph replays draw new masks).
+  int set_dropout(float p, unsigned long long seed);
+  int dropout_state(float* p, unsigned long long* seed, uint32_t* step);   // synchronises
+  enum : uint32_t { SITE_ENC = 0x100, SITE_CVAE = 0x200, SITE_DEC = 0x300 };   // + 8 * layer + {0 attn, 1 out-proj, 2 ffn hidden, 3 ffn out, 4 cross attn, 5 cross out-proj}
+  DropDesc drop_site(uint32_t site) const;
   void reset_launches() { launches_ = 0; }
   // 0: image is float32 [B, K, 3, H, W] in [0, 1] (policy.py:264 signature); 1: uint8 [B, K, H, W, 3] (dataset frames)
   int set_image_format(int fmt) { if (fmt != 0 && fmt != 1) { set_error("image format must be 0 (f32 CHW) or 1 (u8 HWC)"); return -1; } image_fmt_ = fmt; return 0; }
   int image_fmt_ = 0;
   int set_concurrent(bool on) { if (ensure_streams()) return -1; concurrent_ = on; return 0; }
   void set_lr(float lr, float lr_backbone) { cfg_.lr = lr; cfg_.lr_backbone = lr_backbone; }
+  // device pointer to the incoming gradient of {l1, kl, loss} (autograd hands it over on the device); null = the scalar
+  // loss_grad argument of backward() applies to `loss` alone.  Sticky until changed.
+  void set_loss_grad(const float* gvec3) { loss_gvec_ = gvec3; }
+  const float* loss_gvec_ = nullptr;
+  int join_lanes(cudaStream_t st) { return wg_join(st); }     // st waits for every internal lane (e.g. an async zero_grad)
 
  private:
   // ---- helpers (engine_fwd.cu / engine_bwd.cu)
   int linear(const bf16* X, int M, const LinW& w, uint32_t flags, const float* res_f32, float* out_f32, bf16* out_bf16,
-             const bf16* aux, cudaStream_t st, bool splitk = false);
+             const bf16* aux, cudaStream_t st, bool splitk = false, uint32_t drop = 0);
   int linear_dx(const bf16* dY, int M, const LinW& w, uint32_t flags, const float* res_f32, const bf16* aux, float* out_f32,
-                bf16* out_bf16, cudaStream_t st, bool splitk = false);
+                bf16* out_bf16, cudaStream_t st, bool splitk = false, float alpha = 1.f);
   int linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cudaStream_t st);
+  // drop = dropout site of the attention weights (0 = none); P2 receives dropout(P) and multiplies V
   int attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv, const uint8_t* mask,
-               bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st, bool v_on_aux = false, float* S = nullptr);
+               bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st, bool v_on_aux = false, float* S = nullptr,
+               uint32_t drop = 0, bf16* P2 = nullptr);
   int attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv,
                const bf16* P, bf16* dQ, long long lddq, bf16* dK, long long lddk, bf16* dV, long long lddv, int B, int Lq,
-               int Lk, cudaStream_t st, float* S = nullptr, bf16* dS = nullptr, bool use_aux = true);
+               int Lk, cudaStream_t st, float* S = nullptr, bf16* dS = nullptr, bool use_aux = true, uint32_t drop = 0,
+               const bf16* P2 = nullptr);
   int enc_layer_fwd(const EncW& w, EncActs& a, const float* x, const float* pos, const float* next_pos, int L,
-                    const uint8_t* mask, int B, bool emit_next, bf16* next_xb, bf16* next_xpb, cudaStream_t st);
+                    const uint8_t* mask, int B, bool emit_next, bf16* next_xb, bf16* next_xpb, cudaStream_t st, uint32_t site);
   int enc_layer_bwd(const EncW& w, EncActs& a, const float* x_in, const float* dx2, const float* dx2b, float* dx_out,
-                    float* gxp_out, int L, int B, cudaStream_t st);
+                    float* gxp_out, int L, int B, cudaStream_t st, uint32_t site);
   int backbone_fwd(int cam, int B, const float* image, cudaStream_t st);
   int backbone_bwd(int cam, int B, cudaStream_t st);
   int dec_self_fwd(int B, cudaStream_t st);     // query self-attention block: depends on weights only
@@ -259,6 +280,10 @@ class Engine {
   int fh_[6] = {0}, fw_[6] = {0};   // spatial dims: [0] image, [1] conv1 out, [2] pool out (layer1), [3] layer2, [4] layer3, [5] layer4
   int cur_B_ = 0;
   bool have_actions_ = false;
+  float drop_p_ = 0.f;                          // configured dropout probability (0 = off)
+  unsigned long long drop_seed_ = 0;
+  uint32_t* drop_step_dev_ = nullptr;           // device step counter
+  bool drop_active_ = false;                    // the last forward applied dropout (its backward regenerates the masks)
 
   // weights
   std::vector<EncW> enc_w_, cvae_w_;

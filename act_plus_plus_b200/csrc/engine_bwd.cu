@@ -52,10 +52,11 @@ __global__ void conv1_grad_fold_kernel(const float* __restrict__ tmp, const floa
 
 // dX[M,K] = dY[M,N] * W[N,K]   (A = dY K-major, B = W read MN-major)
 int Engine::linear_dx(const bf16* dY, int M, const LinW& w, uint32_t flags, const float* res_f32, const bf16* aux,
-                      float* out_f32, bf16* out_bf16, cudaStream_t st, bool splitk) {
+                      float* out_f32, bf16* out_bf16, cudaStream_t st, bool splitk, float alpha) {
   MatDesc A, B;
   A.ptr = dY; A.ld = w.N; B.ptr = w.w; B.mn_major = 1; B.ld = w.K;
   EpiDesc e;
+  e.alpha = alpha;
   e.flags = flags | (out_f32 ? EPI_OUT_F32 : 0) | (out_bf16 ? EPI_OUT_BF16 : 0) | (res_f32 ? EPI_RES_F32 : 0) | (aux ? EPI_MASK_POS : 0);
   e.res_f32 = res_f32; e.out_f32 = out_f32; e.out_bf16 = out_bf16; e.aux_bf16 = aux; e.ldc = w.K; e.ldr = w.K;
   int bn = 0, ks = 1;
@@ -84,16 +85,18 @@ int Engine::linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cuda
 
 int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv,
                      const bf16* P, bf16* dQ, long long lddq, bf16* dK, long long lddk, bf16* dV, long long lddv, int B,
-                     int Lq, int Lk, cudaStream_t st, float* S, bf16* dS, bool use_aux) {
+                     int Lq, int Lk, cudaStream_t st, float* S, bf16* dS, bool use_aux, uint32_t drop, const bf16* P2) {
   if (!S) S = Sbuf_;
   if (!dS) dS = dSbuf_;
+  const bool dropping = drop && drop_active_;      // O = dropout(P) V: dV sees the dropped weights, dP is masked again
+  ACT_CHECK(!dropping || P2, "attention dropout backward needs the dropped probabilities");
   const int h = cfg_.nheads, hd = 64, Lkp = roundup(Lk, 8);
   const long long ph = 1LL * Lq * Lkp, pb = 1LL * h * Lq * Lkp;
   // dV and dK only feed the projections' gradients: they run on the aux lane beside dP -> softmax backward -> dQ
   cudaStream_t ax = use_aux ? aux_fork(st) : st;
   {  // dV[j,d] = sum_i P[i,j] dO[i,d]
     MatDesc a, b; EpiDesc e;
-    a.ptr = P; a.mn_major = 1; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
+    a.ptr = dropping ? P2 : P; a.mn_major = 1; a.ld = Lkp; a.sz0 = ph; a.sz1 = pb;
     b.ptr = dO; b.mn_major = 1; b.ld = 512; b.sz0 = hd; b.sz1 = 1LL * Lq * 512;
     e.flags = EPI_OUT_BF16; e.out_bf16 = dV; e.ldc = lddv; e.osz0 = hd; e.osz1 = Lk * lddv;
     ++launches_;
@@ -105,8 +108,10 @@ int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K
     b.ptr = V; b.ld = ldv; b.sz0 = hd; b.sz1 = Lk * ldv;
     if (tc_attn_scores_applicable(Lk, Lkp)) {
       ++launches_;
-      if (tc_attn_scores(1, a, b, Lq, Lk, Lkp, h, B, 0.125f, nullptr, P, dS, st)) return -1;
+      const DropDesc dd = dropping ? drop_site(drop) : DropDesc();
+      if (tc_attn_scores(1, a, b, Lq, Lk, Lkp, h, B, 0.125f, nullptr, P, dS, st, dropping ? &dd : nullptr)) return -1;
     } else {
+      ACT_CHECK(!dropping, "attention dropout is implemented in the fused scores kernels only (ACT_FUSED_ATTN=0 is set)");
       e.flags = EPI_OUT_F32; e.out_f32 = S; e.ldc = Lkp; e.osz0 = ph; e.osz1 = pb;
       ++launches_;
       if (tc_gemm(Lq, Lk, hd, h, B, a, b, e, 1, st)) return -1;
@@ -137,24 +142,31 @@ int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K
 // Reverse of enc_layer_fwd.  Input gradient = dx2 (+ dx2b); outputs dx_out (wrt x) and gxp_out (wrt x + pos, i.e. the
 // q/k branch) -- the caller adds them (and reduces gxp_out into learned position embeddings where they exist).
 int Engine::enc_layer_bwd(const EncW& w, EncActs& a, const float* x_in, const float* dx2, const float* dx2b, float* dx_out,
-                          float* gxp_out, int L, int B, cudaStream_t st) {
+                          float* gxp_out, int L, int B, cudaStream_t st, uint32_t site) {
   (void)x_in;
   const int M = B * L, d = cfg_.hidden_dim, ff = cfg_.dim_ff;
+  // train-mode dropout: the gradient handed to a linear layer whose output was dropped is masked again (regenerated
+  // mask); the saved FFN hidden activation already carries its mask (zeros), so its backward only needs the 1/(1-p)
+  const DropDesc d1 = drop_site(site + 1), d3 = drop_site(site + 3);
+  const DropDesc* pd1 = drop_active_ ? &d1 : nullptr;
+  const DropDesc* pd3 = drop_active_ ? &d3 : nullptr;
+  const float hs = drop_active_ ? 1.f / (1.f - drop_p_) : 1.f;
   bf16 *g1 = gy_alloc(1LL * M * d), *ghh = gy_alloc(1LL * M * ff), *g1b = gy_alloc(1LL * M * d);
   bf16 *gqk = gy_alloc(2LL * M * d), *gv = gy_alloc(1LL * M * d);
   if (!g1 || !ghh || !g1b || !gqk || !gv) return -1;
-  RUN(ln_bwd(dx2, dx2b, a.t2, a.mean2, a.rstd2, w.n2.g, gA_, g1, w.n2.gg, w.n2.gb, M, d, st));
+  RUN(ln_bwd(dx2, dx2b, a.t2, a.mean2, a.rstd2, w.n2.g, gA_, g1, w.n2.gg, w.n2.gb, M, d, st, pd3));
   if (linear_dwb(g1, M, w.l2, a.hh, st)) return -1;
-  if (linear_dx(g1, M, w.l2, 0, nullptr, a.hh, nullptr, ghh, st)) return -1;
+  if (linear_dx(g1, M, w.l2, 0, nullptr, a.hh, nullptr, ghh, st, false, hs)) return -1;
   if (linear_dwb(ghh, M, w.l1, a.x1b, st)) return -1;
   float* gBz = splitk_on() ? gz_alloc(1LL * M * d) : gB_;        // zeroed slice: the K = 3200 data gradient runs split-K
   if (!gBz) return -1;
   if (zero_b_pending_) ACT_CUDA(cudaStreamWaitEvent(st, ev_zero_b_, 0));
   if (linear_dx(ghh, M, w.l1, 0, gA_, nullptr, gBz, nullptr, st, true)) return -1;
-  RUN(ln_bwd(gBz, nullptr, a.t1, a.mean1, a.rstd1, w.n1.g, gA_, g1b, w.n1.gg, w.n1.gb, M, d, st));
+  RUN(ln_bwd(gBz, nullptr, a.t1, a.mean1, a.rstd1, w.n1.g, gA_, g1b, w.n1.gg, w.n1.gb, M, d, st, pd1));
   if (linear_dwb(g1b, M, w.sa.o, a.o, st)) return -1;
   if (linear_dx(g1b, M, w.sa.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
-  if (attn_bwd(gb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gqk, 2 * d, gqk + d, 2 * d, gv, d, B, L, L, st)) return -1;
+  if (attn_bwd(gb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gqk, 2 * d, gqk + d, 2 * d, gv, d, B, L, L, st, nullptr, nullptr,
+               true, site + 0, a.P2)) return -1;
   if (linear_dwb(gqk, M, w.sa.qk, a.xpb, st)) return -1;
   if (linear_dwb(gv, M, w.sa.v, a.xb, st)) return -1;
   cudaStream_t ax = aux_fork(st);                    // the two input gradients are independent
@@ -172,7 +184,7 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
   const DecW& w = dec_w_[0];
   DecActs& a = dec_a_;
   RUN(act_loss(a_hat_, in_actions_, in_actions_bs_, in_is_pad_, in_is_pad_bs_, mu_, logvar_, B, nq, A, Z, cfg_.kl_weight,
-               loss_grad, losses_ + 4, d_a_hat_, d_mu_, d_logvar_, st));
+               loss_grad, losses_ + 4, d_a_hat_, d_mu_, d_logvar_, st, loss_gvec_));
   SgemmArgs g;
   // action_head: dW[a,c] += sum_m d_a[m,a] hs[m,c]; db; d_hs = d_a W
   g = SgemmArgs(); g.I = A; g.J = d; g.R = Md; g.A = d_a_hat_; g.ai = act::lin(1); g.ar = act::lin(A);
@@ -193,9 +205,12 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
   bf16 *gv = gy_alloc(1LL * Md * d);
   if (!g3 || !ghh || !g2 || !gq || !gk || !gcv || !g1 || !gqk || !gv) return -1;
   RUN(ln_bwd(d_hs_, nullptr, a.y3, hs_mean_, hs_rstd_, dec_norm_.g, gA_, nullptr, dec_norm_.gg, dec_norm_.gb, Md, d, st));
-  RUN(ln_bwd(gA_, nullptr, a.t3, a.mean3, a.rstd3, w.n3.g, gB_, g3, w.n3.gg, w.n3.gb, Md, d, st));
+  const DropDesc dd1 = drop_site(SITE_DEC + 1), dd3 = drop_site(SITE_DEC + 3), dd5 = drop_site(SITE_DEC + 5);
+  const DropDesc *pdd1 = drop_active_ ? &dd1 : nullptr, *pdd3 = drop_active_ ? &dd3 : nullptr, *pdd5 = drop_active_ ? &dd5 : nullptr;
+  const float hs = drop_active_ ? 1.f / (1.f - drop_p_) : 1.f;
+  RUN(ln_bwd(gA_, nullptr, a.t3, a.mean3, a.rstd3, w.n3.g, gB_, g3, w.n3.gg, w.n3.gb, Md, d, st, pdd3));
   if (linear_dwb(g3, Md, w.l2, a.hh, st)) return -1;
-  if (linear_dx(g3, Md, w.l2, 0, nullptr, a.hh, nullptr, ghh, st)) return -1;
+  if (linear_dx(g3, Md, w.l2, 0, nullptr, a.hh, nullptr, ghh, st, false, hs)) return -1;
   if (linear_dwb(ghh, Md, w.l1, a.y2b, st)) return -1;
   float* gAz = splitk_on() ? gz_alloc(1LL * Md * d) : gA_;
   if (!gAz) return -1;
@@ -203,10 +218,10 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
   if (linear_dx(ghh, Md, w.l1, 0, gB_, nullptr, gAz, nullptr, st, true)) return -1;
   // norm2, cross-attention.  dgB_ (wrt y1) and dgE_ (wrt y1 + query_pos) are private to the decoder: the query
   // self-attention backward below consumes them on lane 1 while this stream goes on with the encoder layers.
-  RUN(ln_bwd(gAz, nullptr, a.t2, a.mean2, a.rstd2, w.n2.g, dgB_, g2, w.n2.gg, w.n2.gb, Md, d, st));
+  RUN(ln_bwd(gAz, nullptr, a.t2, a.mean2, a.rstd2, w.n2.g, dgB_, g2, w.n2.gg, w.n2.gb, Md, d, st, pdd5));
   if (linear_dwb(g2, Md, w.ca.o, a.co, st)) return -1;
   if (linear_dx(g2, Md, w.ca.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
-  if (attn_bwd(gb2_, a.q, d, a.k, d, a.cv, d, a.cP, gq, d, gk, d, gcv, d, B, nq, L_, st)) return -1;
+  if (attn_bwd(gb2_, a.q, d, a.k, d, a.cv, d, a.cP, gq, d, gk, d, gcv, d, B, nq, L_, st, nullptr, nullptr, true, SITE_DEC + 4, a.cP2)) return -1;
   if (linear_dwb(gq, Md, w.ca.q, a.y1pb, st)) return -1;
   if (linear_dx(gq, Md, w.ca.q, 0, nullptr, nullptr, dgE_, nullptr, st)) return -1;          // wrt y1 + query_pos
   if (linear_dwb(gk, Me, w.ca.k, mem_pb_, st)) return -1;
@@ -224,10 +239,11 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
   {   // query self-attention block: a leaf of the backward graph (its only consumers are weight / query_embed gradients)
     cudaStream_t dl = aux_fork(st, 1);
     if (reduce_batch_on(dl, dgE_, 1LL * nq * d, nq * d, g_query)) return -1;
-    RUN(ln_bwd(dgB_, dgE_, a.t1, a.mean1, a.rstd1, w.n1.g, dgA_, g1, w.n1.gg, w.n1.gb, Md, d, dl));
+    RUN(ln_bwd(dgB_, dgE_, a.t1, a.mean1, a.rstd1, w.n1.g, dgA_, g1, w.n1.gg, w.n1.gb, Md, d, dl, pdd1));
     if (linear_dwb(g1, Md, w.sa.o, a.o, dl)) return -1;
     if (linear_dx(g1, Md, w.sa.o, 0, nullptr, nullptr, nullptr, dgb2_, dl)) return -1;
-    if (attn_bwd(dgb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gqk, 2 * d, gqk + d, 2 * d, gv, d, B, nq, nq, dl, Sbuf2_, dSbuf2_, false)) return -1;
+    if (attn_bwd(dgb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gqk, 2 * d, gqk + d, 2 * d, gv, d, B, nq, nq, dl, Sbuf2_, dSbuf2_, false,
+                 SITE_DEC + 0, a.P2)) return -1;
     if (linear_dwb(gqk, Md, w.sa.qk, a.xpb, dl)) return -1;
     if (linear_dwb(gv, Md, w.sa.v, a.xb, dl)) return -1;
     if (linear_dx(gqk, Md, w.sa.qk, 0, nullptr, nullptr, dgE_, nullptr, dl)) return -1;
@@ -244,7 +260,7 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
   const float* dx2 = gMem_;
   const float* dx2b = gMemPos_;
   for (int l = cfg_.enc_layers - 1; l >= 0; --l) {
-    if (enc_layer_bwd(enc_w_[l], enc_a_[l], nullptr, dx2, dx2b, gC_, gD_, L_, B, st)) return -1;
+    if (enc_layer_bwd(enc_w_[l], enc_a_[l], nullptr, dx2, dx2b, gC_, gD_, L_, B, st, SITE_ENC + 8 * l)) return -1;
     if (reduce_batch(gD_, 1LL * L_ * d, 2 * d, g_addpos)) return -1;
     dx2 = gC_; dx2b = gD_;
   }
@@ -307,7 +323,7 @@ int Engine::cvae_bwd(cudaStream_t st) {
     // data-parallel step: collectives run in enqueue order, so the backbone branch (other stream) is enqueued at the
     // point of this branch where its gradients become final -- after dp_bb_slot_ encoder layers
     if (dp_bb_pending_ && nl - 1 - l == dp_bb_slot_ && backbone_bwd_and_step(dp_main_st_)) return -1;
-    if (enc_layer_bwd(cvae_w_[l], cvae_a_[l], nullptr, dx2, dx2b, gC_, gD_, Lc_, B, st)) return -1;
+    if (enc_layer_bwd(cvae_w_[l], cvae_a_[l], nullptr, dx2, dx2b, gC_, gD_, Lc_, B, st, SITE_CVAE + 8 * l)) return -1;
     dx2 = gC_; dx2b = gD_;
     if (inline_opt_step_ > 0 && l < 16 && l >= dp_inline_from_ && cvae_layer_n_[l] > 0) {
       // this layer's gradients are final and nothing below reads its weights: update it under the remaining layers
@@ -449,6 +465,7 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
   ACT_CHECK(!p2p || (peers_.world > 1 && dp_stream_ != nullptr), "peer-memory data-parallel step without connected peers");
   ACT_CHECK(!(p2p && cb), "peer-memory data-parallel step and an all-reduce callback are exclusive");
   if (ensure_streams()) return -1;
+  if (begin_opt_step(step, st)) return -1;                  // first launch of the step: every optimiser lane forks after it
   // the peer-memory step ends with a barrier: every rank has finished reading this rank's gradients and writing its
   // parameters before the caller's stream goes on (next zero_grad / forward)
   auto p2p_finish = [&]() -> int {
@@ -475,7 +492,7 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
       for (int r : {R_MAIN, R_CVAE, R_BACKBONE})
         if (region_n_[r] > 0 && cb(cb_user, region_off_[r], region_n_[r], st)) { set_error("gradient all-reduce callback failed"); return -1; }
     }
-    return adamw(step, st);
+    return adamw(step, st, false);
   }
   struct Guard {                                            // the hook is only live inside this call
     Engine* e;
@@ -502,6 +519,7 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
   if (dp && main_regions()) return -1;
   if (fork_side(st)) return -1;
   auto cvae_branch = [&]() -> int {
+    if (cfg_.no_encoder) return 0;                          // encoder=None: no CVAE branch, region R_CVAE is empty
     inline_opt_step_ = step;
     const int rc = cvae_bwd(side_);
     inline_opt_step_ = 0;
@@ -557,7 +575,7 @@ int Engine::backward(int stage, float loss_grad, cudaStream_t st) {
     if (fork_side(st)) return -1;
     if (concurrent_) sc = side_;
   }
-  if (both || stage == 2) { if (cvae_bwd(sc)) return -1; }
+  if ((both || stage == 2) && !cfg_.no_encoder) { if (cvae_bwd(sc)) return -1; }
   if (both || stage == 3) {
     cgy_off_ = 0;
     for (int k = 0; k < cfg_.num_cameras; ++k)

@@ -38,6 +38,8 @@ int Engine::alloc_workspace() {
 #define A_(T, n) ({ T* _p = alloc<T>(n); if (_p == nullptr) return -1; _p; })
   shadow_ = A_(bf16, total_floats_);
   one_ = A_(float, 8);
+  drop_step_dev_ = reinterpret_cast<uint32_t*>(A_(float, 8));
+  opt_step_dev_ = reinterpret_cast<int*>(A_(float, 8));
   { float one = 1.f; cudaMemcpy(one_, &one, sizeof(float), cudaMemcpyHostToDevice); }
   // packed conv operands + folded BN
   for (int k = 0; k < cfg_.num_cameras; ++k) {
@@ -86,17 +88,19 @@ int Engine::alloc_workspace() {
   auto enc_alloc = [&](EncActs& a, long long M, int L, int Lp) -> int {
     a.xb = A_(bf16, M * d); a.xpb = A_(bf16, M * d); a.qk = A_(bf16, M * 2 * d); a.v = A_(bf16, M * d);
     a.P = A_(bf16, 1LL * Bm * h * L * Lp); a.o = A_(bf16, M * d); a.x1b = A_(bf16, M * d); a.hh = A_(bf16, M * ff);
+    if (cfg_.train) a.P2 = A_(bf16, 1LL * Bm * h * L * Lp);
     a.t1 = A_(float, M * d); a.x1 = A_(float, M * d); a.t2 = A_(float, M * d); a.x2 = A_(float, M * d);
     a.mean1 = A_(float, M); a.rstd1 = A_(float, M); a.mean2 = A_(float, M); a.rstd2 = A_(float, M);
     return 0;
   };
   enc_a_.resize(cfg_.enc_layers); cvae_a_.resize(cfg_.enc_layers);
   for (auto& a : enc_a_) if (enc_alloc(a, Me, L_, Lp_)) return -1;
-  if (cfg_.train) for (auto& a : cvae_a_) if (enc_alloc(a, Mc, Lc_, Lcp_)) return -1;
+  if (cfg_.train && !cfg_.no_encoder) for (auto& a : cvae_a_) if (enc_alloc(a, Mc, Lc_, Lcp_)) return -1;
   {
     DecActs& a = dec_a_;
     a.xb = A_(bf16, Md * d); a.xpb = A_(bf16, Md * d); a.qk = A_(bf16, Md * 2 * d); a.v = A_(bf16, Md * d);
     a.P = A_(bf16, 1LL * Bm * h * nq * nqp_); a.o = A_(bf16, Md * d);
+    if (cfg_.train) { a.P2 = A_(bf16, 1LL * Bm * h * nq * nqp_); a.cP2 = A_(bf16, 1LL * Bm * h * nq * Lp_); }
     a.t1 = A_(float, Md * d); a.y1 = A_(float, Md * d); a.y1pb = A_(bf16, Md * d);
     a.mean1 = A_(float, Md); a.rstd1 = A_(float, Md);
     a.q = A_(bf16, Md * d); a.k = A_(bf16, Me * d); a.cv = A_(bf16, Me * d);
@@ -189,12 +193,13 @@ int Engine::alloc_workspace() {
 
 // --------------------------------------------------------------------------------------------- GEMM helpers
 int Engine::linear(const bf16* X, int M, const LinW& w, uint32_t flags, const float* res_f32, float* out_f32,
-                   bf16* out_bf16, const bf16* aux, cudaStream_t st, bool splitk) {
+                   bf16* out_bf16, const bf16* aux, cudaStream_t st, bool splitk, uint32_t drop) {
   MatDesc A, B;
   A.ptr = X; A.ld = w.K; B.ptr = w.w; B.ld = w.K;
   EpiDesc e;
   e.flags = flags | (w.b ? EPI_BIAS : 0) | (out_f32 ? EPI_OUT_F32 : 0) | (out_bf16 ? EPI_OUT_BF16 : 0) |
             (res_f32 ? EPI_RES_F32 : 0) | (aux ? EPI_MASK_POS : 0);
+  if (drop && drop_active_) { e.flags |= EPI_DROPOUT; e.drop = drop_site(drop); splitk = false; }
   e.bias = w.b; e.res_f32 = res_f32; e.out_f32 = out_f32; e.out_bf16 = out_bf16; e.aux_bf16 = aux;
   e.ldc = w.N; e.ldr = w.N;
   int bn = 0, ks = 1;
@@ -224,8 +229,11 @@ int Engine::zero_forward_outputs(cudaStream_t st, bool with_cvae) {
 
 // softmax(Q K^T / sqrt(64) + mask) V per (batch, head); Q/K/V are strided head views of projection buffers.
 int Engine::attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv,
-                     const uint8_t* mask, bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st, bool v_on_aux, float* S) {
+                     const uint8_t* mask, bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st, bool v_on_aux, float* S,
+                     uint32_t drop, bf16* P2) {
   if (!S) S = Sbuf_;
+  const bool dropping = drop && drop_active_;
+  ACT_CHECK(!dropping || P2, "attention dropout needs the second probability buffer (train workspace)");
   const int h = cfg_.nheads, hd = 64, Lkp = roundup(Lk, 8);
   MatDesc a, b;
   EpiDesc e;
@@ -234,8 +242,10 @@ int Engine::attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk,
   if (tc_attn_scores_applicable(Lk, Lkp)) {
     // scores + mask + softmax in one kernel: the fp32 score tile stays in TMEM (csrc/attn_kernel.cuh)
     ++launches_;
-    if (tc_attn_scores(0, a, b, Lq, Lk, Lkp, h, B, 0.125f, mask, nullptr, P, st)) return -1;
+    const DropDesc dd = dropping ? drop_site(drop) : DropDesc();
+    if (tc_attn_scores(0, a, b, Lq, Lk, Lkp, h, B, 0.125f, mask, nullptr, P, st, dropping ? &dd : nullptr, dropping ? P2 : nullptr)) return -1;
   } else {
+    ACT_CHECK(!dropping, "attention dropout is implemented in the fused scores kernels only (ACT_FUSED_ATTN=0 is set)");
     e.flags = EPI_OUT_F32; e.alpha = 0.125f; e.out_f32 = S;
     e.ldc = Lkp; e.osz0 = 1LL * Lq * Lkp; e.osz1 = 1LL * h * Lq * Lkp;
     ++launches_;
@@ -245,7 +255,7 @@ int Engine::attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk,
   if (v_on_aux && aux_join(st)) return -1;           // V was projected on the aux lane
   MatDesc pa, vb;
   EpiDesc eo;
-  pa.ptr = P; pa.ld = Lkp; pa.sz0 = 1LL * Lq * Lkp; pa.sz1 = 1LL * h * Lq * Lkp;
+  pa.ptr = dropping ? P2 : P; pa.ld = Lkp; pa.sz0 = 1LL * Lq * Lkp; pa.sz1 = 1LL * h * Lq * Lkp;
   vb.ptr = V; vb.mn_major = 1; vb.ld = ldv; vb.sz0 = hd; vb.sz1 = Lk * ldv;
   eo.flags = EPI_OUT_BF16; eo.out_bf16 = O; eo.ldc = 512; eo.osz0 = hd; eo.osz1 = 1LL * Lq * 512;
   ++launches_;
@@ -255,18 +265,18 @@ int Engine::attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk,
 // One post-norm encoder layer (transformer.py:211-224).  a.xb / a.xpb (bf16 x and x+pos) are filled by the caller;
 // the second LayerNorm also emits the next consumer's bf16(x) / bf16(x + next_pos).
 int Engine::enc_layer_fwd(const EncW& w, EncActs& a, const float* x, const float* pos, const float* next_pos, int L,
-                          const uint8_t* mask, int B, bool emit_next, bf16* next_xb, bf16* next_xpb, cudaStream_t st) {
+                          const uint8_t* mask, int B, bool emit_next, bf16* next_xb, bf16* next_xpb, cudaStream_t st, uint32_t site) {
   (void)pos;
   const int M = B * L, d = cfg_.hidden_dim;
   cudaStream_t ax = aux_fork(st);                    // V projection beside QK projection -> QK^T -> softmax
   if (linear(a.xb, M, w.sa.v, 0, nullptr, nullptr, a.v, nullptr, ax)) return -1;
   if (linear(a.xpb, M, w.sa.qk, 0, nullptr, nullptr, a.qk, nullptr, st)) return -1;
-  if (attn_fwd(a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, mask, a.P, a.o, B, L, L, st, ax != st)) return -1;
-  if (linear(a.o, M, w.sa.o, 0, x, a.t1, nullptr, nullptr, st)) return -1;
+  if (attn_fwd(a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, mask, a.P, a.o, B, L, L, st, ax != st, nullptr, site + 0, a.P2)) return -1;
+  if (linear(a.o, M, w.sa.o, 0, x, a.t1, nullptr, nullptr, st, false, site + 1)) return -1;      // x + dropout1(attn)
   RUN(ln_fwd(a.t1, w.n1.g, w.n1.b, nullptr, 1, a.x1, a.x1b, nullptr, a.mean1, a.rstd1, M, d, st));
-  if (linear(a.x1b, M, w.l1, EPI_RELU, nullptr, nullptr, a.hh, nullptr, st)) return -1;
+  if (linear(a.x1b, M, w.l1, EPI_RELU, nullptr, nullptr, a.hh, nullptr, st, false, site + 2)) return -1;   // dropout(relu(.))
   if (zero_f_pending_) ACT_CUDA(cudaStreamWaitEvent(st, ev_zero_f_, 0));      // a.t2 was zeroed for the split-K reduction
-  if (linear(a.hh, M, w.l2, 0, a.x1, a.t2, nullptr, nullptr, st, true)) return -1;
+  if (linear(a.hh, M, w.l2, 0, a.x1, a.t2, nullptr, nullptr, st, true, site + 3)) return -1;     // x + dropout2(ffn)
   RUN(ln_fwd(a.t2, w.n2.g, w.n2.b, next_pos, L, a.x2, emit_next ? next_xb : nullptr, emit_next ? next_xpb : nullptr,
              a.mean2, a.rstd2, M, d, st));
   return 0;
@@ -284,7 +294,7 @@ __global__ void build_cvae_mask_kernel(const uint8_t* __restrict__ is_pad, long 
 // DETRVAE.encode training branch (detr_vae.py:115-151)
 int Engine::cvae_fwd(int B, const float* qpos, const float* actions, long long actions_bs, const uint8_t* is_pad,
                      long long is_pad_bs, const float* eps, cudaStream_t st) {
-  ACT_CHECK(cfg_.train, "this engine was created without the CVAE-encoder workspace (train = 0)");
+  ACT_CHECK(cfg_.train && !cfg_.no_encoder, "this engine was created without the CVAE-encoder workspace (train = 0 or no_encoder)");
   const int d = cfg_.hidden_dim, nq = cfg_.num_queries, S = cfg_.state_dim, A = cfg_.action_dim, Z = cfg_.latent_dim;
   SgemmArgs g;
   // token 0: cls_embed broadcast over the batch
@@ -311,7 +321,7 @@ int Engine::cvae_fwd(int B, const float* qpos, const float* actions, long long a
     const float* x = l == 0 ? tokC_ : cvae_a_[l - 1].x2;
     const bool more = l + 1 < nl;
     if (enc_layer_fwd(cvae_w_[l], cvae_a_[l], x, pos, pos, Lc_, maskC_, B, more, more ? cvae_a_[l + 1].xb : nullptr,
-                      more ? cvae_a_[l + 1].xpb : nullptr, st)) return -1;
+                      more ? cvae_a_[l + 1].xpb : nullptr, st, SITE_CVAE + 8 * l)) return -1;
   }
   // latent_proj on the cls output rows
   g = SgemmArgs(); g.I = B; g.J = 2 * Z; g.R = d; g.A = cvae_a_[nl - 1].x2; g.ai = act::lin(1LL * Lc_ * d); g.ar = act::lin(1);
@@ -349,8 +359,8 @@ int Engine::stem_launch(int cam, int B, ConvLaunch* c, WgradLaunch* w) {
     // the filters shifted by 8*j columns).  The output [B, Ho, Wo, 64] is the same memory as [B, Ho, Wo/g, 64*g].
     // The issuer sustains one M=128 MMA per ~55 ns whatever N <= 128 is and ~75 ns at N = 256 (section 4.1 of DESIGN.md),
     // so wider N is the only way to fill the tensor pipe with a 64-channel output.  ACT_STEM_GROUP=1|2|4 overrides.
-    static int grp_env = -1;
-    if (grp_env < 0) { const char* e = getenv("ACT_STEM_GROUP"); grp_env = e ? atoi(e) : 4; }
+    const char* ge = getenv("ACT_STEM_GROUP");             // read per call: the parity tests switch it between engines
+    const int grp_env = ge ? atoi(ge) : 4;
     int g = grp_env >= 4 ? 4 : grp_env >= 2 ? 2 : 1;
     while (g > 1 && Wo % g) g /= 2;
     c->planes[0] = pl[0]; c->planes[1] = pl[1]; c->nplanes = 2; c->ntaps = 7;
@@ -445,8 +455,8 @@ int Engine::dec_self_fwd(int B, cudaStream_t st) {
   RUN(add_pos_cast(tgt0_, qpos_embed, nq, a.xb, a.xpb, Md, d, st));            // tgt = 0 (transformer.py:109)
   if (linear(a.xpb, Md, w.sa.qk, 0, nullptr, nullptr, a.qk, nullptr, st)) return -1;
   if (linear(a.xb, Md, w.sa.v, 0, nullptr, nullptr, a.v, nullptr, st)) return -1;
-  if (attn_fwd(a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, nullptr, a.P, a.o, B, nq, nq, st, false, Sbuf2_)) return -1;
-  if (linear(a.o, Md, w.sa.o, 0, tgt0_, a.t1, nullptr, nullptr, st)) return -1;
+  if (attn_fwd(a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, nullptr, a.P, a.o, B, nq, nq, st, false, Sbuf2_, SITE_DEC + 0, a.P2)) return -1;
+  if (linear(a.o, Md, w.sa.o, 0, tgt0_, a.t1, nullptr, nullptr, st, false, SITE_DEC + 1)) return -1;
   RUN(ln_fwd(a.t1, w.n1.g, w.n1.b, qpos_embed, nq, a.y1, nullptr, a.y1pb, a.mean1, a.rstd1, Md, d, st));
   if (linear(a.y1pb, Md, w.ca.q, 0, nullptr, nullptr, a.q, nullptr, st)) return -1;
   return 0;
@@ -458,18 +468,56 @@ int Engine::dec_cross_fwd(int B, cudaStream_t st) {
   cudaStream_t ax = aux_fork(st);
   if (linear(mem_b_, Me, w.ca.v, 0, nullptr, nullptr, a.cv, nullptr, ax)) return -1;
   if (linear(mem_pb_, Me, w.ca.k, 0, nullptr, nullptr, a.k, nullptr, st)) return -1;
-  if (attn_fwd(a.q, d, a.k, d, a.cv, d, nullptr, a.cP, a.co, B, nq, L_, st, ax != st)) return -1;
-  if (linear(a.co, Md, w.ca.o, 0, a.y1, a.t2, nullptr, nullptr, st)) return -1;
+  if (attn_fwd(a.q, d, a.k, d, a.cv, d, nullptr, a.cP, a.co, B, nq, L_, st, ax != st, nullptr, SITE_DEC + 4, a.cP2)) return -1;
+  if (linear(a.co, Md, w.ca.o, 0, a.y1, a.t2, nullptr, nullptr, st, false, SITE_DEC + 5)) return -1;
   RUN(ln_fwd(a.t2, w.n2.g, w.n2.b, nullptr, 1, a.y2, a.y2b, nullptr, a.mean2, a.rstd2, Md, d, st));
-  if (linear(a.y2b, Md, w.l1, EPI_RELU, nullptr, nullptr, a.hh, nullptr, st)) return -1;
+  if (linear(a.y2b, Md, w.l1, EPI_RELU, nullptr, nullptr, a.hh, nullptr, st, false, SITE_DEC + 2)) return -1;
   if (zero_f_pending_) ACT_CUDA(cudaStreamWaitEvent(st, ev_zero_f_, 0));
-  if (linear(a.hh, Md, w.l2, 0, a.y2, a.t3, nullptr, nullptr, st, true)) return -1;
+  if (linear(a.hh, Md, w.l2, 0, a.y2, a.t3, nullptr, nullptr, st, true, SITE_DEC + 3)) return -1;
   RUN(ln_fwd(a.t3, w.n3.g, w.n3.b, nullptr, 1, a.y3, nullptr, nullptr, a.mean3, a.rstd3, Md, d, st));
   RUN(ln_fwd(a.y3, dec_norm_.g, dec_norm_.b, nullptr, 1, hs_, nullptr, nullptr, hs_mean_, hs_rstd_, Md, d, st));
   return 0;
 }
 
-// ACTPolicy.__call__ (policy.py:264-332) minus the Python glue: normalise (fused into conv1's im2col), DETRVAE.forward
+int Engine::set_dropout(float p, unsigned long long seed) {
+  ACT_CHECK(p >= 0.f && p < 1.f, "dropout probability must be in [0, 1)");
+  drop_p_ = p; drop_seed_ = seed;
+  return 0;
+}
+int Engine::dropout_state(float* p, unsigned long long* seed, uint32_t* step) {
+  if (p) *p = drop_p_;
+  if (seed) *seed = drop_seed_;
+  if (step) ACT_CUDA(cudaMemcpy(step, drop_step_dev_, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  return 0;
+}
+DropDesc Engine::drop_site(uint32_t site) const {
+  DropDesc d;
+  if (!drop_active_) return d;
+  d.seed_lo = static_cast<uint32_t>(drop_seed_); d.seed_hi = static_cast<uint32_t>(drop_seed_ >> 32);
+  d.site = site; d.thresh = dropout_threshold(drop_p_); d.scale = 1.f / (1.f - drop_p_); d.step = drop_step_dev_;
+  return d;
+}
+
+// Parity diagnostics (act_engine_debug_buffer): internal activations of the last forward.
+int Engine::debug_buffer(const char* name, void** ptr, long long* numel, int* dtype) {
+  ACT_CHECK(name && ptr && numel && dtype, "debug_buffer: null argument");
+  ACT_CHECK(cur_B_ > 0, "debug_buffer: no forward has run");
+  const std::string n(name);
+  const long long d = cfg_.hidden_dim;
+  if (n == "src") { *ptr = src_; *numel = 1LL * cur_B_ * L_ * d; *dtype = 0; return 0; }
+  if (n == "memory") { *ptr = enc_a_[cfg_.enc_layers - 1].x2; *numel = 1LL * cur_B_ * L_ * d; *dtype = 0; return 0; }
+  if (n == "hs") { *ptr = hs_; *numel = 1LL * cur_B_ * cfg_.num_queries * d; *dtype = 0; return 0; }
+  if (n.compare(0, 4, "feat") == 0) {
+    const int k = atoi(n.c_str() + 4);
+    ACT_CHECK(k >= 0 && k < cfg_.num_cameras, "debug_buffer: camera index out of range");
+    *ptr = cam_a_[k].blk[7].y; *numel = 1LL * cur_B_ * Hf_ * Wf_ * 512; *dtype = 1;
+    return 0;
+  }
+  set_error("debug_buffer: unknown buffer " + n);
+  return -1;
+}
+
+// ACTPolicy.__call__ (policy.py:264-332) minus the Python glue: normalise (fused into the stem's image pack), DETRVAE.forward
 // (detr_vae.py:163-254), and for the training/validation call the L1 + KL loss (policy.py:309-318).
 int Engine::forward(int B, const float* qpos, const float* image, const float* actions, long long actions_bs,
                     const uint8_t* is_pad, long long is_pad_bs, const float* eps, float* a_hat, float* is_pad_hat,
@@ -479,13 +527,23 @@ int Engine::forward(int B, const float* qpos, const float* image, const float* a
   ACT_CHECK(qpos && image, "qpos / image must not be null");
   const int d = cfg_.hidden_dim, nq = cfg_.num_queries, S = cfg_.state_dim, A = cfg_.action_dim, Z = cfg_.latent_dim;
   cur_B_ = B; have_actions_ = actions != nullptr;
+  // dropout applies to training calls of a train-mode policy (the reference's validation runs under .eval())
+  drop_active_ = have_actions_ && cfg_.train && drop_p_ > 0.f;
+  if (drop_active_) RUN(bump_counter(drop_step_dev_, st));
   in_qpos_ = qpos; in_image_ = image; in_actions_ = actions; in_actions_bs_ = actions_bs; in_is_pad_ = is_pad; in_is_pad_bs_ = is_pad_bs;
   ACT_CUDA(cudaMemcpyAsync(pos_main_, P("additional_pos_embed.weight"), sizeof(float) * 2 * d, cudaMemcpyDeviceToDevice, st));
-  if (ensure_streams() || zero_forward_outputs(st, have_actions_)) return -1;
+  if (ensure_streams() || zero_forward_outputs(st, have_actions_ && !cfg_.no_encoder)) return -1;
   // The CVAE encoder (-> z -> latent token) and the camera backbones (-> image tokens) are independent until the main
   // encoder reads src_: the CVAE branch runs on the side stream so its small launches fill the SMs the convs leave idle.
   cudaStream_t sc = st;
-  if (have_actions_) {
+  if (have_actions_ && cfg_.no_encoder) {
+    // encoder=None (detr_vae.py:109-112): latent_sample = 0 also in the training call; mu = logvar = None upstream and
+    // kl = 0 (policy.py:306-307) -- zero mu / logvar give exactly that in the loss kernel (and zero KL gradients)
+    ACT_CHECK(is_pad != nullptr, "training call needs is_pad");
+    ACT_CUDA(cudaMemsetAsync(z_, 0, sizeof(float) * B * Z, st));
+    ACT_CUDA(cudaMemsetAsync(mu_, 0, sizeof(float) * B * Z, st));
+    ACT_CUDA(cudaMemsetAsync(logvar_, 0, sizeof(float) * B * Z, st));
+  } else if (have_actions_) {
     ACT_CHECK(is_pad && eps, "training call needs is_pad and eps");
     if (fork_side(st)) return -1;
     if (concurrent_) sc = side_;
@@ -516,7 +574,7 @@ int Engine::forward(int B, const float* qpos, const float* image, const float* a
     const float* x = l == 0 ? src_ : enc_a_[l - 1].x2;
     const bool more = l + 1 < nl;
     if (enc_layer_fwd(enc_w_[l], enc_a_[l], x, pos_main_, pos_main_, L_, nullptr, B, true, more ? enc_a_[l + 1].xb : mem_b_,
-                      more ? enc_a_[l + 1].xpb : mem_pb_, st)) return -1;
+                      more ? enc_a_[l + 1].xpb : mem_pb_, st, SITE_ENC + 8 * l)) return -1;
   }
   if (dl == st) { if (dec_self_fwd(B, st)) return -1; }
   else if (aux_join(st, 1)) return -1;

@@ -225,7 +225,11 @@ void Engine::build_tensor_table() {
   for (int i = 0; i < cfg_.dec_layers; ++i)
     dec_layer("transformer.decoder.layers." + std::to_string(i) + ".", i == 0 ? T_PARAM : T_PARAM_DEAD, i == 0 ? R_MAIN : R_DEAD);
   add("transformer.decoder.norm.weight", {d}, T_PARAM, R_MAIN); add("transformer.decoder.norm.bias", {d}, T_PARAM, R_MAIN);
-  for (int i = 0; i < cfg_.enc_layers; ++i) enc_layer("encoder.layers." + std::to_string(i) + ".", T_PARAM, R_CVAE);
+  // encoder=None (detr_vae.py:373-377): no CVAE-encoder stack; its token / latent projections still exist in the
+  // state_dict but never take part in a forward, so autograd leaves their .grad None and AdamW skips them
+  const bool cvae = cfg_.no_encoder == 0;
+  const int ck = cvae ? T_PARAM : T_PARAM_NOGRAD, cr = cvae ? R_CVAE : R_NOGRAD;
+  if (cvae) for (int i = 0; i < cfg_.enc_layers; ++i) enc_layer("encoder.layers." + std::to_string(i) + ".", T_PARAM, R_CVAE);
   add("action_head.weight", {A, d}, T_PARAM, R_MAIN); add("action_head.bias", {A}, T_PARAM, R_MAIN);
   add("is_pad_head.weight", {1, d}, T_PARAM_NOGRAD, R_NOGRAD); add("is_pad_head.bias", {1}, T_PARAM_NOGRAD, R_NOGRAD);
   add("query_embed.weight", {nq, d}, T_PARAM, R_MAIN);
@@ -246,10 +250,10 @@ void Engine::build_tensor_table() {
       }
   }
   add("input_proj_robot_state.weight", {d, S}, T_PARAM, R_MAIN); add("input_proj_robot_state.bias", {d}, T_PARAM, R_MAIN);
-  add("cls_embed.weight", {1, d}, T_PARAM, R_CVAE);
-  add("encoder_action_proj.weight", {d, A}, T_PARAM, R_CVAE); add("encoder_action_proj.bias", {d}, T_PARAM, R_CVAE);
-  add("encoder_joint_proj.weight", {d, S}, T_PARAM, R_CVAE); add("encoder_joint_proj.bias", {d}, T_PARAM, R_CVAE);
-  add("latent_proj.weight", {2 * Z, d}, T_PARAM, R_CVAE); add("latent_proj.bias", {2 * Z}, T_PARAM, R_CVAE);
+  add("cls_embed.weight", {1, d}, ck, cr);
+  add("encoder_action_proj.weight", {d, A}, ck, cr); add("encoder_action_proj.bias", {d}, ck, cr);
+  add("encoder_joint_proj.weight", {d, S}, ck, cr); add("encoder_joint_proj.bias", {d}, ck, cr);
+  add("latent_proj.weight", {2 * Z, d}, ck, cr); add("latent_proj.bias", {2 * Z}, ck, cr);
   add("latent_out_proj.weight", {d, Z}, T_PARAM, R_MAIN); add("latent_out_proj.bias", {d}, T_PARAM, R_MAIN);
   add("additional_pos_embed.weight", {2, d}, T_PARAM, R_MAIN);
 
@@ -264,7 +268,7 @@ void Engine::build_tensor_table() {
     region_n_[r] = off - region_off_[r];
   }
   total_floats_ = off;
-  for (int l = 0; l < cfg_.enc_layers && l < 16; ++l) {     // contiguous span of CVAE-encoder layer l inside R_CVAE
+  for (int l = 0; cvae && l < cfg_.enc_layers && l < 16; ++l) {     // contiguous span of CVAE-encoder layer l inside R_CVAE
     const std::string pre = "encoder.layers." + std::to_string(l) + ".";
     long long lo = -1, hi = -1;
     for (auto& t : tensors_)
@@ -317,7 +321,7 @@ void Engine::setup_views() {
   };
   enc_w_.clear(); cvae_w_.clear(); dec_w_.clear();
   for (int i = 0; i < cfg_.enc_layers; ++i) enc_w_.push_back(enc("transformer.encoder.layers." + std::to_string(i) + "."));
-  for (int i = 0; i < cfg_.enc_layers; ++i) cvae_w_.push_back(enc("encoder.layers." + std::to_string(i) + "."));
+  if (!cfg_.no_encoder) for (int i = 0; i < cfg_.enc_layers; ++i) cvae_w_.push_back(enc("encoder.layers." + std::to_string(i) + "."));
   for (int i = 0; i < cfg_.dec_layers; ++i) {
     const std::string p = "transformer.decoder.layers." + std::to_string(i) + ".";
     DecW w;
@@ -429,10 +433,17 @@ int Engine::zero_grad(cudaStream_t st, bool async) {
   return 0;
 }
 
+int Engine::begin_opt_step(int step, cudaStream_t st) {
+  ACT_CHECK(step >= 0, "optimizer step must be >= 0 (0 = advance the device counter)");
+  ++launches_;
+  return set_counter(opt_step_dev_, step, step == 0, st);
+}
+
 int Engine::adamw_range(long long off, long long n, float lr, bool shadow, int step, cudaStream_t st, int blocks_per_sm) {
   ACT_CHECK(params_ && grads_ && m_ && v_, "optimizer state not bound");
   if (n <= 0) return 0;
   AdamWArgs a;
+  a.step_dev = opt_step_dev_; a.abort_flag = dp_status_;
   a.p = params_ + off; a.g = grads_ + off; a.m = m_ + off; a.v = v_ + off; a.shadow = shadow ? shadow_ + off : nullptr;
   a.n = n; a.lr = lr; a.beta1 = cfg_.beta1; a.beta2 = cfg_.beta2; a.eps = cfg_.adam_eps; a.wd = cfg_.weight_decay;
   a.step = step; a.mode = 0; a.background = blocks_per_sm;
@@ -443,8 +454,9 @@ int Engine::adamw_range(long long off, long long n, float lr, bool shadow, int s
 int Engine::adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm) {
   ACT_CHECK(params_ && grads_ && m_ && v_, "optimizer state not bound");
   AdamWArgs a;
+  a.step_dev = opt_step_dev_; a.abort_flag = dp_status_;
   const long long o = region_off_[r];
-  const bool shadow = r == R_MAIN || r == R_CVAE || (r == R_DEAD && cfg_.faithful_decoder != 0);
+  const bool shadow = r == R_MAIN || r == R_CVAE;
   a.p = params_ + o; a.g = grads_ + o; a.m = m_ + o; a.v = v_ + o; a.shadow = shadow ? shadow_ + o : nullptr;
   a.n = region_n_[r]; a.lr = r == R_BACKBONE ? cfg_.lr_backbone : cfg_.lr; a.beta1 = cfg_.beta1; a.beta2 = cfg_.beta2;
   a.eps = cfg_.adam_eps; a.wd = cfg_.weight_decay; a.step = step; a.mode = r == R_DEAD ? 1 : 0;
@@ -627,8 +639,9 @@ int Engine::dp_status() {
   return static_cast<int>(s);
 }
 
-int Engine::adamw(int step, cudaStream_t st) {
+int Engine::adamw(int step, cudaStream_t st, bool begin) {
   if (wg_join(st)) return -1;
+  if (begin && begin_opt_step(step, st)) return -1;
   const int order[4] = {R_MAIN, R_CVAE, R_BACKBONE, R_DEAD};
   for (int r : order)
     if (adamw_region(r, step, st)) return -1;

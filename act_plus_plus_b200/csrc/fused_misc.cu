@@ -1,5 +1,5 @@
 // Small fused kernels of the ACT path: strided fp32 mini-GEMM (the K<=32 / N<=64 projections and their gradients),
-// L1+KL loss with its gradients, reparametrisation, max-pool fwd/bwd, conv1 im2col with fused ImageNet normalise.
+// L1+KL loss with its gradients, reparametrisation, max-pool fwd/bwd.
 #include "kernels.h"
 
 namespace act {
@@ -138,7 +138,11 @@ __global__ void act_loss_kernel(const float* __restrict__ a_hat, const float* __
                                 const uint8_t* __restrict__ is_pad, long long pad_bs, const float* __restrict__ mu,
                                 const float* __restrict__ logvar, int B, int nq, int A, int Z, float kl_weight,
                                 float gscale, float* __restrict__ losses, float* __restrict__ d_a_hat,
-                                float* __restrict__ d_mu, float* __restrict__ d_logvar) {
+                                float* __restrict__ d_mu, float* __restrict__ d_logvar, const float* __restrict__ gvec) {
+  // gvec (device, optional) = the incoming gradient of the three returned scalars {l1, kl, loss}: any of them may be the
+  // root of loss.backward() (policy.py:316-318 returns all three); loss = l1 + kl_weight * kl
+  const float gl = gvec ? gvec[0] + gvec[2] : gscale;
+  const float gk = gvec ? gvec[1] + kl_weight * gvec[2] : gscale * kl_weight;
   __shared__ float red[32];
   __shared__ float tot[2];
   const int tid = threadIdx.x, nthr = blockDim.x;
@@ -152,14 +156,14 @@ __global__ void act_loss_kernel(const float* __restrict__ a_hat, const float* __
     const float diff = a_hat[i] - actions[b * act_bs + static_cast<long long>(q) * A + a];
     const bool pad = is_pad[b * pad_bs + q] != 0;
     if (!pad) s += fabsf(diff);
-    if (d_a_hat) d_a_hat[i] = pad ? 0.f : gscale * inv_n * ((diff > 0.f) ? 1.f : (diff < 0.f ? -1.f : 0.f));
+    if (d_a_hat) d_a_hat[i] = pad ? 0.f : gl * inv_n * ((diff > 0.f) ? 1.f : (diff < 0.f ? -1.f : 0.f));
   }
   float k = 0.f;
   for (int i = tid; i < B * Z; i += nthr) {
     const float m = mu[i], lv = logvar[i], e = __expf(lv);
     k += -0.5f * (1.f + lv - m * m - e);
-    if (d_mu) d_mu[i] = gscale * kl_weight * m / B;
-    if (d_logvar) d_logvar[i] = gscale * kl_weight * 0.5f * (e - 1.f) / B;
+    if (d_mu) d_mu[i] = gk * m / B;
+    if (d_logvar) d_logvar[i] = gk * 0.5f * (e - 1.f) / B;
   }
   for (int pass = 0; pass < 2; ++pass) {
     float v = pass == 0 ? s : k;
@@ -182,9 +186,9 @@ __global__ void act_loss_kernel(const float* __restrict__ a_hat, const float* __
 }
 int act_loss(const float* a_hat, const float* actions, long long act_bs, const uint8_t* is_pad, long long pad_bs,
              const float* mu, const float* logvar, int B, int nq, int A, int Z, float kl_weight, float gscale,
-             float* losses, float* d_a_hat, float* d_mu, float* d_logvar, cudaStream_t st) {
+             float* losses, float* d_a_hat, float* d_mu, float* d_logvar, cudaStream_t st, const float* gvec) {
   act_loss_kernel<<<1, 1024, 0, st>>>(a_hat, actions, act_bs, is_pad, pad_bs, mu, logvar, B, nq, A, Z, kl_weight, gscale,
-                                      losses, d_a_hat, d_mu, d_logvar);
+                                      losses, d_a_hat, d_mu, d_logvar, gvec);
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -446,47 +450,36 @@ int stem_pack_image(const float* img_cam, long long img_bs, bf16* out, int B, in
   return 0;
 }
 
-// ------------------------------------------------------------------------------------------ conv1 im2col
-// image fp32 [B, K, 3, H, W] (values in [0,1]) of camera `cam` -> A [B*Ho*Wo, KP] bf16 with column (c*7+kh)*7+kw,
-// ImageNet normalisation (policy.py:268-272) fused, zero padding applied in normalised space, columns >= 147 zero.
-__global__ void im2col_conv1_kernel(const float* __restrict__ img, long long img_bs, bf16* __restrict__ out, int B, int H,
-                                    int W, int Ho, int Wo, int KP) {
-  const float mean[3] = {0.485f, 0.456f, 0.406f};
-  const float istd[3] = {1.f / 0.229f, 1.f / 0.224f, 1.f / 0.225f};
-  const int G = KP / 8;
-  const long long total = 1LL * B * Ho * Wo * G;
-  for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
-    const int g = static_cast<int>(i % G);
-    long long r = i / G;
-    const int ox = static_cast<int>(r % Wo); r /= Wo;
-    const int oy = static_cast<int>(r % Ho);
-    const int b = static_cast<int>(r / Ho);
-    float v[8];
+
+
+// ------------------------------------------------------------------------------------------ dropout utilities
+__global__ void dropout_mask_kernel(DropDesc d, uint32_t step, long long n8, long long n, uint8_t* __restrict__ out) {
+  for (long long g = blockIdx.x * 1LL * blockDim.x + threadIdx.x; g < n8; g += gridDim.x * 1LL * blockDim.x) {
+    const uint32_t m = drop_keep8(d, static_cast<unsigned long long>(g), step);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int k = g * 8 + e;
-      float val = 0.f;
-      if (k < 147) {
-        const int c = k / 49, kh = (k % 49) / 7, kw = k % 7;
-        const int iy = 2 * oy + kh - 3, ix = 2 * ox + kw - 3;
-        if (iy >= 0 && iy < H && ix >= 0 && ix < W)
-          val = (__ldg(img + b * img_bs + (1LL * c * H + iy) * W + ix) - mean[c]) * istd[c];
-      }
-      v[e] = val;
-    }
-    uint4 o;
-    __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
-#pragma unroll
-    for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
-    *reinterpret_cast<uint4*>(out + (i / G) * KP + g * 8) = o;
+    for (int i = 0; i < 8; ++i)
+      if (8 * g + i < n) out[8 * g + i] = (m >> i) & 1u;
   }
 }
-int im2col_conv1(const float* img_cam, long long img_bs, bf16* out, int B, int H, int W, int KP, cudaStream_t st) {
-  ACT_CHECK(KP % 8 == 0 && KP >= 152, "conv1 im2col width must be a multiple of 8 >= 152");
-  const int Ho = (H + 6 - 7) / 2 + 1, Wo = (W + 6 - 7) / 2 + 1;
-  const long long total = 1LL * B * Ho * Wo * (KP / 8);
-  const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 32));
-  im2col_conv1_kernel<<<blocks, 256, 0, st>>>(img_cam, img_bs, out, B, H, W, Ho, Wo, KP);
+uint32_t dropout_threshold(float p) {
+  const double keep = 1.0 - static_cast<double>(p);
+  long long t = static_cast<long long>(keep * 65536.0 + 0.5);
+  return static_cast<uint32_t>(std::min<long long>(std::max<long long>(t, 0), 0x10000));
+}
+int dropout_mask(unsigned long long seed, uint32_t site, uint32_t step, float p, long long n, uint8_t* out, cudaStream_t st) {
+  ACT_CHECK(p >= 0.f && p < 1.f && n >= 0 && out != nullptr, "dropout_mask: bad arguments");
+  if (n == 0) return 0;
+  DropDesc d;
+  d.seed_lo = static_cast<uint32_t>(seed); d.seed_hi = static_cast<uint32_t>(seed >> 32); d.site = site;
+  d.thresh = dropout_threshold(p); d.scale = 1.f / (1.f - p);
+  const long long n8 = (n + 7) / 8;
+  dropout_mask_kernel<<<static_cast<int>(std::min<long long>((n8 + 255) / 256, 148 * 8)), 256, 0, st>>>(d, step, n8, n, out);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+__global__ void bump_counter_kernel(uint32_t* c) { *c += 1u; }
+int bump_counter(uint32_t* counter, cudaStream_t st) {
+  bump_counter_kernel<<<1, 1, 0, st>>>(counter);
   ACT_CUDA(cudaGetLastError());
   return 0;
 }

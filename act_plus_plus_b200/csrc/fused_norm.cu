@@ -91,11 +91,16 @@ template <int V>
 __global__ void ln_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ dy2, const float* __restrict__ t,
                               const float* __restrict__ mean, const float* __restrict__ rstd,
                               const float* __restrict__ gamma, float* __restrict__ dt, bf16* __restrict__ dtb,
-                              float* __restrict__ dgamma, float* __restrict__ dbeta, int M, int rows_per_block) {
+                              float* __restrict__ dgamma, float* __restrict__ dbeta, int M, int rows_per_block,
+                              const DropDesc drop) {
   pdl_trigger(); pdl_wait();
   constexpr int D = 128 * V;
   constexpr int WARPS = 4;
   __shared__ float red[2][WARPS][D];
+  // train-mode dropout: t = x + dropout(h), so the bf16 copy (= the gradient handed to the producing linear layer) is
+  // mask * dt / (1 - p) while the fp32 copy (the residual path) stays dt; the mask is regenerated, never stored
+  const bool dropping = drop_on(drop);
+  const uint32_t dstep = dropping ? __ldg(drop.step) : 0u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float4 ag[V], ab[V];
 #pragma unroll
@@ -134,7 +139,15 @@ __global__ void ln_bwd_kernel(const float* __restrict__ dy, const float* __restr
       o.x = rs * (g[j].x - s1 - xh[j].x * s2); o.y = rs * (g[j].y - s1 - xh[j].y * s2);
       o.z = rs * (g[j].z - s1 - xh[j].z * s2); o.w = rs * (g[j].w - s1 - xh[j].w * s2);
       if (dt) *reinterpret_cast<float4*>(dt + base + 4 * c) = o;
-      if (dtb) *reinterpret_cast<uint2*>(dtb + base + 4 * c) = pack4_bf16(o.x, o.y, o.z, o.w);
+      if (dtb) {
+        if (dropping) {
+          const unsigned long long e = static_cast<unsigned long long>(base) + 4 * c;
+          const uint32_t m = drop_keep8(drop, e >> 3, dstep) >> (e & 7);
+          o.x = (m & 1u) ? o.x * drop.scale : 0.f; o.y = (m & 2u) ? o.y * drop.scale : 0.f;
+          o.z = (m & 4u) ? o.z * drop.scale : 0.f; o.w = (m & 8u) ? o.w * drop.scale : 0.f;
+        }
+        *reinterpret_cast<uint2*>(dtb + base + 4 * c) = pack4_bf16(o.x, o.y, o.z, o.w);
+      }
     }
   }
   if (dgamma == nullptr) return;
@@ -155,14 +168,15 @@ __global__ void ln_bwd_kernel(const float* __restrict__ dy, const float* __restr
 }
 
 int ln_bwd(const float* dy, const float* dy2, const float* t, const float* mean, const float* rstd, const float* gamma,
-           float* dt, bf16* dtb, float* dgamma, float* dbeta, int M, int D, cudaStream_t st) {
+           float* dt, bf16* dtb, float* dgamma, float* dbeta, int M, int D, cudaStream_t st, const DropDesc* dropp) {
+  const DropDesc drop = dropp ? *dropp : DropDesc();
   ACT_CHECK(D == 512 || D == 256, "LayerNorm width must be 256 or 512");
   if (M <= 0) return 0;
   int rpb = 16;
   while (rpb > 4 && (M + rpb - 1) / rpb < 148 * 2) rpb >>= 1;
   dim3 grid((M + rpb - 1) / rpb), block(128);
-  if (D == 512) ACT_CUDA(launch_pdl(ln_bwd_kernel<4>, dim3(grid), dim3(block), 0, st, dy, dy2, t, mean, rstd, gamma, dt, dtb, dgamma, dbeta, M, rpb));
-  else ACT_CUDA(launch_pdl(ln_bwd_kernel<2>, dim3(grid), dim3(block), 0, st, dy, dy2, t, mean, rstd, gamma, dt, dtb, dgamma, dbeta, M, rpb));
+  if (D == 512) ACT_CUDA(launch_pdl(ln_bwd_kernel<4>, dim3(grid), dim3(block), 0, st, dy, dy2, t, mean, rstd, gamma, dt, dtb, dgamma, dbeta, M, rpb, drop));
+  else ACT_CUDA(launch_pdl(ln_bwd_kernel<2>, dim3(grid), dim3(block), 0, st, dy, dy2, t, mean, rstd, gamma, dt, dtb, dgamma, dbeta, M, rpb, drop));
   ACT_CUDA(cudaGetLastError());
   return 0;
 }

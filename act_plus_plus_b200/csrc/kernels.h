@@ -22,7 +22,11 @@ int pack_conv1_weights(const float* w, bf16* wpk, int KP, cudaStream_t st);     
 int ln_fwd(const float* t, const float* gamma, const float* beta, const float* pos, int L, float* y, bf16* yb, bf16* ypb,
            float* mean, float* rstd, int M, int D, cudaStream_t st);
 int ln_bwd(const float* dy, const float* dy2, const float* t, const float* mean, const float* rstd, const float* gamma,
-           float* dt, bf16* dtb, float* dgamma, float* dbeta, int M, int D, cudaStream_t st);
+           float* dt, bf16* dtb, float* dgamma, float* dbeta, int M, int D, cudaStream_t st, const DropDesc* drop = nullptr);
+// uint8 keep mask (1 = kept) of elements [0, n) of dropout stream (seed, site, step): what the fused kernels regenerate
+int dropout_mask(unsigned long long seed, uint32_t site, uint32_t step, float p, long long n, uint8_t* out, cudaStream_t st);
+int bump_counter(uint32_t* counter, cudaStream_t st);
+uint32_t dropout_threshold(float p);        // keep iff 16-bit lane < threshold = round((1 - p) * 65536)
 int add_pos_cast(const float* x, const float* pos, int L, bf16* xb, bf16* xpb, int M, int D, cudaStream_t st);
 int softmax_fwd(const float* S, const uint8_t* mask, bf16* P, int R, int L, int Lp, int rows_per_batch, cudaStream_t st);
 int softmax_bwd(const bf16* P, const float* dP, bf16* dS, int R, int L, int Lp, float scale, cudaStream_t st);
@@ -47,7 +51,7 @@ struct SgemmArgs {         // C(i,j) (+)= alpha * sum_r A(i,r) * B(r,j) (+ bias[
 int sgemm_generic(const SgemmArgs& a, cudaStream_t st);
 int act_loss(const float* a_hat, const float* actions, long long act_bs, const uint8_t* is_pad, long long pad_bs,
              const float* mu, const float* logvar, int B, int nq, int A, int Z, float kl_weight, float gscale,
-             float* losses, float* d_a_hat, float* d_mu, float* d_logvar, cudaStream_t st);
+             float* losses, float* d_a_hat, float* d_mu, float* d_logvar, cudaStream_t st, const float* gvec = nullptr);
 int reparam_fwd(const float* info, const float* eps, float* mu, float* logvar, float* z, int B, int Z, cudaStream_t st);
 int reparam_bwd(const float* dz, const float* eps, const float* logvar, const float* d_mu_kl, const float* d_lv_kl,
                 float* d_info, int B, int Z, cudaStream_t st);
@@ -56,7 +60,6 @@ int maxpool_bwd(const bf16* dy, const uint8_t* idx, const bf16* x, bf16* dx, int
 // image fp32 [B,3,H,W] (batch stride img_bs) -> ImageNet-normalised NHWC4 bf16 [B][H][Wp][4], 3 zero pixels left pad
 int stem_pack_image(const float* img_cam, long long img_bs, bf16* out, int B, int H, int W, int Wp, cudaStream_t st);
 int stem_pack_image_u8(const uint8_t* img_cam, long long img_bs, bf16* out, int B, int H, int W, int Wp, cudaStream_t st);
-int im2col_conv1(const float* img_cam, long long img_bs, bf16* out, int B, int H, int W, int KP, cudaStream_t st);
 
 // ---- optim.cu
 struct AdamWArgs {
@@ -64,10 +67,26 @@ struct AdamWArgs {
   long long n;
   float lr, beta1, beta2, eps, wd;
   int step;          // 1-based
+  const int* step_dev = nullptr;   // when set, the kernels read the step from this device counter instead (bias corrections
+                                   // computed on the device): a captured CUDA graph then advances with every replay
+  const uint32_t* abort_flag = nullptr;   // data-parallel kernels: non-zero = an earlier barrier failed, do nothing
   int mode;          // 0 = full AdamW, 1 = weight decay only (gradient identically zero)
   int background = 0;   // n > 0: launch n blocks per SM (n x 256 threads) so concurrently running tensor-core CTAs still find a slot
 };
 int adamw_step(const AdamWArgs& a, cudaStream_t st);
+int set_counter(int* counter, int value, bool increment, cudaStream_t st);      // counter = value, or counter += 1
+// bias corrections of torch.optim.AdamW for step t: bc1 = 1 - b1^t, rs = 1 / sqrt(1 - b2^t); block-uniform
+__device__ __forceinline__ void adam_bias(const AdamWArgs& a, float bc1_host, float rs_host, float* bc1, float* rs) {
+  if (a.step_dev == nullptr) { *bc1 = bc1_host; *rs = rs_host; return; }
+  __shared__ float s_bias[2];
+  if (threadIdx.x == 0) {
+    const double t = static_cast<double>(*a.step_dev);
+    s_bias[0] = static_cast<float>(1.0 - pow(static_cast<double>(a.beta1), t));
+    s_bias[1] = static_cast<float>(1.0 / sqrt(1.0 - pow(static_cast<double>(a.beta2), t)));
+  }
+  __syncthreads();
+  *bc1 = s_bias[0]; *rs = s_bias[1];
+}
 
 // ---- dp_p2p.cu: data-parallel AdamW fused with the gradient exchange over NVLink peer memory
 constexpr int DP_MAX_WORLD = 8, DP_MAX_SITES = 64;

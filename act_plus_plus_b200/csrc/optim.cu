@@ -8,8 +8,10 @@ namespace act {
 // p *= 1 - lr*wd; m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; p -= lr/(1-b1^t) * m / (sqrt(v)/sqrt(1-b2^t) + eps)
 // Also refreshes the bf16 shadow used as tensor-core operand.  mode 1: gradient identically zero (dead decoder
 // layers) -> m, v stay 0 and only the decoupled decay touches p.
-__global__ void adamw_kernel(AdamWArgs a, float bc1, float rsqrt_bc2) {
+__global__ void adamw_kernel(AdamWArgs a, float bc1_host, float rs_host) {
   pdl_trigger(); pdl_wait();
+  float bc1, rsqrt_bc2;
+  adam_bias(a, bc1_host, rs_host, &bc1, &rsqrt_bc2);
   const long long n4 = a.n / 4;
   const float decay = 1.f - a.lr * a.wd;
   const float step_size = a.lr / bc1;
@@ -62,6 +64,13 @@ int adamw_step(const AdamWArgs& a, cudaStream_t st) {
   const long long n4 = a.n / 4;
   const int blocks = static_cast<int>(std::max<long long>(1, std::min<long long>((n4 + 255) / 256, 148 * (a.background > 0 ? std::min(a.background, 8) : 8))));
   ACT_CUDA(launch_pdl(adamw_kernel, dim3(blocks), dim3(256), 0, st, a, static_cast<float>(bc1), static_cast<float>(1.0 / std::sqrt(bc2))));
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+__global__ void set_counter_kernel(int* c, int value, int increment) { *c = increment ? *c + 1 : value; }
+int set_counter(int* counter, int value, bool increment, cudaStream_t st) {
+  set_counter_kernel<<<1, 1, 0, st>>>(counter, value, increment ? 1 : 0);
   ACT_CUDA(cudaGetLastError());
   return 0;
 }

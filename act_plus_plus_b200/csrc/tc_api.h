@@ -6,6 +6,7 @@
 #include <stdint.h>
 #include <string>
 #include "tc_kernel.cuh"
+#include "dropout.cuh"
 
 namespace act {
 
@@ -56,6 +57,7 @@ struct EpiDesc {
   float* out_f32 = nullptr;
   bf16* out_bf16 = nullptr;
   long long ldc = 0, ldr = 0, osz0 = 0, osz1 = 0, rsz0 = 0, rsz1 = 0;
+  DropDesc drop;                        // EPI_DROPOUT (plain GEMMs only): keep mask indexed row * N + column
 };
 
 // D[z][M,N] = epi(A[z] * B[z]^T).  bn_hint / stages_hint = 0 -> heuristic.
@@ -89,10 +91,13 @@ int tc_conv(const ConvLaunch& c, cudaStream_t stream, int bn_hint = 0, int stage
 // dense 3x3 / stride-1 tap sets: halo patch resident in shared memory (conv3_kernel.cuh); ACT_CONV3=0 disables it
 bool tc_conv3_applicable(const ConvLaunch& c);
 void tc_set_sm_reserve(int n);
-// Attention scores fused with softmax (bwd = 0) / softmax backward (bwd = 1) for head_dim 64 and Lk <= 320 keys.
+// Attention scores fused with softmax (bwd = 0) / softmax backward (bwd = 1) for head_dim 64 and Lk <= 1024 keys
+// (one TMEM-resident pass up to 320 keys, two chunked passes beyond).  drop (optional, train mode): dropout on the
+// attention weights -- forward also writes out2 = dropout(P), backward masks dP (csrc/dropout.cuh).
 bool tc_attn_scores_applicable(int Lk, int Lkp);
 int tc_attn_scores(int bwd, const MatDesc& A, const MatDesc& B, int Lq, int Lk, int Lkp, int heads, int batch, float scale,
-                   const uint8_t* mask, const bf16* P, bf16* out, cudaStream_t stream);
+                   const uint8_t* mask, const bf16* P, bf16* out, cudaStream_t stream, const DropDesc* drop = nullptr,
+                   bf16* out2 = nullptr);
    // persistent launches that follow leave n SMs free for a concurrent branch
 int tc_conv3(const ConvLaunch& c, cudaStream_t stream, int bn_hint = 0);
 

@@ -10,6 +10,7 @@
 // Operands land in 128B-swizzled shared memory via TMA; accumulators live in TMEM (fp32).
 #pragma once
 #include "ptx.cuh"
+#include "dropout.cuh"
 
 namespace act {
 
@@ -26,6 +27,7 @@ enum EpiFlags : uint32_t {
   EPI_OUT_BF16 = 1u << 7,
   EPI_ATOMIC = 1u << 8,      // fp32 atomicAdd instead of store (split-K)
   EPI_ROWSCALE = 1u << 9,    // * rowscale[z*rs_ld + row]  (unused hooks keep the struct stable)
+  EPI_DROPOUT = 1u << 10,    // train-mode dropout of (acc + bias) before the residual is added (MODE_GEMM, un-batched)
 };
 
 struct TapDesc {     // one filter tap of an implicit-GEMM convolution
@@ -78,6 +80,8 @@ struct TcParams {
   int vec_ok;                           // all epilogue pointers / strides allow 16-byte vector access
   int vec32_ok;                         // ... and the outputs allow 32-byte (sector-wide) stores
   int debug;                            // experiment switches (ACT_TC_DEBUG): 1 = skip epilogue math+stores, 2 = skip TMA loads
+  DropDesc drop;                        // EPI_DROPOUT: element index = row * drop_ld + column
+  long long drop_ld;
 };
 
 template <int MODE, int A_MN, int B_MN, int BN>
@@ -148,7 +152,7 @@ __device__ __forceinline__ void ldg32(const float* __restrict__ ptr, float (&dst
 // ReLU, ReLU-mask against a saved activation, fp32 / bf16 / atomic output.  o_off / r_off = element offsets of the row.
 // `addends` = false for k-splits other than the first: bias and residual are added exactly once per output element.
 __device__ __forceinline__ void epi_store_chunk(const TcParams& p, const uint32_t (&v)[32], int gn0, long long o_off,
-                                                long long r_off, bool addends = true) {
+                                                long long r_off, bool addends = true, int drop_row = 0) {
   float f[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
@@ -173,6 +177,8 @@ __device__ __forceinline__ void epi_store_chunk(const TcParams& p, const uint32_
       for (int j = 0; j < 32; ++j) if (gn0 + j < p.N) f[j] += __ldg(p.bias + gn0 + j);
     }
   }
+  if (p.flags & EPI_DROPOUT)               // dropout(linear(x)) -- commutes with the ReLU below (scale > 0, mask in {0, 1})
+    drop_apply32(p.drop, static_cast<unsigned long long>(drop_row) * p.drop_ld + gn0, __ldg(p.drop.step), f);
   if ((p.flags & EPI_RES_F32) && addends) {
     const float* rp = p.res_f32 + r_off + gn0;
     if (full) {
@@ -317,7 +323,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
     // ============================================================== TMA producer
     if (elect_one()) {
       const CUtensorMap* amaps[4] = {&amap0, &amap1, &amap2, &amap3};
-      uint32_t it = 0;                                  // running k-block counter across tiles (ring position)
+      uint32_t s = 0, ph = 0;                           // ring position / phase, carried across tiles (no div/mod in the loop)
       if (MODE == MODE_CONV && b_res) {
         mbar_expect_tx(bres_bar, res_bytes);
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
@@ -327,55 +333,55 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
       }
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const TileCoord c = decode_tile<MODE, BN>(p, t);
-        for (int i = 0; i < c.nkb; ++i, ++it) {
+        for (int i = 0; i < c.nkb; ++i) {
           const int kb = c.kb_begin + i;
-          const int s = it % num_stages;
-          const uint32_t ph = (it / num_stages) & 1;
           mbar_wait(&empty_bar[s], ph ^ 1);
           uint8_t* sa = smem + s * stage_bytes;
           uint8_t* sb = sa + Cfg::A_BYTES;
-          if (p.debug & 2) { mbar_arrive(&full_bar[s]); continue; }
+          uint64_t* const fb = &full_bar[s];
+          if (++s == static_cast<uint32_t>(num_stages)) { s = 0; ph ^= 1; }
+          if (p.debug & 2) { mbar_arrive(fb); continue; }
           if (MODE == MODE_GEMM) {
             const uint32_t a_bytes = Cfg::BM * 128;
             const uint32_t b_bytes = BN * 128;
-            mbar_expect_tx(&full_bar[s], a_bytes + b_bytes);
+            mbar_expect_tx(fb, a_bytes + b_bytes);
             if (A_MN) {
-              tma_load_4d(sa, &amap0, &full_bar[s], c.m0, kb * 64, c.z0, c.z1);
-              tma_load_4d(sa + 64 * 128, &amap0, &full_bar[s], c.m0 + 64, kb * 64, c.z0, c.z1);
+              tma_load_4d(sa, &amap0, fb, c.m0, kb * 64, c.z0, c.z1);
+              tma_load_4d(sa + 64 * 128, &amap0, fb, c.m0 + 64, kb * 64, c.z0, c.z1);
             } else {
-              tma_load_4d(sa, &amap0, &full_bar[s], kb * 64, c.m0, c.z0, c.z1);
+              tma_load_4d(sa, &amap0, fb, kb * 64, c.m0, c.z0, c.z1);
             }
             if (B_MN) {
 #pragma unroll
               for (int q = 0; q < BN / 64; ++q)
-                tma_load_4d(sb + q * 64 * 128, &bmap, &full_bar[s], c.n0 + q * 64, kb * 64, c.z0, c.z1);
+                tma_load_4d(sb + q * 64 * 128, &bmap, fb, c.n0 + q * 64, kb * 64, c.z0, c.z1);
             } else {
-              tma_load_4d(sb, &bmap, &full_bar[s], kb * 64, c.n0, c.z0, c.z1);
+              tma_load_4d(sb, &bmap, fb, kb * 64, c.n0, c.z0, c.z1);
             }
           } else if (MODE == MODE_CONV) {
             const int tap = kb / p.cin_blocks, cb = kb % p.cin_blocks;
             const TapDesc td = p.taps[tap];
             const uint32_t a_bytes = p.BW * p.BH * p.BNI * 128;
-            mbar_expect_tx(&full_bar[s], a_bytes + (b_res ? 0u : BN * 128u));
-            tma_load_4d(sa, amaps[td.map], &full_bar[s], cb * 64, c.tw * p.BW + td.dw, c.th * p.BH + td.dh, c.tn * p.BNI);
-            if (!b_res) tma_load_2d(sb, &bmap, &full_bar[s], (td.wslot * p.cin_blocks + cb) * 64, c.n0);
+            mbar_expect_tx(fb, a_bytes + (b_res ? 0u : BN * 128u));
+            tma_load_4d(sa, amaps[td.map], fb, cb * 64, c.tw * p.BW + td.dw, c.th * p.BH + td.dh, c.tn * p.BNI);
+            if (!b_res) tma_load_2d(sb, &bmap, fb, (td.wslot * p.cin_blocks + cb) * 64, c.n0);
           } else {
             // WGRAD: kb = pixel tile index -> (n, ht, wt)
             int u = kb;
             const int wt = u % p.tiles_w; u /= p.tiles_w;
             const int ht = u % p.tiles_h; const int n = u / p.tiles_h;
             const uint32_t box = p.pix_per_box * 128;
-            mbar_expect_tx(&full_bar[s], box * (2 + BN / 64));
+            mbar_expect_tx(fb, box * (2 + BN / 64));
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
               const int tap = (p.taps_per_cta == 2) ? min(c.wg_tap0 + q, p.ntaps - 1) : c.wg_tap0;
               const int ci = (p.taps_per_cta == 2) ? 0 : c.wg_ci0 + q * 64;
               const TapDesc td = p.taps[tap];
-              tma_load_4d(sa + q * box, amaps[td.map], &full_bar[s], ci, wt * p.BW + td.dw, ht * p.BH + td.dh, n);
+              tma_load_4d(sa + q * box, amaps[td.map], fb, ci, wt * p.BW + td.dw, ht * p.BH + td.dh, n);
             }
 #pragma unroll
             for (int q = 0; q < BN / 64; ++q)
-              tma_load_4d(sb + q * box, &bmap, &full_bar[s], c.n0 + q * 64, wt * p.BW, ht * p.BH, n);
+              tma_load_4d(sb + q * box, &bmap, fb, c.n0 + q * 64, wt * p.BW, ht * p.BH, n);
           }
         }
       }
@@ -389,7 +395,8 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
       const uint32_t sbase = smem_u32(smem);
       const uint64_t adesc0 = A_MN ? make_smem_desc(sbase, lbo, 1024) : make_smem_desc(sbase, 16, 1024);
       const uint64_t bdesc0 = B_MN ? make_smem_desc(sbase + Cfg::A_BYTES, lbo, 1024) : make_smem_desc(sbase + Cfg::A_BYTES, 16, 1024);
-      uint32_t it = 0, lt = 0;
+      uint32_t s = 0, ph = 0, lt = 0;                   // ring position / phase carried across tiles
+      const uint32_t stage16 = stage_bytes >> 4;
       const uint64_t bres_desc0 = make_smem_desc(smem_u32(bres), 16, 1024);
       if (MODE == MODE_CONV && b_res) { mbar_wait(bres_bar, 0); tc_fence_after(); }
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
@@ -398,13 +405,11 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
         mbar_wait(&tempty_bar[acc], ((lt >> 1) & 1) ^ 1);      // epilogue drained this buffer (first use: immediate)
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * Cfg::ACC_COLS;
-        for (int i = 0; i < c.nkb; ++i, ++it) {
-          const int s = it % num_stages;
-          const uint32_t ph = (it / num_stages) & 1;
+        for (int i = 0; i < c.nkb; ++i) {
           mbar_wait(&full_bar[s], ph);
           tc_fence_after();
           // descriptors differ from the stage-0 / k-0 ones only in the 14-bit start-address field (16-byte units)
-          const uint32_t soff = (static_cast<uint32_t>(s) * stage_bytes) >> 4;
+          const uint32_t soff = s * stage16;
           uint64_t ad = adesc0 + soff, bd = bdesc0 + soff;
           if (MODE == MODE_CONV && b_res) bd = bres_desc0 + ((static_cast<uint32_t>(c.kb_begin + i) * BN * 128u) >> 4);
           if (MODE == MODE_WGRAD) {
@@ -412,9 +417,10 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
           } else {
 #pragma unroll
             for (int k = 0; k < 4; ++k, ad += (A_MN ? 128 : 2), bd += (B_MN ? 128 : 2))
-              umma_bf16((p.debug & 4) ? tmem_base + (k & 1) * Cfg::ACC_COLS : tmem_d, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+              umma_bf16(tmem_d, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
           umma_commit(&empty_bar[s]);          // frees this smem stage when the MMAs above retire
+          if (++s == static_cast<uint32_t>(num_stages)) { s = 0; ph ^= 1; }
         }
         umma_commit(&tfull_bar[acc]);          // accumulator complete
       }
@@ -481,7 +487,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
             if (gn0 + j < p.Cout) atomicAdd(op + static_cast<long long>(j) * p.Cin, __uint_as_float(v[j]) * p.alpha);
           continue;
         }
-        epi_store_chunk(p, v, gn0, o_off, r_off, p.ksplit <= 1 || c.kb_begin == 0);
+        epi_store_chunk(p, v, gn0, o_off, r_off, p.ksplit <= 1 || c.kb_begin == 0, c.m0 + r);
       }
     }
   }

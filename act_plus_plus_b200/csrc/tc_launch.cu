@@ -232,6 +232,7 @@ static void fill_epi(TcParams& p, const EpiDesc& e) {
   p.flags = e.flags; p.alpha = e.alpha; p.bias = e.bias; p.scale = e.scale; p.res_f32 = e.res_f32;
   p.res_bf16 = e.res_bf16; p.aux_bf16 = e.aux_bf16; p.out_f32 = e.out_f32; p.out_bf16 = e.out_bf16;
   p.ldc = e.ldc; p.ldr = e.ldr; p.osz0 = e.osz0; p.osz1 = e.osz1; p.rsz0 = e.rsz0; p.rsz1 = e.rsz1;
+  p.drop = e.drop;                       // (TcParams is memset to 0 by the callers, which is NOT the "off" state)
 }
 
 static int check_epi(const EpiDesc& e) {
@@ -255,6 +256,9 @@ int tc_gemm(int M, int N, int K, int nz0, int nz1, const MatDesc& A, const MatDe
   if (ksplit < 1) ksplit = 1;
   if (ksplit > 1) ACT_CHECK(epi.flags & EPI_ATOMIC, "split-K needs the atomic epilogue");
   if (ksplit > 1) ACT_CHECK(!(epi.flags & (EPI_RELU | EPI_MASK_POS)), "split-K cannot apply a non-linear epilogue");
+  if (epi.flags & EPI_DROPOUT)
+    ACT_CHECK(ksplit == 1 && nz0 * nz1 == 1 && N % 32 == 0 && epi.drop.step != nullptr && drop_on(epi.drop),
+              "dropout epilogue: plain GEMM with N % 32 == 0 and a device step counter only");
   const int nb = nz0 * nz1;
   const int mt = (M + 127) / 128;
   int bn = bn_hint;
@@ -264,6 +268,7 @@ int tc_gemm(int M, int N, int K, int nz0, int nz1, const MatDesc& A, const MatDe
   memset(&p, 0, sizeof(p));
   p.M = M; p.N = N; p.K = K; p.num_k_blocks = (K + 63) / 64; p.nz0 = nz0; p.ksplit = ksplit;
   fill_epi(p, epi);
+  p.drop_ld = N;
   bool vec = (epi.ldc % 8 == 0) && (epi.osz0 % 8 == 0) && (epi.osz1 % 8 == 0) && (epi.ldr % 8 == 0) &&
              (epi.rsz0 % 8 == 0) && (epi.rsz1 % 8 == 0) && aligned16(epi.out_f32) && aligned16(epi.out_bf16) &&
              aligned16(epi.res_f32) && aligned16(epi.res_bf16) && aligned16(epi.aux_bf16);
@@ -515,14 +520,33 @@ static int launch_attn(const CUtensorMap& am, const CUtensorMap& bm, const AttnP
 bool tc_attn_scores_applicable(int Lk, int Lkp) {
   static int on = -1;
   if (on < 0) { const char* e = getenv("ACT_FUSED_ATTN"); on = !(e && e[0] == '0'); }
-  return on && Lk >= 1 && Lk <= 320 && Lkp % 8 == 0 && Lkp >= Lk;
+  return on && Lk >= 1 && Lk <= AttnCCfg::NCH_MAX * AttnCCfg::CH && Lkp % 8 == 0 && Lkp >= Lk;
+}
+
+template <int BWD>
+static int launch_attn_chunked(const CUtensorMap& am, const CUtensorMap& bm, const AttnParams& p, int items, cudaStream_t stream) {
+  auto kern = attn_scores_chunked_kernel<BWD>;
+  static bool configured = false;
+  if (!configured) {
+    ACT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnCCfg::SMEM));
+    configured = true;
+  }
+  const unsigned ctas = static_cast<unsigned>(std::min(items, num_sms()));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
+  ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(256), static_cast<size_t>(AttnCCfg::SMEM), stream, am, bm, p));
+  if (g_prof.on) { cudaEventRecord(e1, stream); g_prof.ev.push_back(e0); g_prof.ev.push_back(e1); g_prof.flops.push_back(g_next_flops); g_prof.label.push_back(g_next_label); }
+  ACT_CUDA(cudaGetLastError());
+  return 0;
 }
 
 // FWD: out = softmax(scale * A B^T + mask) with A = Q [Lq x 64], B = K [Lk x 64] per (head, batch)
 // BWD: out = scale * P o (dP - rowsum(dP o P)), dP = A B^T with A = dO, B = V
 int tc_attn_scores(int bwd, const MatDesc& A, const MatDesc& B, int Lq, int Lk, int Lkp, int heads, int batch, float scale,
-                   const uint8_t* mask, const bf16* P, bf16* out, cudaStream_t stream) {
-  ACT_CHECK(tc_attn_scores_applicable(Lk, Lkp), "fused attention scores need Lk <= 320 and a padded stride % 8 == 0");
+                   const uint8_t* mask, const bf16* P, bf16* out, cudaStream_t stream, const DropDesc* drop, bf16* out2) {
+  ACT_CHECK(tc_attn_scores_applicable(Lk, Lkp), "fused attention scores need Lk <= 1024 and a padded stride % 8 == 0");
+  ACT_CHECK(!(drop && drop_on(*drop)) || bwd || out2, "fused attention scores: dropout needs the second (dropped) output");
+  ACT_CHECK(!(drop && drop_on(*drop)) || drop->step, "fused attention scores: dropout needs the device step counter");
   ACT_CHECK(!A.mn_major && !B.mn_major && out && (!bwd || P), "fused attention scores: bad operands");
   ACT_CHECK((reinterpret_cast<uintptr_t>(out) & 31) == 0 && (!P || (reinterpret_cast<uintptr_t>(P) & 15) == 0), "fused attention scores: unaligned P / dS");
   const int W = Lk <= 128 ? 128 : 320;
@@ -530,8 +554,23 @@ int tc_attn_scores(int bwd, const MatDesc& A, const MatDesc& B, int Lq, int Lk, 
   memset(&p, 0, sizeof(p));
   p.Lq = Lq; p.Lk = Lk; p.Lkp = Lkp; p.heads = heads; p.batch = batch; p.qtiles = (Lq + 127) / 128; p.scale = scale;
   p.mask = mask; p.P = P; p.out = out; p.vec32 = (Lkp % 16 == 0) ? 1 : 0;
+  p.drop = drop ? *drop : DropDesc();            // (the memset above is not the "off" state: thresh 0 would drop everything)
+  p.out2 = out2;
+  ACT_CHECK(!out2 || (reinterpret_cast<uintptr_t>(out2) & 31) == 0, "fused attention scores: unaligned dropped-P output");
   CUtensorMap am, bm;
   if (mat_tmap(&am, A, Lq, 64, heads, batch, 128)) return -1;
+  if (Lk > 320) {
+    // chunked two-pass kernel: items = (batch, head, group of query tiles), enough groups to fill the chip
+    p.nch = (Lk + AttnCCfg::CH - 1) / AttnCCfg::CH;
+    const int pairs = heads * batch;
+    p.groups = std::max(1, std::min(p.qtiles, (num_sms() + pairs - 1) / pairs));
+    p.tiles_per_group = (p.qtiles + p.groups - 1) / p.groups;
+    p.groups = (p.qtiles + p.tiles_per_group - 1) / p.tiles_per_group;
+    if (mat_tmap(&bm, B, Lk, 64, heads, batch, AttnCCfg::CH)) return -1;
+    g_next_flops = 2.0 * Lq * Lk * 64 * heads * batch;          // algorithmic (the second pass recomputes the scores)
+    if (g_prof.on) { char buf[160]; snprintf(buf, sizeof buf, "attn_%s Lq=%d Lk=%d z=%d chunked nch=%d groups=%d", bwd ? "dS" : "P", Lq, Lk, pairs, p.nch, p.groups); g_next_label = buf; }
+    return bwd ? launch_attn_chunked<1>(am, bm, p, pairs * p.groups, stream) : launch_attn_chunked<0>(am, bm, p, pairs * p.groups, stream);
+  }
   if (mat_tmap(&bm, B, Lk, 64, heads, batch, W == 128 ? 128 : 160)) return -1;
   const int tiles = p.qtiles * heads * batch;
   g_next_flops = 2.0 * Lq * Lk * 64 * heads * batch;

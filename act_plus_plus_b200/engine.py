@@ -22,7 +22,7 @@ class EngineConfig(C.Structure):
                                       "dim_feedforward", "enc_layers", "dec_layers", "num_queries", "state_dim",
                                       "action_dim", "latent_dim")] + \
                [(n, C.c_float) for n in ("kl_weight", "lr", "lr_backbone", "weight_decay", "beta1", "beta2", "adam_eps")] + \
-               [("faithful_decoder", C.c_int), ("train", C.c_int)]
+               [("no_encoder", C.c_int), ("train", C.c_int)]
 
 
 def _stream():
@@ -33,14 +33,15 @@ class ActEngine:
     def __init__(self, batch_max=8, num_cameras=1, img_h=480, img_w=640, hidden_dim=512, nheads=8,
                  dim_feedforward=3200, enc_layers=4, dec_layers=7, num_queries=100, state_dim=14, action_dim=16,
                  latent_dim=32, kl_weight=10.0, lr=1e-5, lr_backbone=1e-5, weight_decay=1e-4, betas=(0.9, 0.999),
-                 eps=1e-8, train=True, device: Optional[torch.device] = None, share: "Optional[ActEngine]" = None):
+                 eps=1e-8, train=True, device: Optional[torch.device] = None, share: "Optional[ActEngine]" = None,
+                 no_encoder: bool = False):
         if not torch.cuda.is_available():
             raise _lib.ActB200Error("act_plus_plus_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.lib = _lib.lib()
         cfg = EngineConfig(batch_max, num_cameras, img_h, img_w, hidden_dim, nheads, dim_feedforward, enc_layers,
                            dec_layers, num_queries, state_dim, action_dim, latent_dim, kl_weight, lr, lr_backbone,
-                           weight_decay, betas[0], betas[1], eps, 0, 1 if train else 0)
+                           weight_decay, betas[0], betas[1], eps, 1 if no_encoder else 0, 1 if train else 0)
         self.cfg = cfg
         self.train_enabled = bool(train)
         self._h = C.c_void_p()
@@ -118,7 +119,8 @@ class ActEngine:
                    nheads=c.nheads, dim_feedforward=c.dim_feedforward, enc_layers=c.enc_layers, dec_layers=c.dec_layers,
                    num_queries=c.num_queries, state_dim=c.state_dim, action_dim=c.action_dim, latent_dim=c.latent_dim,
                    kl_weight=c.kl_weight, lr=c.lr, lr_backbone=c.lr_backbone, weight_decay=c.weight_decay,
-                   betas=(c.beta1, c.beta2), eps=c.adam_eps, train=train, device=master.device, share=master)
+                   betas=(c.beta1, c.beta2), eps=c.adam_eps, train=train, device=master.device, share=master,
+                   no_encoder=bool(c.no_encoder))
 
     @property
     def step_count(self) -> int:
@@ -345,6 +347,38 @@ class ActEngine:
 
     def set_lr(self, lr: float, lr_backbone: float):
         check(self.lib.act_engine_set_lr(self._h, lr, lr_backbone), "act_engine_set_lr")
+
+    # ---- train-mode dropout (act_engine_set_dropout; csrc/dropout.cuh)
+    SITE_ENC, SITE_CVAE, SITE_DEC = 0x100, 0x200, 0x300
+
+    def set_dropout(self, p: float, seed: int = 0):
+        """p = 0 switches dropout off (the reference's .eval()); masks are Philox(seed; element, site, step)."""
+        check(self.lib.act_engine_set_dropout(self._h, float(p), int(seed) & 0xFFFFFFFFFFFFFFFF), "act_engine_set_dropout")
+        self.dropout_p = float(p)
+
+    def dropout_state(self):
+        """(p, seed, step): step = value of the device counter, i.e. the step of the LAST training forward."""
+        p, seed, step = C.c_float(), C.c_uint64(), C.c_uint32()
+        check(self.lib.act_engine_dropout_state(self._h, C.byref(p), C.byref(seed), C.byref(step)), "act_engine_dropout_state")
+        return p.value, seed.value, step.value
+
+    def dropout_mask(self, site: int, n: int, step: Optional[int] = None) -> torch.Tensor:
+        """uint8 keep mask of the first n elements of dropout site `site` (tests: the masks the kernels regenerate)."""
+        p, seed, cur = self.dropout_state()
+        out = torch.empty(n, dtype=torch.uint8, device=self.device)
+        check(self.lib.act_dropout_mask(seed, site, cur if step is None else step, p, n, out.data_ptr(), _stream()),
+              "act_dropout_mask")
+        return out
+
+    def debug_buffer(self, name: str) -> torch.Tensor:
+        """Copy of an internal activation of the last forward ("src", "memory", "hs", "feat<k>"): parity diagnostics."""
+        numel, dtype = C.c_int64(), C.c_int()
+        check(self.lib.act_engine_debug_buffer(self._h, name.encode(), None, 0, C.byref(numel), C.byref(dtype), _stream()),
+              "act_engine_debug_buffer")
+        out = torch.empty(numel.value, dtype=torch.float32 if dtype.value == 0 else torch.bfloat16, device=self.device)
+        check(self.lib.act_engine_debug_buffer(self._h, name.encode(), out.data_ptr(), out.numel() * out.element_size(),
+                                               C.byref(numel), C.byref(dtype), _stream()), "act_engine_debug_buffer")
+        return out
 
     def launches(self, reset: bool = False) -> int:
         return self.lib.act_engine_launches(self._h, 1 if reset else 0)

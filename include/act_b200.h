@@ -104,12 +104,11 @@ int act_reparam_fwd(const float* latent_info, const float* eps, float* mu, float
                     void* stream);
 int act_reparam_bwd(const float* dz, const float* eps, const float* logvar, const float* d_mu_kl,
                     const float* d_logvar_kl, float* d_latent_info, int B, int Z, void* stream);
-/* resnet stem: max-pool 3x3/s2/p1 on NHWC bf16 (+arg-max bytes) and its ReLU-fused backward; conv1 im2col with the
- * ImageNet normalisation of policy.py:268-272 fused (image fp32 [B,3,H,W] with batch stride img_bs elements). */
+/* resnet stem: max-pool 3x3/s2/p1 on NHWC bf16 (+arg-max bytes) and its ReLU-fused backward (torchvision resnet18
+ * `maxpool`, backbone.py:121-124).  The stem conv itself is an implicit GEMM inside the engine (no im2col). */
 int act_maxpool_fwd(const void* x, void* y, uint8_t* argmax, int N, int H, int W, int C, void* stream);
 int act_maxpool_bwd(const void* dy, const uint8_t* argmax, const void* x, void* dx, int N, int H, int W, int C,
                     void* stream);
-int act_im2col_conv1(const float* image, int64_t img_bs, void* out, int B, int H, int W, int KP, void* stream);
 /* torch.optim.AdamW single step over one flat segment (detr/main.py:102-110); mode 1 = decay only (zero gradient). */
 int act_adamw_step(float* p, const float* g, float* m, float* v, void* shadow_bf16, int64_t n, float lr, float beta1,
                    float beta2, float eps, float weight_decay, int step, int mode, void* stream);
@@ -129,7 +128,8 @@ typedef struct {
   int hidden_dim, nheads, dim_feedforward, enc_layers, dec_layers;
   int num_queries, state_dim, action_dim, latent_dim;
   float kl_weight, lr, lr_backbone, weight_decay, beta1, beta2, adam_eps;
-  int faithful_decoder;   /* reserved: execute the dead decoder layers 1.. as the reference does */
+  int no_encoder;         /* 1: DETRVAE built with encoder=None (detr_vae.py:109-112, 373-377): no `encoder.*` tensors,
+                            latent = 0 in every call, kl = 0 (policy.py:306-307) */
   int train;              /* 0: inference-only workspace */
 } act_engine_config;
 
@@ -218,7 +218,33 @@ int act_engine_set_concurrent(act_engine* e, int on);
 int act_engine_set_image_format(act_engine* e, int fmt);
 int act_engine_adamw_step(act_engine* e, int step, void* stream);
 int act_engine_set_lr(act_engine* e, float lr, float lr_backbone);
+/* Train-mode dropout of the transformer blocks (transformer.py:194,197,202-203,219-222,254-266,284-293; p = 0.1 at
+ * detr/main.py:45; nn.MultiheadAttention's attention-weight dropout included).  p = 0 switches it off (`.eval()`).
+ * Masks are a counter-based function Philox4x32-10(seed; element / 8, site, step) regenerated wherever needed -- nothing
+ * is stored; `step` is a device counter bumped by every training forward (CUDA-graph replays draw fresh masks).
+ * Data-parallel ranks pass different seeds.  Applies to act_engine_forward calls WITH actions (and their backward). */
+int act_engine_set_dropout(act_engine* e, float p, uint64_t seed);
+int act_engine_dropout_state(act_engine* e, float* p, uint64_t* seed, uint32_t* step);   /* synchronises */
+/* The keep mask (uint8, 1 = kept) of elements [0, n) of dropout site `site` at `step`: the same function the kernels
+ * evaluate.  Site ids: 0x100 + 8 l + k main encoder layer l, 0x200 + 8 l + k CVAE encoder, 0x300 + k decoder layer 0;
+ * k = 0 attention weights [B, heads, Lq, Lkp], 1 attention out-proj [B L, d], 2 FFN hidden [B L, ff], 3 FFN out [B L, d],
+ * 4 / 5 decoder cross-attention weights / out-proj. */
+int act_dropout_mask(uint64_t seed, uint32_t site, uint32_t step, float p, int64_t n, uint8_t* out, void* stream);
+/* loss.backward() hands autograd's incoming gradient over ON THE DEVICE: gvec3 = d/d{l1, kl, loss} (three floats; the
+ * dict of policy.py:316-318 returns all three scalars and any of them may be the root).  The following
+ * act_engine_backward* calls read it inside the loss kernel instead of the scalar loss_grad argument -- no host
+ * synchronisation in the step.  NULL restores the scalar argument. */
+int act_engine_set_loss_grad(act_engine* e, const float* gvec3);
+/* `stream` waits for every internal lane of the engine (an act_engine_zero_grad_async clear, trailing weight-gradient
+ * launches): closes a CUDA-graph capture that ends between the forward and the backward of a step. */
+int act_engine_join_lanes(act_engine* e, void* stream);
 int act_engine_launches(act_engine* e, int reset);
+/* Parity diagnostics: copy of an internal activation of the LAST forward.  name: "src" (encoder input, fp32
+ * [B, L, d]), "memory" (encoder output, fp32 [B, L, d]), "hs" (decoder output after the final norm, fp32 [B, nq, d]),
+ * "feat<k>" (camera k's layer4 output, bf16 NHWC [B, Hf, Wf, 512]).  dtype: 0 = fp32, 1 = bf16.  dst = NULL only
+ * queries numel / dtype; otherwise numel elements are copied to the device buffer dst (capacity in bytes) on `stream`. */
+int act_engine_debug_buffer(act_engine* e, const char* name, void* dst, int64_t capacity, int64_t* numel, int* dtype,
+                            void* stream);
 
 /* ---- measurement hook: CUDA-event timing of every tcgen05 kernel launched between begin and end on its own stream;
  *      returns summed device time, summed algorithmic FLOPs (2*M*N*K per launch), launch count, longest launch. */

@@ -26,6 +26,7 @@ DEFAULT_CFG = dict(
     hidden_dim=512, nheads=8, dim_feedforward=3200, enc_layers=4, dec_layers=7,
     num_queries=100, state_dim=14, action_dim=16, num_cameras=1, latent_dim=32,
     kl_weight=10, lr=1e-5, lr_backbone=1e-5, weight_decay=1e-4,
+    no_encoder=False,       # detr_vae.py:373-377: encoder = None -> latent 0, kl 0, no `encoder.*` tensors
 )
 
 # torchvision resnet18 topology (backbone.py:121-124 builds it; layer4 is returned, backbone.py:71)
@@ -112,8 +113,9 @@ def state_spec(cfg: dict) -> List[tuple]:
     for i in range(cfg["dec_layers"]):
         spec += _dec_layer_spec(f"transformer.decoder.layers.{i}.", d, ff)
     spec += [("transformer.decoder.norm.weight", (d,), "ln_w"), ("transformer.decoder.norm.bias", (d,), "ln_b")]
-    for i in range(cfg["enc_layers"]):
-        spec += _enc_layer_spec(f"encoder.layers.{i}.", d, ff, False)
+    if not cfg.get("no_encoder"):
+        for i in range(cfg["enc_layers"]):
+            spec += _enc_layer_spec(f"encoder.layers.{i}.", d, ff, False)
     spec += [
         ("action_head.weight", (A, d), "linear"), ("action_head.bias", (A,), "bias:%d" % d),
         ("is_pad_head.weight", (1, d), "linear"), ("is_pad_head.bias", (1,), "bias:%d" % d),
@@ -207,6 +209,8 @@ def state_checksum(sd: Dict[str, torch.Tensor]) -> np.ndarray:
              "backbones.0.0.body.layer4.1.conv2.weight", "action_head.weight", "query_embed.weight"]
     out = []
     for n in names:
+        if n not in sd:                          # no_encoder variant
+            n = "latent_proj.weight"
         t = sd[n].double().flatten()
         out += [float(t.sum()), float(t.abs().sum()), float(t[::997].sum())]
     return np.asarray(out, dtype=np.float64)
@@ -296,8 +300,7 @@ def mha(sd, p: str, query, key, value, nheads: int, key_padding_mask=None, dropo
         m = key_padding_mask[:, None, None, :].expand(B, nheads, Lq, Lk).reshape(B * nheads, Lq, Lk)
         logits = logits.masked_fill(m, float("-inf"))
     attn = torch.softmax(logits, dim=-1)
-    if dropout_p > 0.0:
-        attn = F.dropout(attn, p=dropout_p)
+    attn = _drop(attn, dropout_p, p + "attn")                       # nn.MultiheadAttention(dropout=p): on the weights
     out = torch.bmm(attn, v).transpose(0, 1).reshape(Lq, B, d)
     return F.linear(out, sd[p + "out_proj.weight"], sd[p + "out_proj.bias"])
 
@@ -306,30 +309,42 @@ def _ln(sd, p, x):
     return F.layer_norm(x, (x.shape[-1],), sd[p + "weight"], sd[p + "bias"], 1e-5)
 
 
-def _drop(x, p):
-    return F.dropout(x, p=p) if p > 0.0 else x
+# Mask injection for the dropout parity test: DROP_HOOK(site, x) -> keep mask (0/1, broadcastable to x) or None.
+# Sites are named by the parameter prefix of the layer + {"self_attn.attn", "multihead_attn.attn", "drop1", "drop2",
+# "drop3", "ffn"}.  Without a hook the masks come from torch's global generator like in the reference.
+DROP_HOOK = None
+
+
+def _drop(x, p, site=None):
+    if p <= 0.0:
+        return x
+    if DROP_HOOK is not None:
+        m = DROP_HOOK(site, x)
+        if m is not None:
+            return x * m.to(x.dtype) / (1.0 - p)
+    return F.dropout(x, p=p)
 
 
 def encoder_layer(sd, p: str, src, pos, nheads: int, key_padding_mask=None, dropout_p: float = 0.0):
     """TransformerEncoderLayer.forward_post, transformer.py:211-224."""
     q = k = src + pos
     src2 = mha(sd, p + "self_attn.", q, k, src, nheads, key_padding_mask, dropout_p)
-    src = _ln(sd, p + "norm1.", src + _drop(src2, dropout_p))
-    src2 = F.linear(_drop(F.relu(F.linear(src, sd[p + "linear1.weight"], sd[p + "linear1.bias"])), dropout_p),
+    src = _ln(sd, p + "norm1.", src + _drop(src2, dropout_p, p + "drop1"))
+    src2 = F.linear(_drop(F.relu(F.linear(src, sd[p + "linear1.weight"], sd[p + "linear1.bias"])), dropout_p, p + "ffn"),
                     sd[p + "linear2.weight"], sd[p + "linear2.bias"])
-    return _ln(sd, p + "norm2.", src + _drop(src2, dropout_p))
+    return _ln(sd, p + "norm2.", src + _drop(src2, dropout_p, p + "drop2"))
 
 
 def decoder_layer(sd, p: str, tgt, memory, pos, query_pos, nheads: int, dropout_p: float = 0.0):
     """TransformerDecoderLayer.forward_post, transformer.py:274-295."""
     q = k = tgt + query_pos
     tgt2 = mha(sd, p + "self_attn.", q, k, tgt, nheads, None, dropout_p)
-    tgt = _ln(sd, p + "norm1.", tgt + _drop(tgt2, dropout_p))
+    tgt = _ln(sd, p + "norm1.", tgt + _drop(tgt2, dropout_p, p + "drop1"))
     tgt2 = mha(sd, p + "multihead_attn.", tgt + query_pos, memory + pos, memory, nheads, None, dropout_p)
-    tgt = _ln(sd, p + "norm2.", tgt + _drop(tgt2, dropout_p))
-    tgt2 = F.linear(_drop(F.relu(F.linear(tgt, sd[p + "linear1.weight"], sd[p + "linear1.bias"])), dropout_p),
+    tgt = _ln(sd, p + "norm2.", tgt + _drop(tgt2, dropout_p, p + "drop2"))
+    tgt2 = F.linear(_drop(F.relu(F.linear(tgt, sd[p + "linear1.weight"], sd[p + "linear1.bias"])), dropout_p, p + "ffn"),
                     sd[p + "linear2.weight"], sd[p + "linear2.bias"])
-    return _ln(sd, p + "norm3.", tgt + _drop(tgt2, dropout_p))
+    return _ln(sd, p + "norm3.", tgt + _drop(tgt2, dropout_p, p + "drop3"))
 
 
 def cvae_encode(sd, cfg, qpos, actions, is_pad, eps, dropout_p: float = 0.0):
@@ -352,16 +367,18 @@ def cvae_encode(sd, cfg, qpos, actions, is_pad, eps, dropout_p: float = 0.0):
 
 
 def detrvae_forward(sd, cfg, qpos, image_normalized, actions=None, is_pad=None, eps=None,
-                    dropout_p: float = 0.0, faithful_decoder: bool = False):
+                    dropout_p: float = 0.0, faithful_decoder: bool = False, taps: dict = None):
     """DETRVAE.forward, detr_vae.py:163-254 (RGB path, no depth / pointcloud / vq).
 
     ``image_normalized`` is [B,K,3,H,W] *after* the ImageNet normalisation of policy.py:268-272.
-    Returns dict(a_hat [B,nq,A], is_pad_hat [B,nq,1], mu, logvar)."""
+    Returns dict(a_hat [B,nq,A], is_pad_hat [B,nq,1], mu, logvar).  ``taps`` (optional dict) receives
+    intermediate activations in the engine's layouts (per-stage parity diagnostics): feat{k} = camera k's
+    layer4 output as NHWC, src / memory = encoder input / output as [B, L, d], hs = decoder output [B, nq, d]."""
     B = qpos.shape[0]
     d, nh = cfg["hidden_dim"], cfg["nheads"]
-    if actions is not None:
+    if actions is not None and not cfg.get("no_encoder"):
         latent_sample, mu, logvar = cvae_encode(sd, cfg, qpos, actions, is_pad, eps, dropout_p)
-    else:
+    else:                                                                                  # detr_vae.py:109-112 / :155-158
         mu = logvar = None
         latent_sample = torch.zeros((B, cfg["latent_dim"]), dtype=torch.float32)          # detr_vae.py:157
     latent_input = F.linear(latent_sample, sd["latent_out_proj.weight"], sd["latent_out_proj.bias"])
@@ -369,6 +386,8 @@ def detrvae_forward(sd, cfg, qpos, image_normalized, actions=None, is_pad=None, 
     feats, poss = [], []
     for k in range(cfg["num_cameras"]):
         f = resnet18_layer4(sd, f"backbones.{k}.0.body.", image_normalized[:, k])
+        if taps is not None:
+            taps[f"feat{k}"] = f.detach().permute(0, 2, 3, 1).contiguous()
         poss.append(position_embedding_sine(f.shape[2], f.shape[3], d // 2))
         feats.append(F.conv2d(f, sd["input_proj.weight"], sd["input_proj.bias"]))
     proprio_input = F.linear(qpos, sd["input_proj_robot_state.weight"], sd["input_proj_robot_state.bias"])
@@ -384,6 +403,9 @@ def detrvae_forward(sd, cfg, qpos, image_normalized, actions=None, is_pad=None, 
     memory = src
     for i in range(cfg["enc_layers"]):
         memory = encoder_layer(sd, f"transformer.encoder.layers.{i}.", memory, pos, nh, None, dropout_p)
+    if taps is not None:
+        taps["src"] = src.detach().permute(1, 0, 2).contiguous()
+        taps["memory"] = memory.detach().permute(1, 0, 2).contiguous()
     tgt = torch.zeros((cfg["num_queries"], B, d), dtype=torch.float32)
     # transformer.py:157-186 with return_intermediate=True: every layer output goes through the shared
     # final norm; detr_vae.py:245 keeps index [0] only -> decoder layers 1.. are dead work.
@@ -394,6 +416,8 @@ def detrvae_forward(sd, cfg, qpos, image_normalized, actions=None, is_pad=None, 
         if i == 0:
             first = _ln(sd, "transformer.decoder.norm.", out)
     hs = first.transpose(0, 1)                                                              # [B, nq, d]
+    if taps is not None:
+        taps["hs"] = hs.detach().contiguous()
     a_hat = F.linear(hs, sd["action_head.weight"], sd["action_head.bias"])
     is_pad_hat = F.linear(hs, sd["is_pad_head.weight"], sd["is_pad_head.bias"])
     return dict(a_hat=a_hat, is_pad_hat=is_pad_hat, mu=mu, logvar=logvar)
@@ -413,7 +437,7 @@ def kl_divergence(mu, logvar):
 
 
 def policy_forward(sd, cfg, qpos, image, actions=None, is_pad=None, eps=None, dropout_p: float = 0.0,
-                   faithful_decoder: bool = False):
+                   faithful_decoder: bool = False, taps: dict = None):
     """ACTPolicy.__call__, policy.py:264-332.  Training/validation call returns
     dict(l1, kl, loss, a_hat, mu, logvar); inference call returns dict(a_hat)."""
     image = normalize_image(image)
@@ -421,13 +445,14 @@ def policy_forward(sd, cfg, qpos, image, actions=None, is_pad=None, eps=None, dr
     if actions is not None:
         actions = actions[:, :nq]
         is_pad = is_pad[:, :nq]
-        o = detrvae_forward(sd, cfg, qpos, image, actions, is_pad, eps, dropout_p, faithful_decoder)
-        total_kld = kl_divergence(o["mu"], o["logvar"])
+        o = detrvae_forward(sd, cfg, qpos, image, actions, is_pad, eps, dropout_p, faithful_decoder, taps)
+        # policy.py:306-309: kl = 0 when the model has no CVAE encoder
+        total_kld = torch.zeros(1) if cfg.get("no_encoder") else kl_divergence(o["mu"], o["logvar"])
         all_l1 = F.l1_loss(actions, o["a_hat"], reduction="none")
         l1 = (all_l1 * ~is_pad.unsqueeze(-1)).mean()                   # mean over B*nq*A incl. padded (policy.py:315)
         loss = l1 + total_kld[0] * cfg["kl_weight"]
         return dict(l1=l1, kl=total_kld[0], loss=loss, a_hat=o["a_hat"], mu=o["mu"], logvar=o["logvar"])
-    o = detrvae_forward(sd, cfg, qpos, image, dropout_p=0.0, faithful_decoder=faithful_decoder)
+    o = detrvae_forward(sd, cfg, qpos, image, dropout_p=0.0, faithful_decoder=faithful_decoder, taps=taps)
     return dict(a_hat=o["a_hat"])
 
 
@@ -435,17 +460,18 @@ def trainable_names(cfg: dict) -> List[str]:
     return [n for n, _, kind in state_spec(cfg) if not is_buffer(kind)]
 
 
-def loss_and_grads(sd, cfg, batch) -> Dict[str, object]:
+def loss_and_grads(sd, cfg, batch, dropout_p: float = 0.0) -> Dict[str, object]:
     """loss.backward() of imitate_episodes.py:603-606 through the restatement (autograd on CPU).
     Parameters that autograd never reaches (is_pad_head, decoder layers >= 1) get grad None,
     except decoder layers 1.. which the reference reaches with exact zeros (SURVEY.md 3.2);
     callers treat None as 'skipped by AdamW' and zeros as 'decayed only'."""
     names = trainable_names(cfg)
     leaf = {n: (sd[n].clone().requires_grad_(True) if n in names else sd[n]) for n in sd}
-    out = policy_forward(leaf, cfg, batch["qpos"], batch["image"], batch["actions"], batch["is_pad"], batch["eps"])
+    out = policy_forward(leaf, cfg, batch["qpos"], batch["image"], batch["actions"], batch["is_pad"], batch["eps"],
+                         dropout_p=dropout_p)
     out["loss"].backward()
     grads = {n: leaf[n].grad for n in names}
-    return dict(out={k: v.detach() for k, v in out.items()}, grads=grads)
+    return dict(out={k: (v.detach() if v is not None else None) for k, v in out.items()}, grads=grads)
 
 
 def adamw_step(p, g, m, v, step: int, lr: float, wd: float = 1e-4, b1: float = 0.9, b2: float = 0.999, eps: float = 1e-8):
@@ -481,3 +507,13 @@ class TemporalAggOracle:
         exp_weights = exp_weights / exp_weights.sum()                                      # :409
         exp_weights = torch.from_numpy(exp_weights).unsqueeze(dim=1)                       # :410
         return (actions_for_curr_step * exp_weights).sum(dim=0, keepdim=True)              # :411
+
+
+def temporal_agg_stream(T: int, nq: int, A: int, seed: int):
+    """Chunk stream of the temporal-ensemble fixtures, regenerated identically by the tests (only the outputs are
+    committed for the full-size case): N(0,1) chunks with single exact zeros planted in ~5 % of the rows."""
+    g = torch.Generator().manual_seed(seed)
+    chunks = torch.randn((T, 1, nq, A), generator=g)
+    zero_at = torch.rand((T, nq), generator=g) < 0.05
+    chunks[:, 0][zero_at] = chunks[:, 0][zero_at] * torch.tensor([0.0] + [1.0] * (A - 1))   # plant a single exact zero
+    return chunks

@@ -65,6 +65,19 @@ def test_temporal_agg_oracle_matches_golden_bit_exact():
         assert np.array_equal(out.numpy()[0], g["out"][t]), t
 
 
+def test_temporal_agg_full_size_golden_bit_exact():
+    """BASELINE shape (nq = 100, T = 400: a ring of nq chunks wraps 4x): the literal lines on the regenerated stream
+    reproduce the committed float64 outputs bit for bit."""
+    g = np.load(os.path.join(GOLDEN, "temporal_agg_full.npz"))
+    T, nq, A, seed = [int(x) for x in g["meta"]]
+    chunks = O.temporal_agg_stream(T, nq, A, seed)
+    assert float(chunks.double().sum()) == g["chunk_checksum"][0] and float((chunks == 0).sum()) == g["chunk_checksum"][1]
+    agg = O.TemporalAggOracle(T, nq, A)
+    for t in range(T):
+        out = agg.step(t, chunks[t])
+        assert np.array_equal(out.numpy()[0], g["out"][t]), t
+
+
 def test_temporal_agg_weights_oldest_first_and_zero_filter():
     """imitate_episodes.py:405-409: rows with any exact zero are dropped; index 0 (oldest) has the largest weight."""
     nq, A = 4, 3
