@@ -125,6 +125,15 @@ extern "C" int act_temporal_agg_step(float* ring, const float* chunks, const int
   return temporal_agg_step(ring, chunks, t, out, E, nq, A, k, ST(stream));
 }
 
+extern "C" int act_temporal_agg_step_ex(float* ring, const float* chunks, const int* t, double* out, int E, int nq, int A,
+                                        double k, const float* action_mean, const float* action_std, void* stream) {
+  return temporal_agg_step(ring, chunks, t, out, E, nq, A, k, ST(stream), action_mean, action_std);
+}
+extern "C" int act_chunk_select(const float* chunks, const int* t, double* out, int E, int nq, int A, int base_delay,
+                                const float* action_mean, const float* action_std, void* stream) {
+  return chunk_select(chunks, t, out, E, nq, A, base_delay, action_mean, action_std, ST(stream));
+}
+
 struct act_engine { Engine* eng; };
 
 extern "C" int act_engine_create(const act_engine_config* c, act_engine** out) {
@@ -211,6 +220,14 @@ extern "C" int act_engine_adamw_region(act_engine* e, int step, int region, int 
 extern "C" int act_engine_set_image_format(act_engine* e, int fmt) { return e->eng->set_image_format(fmt); }
 extern "C" int act_engine_set_concurrent(act_engine* e, int on) { return e->eng->set_concurrent(on != 0); }
 extern "C" int act_engine_set_lr(act_engine* e, float lr, float lr_backbone) { e->eng->set_lr(lr, lr_backbone); return 0; }
+extern "C" int act_engine_set_qpos_norm(act_engine* e, const float* mean, const float* std, void* stream) {
+  return e->eng->set_qpos_norm(mean, std, ST(stream));
+}
+extern "C" int act_engine_enable_qpos_norm(act_engine* e, int on) {
+  if (on && !e->eng->qnorm_set_) { set_error("act_engine_enable_qpos_norm: no statistics stored"); return -1; }
+  e->eng->qnorm_on_ = on != 0;
+  return 0;
+}
 extern "C" int act_engine_set_dropout(act_engine* e, float p, uint64_t seed) { return e->eng->set_dropout(p, seed); }
 extern "C" int act_engine_dropout_state(act_engine* e, float* p, uint64_t* seed, uint32_t* step) {
   unsigned long long s = 0;
@@ -242,6 +259,9 @@ extern "C" int act_engine_debug_buffer(act_engine* e, const char* name, void* ds
   return 0;
 }
 
+extern "C" int act_tc_set_skip_mask(uint32_t mask) { tc_set_skip_mask(mask); return 0; }
+extern "C" double act_tc_skipped_flops(void) { return tc_skipped_flops(); }
+extern "C" int act_tc_debug_timestamps(void* buf) { tc_debug_timestamps(static_cast<unsigned long long*>(buf)); return 0; }
 extern "C" int act_tc_profile_begin(void) { tc_profile_begin(); return 0; }
 extern "C" int act_tc_profile_end(double* total_ms, double* total_flops, int* launches, double* max_ms) {
   return tc_profile_end(total_ms, total_flops, launches, max_ms);

@@ -105,6 +105,7 @@ class Engine {
   bool dp_bb_pending_ = false;
   cudaStream_t dp_main_st_ = nullptr;
   int dp_inline_from_ = 0;                       // CVAE layers >= this index are updated inside cvae_bwd, the rest at its end
+  bool inline_opt_on_ = false;
   int inline_opt_step_ = 0;                      // > 0 while backward_and_step runs: cvae_bwd updates each layer as soon as its gradients are final
   long long cvae_layer_off_[16] = {0}, cvae_layer_n_[16] = {0};
   // backward(0) + adamw() with the optimiser of each parameter region trailing that region's last weight gradient, so
@@ -142,6 +143,12 @@ class Engine {
   // Train-mode dropout (transformer.py:194,197,202-203,219-222,254-266,284-293; detr/main.py:45).  p = 0 turns it off
   // (the reference's .eval()).  Masks are Philox functions of (seed, site, step, element) regenerated in the backward;
   // the step counter lives on the device and is bumped by every training forward (CUDA-graph replays draw new masks).
+  // Rollout pre-processing on the device (imitate_episodes.py:290, 370): inference calls z-score the raw qpos inside the
+  // proprio projection's operand load; mean = std = NULL switches it off.  Training calls are never touched (the dataset
+  // normalises, utils.py:160-166).  The vectors are copied.
+  int set_qpos_norm(const float* mean_dev, const float* std_dev, cudaStream_t st);
+  float *qnorm_mean_ = nullptr, *qnorm_std_ = nullptr;
+  bool qnorm_on_ = false, qnorm_set_ = false;
   int set_dropout(float p, unsigned long long seed);
   int dropout_state(float* p, unsigned long long* seed, uint32_t* step);   // synchronises
   enum : uint32_t { SITE_ENC = 0x100, SITE_CVAE = 0x200, SITE_DEC = 0x300 };   // + 8 * layer + {0 attn, 1 out-proj, 2 ffn hidden, 3 ffn out, 4 cross attn, 5 cross out-proj}

@@ -325,7 +325,7 @@ int Engine::cvae_bwd(cudaStream_t st) {
     if (dp_bb_pending_ && nl - 1 - l == dp_bb_slot_ && backbone_bwd_and_step(dp_main_st_)) return -1;
     if (enc_layer_bwd(cvae_w_[l], cvae_a_[l], nullptr, dx2, dx2b, gC_, gD_, Lc_, B, st, SITE_CVAE + 8 * l)) return -1;
     dx2 = gC_; dx2b = gD_;
-    if (inline_opt_step_ > 0 && l < 16 && l >= dp_inline_from_ && cvae_layer_n_[l] > 0) {
+    if (inline_opt_on_ && l < 16 && l >= dp_inline_from_ && cvae_layer_n_[l] > 0) {
       // this layer's gradients are final and nothing below reads its weights: update it under the remaining layers
       cudaStream_t wg = wg_gather(st, NWG);
       if (grads_ready(cvae_layer_off_[l], cvae_layer_n_[l], wg)) return -1;
@@ -496,7 +496,7 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
   }
   struct Guard {                                            // the hook is only live inside this call
     Engine* e;
-    ~Guard() { e->grads_cb_ = nullptr; e->grads_cb_user_ = nullptr; e->inline_opt_step_ = 0; e->dp_bb_pending_ = false; e->dp_fused_ = false; e->dp_inline_from_ = 0; tc_set_sm_reserve(0); }
+    ~Guard() { e->grads_cb_ = nullptr; e->grads_cb_user_ = nullptr; e->inline_opt_on_ = false; e->inline_opt_step_ = 0; e->dp_bb_pending_ = false; e->dp_fused_ = false; e->dp_inline_from_ = 0; tc_set_sm_reserve(0); }
   } guard{this};
   grads_cb_ = cb; grads_cb_user_ = cb_user; opt_step_ = step;
   dp_fused_ = p2p; dp_site_ = 0; if (p2p) dp_ranges_.clear();
@@ -520,9 +520,9 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
   if (fork_side(st)) return -1;
   auto cvae_branch = [&]() -> int {
     if (cfg_.no_encoder) return 0;                          // encoder=None: no CVAE branch, region R_CVAE is empty
-    inline_opt_step_ = step;
+    inline_opt_step_ = step; inline_opt_on_ = true;     // (step may be 0 = "the device counter decides": a flag, not the step, gates the updates)
     const int rc = cvae_bwd(side_);
-    inline_opt_step_ = 0;
+    inline_opt_step_ = 0; inline_opt_on_ = false;
     if (rc) return -1;
     // CVAE region: the encoder layers were updated inside cvae_bwd, the token projections / latent_proj follow here
     cudaStream_t wg = wg_gather(side_, NWG);

@@ -40,6 +40,7 @@ int Engine::alloc_workspace() {
   one_ = A_(float, 8);
   drop_step_dev_ = reinterpret_cast<uint32_t*>(A_(float, 8));
   opt_step_dev_ = reinterpret_cast<int*>(A_(float, 8));
+  qnorm_mean_ = A_(float, 128); qnorm_std_ = A_(float, 128);
   { float one = 1.f; cudaMemcpy(one_, &one, sizeof(float), cudaMemcpyHostToDevice); }
   // packed conv operands + folded BN
   for (int k = 0; k < cfg_.num_cameras; ++k) {
@@ -479,6 +480,15 @@ int Engine::dec_cross_fwd(int B, cudaStream_t st) {
   return 0;
 }
 
+int Engine::set_qpos_norm(const float* mean_dev, const float* std_dev, cudaStream_t st) {
+  ACT_CHECK(!mean_dev == !std_dev, "set_qpos_norm: mean and std must be given together");
+  qnorm_on_ = mean_dev != nullptr;
+  if (!qnorm_on_) return 0;
+  qnorm_set_ = true;
+  ACT_CUDA(cudaMemcpyAsync(qnorm_mean_, mean_dev, sizeof(float) * cfg_.state_dim, cudaMemcpyDeviceToDevice, st));
+  ACT_CUDA(cudaMemcpyAsync(qnorm_std_, std_dev, sizeof(float) * cfg_.state_dim, cudaMemcpyDeviceToDevice, st));
+  return 0;
+}
 int Engine::set_dropout(float p, unsigned long long seed) {
   ACT_CHECK(p >= 0.f && p < 1.f, "dropout probability must be in [0, 1)");
   drop_p_ = p; drop_seed_ = seed;
@@ -559,6 +569,7 @@ int Engine::forward(int B, const float* qpos, const float* image, const float* a
   g = SgemmArgs(); g.I = B; g.J = d; g.R = S; g.A = qpos; g.ai = act::lin(S); g.ar = act::lin(1);
   g.B = P("input_proj_robot_state.weight"); g.br = act::lin(1); g.bj = act::lin(S); g.bias = P("input_proj_robot_state.bias");
   g.C = src_ + d; g.ci = act::lin(1LL * L_ * d); g.cj = act::lin(1);
+  if (qnorm_on_ && !have_actions_) { g.a_mean = qnorm_mean_; g.a_std = qnorm_std_; }     // raw qpos from the rollout loop
   RUN(sgemm_generic(g, st));
   if (sc != st) tc_set_sm_reserve(sm_reserve_);
   for (int k = 0; k < cfg_.num_cameras; ++k)

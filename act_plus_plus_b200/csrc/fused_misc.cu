@@ -62,8 +62,12 @@ __global__ void __launch_bounds__(256) sgemm_short_kernel(SgemmArgs a) {
   const float* Bj = a.B + ioff(a.bj, j);
   const long long sa = a.ar.s, sb = a.br.s;
   float acc = 0.f;
+  if (a.a_mean) {
+    for (int r = 0; r < a.R; ++r) acc += ((__ldg(Ai + r * sa) - __ldg(a.a_mean + r)) / __ldg(a.a_std + r)) * __ldg(Bj + r * sb);
+  } else {
 #pragma unroll 4
-  for (int r = 0; r < a.R; ++r) acc += __ldg(Ai + r * sa) * __ldg(Bj + r * sb);
+    for (int r = 0; r < a.R; ++r) acc += __ldg(Ai + r * sa) * __ldg(Bj + r * sb);
+  }
   acc *= a.alpha;
   if (a.bias) acc += a.bias[j];
   float* c = a.C + ioff(a.ci, i) + ioff(a.cj, j);
@@ -108,6 +112,7 @@ int sgemm_generic(const SgemmArgs& a, cudaStream_t st) {
   if (a.I <= 0 || a.J <= 0) return 0;
   ACT_CHECK(a.I <= 65535, "sgemm_generic: too many rows");
   const bool flat = a.ar.rpb >= a.R && a.br.rpb >= a.R;
+  ACT_CHECK(!a.a_mean || (a.a_std && flat && a.R <= 64 && a.J >= 128), "sgemm: operand z-score is implemented for the short-reduction form only");
   if (flat && a.R <= 64 && a.J >= 128) {
     ACT_CUDA(launch_pdl(sgemm_short_kernel, dim3((a.J + 255) / 256, a.I), dim3(256), 0, st, a));
     ACT_CUDA(cudaGetLastError());

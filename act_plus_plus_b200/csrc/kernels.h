@@ -47,6 +47,8 @@ struct SgemmArgs {         // C(i,j) (+)= alpha * sum_r A(i,r) * B(r,j) (+ bias[
   const float* bias = nullptr;
   float alpha = 1.f;
   int accumulate = 0;
+  // optional z-score of the A operand along r (rollout pre-processing, imitate_episodes.py:290): (A - a_mean[r]) / a_std[r]
+  const float* a_mean = nullptr; const float* a_std = nullptr;
 };
 int sgemm_generic(const SgemmArgs& a, cudaStream_t st);
 int act_loss(const float* a_hat, const float* actions, long long act_bs, const uint8_t* is_pad, long long pad_bs,
@@ -99,7 +101,12 @@ struct DpPeers {           // device pointers valid on THIS device: index `rank`
 };
 int dp_barrier(const DpPeers& peers, uint32_t* epoch, uint32_t* status, int site, cudaStream_t st);
 int dp_adamw_step(const DpPeers& peers, const AdamWArgs& a, long long off, cudaStream_t st);
+// action_mean / action_std (optional, fp32 [A]): out = raw * std + mean in float64 (post_process, imitate_episodes.py:294)
 int temporal_agg_step(float* ring, const float* chunks, const int* t, double* out, int E, int nq, int A, double k,
-                      cudaStream_t st);
+                      cudaStream_t st, const float* action_mean = nullptr, const float* action_std = nullptr);
+// open-loop chunk replay (imitate_episodes.py:415): out[e] = chunks[e, j] with the real-robot base re-timing of :401
+// (the last two action dims are read base_delay steps later), optionally de-normalised; j = t[e] % (nq - base_delay)
+int chunk_select(const float* chunks, const int* t, double* out, int E, int nq, int A, int base_delay,
+                 const float* action_mean, const float* action_std, cudaStream_t st);
 
 }  // namespace act

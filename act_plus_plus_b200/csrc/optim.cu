@@ -82,7 +82,8 @@ int set_counter(int* counter, int value, bool increment, cudaStream_t st) {
 //   non-zero (imitate_episodes.py:405), 3. weights exp(-k*i)/sum over the kept rows in that order (float64),
 //   4. out[e][a] = sum_i float64(row_i[a]) * w_i.
 __global__ void temporal_agg_kernel(float* __restrict__ ring, const float* __restrict__ chunks, const int* __restrict__ tptr,
-                                    double* __restrict__ out, int nq, int A, double k) {
+                                    double* __restrict__ out, int nq, int A, double k, const float* __restrict__ amean,
+                                    const float* __restrict__ astd) {
   extern __shared__ unsigned char sm[];
   int* keep = reinterpret_cast<int*>(sm);                 // [nq] rank among kept rows or -1
   __shared__ int n_keep;
@@ -119,15 +120,37 @@ __global__ void temporal_agg_kernel(float* __restrict__ ring, const float* __res
       const float v = R[(1LL * (tp % nq) * nq + (t - tp)) * A + tid];
       acc += static_cast<double>(v) * (exp(-k * static_cast<double>(keep[i])) / wsum);
     }
+    // post_process (imitate_episodes.py:294): float64 raw action * float32 std + float32 mean, promoted to float64
+    if (astd) acc = acc * static_cast<double>(astd[tid]) + static_cast<double>(amean[tid]);
     out[1LL * e * A + tid] = acc;
   }
 }
 
-int temporal_agg_step(float* ring, const float* chunks, const int* t, double* out, int E, int nq, int A, double k,
-                      cudaStream_t st) {
-  ACT_CHECK(A <= 128 && nq >= 1, "temporal_agg: action_dim <= 128");
+__global__ void chunk_select_kernel(const float* __restrict__ chunks, const int* __restrict__ tptr, double* __restrict__ out,
+                                    int E, int nq, int A, int base_delay, const float* __restrict__ amean,
+                                    const float* __restrict__ astd) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= E * A) return;
+  const int e = i / A, a = i % A;
+  const int j = tptr[e] % (nq - base_delay) + ((base_delay > 0 && a >= A - 2) ? base_delay : 0);
+  double v = static_cast<double>(chunks[(1LL * e * nq + j) * A + a]);
+  if (astd) v = v * static_cast<double>(astd[a]) + static_cast<double>(amean[a]);
+  out[i] = v;
+}
+int chunk_select(const float* chunks, const int* t, double* out, int E, int nq, int A, int base_delay,
+                 const float* action_mean, const float* action_std, cudaStream_t st) {
+  ACT_CHECK(base_delay >= 0 && base_delay < nq && A >= 2 && (!action_std == !action_mean), "chunk_select: bad arguments");
   if (E <= 0) return 0;
-  temporal_agg_kernel<<<E, 128, nq * sizeof(int), st>>>(ring, chunks, t, out, nq, A, k);
+  chunk_select_kernel<<<(E * A + 127) / 128, 128, 0, st>>>(chunks, t, out, E, nq, A, base_delay, action_mean, action_std);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int temporal_agg_step(float* ring, const float* chunks, const int* t, double* out, int E, int nq, int A, double k,
+                      cudaStream_t st, const float* action_mean, const float* action_std) {
+  ACT_CHECK(A <= 128 && nq >= 1 && (!action_std == !action_mean), "temporal_agg: action_dim <= 128, mean and std together");
+  if (E <= 0) return 0;
+  temporal_agg_kernel<<<E, 128, nq * sizeof(int), st>>>(ring, chunks, t, out, nq, A, k, action_mean, action_std);
   ACT_CUDA(cudaGetLastError());
   return 0;
 }

@@ -117,6 +117,9 @@ struct WgradLaunch {
 int tc_wgrad(const WgradLaunch& w, cudaStream_t stream);
 
 // CUDA-event timing of every tensor-core launch between begin and end (algorithmic FLOPs summed per launch)
+void tc_debug_timestamps(unsigned long long* buf);   // diagnostics: CTA 0 of every tc_kernel launch stamps %globaltimer into buf
+void tc_set_skip_mask(uint32_t mask);         // measurement: skip launches of kernel classes (1 gemm, 2 conv, 4 conv3, 8 wgrad, 16 attention)
+double tc_skipped_flops();                    // algorithmic FLOPs of the launches skipped since the mask was set
 void tc_profile_begin();
 void tc_profile_set_dump(const char* path);   // per-launch CSV written by tc_profile_end (empty: off)
 int tc_profile_end(double* total_ms, double* total_flops, int* launches, double* max_ms);

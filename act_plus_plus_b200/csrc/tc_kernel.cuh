@@ -82,7 +82,14 @@ struct TcParams {
   int debug;                            // experiment switches (ACT_TC_DEBUG): 1 = skip epilogue math+stores, 2 = skip TMA loads
   DropDesc drop;                        // EPI_DROPOUT: element index = row * drop_ld + column
   long long drop_ld;
+  unsigned long long* ts;               // diagnostics (act_tc_debug_timestamps): [0] = launch counter, then 8 stamps per launch
 };
+
+__device__ __forceinline__ unsigned long long tc_globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
 
 template <int MODE, int A_MN, int B_MN, int BN>
 struct TcCfg {
@@ -303,6 +310,13 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
   const int total_tiles = p.gx * p.gy * p.gz;
 
   // ---------------------------------------------------------------- setup (overlaps the previous kernel's tail)
+  // stage timestamps of CTA 0 (diagnostics only, p.ts == nullptr in production): slot claimed by thread 0
+  __shared__ unsigned long long* ts_slot;
+  if (p.ts != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+    ts_slot = p.ts + 1 + 8 * atomicAdd(p.ts, 1ull);
+    ts_slot[0] = tc_globaltimer();
+  }
+  const bool stamp = p.ts != nullptr && blockIdx.x == 0;
   pdl_trigger();
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&amap0);
@@ -317,7 +331,9 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (stamp && threadIdx.x == 0) ts_slot[1] = tc_globaltimer();
   pdl_wait();                                  // operands / residuals written by the previous kernel are visible from here
+  if (stamp && threadIdx.x == 0) ts_slot[2] = tc_globaltimer();
 
   if (warp == 0) {
     // ============================================================== TMA producer
@@ -408,6 +424,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
         for (int i = 0; i < c.nkb; ++i) {
           mbar_wait(&full_bar[s], ph);
           tc_fence_after();
+          if (stamp && lt == 0 && i == 0) ts_slot[3] = tc_globaltimer();
           // descriptors differ from the stage-0 / k-0 ones only in the 14-bit start-address field (16-byte units)
           const uint32_t soff = s * stage16;
           uint64_t ad = adesc0 + soff, bd = bdesc0 + soff;
@@ -423,6 +440,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
           if (++s == static_cast<uint32_t>(num_stages)) { s = 0; ph ^= 1; }
         }
         umma_commit(&tfull_bar[acc]);          // accumulator complete
+        if (stamp) ts_slot[4] = tc_globaltimer();
       }
     }
   } else {
@@ -463,6 +481,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
 
       mbar_wait(&tfull_bar[acc], (lt >> 1) & 1);
       tc_fence_after();
+      if (stamp && warp == 2 && lane == 0) ts_slot[5] = tc_globaltimer();
       const uint32_t tmem_acc = tmem_base + acc * Cfg::ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
 
 #pragma unroll 1
@@ -493,8 +512,10 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
   }
 
   // ---------------------------------------------------------------- teardown
+  if (stamp && warp == 2 && lane == 0) ts_slot[6] = tc_globaltimer();
   tc_fence_before();
   __syncthreads();
+  if (stamp && threadIdx.x == 0) ts_slot[7] = tc_globaltimer();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::TMEM_COLS);

@@ -126,6 +126,21 @@ int tc_profile_end(double* total_ms, double* total_flops, int* launches, double*
   return 0;
 }
 
+// Measurement switch (act_tc_set_skip_mask): launches of the selected kernel classes are skipped (their FLOPs are still
+// counted), so "serial step time with the class" minus "without it" gives the class's device time from two CUDA-graph
+// replays -- no per-launch event pair in the measurement.  Results of a step run this way are garbage by design.
+static uint32_t g_skip_mask = 0;
+static double g_skipped_flops = 0.0;
+enum { CLS_GEMM = 1, CLS_CONV = 2, CLS_CONV3 = 4, CLS_WGRAD = 8, CLS_ATTN = 16 };
+void tc_set_skip_mask(uint32_t m) { g_skip_mask = m; g_skipped_flops = 0.0; }
+double tc_skipped_flops() { return g_skipped_flops; }
+static bool skip_class(uint32_t cls) {
+  if (!(g_skip_mask & cls)) return false;
+  g_skipped_flops += g_next_flops;
+  return true;
+}
+static unsigned long long* g_ts = nullptr;
+void tc_debug_timestamps(unsigned long long* buf) { g_ts = buf; }
 static int g_sm_reserve = 0;
 static int oversub() { static int k = 0; if (!k) { const char* e = getenv("ACT_TC_OVERSUB"); k = e ? std::max(1, atoi(e)) : 1; } return k; }
 // SMs left free by the persistent launches that follow (a concurrent latency-bound branch runs there); 0 = use all.
@@ -166,9 +181,11 @@ static int launch_inst(dim3 tiles, int stages, cudaStream_t stream, const CUtens
   }
   { static int dbg = -1; if (dbg < 0) { const char* e = getenv("ACT_TC_DEBUG"); dbg = e ? atoi(e) : 0; } p.debug = dbg; }
   p.gx = static_cast<int>(tiles.x); p.gy = static_cast<int>(tiles.y); p.gz = static_cast<int>(tiles.z);
+  p.ts = g_ts;
   const long long total = 1LL * tiles.x * tiles.y * tiles.z;
   ACT_CHECK(total > 0 && total < (1LL << 30), "bad tile grid");
   const unsigned ctas = static_cast<unsigned>(std::min<long long>(total, 1LL * oversub() * num_sms()));
+  if (skip_class(MODE == MODE_GEMM ? CLS_GEMM : MODE == MODE_CONV ? CLS_CONV : CLS_WGRAD)) return 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
   ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(Cfg::THREADS), static_cast<size_t>(smem), stream, am[0], am[1], am[2], am[3], bm, p, stages));
@@ -177,10 +194,10 @@ static int launch_inst(dim3 tiles, int stages, cudaStream_t stream, const CUtens
   return 0;
 }
 
-// Tile width for a persistent launch.  Measured on B200 (tools/bench_kernels.py floor): one tcgen05.mma of M=128 costs
-// ~55 ns for N<=128 and ~75 ns for N=256 whatever N is, and a full-chip launch is bounded by L2->SM fill (~85 GB/s per
-// SM when all 148 load), so wide tiles win unless they leave SMs idle.  cost = rounds x (k-blocks x ns/k-block + tile
-// overhead); ties go to the wider tile.
+// Tile width for a persistent launch.  Measured on B200 (tools/bench_kernels.py floor, round 2: the issue loop no longer
+// bounds it): one M=128 tcgen05.mma costs 28 / 38 / 74 ns at N = 64 / 128 / 256 (ideal 16 / 33 / 65), and a full-chip
+// launch is bounded by L2->SM fill (~85 GB/s per SM when all 148 load), so wide tiles win unless they leave SMs idle.
+// cost = rounds x (k-blocks x ns/k-block + tile overhead); ties go to the wider tile.
 static int pick_bn(int N, long long row_tiles, int kblocks) {
   int best = 64;
   double best_cost = 1e30;
@@ -192,7 +209,7 @@ static int pick_bn(int N, long long row_tiles, int kblocks) {
     const double active = std::min<double>(1.0, double(tiles) / num_sms());
     const double kb = 16.0 + c / 8.0;                                   // KB of smem fill per k-block
     const double load_ns = kb * std::max(5.0, 12.0 * active);
-    const double mma_ns = c == 256 ? 300.0 : 225.0;
+    const double mma_ns = c == 256 ? 296.0 : c == 128 ? 152.0 : 112.0;
     const double cost = static_cast<double>(rounds) * (kblocks * std::max(load_ns, mma_ns) + 800.0 + 6.0 * c);
     if (cost <= best_cost * 1.0001) { best_cost = std::min(cost, best_cost); best = c; }
   }
@@ -214,7 +231,7 @@ void plan_splitk(int M, int N, int K, int* bn_out, int* ks_out) {
       const long long tiles = base * k;
       const long long rounds = (tiles + num_sms() - 1) / num_sms();
       const double active = std::min<double>(1.0, double(tiles) / num_sms());
-      const double t_kb = std::max((16.0 + c / 8.0) * std::max(5.0, 12.0 * active), c == 256 ? 300.0 : 228.0);
+      const double t_kb = std::max((16.0 + c / 8.0) * std::max(5.0, 12.0 * active), c == 256 ? 296.0 : c == 128 ? 152.0 : 112.0);
       const double cost = rounds * (((kb + k - 1) / k) * t_kb + t_epi);
       if (cost < best * 0.999) { best = cost; *bn_out = c; *ks_out = k; }
     }
@@ -373,6 +390,7 @@ static int launch_conv3(long long total, cudaStream_t stream, const CUtensorMap&
     configured = true;
   }
   const unsigned ctas = static_cast<unsigned>(std::min<long long>(total, 1LL * oversub() * num_sms()));
+  if (skip_class(CLS_CONV3)) return 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
   ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(320), static_cast<size_t>(Cfg::SMEM), stream, am, bm, p));
@@ -431,7 +449,7 @@ int tc_conv3(const ConvLaunch& c, cudaStream_t stream, int bn_hint) {
       if (c.Cout % cc) continue;
       const long long tiles = mtiles * (c.Cout / cc);
       const long long rounds = (tiles + num_sms() - 1) / num_sms();
-      const double cost = rounds * (p.cin_blocks * c.ntaps * 4 * (cc == 256 ? 75.0 : 56.0) + 1000.0 + 6.0 * cc);
+      const double cost = rounds * (p.cin_blocks * c.ntaps * 4 * (cc == 256 ? 74.0 : cc == 128 ? 38.0 : 28.0) + 1000.0 + 6.0 * cc);
       if (cost <= bc * 1.0001) { bc = std::min(bc, cost); bn = cc; }
     }
   }
@@ -473,7 +491,7 @@ int tc_wgrad(const WgradLaunch& w, cudaStream_t stream) {
   if (ks <= 0) {
     // persistent launch: rounds x (k-blocks per split x MMA time + epilogue); pick the split with the lowest cost
     const long long base = 1LL * ygroups * xt;
-    const double t_kb = (p.pix_per_box / 16) * 57.0, t_epi = 2500.0;
+    const double t_kb = (p.pix_per_box / 16) * (bn == 128 ? 38.0 : 28.0), t_epi = 2500.0;
     double best = 1e30;
     ks = 1;
     for (int c = 1; c <= std::min(96, p.num_k_blocks); ++c) {
@@ -509,6 +527,7 @@ static int launch_attn(const CUtensorMap& am, const CUtensorMap& bm, const AttnP
     configured = true;
   }
   const unsigned ctas = static_cast<unsigned>(std::min(tiles, num_sms()));
+  if (skip_class(CLS_ATTN)) return 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
   ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(256), static_cast<size_t>(Cfg::SMEM), stream, am, bm, p));
@@ -532,6 +551,7 @@ static int launch_attn_chunked(const CUtensorMap& am, const CUtensorMap& bm, con
     configured = true;
   }
   const unsigned ctas = static_cast<unsigned>(std::min(items, num_sms()));
+  if (skip_class(CLS_ATTN)) return 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
   ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(256), static_cast<size_t>(AttnCCfg::SMEM), stream, am, bm, p));

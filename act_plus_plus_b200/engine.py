@@ -208,8 +208,30 @@ class ActEngine:
         else:
             check(self.lib.act_engine_zero_grad(self._h, _stream()), "act_engine_zero_grad")
 
-    def backward_and_step(self, loss_grad: float = 1.0):
-        """loss.backward(); optimizer.step() as one call: each region's AdamW overlaps the remaining backward."""
+    def set_loss_grad(self, gvec: Optional[torch.Tensor]):
+        """Device vector d/d{l1, kl, loss} read by the following backward calls (None: the scalar loss_grad argument)."""
+        if gvec is not None:
+            assert gvec.is_cuda and gvec.dtype == torch.float32 and gvec.numel() == 3 and gvec.is_contiguous()
+        self._gvec = gvec                                  # keep alive while the engine points at it
+        check(self.lib.act_engine_set_loss_grad(self._h, gvec.data_ptr() if gvec is not None else None), "act_engine_set_loss_grad")
+
+    def join_lanes(self):
+        """The current stream waits for the engine's internal lanes (closes a graph capture after a forward)."""
+        check(self.lib.act_engine_join_lanes(self._h, _stream()), "act_engine_join_lanes")
+
+    def note_graph_step(self):
+        """Book-keeping after a CUDA-graph replay of backward+step (the device counters advanced inside the graph)."""
+        self._shared["step"] += 1
+        self._shared["version"] += 1
+        self._synced_version = self._shared["version"]
+
+    def backward_and_step(self, loss_grad: float = 1.0, advance_on_device: bool = False):
+        """loss.backward(); optimizer.step() as one call: each region's AdamW overlaps the remaining backward.
+        advance_on_device: the optimiser step number is taken from (and advanced in) the engine's device counter, so a
+        CUDA graph of this call stays correct on replay; the caller then does the host book-keeping (note_graph_step)."""
+        if advance_on_device:
+            check(self.lib.act_engine_backward_and_step(self._h, 0, float(loss_grad), _stream()), "act_engine_backward_and_step")
+            return
         self._shared["step"] += 1
         check(self.lib.act_engine_backward_and_step(self._h, self._shared["step"], float(loss_grad), _stream()),
               "act_engine_backward_and_step")
@@ -291,9 +313,13 @@ class ActEngine:
     def dp_connected(self) -> bool:
         return getattr(self, "_dp_world", 1) > 1
 
-    def backward_and_step_p2p(self, loss_grad: float = 1.0):
+    def backward_and_step_p2p(self, loss_grad: float = 1.0, advance_on_device: bool = False):
         """Data-parallel loss.backward(); optimizer.step() with the gradient exchange fused into the optimiser kernel
         over peer memory (act_engine_backward_and_step_p2p).  Every rank must call it for the same step."""
+        if advance_on_device:
+            check(self.lib.act_engine_backward_and_step_p2p(self._h, 0, float(loss_grad), _stream()),
+                  "act_engine_backward_and_step_p2p")
+            return
         self._shared["step"] += 1
         check(self.lib.act_engine_backward_and_step_p2p(self._h, self._shared["step"], float(loss_grad), _stream()),
               "act_engine_backward_and_step_p2p")

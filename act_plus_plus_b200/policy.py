@@ -357,7 +357,8 @@ class DETRVAE(nn.Module):
         self._pending = None
         eng.set_lr(lr, lr_backbone)
         sg = self._graphs.get(id(eng))
-        if sg is not None and self.use_graphs:
+        # (the NCCL-hook exchange counts its optimiser step on the host: it is launched directly, not replayed)
+        if sg is not None and self.use_graphs and (self._dp_group is None or eng.dp_connected):
             sg.gvec.copy_(g, non_blocking=True)
             if sg.bwd is None or getattr(sg, "lr", None) != (lr, lr_backbone):
                 eng.set_loss_grad(sg.gvec)
@@ -368,6 +369,8 @@ class DETRVAE(nn.Module):
                     warnings.warn(f"act_plus_plus_b200: CUDA-graph capture of backward+step failed ({ex}); launching directly")
                     self.use_graphs = False
                     sg.bwd = None
+                finally:
+                    eng.set_loss_grad(None)               # the graph keeps reading sg.gvec; eager calls use their own
             if sg.bwd is not None:
                 sg.bwd.replay()
                 eng.note_graph_step()

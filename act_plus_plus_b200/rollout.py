@@ -52,45 +52,130 @@ class TemporalEnsembler:
         return self.out
 
 
+class DeviceRollout:
+    """The rollout loop's per-step device work for E environments on ONE engine, with every pre/post-processing step of
+    imitate_episodes.py fused into kernels that already run (no eager torch op per step):
+      * `pre_process` (qpos z-score, :290, 370) inside the proprio projection's operand load (act_engine_set_qpos_norm),
+      * uint8 HWC frames -> /255 -> CHW -> ImageNet normalise inside the stem's image pack (utils.py:133-158, policy.py:268),
+      * `post_process` (action * std + mean, :294, 436) inside the ensemble / chunk-select kernel's float64 store,
+      * temporal_agg (:403-411) or open-loop chunk replay (:415) with the real-robot BASE_DELAY re-timing (:311-313, 401).
+    `submit()` / `step_submitted()` double-buffer the host->device copy of the NEXT observation under the current step."""
+
+    def __init__(self, eng, num_envs: int, stats: Optional[dict] = None, temporal_agg: bool = True, base_delay: int = 0,
+                 k: float = 0.01):
+        c = eng.cfg
+        assert num_envs <= c.batch_max, "engine workspace smaller than the number of environments"
+        assert not (temporal_agg and base_delay), "the reference re-times the base only in open-loop replay (imitate_episodes.py:311-313)"
+        self.eng, self.E, self.nq, self.A = eng, num_envs, c.num_queries, c.action_dim
+        self.temporal_agg, self.base_delay, self.k = temporal_agg, int(base_delay), float(k)
+        self.device = eng.device
+        self.lib = _lib.lib()
+        self.ring = torch.zeros((num_envs, self.nq, self.nq, self.A), dtype=torch.float32, device=self.device) if temporal_agg else None
+        self.out = torch.empty((num_envs, self.A), dtype=torch.float64, device=self.device)
+        self.t = torch.zeros(num_envs, dtype=torch.int32, device=self.device)
+        self.t_host = 0
+        self.chunks = None
+        self.a_mean = self.a_std = None
+        if stats is not None:
+            f = lambda v: torch.as_tensor(v, dtype=torch.float32).to(self.device).contiguous()
+            self.a_mean, self.a_std = f(stats["action_mean"]), f(stats["action_std"])
+            self._qm, self._qs = f(stats["qpos_mean"]), f(stats["qpos_std"])
+            check(self.lib.act_engine_set_qpos_norm(eng._h, self._qm.data_ptr(), self._qs.data_ptr(),
+                                                    torch.cuda.current_stream().cuda_stream), "act_engine_set_qpos_norm")
+            check(self.lib.act_engine_enable_qpos_norm(eng._h, 0), "act_engine_enable_qpos_norm")   # on only around our queries
+        self._copy_stream, self._slots, self._head, self._tail = None, [], 0, 0
+
+    def reset(self):
+        self.t.zero_(); self.t_host = 0
+        if self.ring is not None:
+            self.ring.zero_()
+
+    def step(self, qpos: torch.Tensor, image: torch.Tensor) -> torch.Tensor:
+        """qpos [E, S] raw (with stats) or normalised, image float [E, K, 3, H, W] in [0, 1] or uint8 [E, K, H, W, 3]
+        -> target action [E, A] float64 on the device (de-normalised when stats were given)."""
+        st = torch.cuda.current_stream().cuda_stream
+        am = self.a_mean.data_ptr() if self.a_mean is not None else None
+        asd = self.a_std.data_ptr() if self.a_std is not None else None
+        qf = 1 if self.temporal_agg else self.nq - self.base_delay
+        if self.t_host % qf == 0:
+            if self.a_mean is not None:
+                check(self.lib.act_engine_enable_qpos_norm(self.eng._h, 1), "act_engine_enable_qpos_norm")
+            try:
+                self.chunks = self.eng.forward(qpos, image)["a_hat"]        # [E, nq, A]
+            finally:
+                if self.a_mean is not None:
+                    check(self.lib.act_engine_enable_qpos_norm(self.eng._h, 0), "act_engine_enable_qpos_norm")
+        if self.temporal_agg:
+            check(self.lib.act_temporal_agg_step_ex(self.ring.data_ptr(), self.chunks.data_ptr(), self.t.data_ptr(),
+                                                    self.out.data_ptr(), self.E, self.nq, self.A, C.c_double(self.k), am, asd, st),
+                  "act_temporal_agg_step_ex")
+        else:
+            check(self.lib.act_chunk_select(self.chunks.data_ptr(), self.t.data_ptr(), self.out.data_ptr(), self.E, self.nq,
+                                            self.A, self.base_delay, am, asd, st), "act_chunk_select")
+        self.t += 1
+        self.t_host += 1
+        return self.out
+
+    # ---- host-fed loop: pinned observations in, double-buffered
+    def submit(self, h_qpos: torch.Tensor, h_image: torch.Tensor):
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+            self._slots = [dict(qpos=torch.empty(h_qpos.shape, dtype=h_qpos.dtype, device=self.device),
+                                image=torch.empty(h_image.shape, dtype=h_image.dtype, device=self.device),
+                                ready=torch.cuda.Event(), free=None) for _ in range(2)]
+        assert self._tail - self._head < 2, "two observations are already in flight: call step_submitted() first"
+        s = self._slots[self._tail % 2]
+        with torch.cuda.stream(self._copy_stream):
+            if s["free"] is not None:
+                self._copy_stream.wait_event(s["free"])
+            s["qpos"].copy_(h_qpos, non_blocking=True)
+            s["image"].copy_(h_image, non_blocking=True)
+            s["ready"].record(self._copy_stream)
+        self._tail += 1
+
+    def step_submitted(self) -> torch.Tensor:
+        assert self._head < self._tail, "nothing submitted"
+        s = self._slots[self._head % 2]
+        self._head += 1
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(s["ready"])
+        out = self.step(s["qpos"], s["image"])
+        ev = torch.cuda.Event(); ev.record(cur); s["free"] = ev
+        return out
+
+
 class BatchedRollout:
-    """One policy query per environment per step (query_frequency = 1 with temporal_agg, imitate_episodes.py:308-309)
-    followed by the ensemble; optional device-side pre/post-processing (qpos z-score :368-371, action
-    de-normalisation :436-438) so the only host traffic per step is observations in, [E, A] actions out."""
+    """Policy-level wrapper (imitate_episodes.py:307-310, 338-339, 368-438) for E environments sharded statically across
+    ranks: this rank's [lo, hi) environments run through one DeviceRollout on the policy's inference
+    engine; the only host traffic per step is observations in, [E_local, A] float64 actions out."""
 
     def __init__(self, policy, num_envs_global: int, rank: int = 0, world: int = 1, stats: Optional[dict] = None,
-                 temporal_agg: bool = True):
+                 temporal_agg: bool = True, base_delay: int = 0):
         self.policy = policy
         self.lo, self.hi = shard_range(num_envs_global, rank, world)
         self.E = self.hi - self.lo
         m = policy.model
         self.nq, self.A = m.num_queries, m.action_dim
-        self.temporal_agg = temporal_agg
-        self.ens = TemporalEnsembler(self.E, self.nq, self.A, device=m.device) if temporal_agg else None
-        self.stats = None
-        if stats is not None:
-            dev = m.device
-            self.stats = {k: torch.as_tensor(v, dtype=torch.float32, device=dev) for k, v in stats.items()}
+        self.temporal_agg, self.base_delay, self.stats = temporal_agg, base_delay, stats
+        self._dev = None
         self.t = 0
+
+    def _device_rollout(self, qpos, image) -> DeviceRollout:
+        eng = self.policy.model._engine_for(qpos, image, False)
+        if self._dev is None or self._dev.eng is not eng:
+            self._dev = DeviceRollout(eng, self.E, self.stats, self.temporal_agg, self.base_delay)
+            self._dev.t.fill_(self.t); self._dev.t_host = self.t
+        return self._dev
 
     def reset(self):
         self.t = 0
-        if self.ens is not None:
-            self.ens.reset()
+        if self._dev is not None:
+            self._dev.reset()
 
     @torch.inference_mode()
     def step(self, qpos: torch.Tensor, image: torch.Tensor) -> torch.Tensor:
-        """qpos [E_local, S] (raw if stats given, else already normalised), image [E_local, K, 3, H, W] in [0,1]
-        -> target action [E_local, A] float64 (de-normalised if stats given)."""
-        if self.stats is not None:
-            qpos = (qpos - self.stats["qpos_mean"]) / self.stats["qpos_std"]
-        if self.ens is not None:
-            chunks = self.policy(qpos, image)                               # [E, nq, A], queried every step (:308-309)
-            raw = self.ens.step(chunks, self.t)
-        else:                                                               # open-loop chunk replay (:397-415)
-            if self.t % self.nq == 0:
-                self._chunks = self.policy(qpos, image)
-            raw = self._chunks[:, self.t % self.nq].double()
+        """qpos [E_local, S] (raw if stats given, else already normalised), image [E_local, K, 3, H, W] in [0,1] (or uint8
+        [E_local, K, H, W, 3]) -> target action [E_local, A] float64 (de-normalised if stats given)."""
+        out = self._device_rollout(qpos, image).step(qpos, image)
         self.t += 1
-        if self.stats is not None:
-            raw = raw * self.stats["action_std"].double() + self.stats["action_mean"].double()
-        return raw
+        return out

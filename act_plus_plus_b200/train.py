@@ -2,12 +2,10 @@
 (batch sharded across ranks, gradients averaged with NCCL over NVLink while later backward stages still run)."""
 from __future__ import annotations
 
-import os
-
 import torch
 
 from .dp import GradReducer
-from .engine import R_BACKBONE, R_CVAE, R_DEAD, R_MAIN, ActEngine
+from .engine import R_BACKBONE, R_CVAE, R_MAIN, ActEngine
 
 
 def backward_data_parallel(eng: ActEngine, group, loss_grad: float = 1.0, bucket_elems: int = 0):
@@ -15,42 +13,14 @@ def backward_data_parallel(eng: ActEngine, group, loss_grad: float = 1.0, bucket
     its own stream, ordered after the compute stream at enqueue time), so the transfer of the transformer gradients
     overlaps the CVAE-encoder and backbone backward.  Regions are contiguous slices of the flat gradient buffer."""
     red = GradReducer(eng.flat_grads, group, bucket_elems)
-    # stage 4 = CVAE-encoder and backbone backward as two concurrent branches (ACT_DP_STAGES=123 keeps them serial,
-    # which starts the CVAE region's all-reduce earlier at the price of the lost overlap)
-    plan = (((1, (R_MAIN,)), (2, (R_CVAE,)), (3, (R_BACKBONE,))) if os.environ.get("ACT_DP_STAGES", "14") == "123"
-            else ((1, (R_MAIN,)), (4, (R_CVAE, R_BACKBONE))))
-    for stage, regions in plan:
+    # (used when loss.backward() and optimizer.step() stay separate calls; the fused step goes through
+    # backward_and_step_hooked / the peer-memory kernel)  stage 4 = CVAE-encoder and backbone backward as two branches
+    for stage, regions in ((1, (R_MAIN,)), (4, (R_CVAE, R_BACKBONE))):
         eng.backward(stage, loss_grad)
         for region in regions:
             off, n = eng.region(region)
             red.reduce(off, n)
     red.wait()
-
-
-def backward_and_step_data_parallel(eng: ActEngine, group, loss_grad: float = 1.0, bucket_elems: int = 0):
-    """Data-parallel loss.backward() + optimizer.step(): backward stage 1 (heads + transformer) -> all-reduce of that
-    region -> its AdamW on a side stream as soon as the reduction lands, all of it under backward stage 4 (CVAE encoder
-    || backbones); the two remaining regions are reduced and updated after stage 4."""
-    cur = torch.cuda.current_stream()
-    side = _side_stream(eng)
-    step = eng.begin_optimizer_step()
-    red_main = GradReducer(eng.flat_grads, group, bucket_elems)
-    eng.backward(1, loss_grad)
-    red_main.reduce(*eng.region(R_MAIN))
-    side.wait_stream(cur)                       # every read of the main-region weights (stage 1) is ordered before
-    with torch.cuda.stream(side):
-        red_main.wait()
-        eng.adamw_region(step, R_MAIN, 3)
-        eng.adamw_region(step, R_DEAD, 3)
-    eng.backward(4, loss_grad)
-    red = GradReducer(eng.flat_grads, group, bucket_elems)
-    for region in (R_CVAE, R_BACKBONE):
-        red.reduce(*eng.region(region))
-    red.wait()
-    eng.adamw_region(step, R_CVAE)
-    eng.adamw_region(step, R_BACKBONE)
-    cur.wait_stream(side)
-    eng.end_optimizer_step()
 
 
 def backward_and_step_hooked(eng: ActEngine, group, loss_grad: float = 1.0):
@@ -87,33 +57,70 @@ def _external_stream(ptr: int, device) -> "torch.cuda.Stream":
     return _EXT_STREAMS[key]
 
 
-_SIDE_STREAMS = {}
-
-
-def _side_stream(eng: ActEngine) -> "torch.cuda.Stream":
-    key = (id(eng), torch.cuda.current_device())
-    if key not in _SIDE_STREAMS:
-        _SIDE_STREAMS[key] = torch.cuda.Stream()
-    return _SIDE_STREAMS[key]
-
-
-def train_step(eng: ActEngine, qpos, image, actions, is_pad, eps=None, dp_group=None) -> torch.Tensor:
-    """Returns the device tensor [l1, kl, loss] of this rank's shard."""
+def train_step(eng: ActEngine, qpos, image, actions, is_pad, eps=None, dp_group=None, advance_on_device: bool = False) -> torch.Tensor:
+    """One optimisation step; returns the device tensor [l1, kl, loss] of this rank's shard.  The gradient clear runs
+    beside the forward, every parameter region's AdamW beside the remaining backward.  Data parallel: the exchange is
+    fused into the optimiser kernel over NVLink peer memory when `eng.dp_connect(group)` succeeded, NCCL all-reduces
+    enqueued from the engine's gradient-ready hook otherwise.  advance_on_device: see ActEngine.backward_and_step."""
     eng.zero_grad(overlap_forward=True)
     out = eng.forward(qpos, image, actions, is_pad, eps)
     if dp_group is None:
-        eng.backward_and_step(1.0)
+        eng.backward_and_step(1.0, advance_on_device=advance_on_device)
     elif eng.dp_connected:
-        # gradient exchange fused into the optimiser kernel over NVLink peer memory (eng.dp_connect(group) was called)
-        eng.backward_and_step_p2p(1.0)
-    elif os.environ.get("ACT_DP_HOOK", "1") == "1":
-        backward_and_step_hooked(eng, dp_group, 1.0)
-    elif os.environ.get("ACT_DP_OVERLAP_OPT", "1") == "1":
-        backward_and_step_data_parallel(eng, dp_group, 1.0)
+        eng.backward_and_step_p2p(1.0, advance_on_device=advance_on_device)
     else:
-        backward_data_parallel(eng, dp_group, 1.0)
-        eng.adamw_step()
+        backward_and_step_hooked(eng, dp_group, 1.0)
     return out["losses"]
+
+
+class GraphedTrainStep:
+    """`train_step` at fixed shapes as ONE CUDA graph (no tracing compiler: the engine's own launch sequence, with its
+    forked streams turned into parallel graph branches).  `step(batch)` copies the batch into static device buffers and
+    replays; the optimiser step number and the dropout step advance through device counters inside the graph, so every
+    replay is a genuine new step.  Falls back to direct launches when capture is not possible."""
+
+    def __init__(self, eng: ActEngine, example: dict, dp_group=None, warmup: int = 2, stream_priority: int = -1):
+        self.eng, self.group = eng, dp_group
+        self.static = {k: torch.empty_like(v, device=eng.device) for k, v in example.items()}
+        self.graph, self.losses = None, None
+        for k, v in example.items():
+            self.static[k].copy_(v)
+        for _ in range(max(1, warmup)):                      # eager steps: lazy host set-up, device counters seeded
+            self._direct(self.static)
+        torch.cuda.synchronize(eng.device)
+        native = dp_group is None or eng.dp_connected        # the NCCL-hook path counts its step on the host
+        try:
+            s = torch.cuda.Stream(device=eng.device, priority=stream_priority)
+            s.wait_stream(torch.cuda.current_stream(eng.device))
+            with torch.cuda.stream(s):
+                self._direct(self.static)
+            torch.cuda.current_stream(eng.device).wait_stream(s)
+            torch.cuda.synchronize(eng.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.losses = train_step(eng, self.static["qpos"], self.static["image"], self.static["actions"],
+                                         self.static["is_pad"], self.static["eps"], dp_group, advance_on_device=native)
+            self.graph, self._native = g, native
+            torch.cuda.synchronize(eng.device)
+        except Exception as ex:                              # capture is an optimisation, never a requirement
+            import warnings
+            warnings.warn(f"act_plus_plus_b200: CUDA-graph capture of the training step failed ({ex}); launching directly")
+            self.graph = None
+
+    def _direct(self, b):
+        return train_step(self.eng, b["qpos"], b["image"], b["actions"], b["is_pad"], b["eps"], self.group)
+
+    def step(self, batch: dict) -> torch.Tensor:
+        if self.graph is None:
+            return self._direct(batch)
+        for k, v in batch.items():
+            self.static[k].copy_(v, non_blocking=True)       # device->device (or pinned host->device), part of the step
+        self.graph.replay()
+        if self._native:
+            self.eng.note_graph_step()
+        else:
+            self.eng._shared["version"] += 1; self.eng._synced_version = self.eng._shared["version"]
+        return self.losses
 
 
 class InputPrefetcher:

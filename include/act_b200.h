@@ -117,6 +117,16 @@ int act_adamw_step(float* p, const float* g, float* m, float* v, void* shadow_bf
 int act_temporal_agg_step(float* ring, const float* chunks, const int* t, double* out, int E, int nq, int A, double k,
                           void* stream);
 
+/* Same with the de-normalisation of imitate_episodes.py:294 fused (post_process: action = raw * std + mean, float64 raw
+ * with float32 statistics): action_mean / action_std fp32 [A] device pointers (both or neither). */
+int act_temporal_agg_step_ex(float* ring, const float* chunks, const int* t, double* out, int E, int nq, int A, double k,
+                             const float* action_mean, const float* action_std, void* stream);
+/* Open-loop chunk replay (imitate_episodes.py:415 `raw_action = all_actions[:, t % query_frequency]`) with the real-robot
+ * base re-timing of :311-313, 401 (query_frequency = nq - base_delay; the last two action dims are read base_delay steps
+ * later: cat([a[:, :-D, :-2], a[:, D:, -2:]])) and the optional de-normalisation: out float64 [E, A]. */
+int act_chunk_select(const float* chunks, const int* t, double* out, int E, int nq, int A, int base_delay,
+                     const float* action_mean, const float* action_std, void* stream);
+
 /* ---- the policy engine: DETRVAE forward / backward / AdamW as one stream-ordered object -----------------------
  * Replaces detr/main.py:92-112 (build_ACT_model_and_optimizer), ACTPolicy.__call__ (policy.py:264-332),
  * loss.backward() / optimizer.step() of imitate_episodes.py:603-607.  Parameters, gradients and Adam moments are
@@ -223,6 +233,11 @@ int act_engine_set_lr(act_engine* e, float lr, float lr_backbone);
  * Masks are a counter-based function Philox4x32-10(seed; element / 8, site, step) regenerated wherever needed -- nothing
  * is stored; `step` is a device counter bumped by every training forward (CUDA-graph replays draw fresh masks).
  * Data-parallel ranks pass different seeds.  Applies to act_engine_forward calls WITH actions (and their backward). */
+/* Rollout pre-processing on the device (imitate_episodes.py:290, 370 `pre_process`): inference calls (actions == NULL)
+ * z-score the raw qpos inside the proprio projection, (qpos - mean) / std in fp32 like the reference; NULL, NULL = off. */
+int act_engine_set_qpos_norm(act_engine* e, const float* mean, const float* std, void* stream);
+/* host-side switch over the stored statistics (no device work): a rollout object turns it on around its own queries */
+int act_engine_enable_qpos_norm(act_engine* e, int on);
 int act_engine_set_dropout(act_engine* e, float p, uint64_t seed);
 int act_engine_dropout_state(act_engine* e, float* p, uint64_t* seed, uint32_t* step);   /* synchronises */
 /* The keep mask (uint8, 1 = kept) of elements [0, n) of dropout site `site` at `step`: the same function the kernels
@@ -248,6 +263,16 @@ int act_engine_debug_buffer(act_engine* e, const char* name, void* dst, int64_t 
 
 /* ---- measurement hook: CUDA-event timing of every tcgen05 kernel launched between begin and end on its own stream;
  *      returns summed device time, summed algorithmic FLOPs (2*M*N*K per launch), launch count, longest launch. */
+/* Differential timing: skip every launch of the selected tensor-core kernel classes (bit 0 GEMM, 1 tap-table conv,
+ * 2 halo-resident 3x3 conv, 3 conv weight gradient, 4 fused attention scores).  Timing a serial CUDA-graph replay of the
+ * step with and without a class gives that class's device time without per-launch events.  Outputs are garbage while a
+ * mask is set.  act_tc_skipped_flops: algorithmic FLOPs of the launches skipped since the mask was last set. */
+int act_tc_set_skip_mask(uint32_t mask);
+double act_tc_skipped_flops(void);
+/* Diagnostics: while buf != NULL, CTA 0 of every tc_kernel launch writes eight %globaltimer stamps (entry, set-up done,
+ * dependency wait over, first operands landed, last MMA issued, accumulator ready, epilogue done, exit) to
+ * buf[1 + 8 * n ..] with n = atomic counter buf[0] (uint64 device memory, zeroed by the caller). */
+int act_tc_debug_timestamps(void* buf);
 int act_tc_profile_begin(void);
 int act_tc_profile_set_dump(const char* csv_path);   /* optional per-launch CSV written by act_tc_profile_end */
 int act_tc_profile_end(double* total_ms, double* total_flops, int* launches, double* max_ms);

@@ -517,3 +517,45 @@ def temporal_agg_stream(T: int, nq: int, A: int, seed: int):
     zero_at = torch.rand((T, nq), generator=g) < 0.05
     chunks[:, 0][zero_at] = chunks[:, 0][zero_at] * torch.tensor([0.0] + [1.0] * (A - 1))   # plant a single exact zero
     return chunks
+
+
+# --------------------------------------------------------------------------------------
+# data ingest contract (utils.py:47-52, 60-175, 239-248), literal per-item restatement without h5py
+# --------------------------------------------------------------------------------------
+def batch_sampler_reference(batch_size, episode_len_l, sample_weights):
+    """utils.py:239-248 verbatim (numpy global RandomState)."""
+    sample_probs = np.array(sample_weights) / np.sum(sample_weights) if sample_weights is not None else None
+    sum_dataset_len_l = np.cumsum([0] + [np.sum(episode_len) for episode_len in episode_len_l])
+    while True:
+        batch = []
+        for _ in range(batch_size):
+            episode_idx = np.random.choice(len(episode_len_l), p=sample_probs)
+            step_idx = np.random.randint(sum_dataset_len_l[episode_idx], sum_dataset_len_l[episode_idx + 1])
+            batch.append(step_idx)
+        yield batch
+
+
+def episodic_getitem_reference(episodes, norm_stats, chunk_size, index):
+    """EpisodicDataset.__getitem__ (utils.py:60-175, ACT branch, no augmentation) over in-memory episodes
+    [dict(frames uint8 [T,K,H,W,3], qpos [T,S], action [T,A], sim bool)] -> (image f32 [K,3,H,W], qpos, action, is_pad)."""
+    episode_len = [e["action"].shape[0] for e in episodes]
+    cumulative_len = np.cumsum(episode_len)
+    episode_index = int(np.argmax(cumulative_len > index))                                  # :49
+    start_ts = int(index - (cumulative_len[episode_index] - episode_len[episode_index]))   # :50
+    ep = episodes[episode_index]
+    action = ep["action"]
+    max_episode_len = max(episode_len)
+    if ep["sim"]:
+        action, action_len = action[start_ts:], episode_len[episode_index] - start_ts      # :109-110
+    else:
+        action = action[max(0, start_ts - 1):]                                              # :112
+        action_len = episode_len[episode_index] - max(0, start_ts - 1)
+    padded_action = np.zeros((max_episode_len, action.shape[1]), dtype=np.float32)          # :116
+    padded_action[:action_len] = action
+    is_pad = np.zeros(max_episode_len)
+    is_pad[action_len:] = 1
+    padded_action, is_pad = padded_action[:chunk_size], is_pad[:chunk_size]                 # :121-122
+    image_data = torch.einsum("k h w c -> k c h w", torch.from_numpy(ep["frames"][start_ts])) / 255.0   # :139, 157
+    action_data = (torch.from_numpy(padded_action).float() - norm_stats["action_mean"]) / norm_stats["action_std"]   # :164
+    qpos_data = (torch.from_numpy(ep["qpos"][start_ts]).float() - norm_stats["qpos_mean"]) / norm_stats["qpos_std"]  # :166
+    return image_data, qpos_data, action_data, torch.from_numpy(is_pad).bool()

@@ -155,3 +155,39 @@ def test_dp_gradient_average_equals_full_batch_gloo(tmp_path):
     want = torch.stack([full["out"]["l1"], full["out"]["kl"], full["out"]["loss"]])
     assert torch.allclose(got["losses"], want, rtol=1e-5)
     assert got["acts"].shape == (3, 3) and torch.equal(got["acts"][:, 0], torch.tensor([0.0, 1.0, 1.0]))
+
+
+def test_batch_sampler_and_episode_pool_match_reference_contract():
+    """utils.py:239-248 (BatchSampler) and :60-175 (EpisodicDataset.__getitem__): same index stream under the same numpy
+    seed, and a gathered batch equals the per-item reference outputs (frames stay uint8 HWC: /255 + permute compared)."""
+    import numpy as np
+    import torch
+    from oracle import act_oracle as O
+    from act_plus_plus_b200.data import EpisodePool, batch_sampler
+    rs = np.random.RandomState(0)
+    K, Hh, Ww, S, A, chunk = 2, 6, 8, 14, 16, 20
+    lens = [[25, 31], [18]]                                  # two dataset dirs
+    episodes = []
+    for i, T in enumerate([25, 31, 18]):
+        episodes.append(dict(frames=rs.randint(0, 256, (T, K, Hh, Ww, 3), dtype=np.uint8), qpos=rs.randn(T, S).astype(np.float32),
+                             action=rs.randn(T, A).astype(np.float32), sim=(i != 1)))
+    stats = dict(qpos_mean=torch.randn(S), qpos_std=torch.rand(S) + 0.5, action_mean=torch.randn(A), action_std=torch.rand(A) + 0.5)
+    np.random.seed(123)
+    ref_it = O.batch_sampler_reference(5, lens, [0.7, 0.3])
+    ref_batches = [next(ref_it) for _ in range(4)]
+    np.random.seed(123)
+    it = batch_sampler(5, lens, [0.7, 0.3])
+    batches = [next(it) for _ in range(4)]
+    assert ref_batches == batches
+    pool = EpisodePool({k: v.numpy() for k, v in stats.items()}, chunk)
+    for e in episodes:
+        pool.add_episode(e["frames"], e["qpos"], e["action"], e["sim"])
+    assert len(pool) == 74
+    idx = batches[0] + [0, 24, 25, 55, 56, 73]              # include episode boundaries / last steps
+    b = pool.gather(idx)
+    assert b["image"].dtype == torch.uint8 and b["image"].shape == (len(idx), K, Hh, Ww, 3)
+    for n, i in enumerate(idx):
+        img, q, a, pad = O.episodic_getitem_reference(episodes, stats, chunk, i)
+        assert torch.equal(b["image"][n].permute(0, 3, 1, 2).float() / 255.0, img)
+        assert torch.equal(b["qpos"][n], q) and torch.equal(b["is_pad"][n], pad)
+        assert torch.equal(b["actions"][n], a), (i, (b["actions"][n] - a).abs().max())

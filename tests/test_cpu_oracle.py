@@ -122,3 +122,45 @@ def test_sinusoid_table_and_sine_embedding_shapes():
     assert pos.shape == (1, 512, 15, 20)
     # y embedding constant along x, x embedding constant along y (position_encoding.py:36-52)
     assert torch.equal(pos[0, :256, :, 0], pos[0, :256, :, 5]) and torch.equal(pos[0, 256:, 0, :], pos[0, 256:, 7, :])
+
+
+def test_bf16_operand_error_budget_of_the_backbone():
+    """Where the engine's a_hat error budget goes (GPU-measured on full_k1_b8: relative error 0.61 % at the layer4
+    features, 0.59 % after the encoder, 0.39 % after the decoder -- the transformer adds nothing net).  Emulating the
+    engine's roundings in the fp32 oracle reproduces that figure and splits it: bf16 weights alone 0.35 %, bf16 stored
+    activations alone 0.49 %, an fp32 identity trunk would only bring the total from 0.60 % to 0.50 %.  So the margin to
+    the 1e-2 tolerance is what "bf16 operands, fp32 accumulate" (BASELINE.json north_star) costs on this network, not a
+    defect of one kernel."""
+    import torch.nn.functional as F
+    cfg = O.make_cfg()
+    sd = O.init_state_dict(cfg, 3)
+    x0 = O.normalize_image(O.make_inputs(cfg, 1, 480, 640, 3)["image"])[:, 0]
+    bf = lambda t: t.bfloat16().float()
+
+    def run(rw, ra, ridt, rimg):
+        Wt = (lambda n: bf(sd[n])) if rw else (lambda n: sd[n])
+        A = bf if ra else (lambda t: t)
+        p = "backbones.0.0.body."
+        x = F.conv2d(bf(x0) if rimg else x0, Wt(p + "conv1.weight"), stride=2, padding=3)
+        x = F.max_pool2d(A(F.relu(O.frozen_bn(sd, p + "bn1.", x))), 3, 2, 1)
+        xi = x
+        for name, cin, cout, stride in O._RESNET_STAGES:
+            for blk in range(2):
+                q, s = f"{p}{name}.{blk}.", (stride if blk == 0 else 1)
+                out = A(F.relu(O.frozen_bn(sd, q + "bn1.", F.conv2d(x, Wt(q + "conv1.weight"), stride=s, padding=1))))
+                out = O.frozen_bn(sd, q + "bn2.", F.conv2d(out, Wt(q + "conv2.weight"), stride=1, padding=1))
+                idt = xi
+                if (q + "downsample.0.weight") in sd:
+                    idt = O.frozen_bn(sd, q + "downsample.1.", F.conv2d(x, Wt(q + "downsample.0.weight"), stride=s))
+                    idt = bf(idt) if ridt else idt
+                y = F.relu(out + idt)
+                xi, x = (bf(y) if ridt else y), A(y)
+        return xi
+
+    ref = run(False, False, False, False)
+    rel = lambda y: float((y - ref).norm() / ref.norm())
+    all_bf16, fp32_trunk = rel(run(True, True, True, True)), rel(run(True, True, False, True))
+    w_only, a_only = rel(run(True, False, False, False)), rel(run(False, True, True, False))
+    assert 4.5e-3 < all_bf16 < 7.5e-3, all_bf16              # the engine's measured 6.1e-3
+    assert 2.5e-3 < w_only < 4.5e-3 and 3.5e-3 < a_only < 6e-3, (w_only, a_only)
+    assert 0.75 < fp32_trunk / all_bf16 < 0.95, (fp32_trunk, all_bf16)

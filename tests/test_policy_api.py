@@ -10,9 +10,10 @@ pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
 
 
-def _policy_config(K=1, lr=1e-5):
-    # imitate_episodes.py:78-94
-    return {'lr': lr, 'num_queries': 100, 'kl_weight': 10, 'hidden_dim': 512, 'dim_feedforward': 3200,
+def _policy_config(K=1, lr=1e-5, dropout=0.0, **extra):
+    # imitate_episodes.py:78-94 (+ dropout 0 where a test compares against the deterministic goldens; the reference's
+    # default 0.1 is exercised by test_train_mode_dropout_and_eval_mode / tests/test_dropout.py)
+    return {'dropout': dropout, **extra, 'lr': lr, 'num_queries': 100, 'kl_weight': 10, 'hidden_dim': 512, 'dim_feedforward': 3200,
             'lr_backbone': 1e-5, 'backbone': 'resnet18', 'enc_layers': 4, 'dec_layers': 7, 'nheads': 8,
             'camera_names': [f'cam{k}' for k in range(K)], 'vq': False, 'vq_class': None, 'vq_dim': None,
             'action_dim': 16, 'no_encoder': False}
@@ -73,6 +74,90 @@ def test_train_step_like_imitate_episodes():
     assert out2["loss"].item() != loss.item()
 
 
+def test_train_mode_dropout_and_eval_mode():
+    """policy.train() applies the reference's dropout 0.1 to training calls (detr/main.py:45), policy.eval() is the
+    deterministic validation path (imitate_episodes.py:566-571)."""
+    from act_plus_plus_b200.policy import ACTPolicy
+    gold, cfg, sd, batch, K = _load_case("small_k1")
+    cfgd = _policy_config(K)
+    del cfgd["dropout"]                                   # default, as imitate_episodes.py builds the dict
+    policy = ACTPolicy(dict(cfgd, seed=3))
+    policy.deserialize({"model." + k: v for k, v in sd.items()})
+    assert policy.model.dropout_p == 0.1
+    policy.train()
+    with torch.no_grad():
+        a = policy(batch["qpos"], batch["image"], batch["actions"], batch["is_pad"])
+        b = policy(batch["qpos"], batch["image"], batch["actions"], batch["is_pad"])
+    assert abs(a["l1"].item() - b["l1"].item()) > 1e-5     # fresh masks every call
+    policy.eval()
+    with torch.inference_mode():
+        v = policy(batch["qpos"], batch["image"], batch["actions"], batch["is_pad"])
+    assert abs(v["kl"].item() - float(gold["kl"])) / float(gold["kl"]) < 1e-3
+    names = [n for n, _ in policy.named_parameters()]
+    assert "model.action_head.weight" in names and len(names) > 100 and len(list(policy.parameters())) == len(names)
+
+
+def test_fused_step_with_cuda_graphs_matches_separate_calls():
+    """args_override['fused_step']: loss.backward() is deferred to optimizer.step() (one overlapped engine call, replayed
+    from CUDA graphs from the third step on).  Six steps must land on the same parameters as the plain
+    backward-then-step policy (dropout 0, same reparametrisation noise)."""
+    from act_plus_plus_b200.policy import ACTPolicy
+    gold, cfg, sd, batch, K = _load_case("small_k1")
+    res = []
+    for fused in (False, True):
+        policy = ACTPolicy(_policy_config(K, lr=1e-3, fused_step=fused))
+        policy.deserialize({"model." + k: v for k, v in sd.items()})
+        policy.train()
+        opt = policy.configure_optimizers()
+        losses = []
+        for it in range(6):
+            torch.manual_seed(100 + it)                    # the policy draws eps from torch's generator (detr_vae.py:21)
+            out = policy(batch["qpos"], batch["image"], batch["actions"], batch["is_pad"])
+            out["loss"].backward()
+            opt.step()
+            opt.zero_grad()
+            losses.append(out["loss"].item())
+        torch.cuda.synchronize()
+        if fused:
+            assert policy.model._graphs, "the fused policy did not capture its step graphs"
+            assert all(g.fwd is not None and g.bwd is not None for g in policy.model._graphs.values())
+        res.append((losses, policy.serialize()["model.action_head.weight"].clone(), policy.model._master.step_count))
+    (la, wa, sa), (lb, wb, sb) = res
+    assert sa == sb == 6
+    assert abs(la[0] - lb[0]) <= 1e-5 * abs(la[0])
+    assert all(abs(x - y) <= 2e-2 * abs(x) for x, y in zip(la, lb)), (la, lb)     # Adam amplifies fp32 atomic-order noise
+    assert la[-1] < la[0]
+    moved = (wa - torch.from_numpy(np.asarray(sd["action_head.weight"])).cuda()).abs().mean().item()
+    assert moved > 1e-3 and (wa - wb).abs().mean().item() < 0.05 * moved
+
+
+def test_no_encoder_variant_through_the_policy():
+    """no_encoder=True (detr_vae.py:109-112, 373-377; policy.py:306-307): kl = 0, loss = l1, no `encoder.*` keys."""
+    from oracle import act_oracle as O
+    from act_plus_plus_b200.policy import ACTPolicy
+    gold = np.load(os.path.join(GOLDEN, "act_small_noenc_k1.npz"))
+    B, H, W, K, seed = [int(x) for x in gold["meta"]]
+    cfg = O.make_cfg(num_cameras=K, no_encoder=True)
+    sd = O.init_state_dict(cfg, seed)
+    batch = {k: v.cuda() for k, v in O.make_inputs(cfg, B, H, W, seed).items()}
+    policy = ACTPolicy(dict(_policy_config(K), no_encoder=True))
+    st = policy.deserialize({"model." + k: v for k, v in sd.items()})
+    assert not st.missing_keys and not st.unexpected_keys
+    assert policy.model.encoder is None and not any(k.startswith("model.encoder.") for k in policy.serialize())
+    policy.train()
+    out = policy(batch["qpos"], batch["image"], batch["actions"], batch["is_pad"])
+    assert out["kl"].item() == 0.0
+    assert abs(out["loss"].item() - float(gold["loss"])) / float(gold["loss"]) < 1e-3
+    out["loss"].backward()
+    policy.configure_optimizers().step()
+    a2, _, (mu, logvar), _, _ = policy.model(batch["qpos"], batch["image"], None, batch["actions"], batch["is_pad"])
+    assert mu is None and logvar is None
+    policy.eval()
+    with torch.inference_mode():
+        a_hat = policy(batch["qpos"], batch["image"])
+    assert a_hat.shape == (B, 100, 16)
+
+
 def test_inference_and_validation_calls():
     from act_plus_plus_b200.policy import ACTPolicy
     gold, cfg, sd, batch, K = _load_case("small_k3")
@@ -130,6 +215,36 @@ def test_batched_rollout_matches_reference_ensemble_lines():
         for e in range(E):
             ref = oracles[e].step(t, chunks[e][None])[0] * stats["action_std"].double() + stats["action_mean"].double()
             assert torch.allclose(out[e].cpu(), ref, rtol=1e-12, atol=1e-12), (t, e)
+
+
+def test_open_loop_replay_with_base_delay_matches_reference_lines():
+    """No temporal_agg, real-robot timing (imitate_episodes.py:307, 311-313, 401, 415): query every nq - BASE_DELAY steps,
+    all_actions = cat([a[:, :-D, :-2], a[:, D:, -2:]], 2), raw_action = all_actions[:, t % query_frequency]; uint8 frames,
+    raw qpos and de-normalisation handled on the device."""
+    from act_plus_plus_b200.rollout import BatchedRollout
+    from act_plus_plus_b200.policy import ACTPolicy
+    torch.manual_seed(0)
+    pol = ACTPolicy(dict(_policy_config(1), seed=6))
+    pol.eval()
+    E, H, W, D = 2, 96, 128, 13
+    nq, A = pol.model.num_queries, pol.model.action_dim
+    stats = dict(qpos_mean=torch.randn(14), qpos_std=torch.rand(14) + 0.5, action_mean=torch.randn(A), action_std=torch.rand(A) + 0.5)
+    ro = BatchedRollout(pol, num_envs_global=E, stats=stats, temporal_agg=False, base_delay=D)
+    qf = nq - D
+    g = torch.Generator().manual_seed(2)
+    all_actions = None
+    for t in range(qf + 5):
+        qpos = torch.randn((E, 14), generator=g).cuda()
+        u8 = torch.randint(0, 256, (E, 1, H, W, 3), generator=g, dtype=torch.uint8).cuda()
+        out = ro.step(qpos, u8)
+        if t % qf == 0:
+            img = (u8.permute(0, 1, 4, 2, 3).float() / 255.0).contiguous()
+            with torch.inference_mode():
+                a = pol((qpos - stats["qpos_mean"].cuda()) / stats["qpos_std"].cuda(), img).cpu()
+            all_actions = torch.cat([a[:, :-D, :-2], a[:, D:, -2:]], dim=2)                      # :401
+        raw = all_actions[:, t % qf].double()                                                   # :415
+        ref = raw * stats["action_std"].double() + stats["action_mean"].double()                # :294
+        assert torch.allclose(out.cpu(), ref, rtol=1e-12, atol=1e-12), t
 
 
 def test_input_prefetcher_delivers_batches_in_order():

@@ -183,3 +183,32 @@ def bench_attn():
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "attn":
     bench_attn()
+
+
+def bench_dw_sweep():
+    """Weight-gradient GEMMs (dW = dY^T X, both operands MN-major, fp32 atomic accumulation): time over split-K / tile width,
+    the data behind plan_splitk's cost model."""
+    shapes = [("dw_ffn1", 3200, 512, 2416), ("dw_ffn2", 512, 3200, 2416), ("dw_attn", 512, 512, 2416), ("dw_qk", 1024, 512, 2416),
+              ("dw_cvae_ffn1", 3200, 512, 816), ("dw_cvae_attn", 512, 512, 816), ("dw_dec_ffn1", 3200, 512, 800)]
+    for name, M, N, K in shapes:
+        a = torch.randn(K, M, device="cuda").bfloat16(); b = torch.randn(K, N, device="cuda").bfloat16()
+        out = torch.zeros(M, N, device="cuda", dtype=torch.float32)
+        epi = ops.make_epilogue(out_f32=out, ldc=N, atomic=True)
+        best = None
+        row = {}
+        for bn in (64, 128, 256):
+            for ks in (1, 2, 3, 4, 6, 8, 12, 16):
+                if ks > (K + 63) // 64:
+                    continue
+                t = graph_time(lambda: ops.tc_gemm_raw(M, N, K, 1, 1, a, 1, M, 0, 0, b, 1, N, 0, 0, epi, ks, bn, 0))
+                row[f"bn{bn}_ks{ks}"] = round(t, 2)
+                if best is None or t < best[0]:
+                    best = (t, bn, ks)
+        A, Bt = a.t(), b
+        ref = graph_time(lambda: torch.matmul(A, Bt))
+        print(json.dumps(dict(kind="dw_sweep", name=name, M=M, N=N, K=K, best_us=round(best[0], 2), best_bn=best[1], best_ks=best[2],
+                              cublas_us=round(ref, 2), us=row)), flush=True)
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "dw":
+    bench_dw_sweep()
