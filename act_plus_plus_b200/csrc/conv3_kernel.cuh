@@ -44,7 +44,7 @@ conv3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ C
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.gx * p.gy;
 
-  pdl_trigger();
+  if (!p.pdl_late) pdl_trigger();              // (see tc_kernel: the late trigger keeps dependents from squatting on SMs)
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&amap);
     prefetch_tmap(&bmap);
@@ -126,6 +126,7 @@ conv3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ C
         }
         umma_commit(&tfull[acc]);
       }
+      if (p.pdl_late) pdl_trigger();
     }
   } else {
     // ============================================================== epilogue warps (2..9): two per TMEM lane quadrant

@@ -108,6 +108,11 @@ class Engine {
   bool inline_opt_on_ = false;
   int inline_opt_step_ = 0;                      // > 0 while backward_and_step runs: cvae_bwd updates each layer as soon as its gradients are final
   long long cvae_layer_off_[16] = {0}, cvae_layer_n_[16] = {0};
+  // per camera: the layer4 conv weights (75 % of a ResNet-18's parameters) are a contiguous tail of the camera's span in
+  // R_BACKBONE.  Their gradients are final a quarter into the backbone backward (it runs layer4 -> stem), so inside
+  // backward_and_step they are folded, exchanged and updated early; only the small remainder trails the branch.
+  long long bb_l4_off_[8] = {0}, bb_l4_n_[8] = {0}, bb_rest_off_[8] = {0}, bb_rest_n_[8] = {0};
+  bool bb_early_ = false;                        // set while backbone_bwd_and_step runs
   // backward(0) + adamw() with the optimiser of each parameter region trailing that region's last weight gradient, so
   // the HBM-bound AdamW of the transformer / CVAE regions overlaps the tensor-bound backbone backward
   // grads_ready: data-parallel hook.  Called on the host while the step is enqueued, once per contiguous range of the
@@ -171,7 +176,7 @@ class Engine {
              const bf16* aux, cudaStream_t st, bool splitk = false, uint32_t drop = 0);
   int linear_dx(const bf16* dY, int M, const LinW& w, uint32_t flags, const float* res_f32, const bf16* aux, float* out_f32,
                 bf16* out_bf16, cudaStream_t st, bool splitk = false, float alpha = 1.f);
-  int linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cudaStream_t st);
+  int linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cudaStream_t st, bool shared_weight = false);
   // drop = dropout site of the attention weights (0 = none); P2 receives dropout(P) and multiplies V
   int attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv, const uint8_t* mask,
                bf16* P, bf16* O, int B, int Lq, int Lk, cudaStream_t st, bool v_on_aux = false, float* S = nullptr,

@@ -69,13 +69,16 @@ int Engine::linear_dx(const bf16* dY, int M, const LinW& w, uint32_t flags, cons
 }
 
 // dW[N,K] += dY^T X ; db[N] += colsum(dY)
-int Engine::linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cudaStream_t st) {
+// shared_weight: the same weight takes gradient from several calls of one step (input_proj, once per camera)
+int Engine::linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cudaStream_t st, bool shared_weight) {
   MatDesc A, B;
   A.ptr = dY; A.mn_major = 1; A.ld = w.N; B.ptr = X; B.mn_major = 1; B.ld = w.K;
   EpiDesc e;
   e.flags = EPI_OUT_F32 | EPI_ATOMIC; e.out_f32 = w.gw; e.ldc = w.K;
   int bn = 64, ks = 1;
   plan_splitk(w.N, w.K, M, &bn, &ks);
+  // one split and one contributor: plain (sector-wide) stores into the zeroed gradient instead of 6.5 MB of fp32 L2 atomics
+  if (ks == 1 && !shared_weight) e.flags = EPI_OUT_F32;
   ++launches_;
   cudaStream_t wg = wg_fork(st);                       // dY (from the arena) is final on st at this point
   if (tc_gemm(w.N, w.K, M, 1, 1, A, B, e, ks, wg, bn)) return -1;
@@ -290,7 +293,7 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
     ++launches_;
     ACT_CUDA(cudaGetLastError());
     const bf16* feat = cam_a_[k].blk[7].y;
-    if (linear_dwb(gtok, Mf, input_proj_, feat, st)) return -1;
+    if (linear_dwb(gtok, Mf, input_proj_, feat, st, cfg_.num_cameras > 1)) return -1;
     if (linear_dx(gtok, Mf, input_proj_, 0, nullptr, feat, nullptr, d_feat_ + 1LL * k * cfg_.batch_max * Hf_ * Wf_ * 512, st)) return -1;
   }
   return aux_join(st, 1);                            // the decoder self-attention backward (lane 1)
@@ -413,6 +416,15 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
       RUN(conv_dgrad(s1, ga, bw.c1.wpkt, e1, nullptr, st, bw.c1.wpkt2));
     }
     g = dx;
+    if (i == 6 && bb_early_ && folds.n > 0) {
+      // layer4's weight gradients are all staged: fold them, then exchange + update that range on the optimiser lane
+      // while the remaining three stages of the backward run (its packed operands are rebuilt with the others at the end)
+      cudaStream_t ol = wg_gather(st, NWG);
+      RUN(wgrad_fold_batched(folds, ol));
+      folds.n = 0;
+      if (grads_ready(bb_l4_off_[cam], bb_l4_n_[cam], ol)) return -1;
+      if (adamw_range(bb_l4_off_[cam], bb_l4_n_[cam], cfg_.lr_backbone, false, opt_step_, ol, 3)) return -1;
+    }
   }
   wg = wg_gather(st);
   RUN(wgrad_fold_batched(folds, wg));
@@ -450,13 +462,25 @@ int Engine::grads_ready(long long off, long long n, cudaStream_t st) {
 int Engine::backbone_bwd_and_step(cudaStream_t st) {
   dp_bb_pending_ = false;
   cgy_off_ = 0;
+  { static int early = -1; if (early < 0) { const char* e = getenv("ACT_BB_EARLY"); early = (e && e[0] == '1') ? 1 : 0; }   // opt-in: measured neutral at N=1, -0.4 % at N=2 (one more barrier site)
+    bb_early_ = early != 0 && cfg_.num_cameras <= 8 && concurrent_; }
   tc_set_sm_reserve(sm_reserve_);
   for (int k = 0; k < cfg_.num_cameras; ++k)
     if (backbone_bwd(k, cur_B_, st)) { tc_set_sm_reserve(0); return -1; }
   tc_set_sm_reserve(0);
   cudaStream_t wg = wg_gather(st, NWG);
-  if (grads_ready(region_off_[R_BACKBONE], region_n_[R_BACKBONE], wg)) return -1;
-  return adamw_region(R_BACKBONE, opt_step_, wg, dp_fused_ ? 6 : 3);
+  if (!bb_early_) {
+    if (grads_ready(region_off_[R_BACKBONE], region_n_[R_BACKBONE], wg)) return -1;
+    return adamw_region(R_BACKBONE, opt_step_, wg, dp_fused_ ? 6 : 3);
+  }
+  bb_early_ = false;
+  // the remainder of every camera's span (stem .. layer3): one barrier covers all of them on the peer-memory path
+  for (int k = 0; k < cfg_.num_cameras; ++k) {
+    if ((!dp_fused_ || k == 0) && grads_ready(bb_rest_off_[k], bb_rest_n_[k], wg)) return -1;
+    if (adamw_range(bb_rest_off_[k], bb_rest_n_[k], cfg_.lr_backbone, false, opt_step_, wg, dp_fused_ ? 6 : 3)) return -1;
+  }
+  if (dp_fused_) { dp_pack_pending_ = true; return 0; }     // re-pack after the closing barrier (every rank's slices landed)
+  return repack_conv_operands(wg);
 }
 
 int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsReadyFn cb, void* cb_user, bool p2p) {

@@ -278,6 +278,17 @@ void Engine::build_tensor_table() {
       }
     cvae_layer_off_[l] = lo; cvae_layer_n_[l] = hi - lo;
   }
+  for (int k = 0; k < cfg_.num_cameras && k < 8; ++k) {     // camera k's span of R_BACKBONE, split at the first layer4 tensor
+    const std::string pre = "backbones." + std::to_string(k) + ".0.body.", l4 = pre + "layer4.";
+    long long lo = -1, hi = -1, l4lo = -1;
+    for (auto& t : tensors_)
+      if (t.region == R_BACKBONE && t.name.compare(0, pre.size(), pre) == 0) {
+        if (lo < 0 || t.offset < lo) lo = t.offset;
+        hi = std::max(hi, t.offset + (t.numel + 7) / 8 * 8);
+        if (t.name.compare(0, l4.size(), l4) == 0 && (l4lo < 0 || t.offset < l4lo)) l4lo = t.offset;
+      }
+    bb_rest_off_[k] = lo; bb_rest_n_[k] = l4lo - lo; bb_l4_off_[k] = l4lo; bb_l4_n_[k] = hi - l4lo;
+  }
   for (size_t i = 0; i < tensors_.size(); ++i) index_[tensors_[i].name] = static_cast<int>(i);
 }
 

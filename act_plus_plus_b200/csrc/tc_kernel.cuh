@@ -82,6 +82,7 @@ struct TcParams {
   int debug;                            // experiment switches (ACT_TC_DEBUG): 1 = skip epilogue math+stores, 2 = skip TMA loads
   DropDesc drop;                        // EPI_DROPOUT: element index = row * drop_ld + column
   long long drop_ld;
+  int pdl_late;                         // 1: let the dependent kernel start when this CTA has issued its last MMA (not at entry)
   unsigned long long* ts;               // diagnostics (act_tc_debug_timestamps): [0] = launch counter, then 8 stamps per launch
 };
 
@@ -311,18 +312,22 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
 
   // ---------------------------------------------------------------- setup (overlaps the previous kernel's tail)
   // stage timestamps of CTA 0 (diagnostics only, p.ts == nullptr in production): slot claimed by thread 0
-  __shared__ unsigned long long* ts_slot;
+  unsigned long long*& ts_slot = *reinterpret_cast<unsigned long long**>(tmem_slot + 2);   // (inside the 16 bytes behind the barriers)
   if (p.ts != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
     ts_slot = p.ts + 1 + 8 * atomicAdd(p.ts, 1ull);
     ts_slot[0] = tc_globaltimer();
   }
   const bool stamp = p.ts != nullptr && blockIdx.x == 0;
-  pdl_trigger();
+  // Programmatic dependent launch.  Triggering at entry lets the next kernel's CTAs become resident at once -- but they then
+  // sit in griddepcontrol.wait holding a whole SM (ring + TMEM) for as long as this kernel runs (measured: CTAs resident
+  // 9-11 us for a 4.3 us launch period), which starves the other branches of a concurrent step.  The late trigger (after
+  // this CTA's last MMA has been issued) still hides the dependent's set-up under our last epilogue.
+  if (!p.pdl_late) pdl_trigger();
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&amap0);
     prefetch_tmap(&bmap);
     for (int s = 0; s < num_stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 8); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], (blockDim.x >> 5) - 2); }
     mbar_init(bres_bar, 1);
     fence_mbar_init();
   }
@@ -442,6 +447,7 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
         umma_commit(&tfull_bar[acc]);          // accumulator complete
         if (stamp) ts_slot[4] = tc_globaltimer();
       }
+      if (p.pdl_late) pdl_trigger();
     }
   } else {
     // ============================================================== epilogue warps (2..9)
@@ -449,7 +455,10 @@ tc_kernel(const __grid_constant__ CUtensorMap amap0, const __grid_constant__ CUt
     // dominate the step the epilogue is exposed latency, so its width matters more than its instruction count.
     const int q = warp & 3;                  // TMEM lane quadrant this warp may access
     const int r = q * 32 + lane;             // accumulator row handled by this thread
-    const int cbeg = ((warp - 2) >> 2) * (BN / 2), cend = cbeg + BN / 2;
+    // 8 epilogue warps (320 threads): two per quadrant, half of the columns each; 4 epilogue warps (192 threads, the
+    // SM-sharing launch form: two CTAs per SM must fit the register file): one per quadrant, all columns
+    const int halves = ((blockDim.x >> 5) - 2) >> 2;
+    const int cbeg = ((warp - 2) >> 2) * (BN / halves), cend = cbeg + BN / halves;
     uint32_t lt = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
       const TileCoord c = decode_tile<MODE, BN>(p, t);

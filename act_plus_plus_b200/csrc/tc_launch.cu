@@ -139,6 +139,7 @@ static bool skip_class(uint32_t cls) {
   g_skipped_flops += g_next_flops;
   return true;
 }
+static int pdl_late() { static int late = -1; if (late < 0) { const char* e = getenv("ACT_PDL_LATE"); late = (e && e[0] == '0') ? 0 : 1; } return late; }
 static unsigned long long* g_ts = nullptr;
 void tc_debug_timestamps(unsigned long long* buf) { g_ts = buf; }
 static int g_sm_reserve = 0;
@@ -169,11 +170,20 @@ static int launch_inst(dim3 tiles, int stages, cudaStream_t stream, const CUtens
   const int stage_bytes = bres ? Cfg::A_BYTES : Cfg::STAGE_BYTES;
   const int res_bytes = bres ? p.num_k_blocks * BN * 128 : 0;
   const int fit = std::min<int>(Cfg::MAX_STAGES, (200 * 1024 - res_bytes) / stage_bytes);
+  const int stages_in = stages;
   if (stages <= 0) stages = fit;
   stages = std::max(2, std::min(stages, std::min<int>(Cfg::MAX_STAGES, (max_smem - extra - res_bytes) / stage_bytes)));
   ACT_CHECK(stages * stage_bytes + res_bytes + extra <= max_smem, "resident weight operand does not fit in shared memory");
-  // never let two persistent CTAs share an SM (they would serialise on the TMEM allocation)
-  const int smem = std::max(stages * stage_bytes + res_bytes + extra, 116 * 1024);
+  // Two CTAs never share an SM when either needs more than half of TMEM (they would serialise on the allocation) or walks
+  // several tiles (it wants the whole ring).  Single-round launches with <= 256 TMEM columns (most of the batch-8 step:
+  // one tile per CTA, latency-bound) may share (ACT_TC_SHARE=1): a short ring per CTA, two CTAs of different branches
+  // per SM, one running MMAs while the other waits for its operands.
+  static int share = -1;
+  if (share < 0) { const char* e = getenv("ACT_TC_SHARE"); share = (e && e[0] == '1') ? 1 : 0; }
+  const long long total_tiles = 1LL * tiles.x * tiles.y * tiles.z;
+  const bool sharing = share && !bres && Cfg::TMEM_COLS <= 256 && total_tiles <= num_sms() && stages_in <= 0;
+  if (sharing) stages = std::min(stages, std::max(2, (104 * 1024 - extra) / stage_bytes));
+  const int smem = sharing ? stages * stage_bytes + extra : std::max(stages * stage_bytes + res_bytes + extra, 116 * 1024);
   static bool configured = false;     // per instantiation
   if (!configured) {
     ACT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
@@ -182,13 +192,14 @@ static int launch_inst(dim3 tiles, int stages, cudaStream_t stream, const CUtens
   { static int dbg = -1; if (dbg < 0) { const char* e = getenv("ACT_TC_DEBUG"); dbg = e ? atoi(e) : 0; } p.debug = dbg; }
   p.gx = static_cast<int>(tiles.x); p.gy = static_cast<int>(tiles.y); p.gz = static_cast<int>(tiles.z);
   p.ts = g_ts;
+  p.pdl_late = pdl_late();
   const long long total = 1LL * tiles.x * tiles.y * tiles.z;
   ACT_CHECK(total > 0 && total < (1LL << 30), "bad tile grid");
   const unsigned ctas = static_cast<unsigned>(std::min<long long>(total, 1LL * oversub() * num_sms()));
   if (skip_class(MODE == MODE_GEMM ? CLS_GEMM : MODE == MODE_CONV ? CLS_CONV : CLS_WGRAD)) return 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
-  ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(Cfg::THREADS), static_cast<size_t>(smem), stream, am[0], am[1], am[2], am[3], bm, p, stages));
+  ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(sharing ? 192 : Cfg::THREADS), static_cast<size_t>(smem), stream, am[0], am[1], am[2], am[3], bm, p, stages));
   if (g_prof.on) { cudaEventRecord(e1, stream); g_prof.ev.push_back(e0); g_prof.ev.push_back(e1); g_prof.flops.push_back(g_next_flops); g_prof.label.push_back(g_next_label); }
   ACT_CUDA(cudaGetLastError());
   return 0;
@@ -440,6 +451,7 @@ int tc_conv3(const ConvLaunch& c, cudaStream_t stream, int bn_hint) {
              aligned16(c.epi.res_bf16) && aligned16(c.epi.aux_bf16);
   p.vec32_ok = p.vec_ok && conv_out32(c);
   { static int dbg = -1; if (dbg < 0) { const char* e = getenv("ACT_TC_DEBUG"); dbg = e ? atoi(e) : 0; } p.debug = dbg; }
+  p.pdl_late = pdl_late();
   const long long mtiles = 1LL * p.tiles_w * p.tiles_h * c.NIMG;
   int bn = bn_hint;
   if (bn == 0) {

@@ -264,7 +264,10 @@ def test_temporal_agg_full_size_ring_wraps_bit_exact():
 
 
 @pytest.mark.parametrize("B,h,Lq,Lk,masked", [(2, 8, 302, 302, False), (2, 8, 102, 102, True), (3, 8, 100, 302, False),
-                                              (1, 8, 100, 100, False), (2, 8, 130, 320, True)])
+                                              (1, 8, 100, 100, False), (2, 8, 130, 320, True),
+                                              # long rows (3 cameras: 902 keys) -> chunked two-pass kernel, several query tiles per item
+                                              (2, 8, 902, 902, False), (1, 8, 100, 902, False), (1, 8, 300, 520, True),
+                                              (20, 8, 902, 902, False)])
 def test_attn_scores_fused_matches_torch(B, h, Lq, Lk, masked):
     """act_attn_scores: softmax(q k^T / 8 + key_padding_mask) and its backward with the score tile kept in TMEM, against
     plain fp32 torch on the same bf16 operands (nn.MultiheadAttention math, transformer.py:194,254-255)."""
