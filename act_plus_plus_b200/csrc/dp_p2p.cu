@@ -85,12 +85,16 @@ __host__ __device__ inline void dp_slice(long long n4, int rank, int world, long
 
 template <int WORLD, int U>
 __global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs a, long long off, float bc1_host, float rs_host,
-                                                       int ld_sys) {
+                                                       int mode) {
   if (a.abort_flag != nullptr && *a.abort_flag != 0u) return;    // a barrier of this step failed: leave every replica as it is
   float bc1, rsqrt_bc2;
   adam_bias(a, bc1_host, rs_host, &bc1, &rsqrt_bc2);
-  // WORLD > 0: compile-time rank count; WORLD == 0: run-time count.  U float4 chunks per thread and iteration: all
-  // U * world peer loads are issued before the first use (a remote load is ~2 us; bytes in flight set the NVLink rate).
+  // WORLD > 0: compile-time rank count; WORLD == 0: run-time count.  Each thread owns U float4 chunks per iteration and
+  // the loop is software-pipelined over two register buffers: the U * world peer gradient loads and the local p / m / v
+  // loads of iteration k+1 are issued BEFORE iteration k is computed and stored, so a remote load (~2 us) always has a
+  // full iteration of stores and math to hide behind (bytes in flight set the NVLink rate).
+  // mode bits (experiments, tools/dp_exchange_time.py): 1 = system-scope loads, 2 = read the local gradient W times
+  // instead of the peers' (what the loads cost without NVLink), 4 = store to the local replica only.
   constexpr int W = WORLD > 0 ? WORLD : DP_MAX_WORLD;
   const int world = WORLD > 0 ? WORLD : peers.world;
   const long long n4 = a.n / 4;
@@ -101,58 +105,72 @@ __global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs 
   const float inv_world = 1.f / static_cast<float>(world);
   const long long off4 = off / 4;                              // ranges are 16-byte aligned (checked on the host)
   const long long S = gridDim.x * 1LL * blockDim.x;
-  for (long long i0 = lo + blockIdx.x * 1LL * blockDim.x + threadIdx.x; i0 < hi; i0 += U * S) {
-    float4 gs[U][W];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const long long i = i0 + u * S;
-#pragma unroll
-      for (int j = 0; j < W; ++j)
-        if (j < world && i < hi) {
-          const float4* src = reinterpret_cast<const float4*>(peers.grads[j]) + off4 + i;
-          gs[u][j] = ld_sys ? ld_relaxed_sys_v4(src) : ld_cg_v4(src);
-        }
-    }
-    float4 p[U], m[U], v[U];
+  const bool ld_sys = mode & 1, ld_local = mode & 2, st_local = mode & 4;
+  struct Buf { float4 g[U][W]; float4 p[U], m[U], v[U]; };
+  auto issue = [&](Buf& b, long long i0) {
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long i = i0 + u * S;
       if (i < hi) {
-        p[u] = reinterpret_cast<const float4*>(a.p)[i];
-        m[u] = reinterpret_cast<const float4*>(a.m)[i];
-        v[u] = reinterpret_cast<const float4*>(a.v)[i];
+#pragma unroll
+        for (int j = 0; j < W; ++j)
+          if (j < world) {
+            const float4* src = reinterpret_cast<const float4*>(peers.grads[ld_local ? peers.rank : j]) + off4 + i;
+            b.g[u][j] = ld_sys ? ld_relaxed_sys_v4(src) : ld_cg_v4(src);
+          }
+        b.p[u] = reinterpret_cast<const float4*>(a.p)[i];
+        b.m[u] = reinterpret_cast<const float4*>(a.m)[i];
+        b.v[u] = reinterpret_cast<const float4*>(a.v)[i];
       }
     }
+  };
+  auto finish = [&](Buf& b, long long i0) {
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long i = i0 + u * S;
       if (i >= hi) continue;
-      float4 g = gs[u][0];
+      float4 g = b.g[u][0];
 #pragma unroll
       for (int j = 1; j < W; ++j)
-        if (j < world) { g.x += gs[u][j].x; g.y += gs[u][j].y; g.z += gs[u][j].z; g.w += gs[u][j].w; }
+        if (j < world) { g.x += b.g[u][j].x; g.y += b.g[u][j].y; g.z += b.g[u][j].z; g.w += b.g[u][j].w; }
       g.x *= inv_world; g.y *= inv_world; g.z *= inv_world; g.w *= inv_world;
-#define ADAM1(c)                                                            \
-      p[u].c *= decay;                                                      \
-      m[u].c = a.beta1 * m[u].c + (1.f - a.beta1) * g.c;                    \
-      v[u].c = a.beta2 * v[u].c + (1.f - a.beta2) * g.c * g.c;              \
-      p[u].c -= step_size * (m[u].c / (sqrtf(v[u].c) * rsqrt_bc2 + a.eps));
+      float4 p = b.p[u], m = b.m[u], v = b.v[u];
+#define ADAM1(c)                                                  \
+      p.c *= decay;                                               \
+      m.c = a.beta1 * m.c + (1.f - a.beta1) * g.c;                \
+      v.c = a.beta2 * v.c + (1.f - a.beta2) * g.c * g.c;          \
+      p.c -= step_size * (m.c / (sqrtf(v.c) * rsqrt_bc2 + a.eps));
       ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
 #undef ADAM1
-      reinterpret_cast<float4*>(a.m)[i] = m[u];
-      reinterpret_cast<float4*>(a.v)[i] = v[u];
+      reinterpret_cast<float4*>(a.m)[i] = m;
+      reinterpret_cast<float4*>(a.v)[i] = v;
       uint2 o;
       {
-        __nv_bfloat162 l2 = __floats2bfloat162_rn(p[u].x, p[u].y), h2 = __floats2bfloat162_rn(p[u].z, p[u].w);
+        __nv_bfloat162 l2 = __floats2bfloat162_rn(p.x, p.y), h2 = __floats2bfloat162_rn(p.z, p.w);
         o.x = *reinterpret_cast<uint32_t*>(&l2); o.y = *reinterpret_cast<uint32_t*>(&h2);
       }
 #pragma unroll
       for (int j = 0; j < W; ++j) {
-        if (j < world) {
-          reinterpret_cast<float4*>(peers.params[j])[off4 + i] = p[u];
+        if (j < world && (!st_local || j == peers.rank)) {
+          reinterpret_cast<float4*>(peers.params[j])[off4 + i] = p;
           if (a.shadow) reinterpret_cast<uint2*>(peers.shadow[j])[off4 + i] = o;
         }
       }
+    }
+  };
+  {
+    Buf b0, b1;
+    long long i0 = lo + blockIdx.x * 1LL * blockDim.x + threadIdx.x;
+    const long long stride = U * S;
+    issue(b0, i0);
+    while (i0 < hi) {
+      issue(b1, i0 + stride);
+      finish(b0, i0);
+      i0 += stride;
+      if (i0 >= hi) break;
+      issue(b0, i0 + stride);
+      finish(b1, i0);
+      i0 += stride;
     }
   }
   // tail (n % 4 elements): rank 0, first threads of block 0
@@ -186,18 +204,29 @@ int dp_adamw_step(const DpPeers& peers, const AdamWArgs& a, long long off, cudaS
   const double bc1 = 1.0 - std::pow(static_cast<double>(a.beta1), a.step);
   const double bc2 = 1.0 - std::pow(static_cast<double>(a.beta2), a.step);
   const long long n4 = a.n / 4, slice = (n4 + peers.world - 1) / peers.world;
-  const int per_sm = a.background > 0 ? std::min(a.background, 8) : 8;
-  const int unroll = peers.world == 2 ? 4 : peers.world == 4 ? 2 : 1;
-  const int blocks = static_cast<int>(std::max<long long>(1, std::min<long long>((slice + 256LL * unroll - 1) / (256LL * unroll), 148LL * per_sm)));
+  static int mode = -1, per_sm_env = -1;
+  if (mode < 0) { const char* e = getenv("ACT_DP_LD_SYS"); mode = e ? atoi(e) & 7 : 0; }
+  if (per_sm_env < 0) { const char* e = getenv("ACT_DP_PERSM"); per_sm_env = e ? atoi(e) : 0; }
+  const int unroll = peers.world == 2 ? 2 : 1;
   const float f1 = static_cast<float>(bc1), f2 = static_cast<float>(1.0 / std::sqrt(bc2));
-  static int ld_sys = -1;
-  if (ld_sys < 0) { const char* e = getenv("ACT_DP_LD_SYS"); ld_sys = (e && e[0] == '1') ? 1 : 0; }
+  auto launch = [&](auto kern) -> int {
+    static int occ_tab[DP_MAX_WORLD + 1] = {};                   // resident 256-thread blocks per SM of each instantiation
+    int& occ = occ_tab[peers.world];
+    if (occ == 0) { ACT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 256, 0)); occ = std::max(1, occ); }
+    int per_sm = a.background > 0 ? std::min(a.background, occ) : occ;
+    if (per_sm_env > 0) per_sm = std::min(per_sm_env, occ);
+    const int blocks = static_cast<int>(std::max<long long>(1, std::min<long long>((slice + 256LL * unroll - 1) / (256LL * unroll), 148LL * per_sm)));
+    kern<<<blocks, 256, 0, st>>>(peers, a, off, f1, f2, mode);
+    return 0;
+  };
+  int rc;
   switch (peers.world) {
-    case 2: dp_adamw_kernel<2, 4><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2, ld_sys); break;
-    case 4: dp_adamw_kernel<4, 2><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2, ld_sys); break;
-    case 8: dp_adamw_kernel<8, 1><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2, ld_sys); break;
-    default: dp_adamw_kernel<0, 1><<<blocks, 256, 0, st>>>(peers, a, off, f1, f2, ld_sys); break;
+    case 2: rc = launch(dp_adamw_kernel<2, 2>); break;
+    case 4: rc = launch(dp_adamw_kernel<4, 1>); break;
+    case 8: rc = launch(dp_adamw_kernel<8, 1>); break;
+    default: rc = launch(dp_adamw_kernel<0, 1>); break;
   }
+  if (rc) return rc;
   ACT_CUDA(cudaGetLastError());
   return 0;
 }

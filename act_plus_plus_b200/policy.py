@@ -542,7 +542,10 @@ class ACTPolicy(nn.Module):
                 m._apply_mode(eng)
                 losses = eng.forward(qpos, image, actions, is_pad, eps)["losses"]
             return dict(l1=losses[0], kl=losses[1], loss=losses[2])
-        return m._engine_for(qpos, image, False).forward(qpos, image)["a_hat"]
+        eng = m._engine_for(qpos, image, False)
+        if m.use_graphs and not torch.is_grad_enabled():
+            return eng.infer_graphed(qpos, image, tag="policy").clone()    # the graph's output buffer is reused by the next call
+        return eng.forward(qpos, image)["a_hat"]
 
     def configure_optimizers(self):
         return self.optimizer

@@ -101,7 +101,7 @@ class DeviceRollout:
             if self.a_mean is not None:
                 check(self.lib.act_engine_enable_qpos_norm(self.eng._h, 1), "act_engine_enable_qpos_norm")
             try:
-                self.chunks = self.eng.forward(qpos, image)["a_hat"]        # [E, nq, A]
+                self.chunks = self.eng.infer_graphed(qpos, image, tag=("rollout", self.a_mean is not None))        # [E, nq, A]
             finally:
                 if self.a_mean is not None:
                     check(self.lib.act_engine_enable_qpos_norm(self.eng._h, 0), "act_engine_enable_qpos_norm")
