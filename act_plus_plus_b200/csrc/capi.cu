@@ -55,6 +55,11 @@ extern "C" int act_conv_wgrad(int N, int H, int W, int Cin, int Cout, int KH, in
   ConvShape s{N, H, W, Cin, Cout, KH, stride, pad};
   return conv_wgrad(s, BF(x), BF(dy), dw, alpha, scale, ST(stream));
 }
+extern "C" int act_conv_wgrad_noalloc(int N, int H, int W, int Cin, int Cout, int KH, int stride, int pad, const void* x,
+                                      const void* dy, float* dw, float alpha, const float* scale, void* stream) {
+  ConvShape s{N, H, W, Cin, Cout, KH, stride, pad};
+  return conv_wgrad_noalloc(s, BF(x), BF(dy), dw, alpha, scale, ST(stream));
+}
 
 #define BFM(p) static_cast<bf16*>(p)
 extern "C" int act_ln_fwd(const float* t, const float* gamma, const float* beta, const float* pos, int L, float* y,

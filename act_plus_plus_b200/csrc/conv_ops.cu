@@ -265,4 +265,36 @@ int conv_wgrad(const ConvShape& s, const bf16* x, const bf16* dy, float* dw, flo
   return wgrad_fold_batched(jobs, stream);
 }
 
+// ---- the same weight gradient for callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc).  No counterpart in the reference.  The staging tile lives in a
+// file-scope device array of a fixed, modest size (2.25 MiB, held by every GPU that loads the library until exit): it covers
+// KH*KW*Cin*Cout <= 9*256*256, i.e. every resnet18 conv up to and including layer3.  Every call shares the array and
+// re-zeroes the part it uses on `stream` first, so consecutive calls on one stream are independent; calls that overlap on the
+// GPU (different streams, no ordering) race on it.
+static __device__ __align__(256) float g_wgrad_static[CONV_WGRAD_NOALLOC_MAX];
+static float* g_wgrad_static_ptr[64] = {};          // per device: the array's DEVICE address (its name is only a host stand-in)
+
+int conv_wgrad_noalloc(const ConvShape& s, const bf16* x, const bf16* dy, float* dw, float alpha, const float* scale,
+                       cudaStream_t stream) {
+  const int KK = s.KH * s.KH;
+  const long long n = 1LL * KK * s.Cin * s.Cout;
+  ACT_CHECK(n >= 1 && n <= CONV_WGRAD_NOALLOC_MAX,
+            "act_conv_wgrad_noalloc: KH*KW*Cin*Cout exceeds the static scratch (589824 floats = 9*256*256); use act_conv_wgrad");
+  int dev = -1;
+  ACT_CUDA(cudaGetDevice(&dev));
+  ACT_CHECK(dev >= 0 && dev < 64, "act_conv_wgrad_noalloc: device ordinal out of range");
+  if (!g_wgrad_static_ptr[dev]) {                   // set-up, once per device, with that device current
+    float* ptr = nullptr;
+    ACT_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_wgrad_static));
+    ACT_CHECK(ptr != nullptr, "act_conv_wgrad_noalloc: cudaGetSymbolAddress returned a null scratch address");
+    g_wgrad_static_ptr[dev] = ptr;
+  }
+  float* T = g_wgrad_static_ptr[dev];
+  ACT_CUDA(cudaMemsetAsync(T, 0, sizeof(float) * n, stream));      // the array keeps the previous call's sums
+  if (conv_wgrad_staged(s, x, dy, T, stream)) return -1;
+  FoldJobs jobs;
+  jobs.n = 1; jobs.job[0] = FoldJob{T, scale, dw, alpha, s.Cout, s.Cin, KK, 0};
+  return wgrad_fold_batched(jobs, stream);
+}
+
 }  // namespace act

@@ -24,6 +24,10 @@ struct FoldJob { const float* T; const float* scale; float* dw; float alpha; int
 struct FoldJobs { static constexpr int MAX = 64; int n = 0; FoldJob job[MAX]; };
 int conv_wgrad_staged(const ConvShape& s, const bf16* x, const bf16* dy, float* T, cudaStream_t stream);
 int wgrad_fold_batched(FoldJobs& jobs, cudaStream_t stream);   // dW[co][ci][kk] += alpha*scale[co]*T[kk][co][ci], all jobs in one launch
+// allocation-free variant (static device scratch, KK*Cin*Cout <= CONV_WGRAD_NOALLOC_MAX; calls overlapping on the GPU race)
+constexpr long long CONV_WGRAD_NOALLOC_MAX = 9LL * 256 * 256;
+int conv_wgrad_noalloc(const ConvShape& s, const bf16* x, const bf16* dy, float* dw, float alpha, const float* scale,
+                       cudaStream_t stream);
 int conv_wgrad(const ConvShape& s, const bf16* x, const bf16* dy, float* dw, float alpha, const float* scale,
                cudaStream_t stream);
 

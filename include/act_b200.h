@@ -65,6 +65,15 @@ int act_conv_dgrad(int N, int H, int W, int Cin, int Cout, int KH, int stride, i
 /* dw[Cout][Cin][KH][KW] (fp32) += alpha * scale[co] * sum_pixels dy * x  (atomic accumulation). */
 int act_conv_wgrad(int N, int H, int W, int Cin, int Cout, int KH, int stride, int pad, const void* x, const void* dy,
                    float* dw, float alpha, const float* scale, void* stream);
+/* Allocation-free variant of act_conv_wgrad.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments and result; the [KH*KW][Cout][Cin] fp32 staging tile lives in a static device array of 589824 floats
+ * (2.25 MiB per GPU that loads the library, held until exit), so KH*KW*Cin*Cout <= 9*256*256 (every resnet18 conv up to
+ * layer3); larger shapes return nonzero with a message in act_last_error().  The call performs no cudaMalloc / cudaFree.
+ * All calls share the array (each re-zeroes the part it uses on `stream`): calls that overlap on the GPU race. */
+#define ACT_CONV_WGRAD_NOALLOC_MAX_FLOATS 589824
+int act_conv_wgrad_noalloc(int N, int H, int W, int Cin, int Cout, int KH, int stride, int pad, const void* x,
+                           const void* dy, float* dw, float alpha, const float* scale, void* stream);
 
 /* ---- fused bandwidth-bound kernels (warp-shuffle reductions, 128-bit accesses) -------------------------------- */
 /* nn.LayerNorm(d) of transformer.py:200-201,261-263,35: y = LN(t)*gamma+beta (eps 1e-5), d in {256,512}.  Optional
