@@ -637,7 +637,7 @@ def run_ours(args):
 
 # DRAM traffic of the tensor-core kernels measured inside a WARM step (ncu --cache-control none, second step of
 # tools/profile_step.py): mean dram__bytes_read.sum + dram__bytes_write.sum per tcgen05 launch; keyed by (batch, cameras)
-TC_DRAM_WARM = {}
+TC_DRAM_WARM = {(8, 1): 7974248.0}     # bytes per tcgen05 launch (277 launches, 2208.9 MB per step; algorithmic 3149.6 MB)
 TC_DRAM_SOURCE = "profiles/r02_tc_dram_warm.md (ncu --cache-control none, warm step)"
 
 

@@ -14,6 +14,6 @@ timeout 900 ncu --cache-control none --clock-control none --metrics dram__bytes_
 # 3. --set full + source: the halo-resident conv of the inference step (layer1 pair conv and a 128-channel conv), the
 #    FFN up-projection GEMM (N = 256 tiles), and one training-step GEMM at batch 8
 timeout 900 ncu -k regex:conv3_kernel -s 13 -c 6 --set full --import-source on --clock-control none -f -o gpurun_out/ncu_full_conv3_infer python tools/profile_infer.py 128 2 > gpurun_out/ncu_full_conv3.log 2>&1; echo "ncu full conv3 rc=$?"
-timeout 900 ncu --kernel-name-base demangled -k regex:"tc_kernel<0, 0, 0, 256>" -s 6 -c 3 --set full --import-source on --clock-control none -f -o gpurun_out/ncu_full_gemm_infer python tools/profile_infer.py 128 2 > gpurun_out/ncu_full_gemm.log 2>&1; echo "ncu full gemm rc=$?"
-timeout 900 ncu --kernel-name-base demangled -k regex:"tc_kernel<0, 0, 0, 128>" -s 14 -c 4 --set full --import-source on --clock-control none -f -o gpurun_out/ncu_full_gemm_train python tools/profile_step.py 8 2 > gpurun_out/ncu_full_gemm_train.log 2>&1; echo "ncu full gemm train rc=$?"
+timeout 900 ncu --kernel-name-base demangled -k regex:"tc_kernel<.int.0, .int.0, .int.0, .int.256>" -s 6 -c 3 --set full --import-source on --clock-control none -f -o gpurun_out/ncu_full_gemm_infer python tools/profile_infer.py 128 2 > gpurun_out/ncu_full_gemm.log 2>&1; echo "ncu full gemm rc=$?"
+timeout 900 ncu --kernel-name-base demangled -k regex:"tc_kernel<.int.0, .int.0, .int.0, .int.128>" -s 14 -c 4 --set full --import-source on --clock-control none -f -o gpurun_out/ncu_full_gemm_train python tools/profile_step.py 8 2 > gpurun_out/ncu_full_gemm_train.log 2>&1; echo "ncu full gemm train rc=$?"
 ls -la gpurun_out/*.ncu-rep
