@@ -206,6 +206,17 @@ extern "C" int act_engine_dp_set_peers(act_engine* e, int rank, int world, void*
                                        void* const* shadow, void* const* signal) {
   return e->eng->dp_set_peers(rank, world, grads, params, shadow, signal);
 }
+extern "C" int act_engine_dp_use_buffers(act_engine* e, void* shadow, void* signal) { return e->eng->dp_use_buffers(shadow, signal); }
+extern "C" int64_t act_engine_dp_signal_bytes(void) { return Engine::DP_SIGNAL_BYTES; }
+extern "C" int act_engine_dp_set_multicast(act_engine* e, void* mc_grads, void* mc_params, void* mc_shadow) {
+  return e->eng->dp_set_multicast(mc_grads, mc_params, mc_shadow);
+}
+extern "C" int act_multimem_reduce_f32(const float* mc_src, float* dst_local, int64_t n, void* stream) {
+  return multimem_reduce_f32(mc_src, dst_local, n, ST(stream));
+}
+extern "C" int act_multimem_bcast_f32(float* mc_dst, const float* src_local, int64_t n, void* stream) {
+  return multimem_bcast_f32(mc_dst, src_local, n, ST(stream));
+}
 extern "C" int act_engine_backward_and_step_p2p(act_engine* e, int step, float loss_grad, void* stream) {
   return e->eng->backward_and_step(step, loss_grad, ST(stream), nullptr, nullptr, true);
 }

@@ -37,6 +37,21 @@ __device__ __forceinline__ float4 ld_cg_v4(const float4* p) {
   asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
   return v;
 }
+// NVLS (NVSwitch multicast) accesses on a multicast address that is bound to the SAME offset of every rank's buffer:
+// one load returns the switch-reduced sum over all ranks, one store lands in every rank's memory.  The link carries the
+// payload once per rank instead of once per (rank, peer) pair.
+__device__ __forceinline__ float4 multimem_ld_reduce_v4(const float4* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_v4(float4* p, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void multimem_st_b64(uint2* p, const uint2& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -95,7 +110,8 @@ __global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs 
   // full iteration of stores and math to hide behind (bytes in flight set the NVLink rate).
   // mode bits (experiments, tools/dp_exchange_time.py): 1 = system-scope loads, 2 = read the local gradient W times
   // instead of the peers' (what the loads cost without NVLink), 4 = store to the local replica only.
-  constexpr int W = WORLD > 0 ? WORLD : DP_MAX_WORLD;
+  constexpr bool MC = WORLD < 0;                               // WORLD == -1: NVLS multicast, any rank count
+  constexpr int W = MC ? 1 : WORLD > 0 ? WORLD : DP_MAX_WORLD;
   const int world = WORLD > 0 ? WORLD : peers.world;
   const long long n4 = a.n / 4;
   long long lo, hi;
@@ -114,9 +130,13 @@ __global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs 
       if (i < hi) {
 #pragma unroll
         for (int j = 0; j < W; ++j)
-          if (j < world) {
-            const float4* src = reinterpret_cast<const float4*>(peers.grads[ld_local ? peers.rank : j]) + off4 + i;
-            b.g[u][j] = ld_sys ? ld_relaxed_sys_v4(src) : ld_cg_v4(src);
+          if (j < (MC ? 1 : world)) {
+            if (MC) {
+              b.g[u][0] = multimem_ld_reduce_v4(reinterpret_cast<const float4*>(peers.mc_grads) + off4 + i);
+            } else {
+              const float4* src = reinterpret_cast<const float4*>(peers.grads[ld_local ? peers.rank : j]) + off4 + i;
+              b.g[u][j] = ld_sys ? ld_relaxed_sys_v4(src) : ld_cg_v4(src);
+            }
           }
         b.p[u] = reinterpret_cast<const float4*>(a.p)[i];
         b.m[u] = reinterpret_cast<const float4*>(a.m)[i];
@@ -132,7 +152,7 @@ __global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs 
       float4 g = b.g[u][0];
 #pragma unroll
       for (int j = 1; j < W; ++j)
-        if (j < world) { g.x += b.g[u][j].x; g.y += b.g[u][j].y; g.z += b.g[u][j].z; g.w += b.g[u][j].w; }
+        if (!MC && j < world) { g.x += b.g[u][j].x; g.y += b.g[u][j].y; g.z += b.g[u][j].z; g.w += b.g[u][j].w; }
       g.x *= inv_world; g.y *= inv_world; g.z *= inv_world; g.w *= inv_world;
       float4 p = b.p[u], m = b.m[u], v = b.v[u];
 #define ADAM1(c)                                                  \
@@ -149,11 +169,16 @@ __global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs 
         __nv_bfloat162 l2 = __floats2bfloat162_rn(p.x, p.y), h2 = __floats2bfloat162_rn(p.z, p.w);
         o.x = *reinterpret_cast<uint32_t*>(&l2); o.y = *reinterpret_cast<uint32_t*>(&h2);
       }
+      if (MC) {
+        multimem_st_v4(reinterpret_cast<float4*>(peers.mc_params) + off4 + i, p);
+        if (a.shadow) multimem_st_b64(reinterpret_cast<uint2*>(peers.mc_shadow) + off4 + i, o);
+      } else {
 #pragma unroll
-      for (int j = 0; j < W; ++j) {
-        if (j < world && (!st_local || j == peers.rank)) {
-          reinterpret_cast<float4*>(peers.params[j])[off4 + i] = p;
-          if (a.shadow) reinterpret_cast<uint2*>(peers.shadow[j])[off4 + i] = o;
+        for (int j = 0; j < W; ++j) {
+          if (j < world && (!st_local || j == peers.rank)) {
+            reinterpret_cast<float4*>(peers.params[j])[off4 + i] = p;
+            if (a.shadow) reinterpret_cast<uint2*>(peers.shadow[j])[off4 + i] = o;
+          }
         }
       }
     }
@@ -195,6 +220,33 @@ __global__ void __launch_bounds__(256) dp_adamw_kernel(DpPeers peers, AdamWArgs 
   if (threadIdx.x == 0) __threadfence_system();
 }
 
+__global__ void multimem_reduce_kernel(const float4* __restrict__ mc, float4* __restrict__ dst, long long n4) {
+  for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * 1LL * blockDim.x)
+    dst[i] = multimem_ld_reduce_v4(mc + i);
+}
+__global__ void multimem_bcast_kernel(float4* __restrict__ mc, const float4* __restrict__ src, long long n4) {
+  for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * 1LL * blockDim.x)
+    multimem_st_v4(mc + i, src[i]);
+  __syncthreads();
+  if (threadIdx.x == 0) __threadfence_system();
+}
+int multimem_reduce_f32(const float* mc_src, float* dst_local, long long n, cudaStream_t st) {
+  ACT_CHECK(mc_src && dst_local && n > 0 && (n & 3) == 0, "multimem_reduce_f32: n must be a positive multiple of 4");
+  ACT_CHECK(((reinterpret_cast<uintptr_t>(mc_src) | reinterpret_cast<uintptr_t>(dst_local)) & 15) == 0, "multimem_reduce_f32: 16-byte alignment");
+  multimem_reduce_kernel<<<static_cast<int>(std::min<long long>(148 * 8, (n / 4 + 255) / 256)), 256, 0, st>>>(
+      reinterpret_cast<const float4*>(mc_src), reinterpret_cast<float4*>(dst_local), n / 4);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+int multimem_bcast_f32(float* mc_dst, const float* src_local, long long n, cudaStream_t st) {
+  ACT_CHECK(mc_dst && src_local && n > 0 && (n & 3) == 0, "multimem_bcast_f32: n must be a positive multiple of 4");
+  ACT_CHECK(((reinterpret_cast<uintptr_t>(mc_dst) | reinterpret_cast<uintptr_t>(src_local)) & 15) == 0, "multimem_bcast_f32: 16-byte alignment");
+  multimem_bcast_kernel<<<static_cast<int>(std::min<long long>(148 * 8, (n / 4 + 255) / 256)), 256, 0, st>>>(
+      reinterpret_cast<float4*>(mc_dst), reinterpret_cast<const float4*>(src_local), n / 4);
+  ACT_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // a.p / a.m / a.v point at this rank's own buffers at the START of the range (offset `off` floats into the flat buffers);
 // a.g and a.shadow's value are ignored except that a.shadow != nullptr asks for the bf16 shadow to be written.
 int dp_adamw_step(const DpPeers& peers, const AdamWArgs& a, long long off, cudaStream_t st) {
@@ -207,11 +259,12 @@ int dp_adamw_step(const DpPeers& peers, const AdamWArgs& a, long long off, cudaS
   static int mode = -1, per_sm_env = -1;
   if (mode < 0) { const char* e = getenv("ACT_DP_LD_SYS"); mode = e ? atoi(e) & 7 : 0; }
   if (per_sm_env < 0) { const char* e = getenv("ACT_DP_PERSM"); per_sm_env = e ? atoi(e) : 0; }
-  const int unroll = peers.world == 2 ? 2 : 1;
+  const bool mc = peers.mc_grads != nullptr && peers.mc_params != nullptr && (a.shadow == nullptr || peers.mc_shadow != nullptr);
+  const int unroll = mc ? 4 : peers.world == 2 ? 2 : 1;
   const float f1 = static_cast<float>(bc1), f2 = static_cast<float>(1.0 / std::sqrt(bc2));
   auto launch = [&](auto kern) -> int {
     static int occ_tab[DP_MAX_WORLD + 1] = {};                   // resident 256-thread blocks per SM of each instantiation
-    int& occ = occ_tab[peers.world];
+    int& occ = occ_tab[mc ? 0 : peers.world];
     if (occ == 0) { ACT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 256, 0)); occ = std::max(1, occ); }
     int per_sm = a.background > 0 ? std::min(a.background, occ) : occ;
     if (per_sm_env > 0) per_sm = std::min(per_sm_env, occ);
@@ -220,7 +273,8 @@ int dp_adamw_step(const DpPeers& peers, const AdamWArgs& a, long long off, cudaS
     return 0;
   };
   int rc;
-  switch (peers.world) {
+  switch (mc ? -1 : peers.world) {
+    case -1: rc = launch(dp_adamw_kernel<-1, 4>); break;
     case 2: rc = launch(dp_adamw_kernel<2, 2>); break;
     case 4: rc = launch(dp_adamw_kernel<4, 1>); break;
     case 8: rc = launch(dp_adamw_kernel<8, 1>); break;

@@ -131,6 +131,11 @@ class Engine {
   int dp_connect(int rank, int world, const void* blobs, int blob_bytes);         // map every peer's buffers
   int dp_set_peers(int rank, int world, void* const* grads, void* const* params, void* const* shadow, void* const* signal);
   int dp_preset_signal(int peer_rank, uint32_t epoch);
+  // symmetric-memory set-up (before dp_set_peers): move the bf16 shadow into caller-owned memory (contents copied) and use a
+  // caller-owned, zeroed flag block, so that all four exchange buffers can come from one symmetric allocator
+  int dp_use_buffers(void* shadow, void* signal);
+  int dp_set_multicast(void* mc_grads, void* mc_params, void* mc_shadow);      // after dp_set_peers; nullptrs switch it off
+  static constexpr long long DP_SIGNAL_BYTES = 4LL * DP_MAX_SITES * DP_MAX_WORLD;
   int dp_status();                                                                // 0 ok, 1 a barrier timed out (synchronises)
   int dp_world() const { return peers_.world; }
   int dp_slices(long long* off, long long* n, int cap) const {

@@ -432,7 +432,7 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
   const int H1 = fh_[1], W1 = fw_[1];
   bf16* gpool = cgy_alloc(1LL * B * H1 * W1 * 64);
   if (!gpool) return -1;
-  RUN(maxpool_bwd(g, ca.pidx, ca.y1, gpool, B, H1, W1, 64, st));
+  RUN(maxpool_bwd(g, ca.pidx, nullptr, gpool, B, H1, W1, 64, st));      // x == NULL: the arg-max record carries the ReLU mask
   wg = wg_fork(st);
   // dW1 over the same row-window operand the forward read (ca.xp is still resident): tmp[kh][co][kw*4+c]
   ACT_CUDA(cudaMemsetAsync(conv1_tmp_, 0, sizeof(float) * 64 * 64 * 7, wg));

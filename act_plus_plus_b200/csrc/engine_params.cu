@@ -511,14 +511,45 @@ int Engine::repack_conv_operands(cudaStream_t st) {
 // ------------------------------------------------------------------------------------------ peer-memory data parallel
 int Engine::dp_local(void** grads, void** params, void** shadow, void** signal) {
   ACT_CHECK(params_ && grads_ && shadow_, "dp: parameters / gradients not bound");
-  if (!dp_signal_) {
-    dp_signal_ = reinterpret_cast<uint32_t*>(alloc<float>(DP_MAX_SITES * DP_MAX_WORLD));      // own cudaMalloc, zeroed
+  if (!dp_signal_) dp_signal_ = reinterpret_cast<uint32_t*>(alloc<float>(DP_MAX_SITES * DP_MAX_WORLD));      // own cudaMalloc, zeroed
+  if (!dp_epoch_) {
     dp_epoch_ = reinterpret_cast<uint32_t*>(alloc<float>(DP_MAX_SITES));
     dp_status_ = reinterpret_cast<uint32_t*>(alloc<float>(4));
     ACT_CHECK(dp_signal_ && dp_epoch_ && dp_status_, "dp: flag allocation failed");
     ACT_CUDA(cudaDeviceSynchronize());                                                          // alloc's memset
   }
   *grads = grads_; *params = params_; *shadow = shadow_; *signal = dp_signal_;
+  return 0;
+}
+
+int Engine::dp_use_buffers(void* shadow, void* signal) {
+  ACT_CHECK(params_ && shadow_, "dp_use_buffers: engine not bound");
+  ACT_CHECK(peers_.world <= 1, "dp_use_buffers: call before the peers are connected");
+  ACT_CHECK(dp_signal_ == nullptr || signal == nullptr || signal == dp_signal_, "dp_use_buffers: flag block already allocated");
+  ACT_CHECK((reinterpret_cast<uintptr_t>(shadow) & 255) == 0 && (reinterpret_cast<uintptr_t>(signal) & 15) == 0, "dp_use_buffers: alignment");
+  ACT_CUDA(cudaDeviceSynchronize());
+  if (shadow && shadow != shadow_) {
+    ACT_CUDA(cudaMemcpy(shadow, shadow_, sizeof(bf16) * total_floats_, cudaMemcpyDeviceToDevice));
+    shadow_ = static_cast<bf16*>(shadow);                      // the workspace copy stays allocated but unused
+    setup_views();
+  }
+  if (signal && !dp_signal_) {
+    void *g, *p, *s, *sg;
+    dp_signal_ = static_cast<uint32_t*>(signal);
+    ACT_CUDA(cudaMemset(dp_signal_, 0, DP_SIGNAL_BYTES));
+    if (dp_local(&g, &p, &s, &sg)) return -1;                  // allocates the (local) epoch / status words
+  }
+  return 0;
+}
+
+int Engine::dp_set_multicast(void* mc_grads, void* mc_params, void* mc_shadow) {
+  ACT_CHECK(peers_.world > 1, "dp_set_multicast: connect the peers first");
+  ACT_CHECK(((reinterpret_cast<uintptr_t>(mc_grads) | reinterpret_cast<uintptr_t>(mc_params) | reinterpret_cast<uintptr_t>(mc_shadow)) & 15) == 0,
+            "dp_set_multicast: multicast addresses must be 16-byte aligned");
+  ACT_CHECK((mc_grads != nullptr) == (mc_params != nullptr) && (mc_grads != nullptr) == (mc_shadow != nullptr),
+            "dp_set_multicast: give all three multicast addresses or none");
+  peers_.mc_grads = static_cast<float*>(mc_grads); peers_.mc_params = static_cast<float*>(mc_params);
+  peers_.mc_shadow = static_cast<bf16*>(mc_shadow);
   return 0;
 }
 

@@ -232,46 +232,62 @@ int reparam_bwd(const float* dz, const float* eps, const float* logvar, const fl
 // ------------------------------------------------------------------------------------------ max-pool 3x3 / s2 / p1
 // NHWC bf16, 8 channels (16 B) per thread.  Forward also records the arg-max tap (first max in kh,kw scan order,
 // as torch) so the backward is a gather.
-__global__ void maxpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, int N,
-                                   int H, int W, int C, int Ho, int Wo) {
+__global__ void __launch_bounds__(256) maxpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, int N,
+                                                          int H, int W, int C, int Ho, int Wo) {
+  // one thread = 8 channels of TWO horizontally adjacent outputs: their windows share one input column, so a pair costs
+  // 15 loads instead of 18, and all of them are issued before the first compare
   pdl_trigger(); pdl_wait();
-  const int C8 = C / 8;
-  const long long total = 1LL * N * Ho * Wo * C8;
+  const int C8 = C / 8, Wo2 = (Wo + 1) / 2;
+  const long long total = 1LL * N * Ho * Wo2 * C8;
   for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
     const int c8 = static_cast<int>(i % C8);
     long long r = i / C8;
-    const int ox = static_cast<int>(r % Wo); r /= Wo;
+    const int ox = 2 * static_cast<int>(r % Wo2); r /= Wo2;
     const int oy = static_cast<int>(r % Ho);
     const int n = static_cast<int>(r / Ho);
-    float best[8];
-    uint8_t bi[8];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) { best[e] = -INFINITY; bi[e] = 0; }
+    uint4 v[3][5];
+    bool ok[3][5];
 #pragma unroll
     for (int kh = 0; kh < 3; ++kh) {
       const int iy = 2 * oy + kh - 1;
-      if (iy < 0 || iy >= H) continue;
 #pragma unroll
-      for (int kw = 0; kw < 3; ++kw) {
-        const int ix = 2 * ox + kw - 1;
-        if (ix < 0 || ix >= W) continue;
-        const uint4 v = *reinterpret_cast<const uint4*>(x + ((1LL * n * H + iy) * W + ix) * C + c8 * 8);
-        const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&v);
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float2 f = __bfloat1622float2(h2[e]);
-          if (f.x > best[2 * e]) { best[2 * e] = f.x; bi[2 * e] = kh * 3 + kw; }
-          if (f.y > best[2 * e + 1]) { best[2 * e + 1] = f.y; bi[2 * e + 1] = kh * 3 + kw; }
-        }
+      for (int kc = 0; kc < 5; ++kc) {                       // columns 2*ox-1 .. 2*ox+3; column 2*ox+1 feeds both outputs
+        const int ix = 2 * ox + kc - 1;
+        ok[kh][kc] = iy >= 0 && iy < H && ix >= 0 && ix < W;
+        if (ok[kh][kc]) v[kh][kc] = *reinterpret_cast<const uint4*>(x + ((1LL * n * H + iy) * W + ix) * C + c8 * 8);
       }
     }
-    uint4 o;
-    __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
 #pragma unroll
-    for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(best[2 * e], best[2 * e + 1]);
-    const long long ooff = ((1LL * n * Ho + oy) * Wo + ox) * C + c8 * 8;
-    *reinterpret_cast<uint4*>(y + ooff) = o;
-    if (idx) {
+    for (int o = 0; o < 2; ++o) {
+      if (ox + o >= Wo) break;
+      float best[8];
+      uint8_t bi[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { best[e] = -INFINITY; bi[e] = 0; }
+#pragma unroll
+      for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw) {                     // scan order kh, kw: the first maximum wins, as torch
+          const int kc = 2 * o + kw;
+          if (!ok[kh][kc]) continue;
+          const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&v[kh][kc]);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = __bfloat1622float2(h2[e]);
+            if (f.x > best[2 * e]) { best[2 * e] = f.x; bi[2 * e] = kh * 3 + kw; }
+            if (f.y > best[2 * e + 1]) { best[2 * e + 1] = f.y; bi[2 * e + 1] = kh * 3 + kw; }
+          }
+        }
+      uint4 ov;
+      __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&ov);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(best[2 * e], best[2 * e + 1]);
+      const long long ooff = ((1LL * n * Ho + oy) * Wo + ox + o) * C + c8 * 8;
+      *reinterpret_cast<uint4*>(y + ooff) = ov;
+      // tap 9 = "no tap": the window maximum is not positive, so the ReLU fused into the backward passes nothing; the
+      // backward then needs no look at x at all
+#pragma unroll
+      for (int e = 0; e < 8; ++e) if (!(best[e] > 0.f)) bi[e] = 9;
       uint2 p;
       p.x = bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24);
       p.y = bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24);
@@ -323,7 +339,7 @@ __global__ void maxpool_fwd_noidx_kernel(const bf16* __restrict__ x, bf16* __res
 int maxpool_fwd(const bf16* x, bf16* y, uint8_t* idx, int N, int H, int W, int C, cudaStream_t st) {
   ACT_CHECK(C % 8 == 0, "maxpool needs C % 8 == 0");
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
-  const long long total = 1LL * N * Ho * Wo * (C / 8);
+  const long long total = 1LL * N * Ho * ((Wo + 1) / 2) * (C / 8);       // both kernels: two adjacent outputs per thread
   const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
   if (idx) ACT_CUDA(launch_pdl(maxpool_fwd_kernel, dim3(blocks), dim3(256), 0, st, x, y, idx, N, H, W, C, Ho, Wo));
   else ACT_CUDA(launch_pdl(maxpool_fwd_noidx_kernel, dim3(blocks), dim3(256), 0, st, x, y, N, H, W, C, Ho, Wo));
@@ -331,61 +347,85 @@ int maxpool_fwd(const bf16* x, bf16* y, uint8_t* idx, int N, int H, int W, int C
   return 0;
 }
 
-// dx[n,iy,ix,c] = (x > 0 ? 1 : 0) * sum over windows whose arg-max is (iy,ix) of dy   (ReLU of the conv1 block fused)
-__global__ void maxpool_bwd_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx, const bf16* __restrict__ x,
-                                   bf16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo) {
+// dx[n,iy,ix,c] = (x > 0 ? 1 : 0) * sum over windows whose arg-max is (iy,ix) of dy   (ReLU of the conv1 block fused).
+// One thread = 8 channels of a 2x2 block of input pixels (rows 2k, 2k+1; columns 2j, 2j+1): exactly the four windows
+// (k..k+1, j..j+1) reach it, so their arg-max records and gradients are loaded once, all eight loads in flight together
+// (the per-pixel form walked up to four windows one dependent round trip at a time and was latency-bound: 71 us for a
+// 190 MB pass).  x may be NULL: the forward records tap 9 for windows whose maximum is not positive, which is the only
+// case the ReLU mask changes, so the 79 MB read of x is skipped on the engine's path.
+__global__ void __launch_bounds__(256) maxpool_bwd_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx,
+                                                          const bf16* __restrict__ x, bf16* __restrict__ dx, int N, int H,
+                                                          int W, int C, int Ho, int Wo) {
   pdl_trigger(); pdl_wait();
-  const int C8 = C / 8;
-  const long long total = 1LL * N * H * W * C8;
+  const int C8 = C / 8, H2 = (H + 1) / 2, W2 = (W + 1) / 2;
+  const long long total = 1LL * N * H2 * W2 * C8;
   for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
     const int c8 = static_cast<int>(i % C8);
     long long r = i / C8;
-    const int ix = static_cast<int>(r % W); r /= W;
-    const int iy = static_cast<int>(r % H);
-    const int n = static_cast<int>(r / H);
-    float acc[8];
+    const int j = static_cast<int>(r % W2); r /= W2;
+    const int k = static_cast<int>(r % H2);
+    const int n = static_cast<int>(r / H2);
+    uint2 rec[2][2];
+    uint4 g[2][2];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-    // windows containing row iy: 2*oy-1 <= iy <= 2*oy+1  ->  oy in [iy/2, (iy+1)/2]
-    for (int oy = iy / 2; oy <= (iy + 1) / 2; ++oy) {
-      if (oy < 0 || oy >= Ho) continue;
-      const int kh = iy - 2 * oy + 1;
-      if (kh < 0 || kh > 2) continue;
-      for (int ox = ix / 2; ox <= (ix + 1) / 2; ++ox) {
-        if (ox < 0 || ox >= Wo) continue;
-        const int kw = ix - 2 * ox + 1;
-        if (kw < 0 || kw > 2) continue;
-        const long long ooff = ((1LL * n * Ho + oy) * Wo + ox) * C + c8 * 8;
-        const uint2 p = *reinterpret_cast<const uint2*>(idx + ooff);
-        const uint4 g = *reinterpret_cast<const uint4*>(dy + ooff);
-        const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&g);
-        const int me = kh * 3 + kw;
+    for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const int id = ((e < 4 ? p.x : p.y) >> (8 * (e & 3))) & 0xff;
-          if (id == me) {
-            const float2 f = __bfloat1622float2(g2[e >> 1]);
-            acc[e] += (e & 1) ? f.y : f.x;
+      for (int b = 0; b < 2; ++b) {
+        const bool ok = k + a < Ho && j + b < Wo;
+        const long long ooff = ((1LL * n * Ho + min(k + a, Ho - 1)) * Wo + min(j + b, Wo - 1)) * C + c8 * 8;
+        rec[a][b] = ok ? *reinterpret_cast<const uint2*>(idx + ooff) : make_uint2(0x0f0f0f0fu, 0x0f0f0f0fu);
+        g[a][b] = ok ? *reinterpret_cast<const uint4*>(dy + ooff) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+    for (int py = 0; py < 2; ++py) {
+      const int iy = 2 * k + py;
+      if (iy >= H) continue;
+#pragma unroll
+      for (int px = 0; px < 2; ++px) {
+        const int ix = 2 * j + px;
+        if (ix >= W) continue;
+        float acc[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+        // window (k+a, j+b) sees pixel (2k+py, 2j+px) at tap (py - 2a + 1, px - 2b + 1); taps outside 0..2 do not exist
+#pragma unroll
+        for (int a = 0; a <= py; ++a)
+#pragma unroll
+          for (int b = 0; b <= px; ++b) {
+            const uint32_t me = static_cast<uint32_t>((py - 2 * a + 1) * 3 + (px - 2 * b + 1));
+            const uint32_t hit_lo = __vcmpeq4(rec[a][b].x, me * 0x01010101u), hit_hi = __vcmpeq4(rec[a][b].y, me * 0x01010101u);
+            const uint32_t gw[4] = {g[a][b].x, g[a][b].y, g[a][b].z, g[a][b].w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const uint32_t hit = ((e < 4 ? hit_lo : hit_hi) >> (8 * (e & 3))) & 1u;
+              const float f = __uint_as_float((e & 1) ? (gw[e >> 1] & 0xffff0000u) : (gw[e >> 1] << 16));
+              acc[e] += hit ? f : 0.f;
+            }
+          }
+        const long long xoff = ((1LL * n * H + iy) * W + ix) * C + c8 * 8;
+        if (x != nullptr) {
+          const uint4 xv = *reinterpret_cast<const uint4*>(x + xoff);
+          const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&xv);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = __bfloat1622float2(x2[e]);
+            if (!(f.x > 0.f)) acc[2 * e] = 0.f;
+            if (!(f.y > 0.f)) acc[2 * e + 1] = 0.f;
           }
         }
+        uint4 o;
+        __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(acc[2 * e], acc[2 * e + 1]);
+        *reinterpret_cast<uint4*>(dx + xoff) = o;
       }
     }
-    const long long xoff = ((1LL * n * H + iy) * W + ix) * C + c8 * 8;
-    const uint4 xv = *reinterpret_cast<const uint4*>(x + xoff);
-    const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&xv);
-    uint4 o;
-    __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const float2 f = __bfloat1622float2(x2[e]);
-      o2[e] = __floats2bfloat162_rn(f.x > 0.f ? acc[2 * e] : 0.f, f.y > 0.f ? acc[2 * e + 1] : 0.f);
-    }
-    *reinterpret_cast<uint4*>(dx + xoff) = o;
   }
 }
 int maxpool_bwd(const bf16* dy, const uint8_t* idx, const bf16* x, bf16* dx, int N, int H, int W, int C, cudaStream_t st) {
+  ACT_CHECK(C % 8 == 0, "maxpool needs C % 8 == 0");
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
-  const long long total = 1LL * N * H * W * (C / 8);
+  const long long total = 1LL * N * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
   const int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
   ACT_CUDA(launch_pdl(maxpool_bwd_kernel, dim3(blocks), dim3(256), 0, st, dy, idx, x, dx, N, H, W, C, Ho, Wo));
   ACT_CUDA(cudaGetLastError());

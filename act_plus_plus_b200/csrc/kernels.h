@@ -98,7 +98,15 @@ struct DpPeers {           // device pointers valid on THIS device: index `rank`
   float* params[DP_MAX_WORLD] = {nullptr};
   bf16* shadow[DP_MAX_WORLD] = {nullptr};
   uint32_t* signal[DP_MAX_WORLD] = {nullptr};     // [DP_MAX_SITES][DP_MAX_WORLD] epochs per rank
+  // NVLS multicast addresses (optional): one VA bound to the same offset of EVERY rank's buffer through the NVSwitch;
+  // when set, the exchange kernel uses multimem.ld_reduce / multimem.st instead of per-peer loads and stores
+  float* mc_grads = nullptr;
+  float* mc_params = nullptr;
+  bf16* mc_shadow = nullptr;
 };
+// diagnostics of the multicast mapping (tools/nvls_probe.py, tests): dst[i] = sum over ranks of src[i] / every rank's dst[i] = src[i]
+int multimem_reduce_f32(const float* mc_src, float* dst_local, long long n, cudaStream_t st);
+int multimem_bcast_f32(float* mc_dst, const float* src_local, long long n, cudaStream_t st);
 int dp_barrier(const DpPeers& peers, uint32_t* epoch, uint32_t* status, int site, cudaStream_t st);
 int dp_adamw_step(const DpPeers& peers, const AdamWArgs& a, long long off, cudaStream_t st);
 // action_mean / action_std (optional, fp32 [A]): out = raw * std + mean in float64 (post_process, imitate_episodes.py:294)

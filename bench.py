@@ -345,7 +345,9 @@ def infer_legs(eng, dev, envs, steps, rank, world, peaks, lib):
 def policy_api_leg(dev, B, steps, warmup, sd_src, host, fused):
     """The step as a user of the reference would write it (imitate_episodes.py:596-607): ACTPolicy(...) ->
     policy(qpos, image, actions, is_pad)['loss'].backward() -> optimizer.step() -> optimizer.zero_grad(), fed from pinned
-    host batches (H2D every step) with a loss read-back every step.  fused = args_override['fused_step']."""
+    host batches (H2D every step) with a loss read-back every step (an asynchronous copy into pinned memory that is read one
+    step later -- the reference loop itself only detaches the loss dict per step, imitate_episodes.py:608, so the host is
+    never made to wait for the step it has just enqueued).  fused = args_override['fused_step']."""
     import torch
     from act_plus_plus_b200.policy import ACTPolicy
     cfg = {'lr': 1e-5, 'num_queries': NQ, 'kl_weight': 10, 'hidden_dim': 512, 'dim_feedforward': 3200, 'lr_backbone': 1e-5,
@@ -366,6 +368,9 @@ def policy_api_leg(dev, B, steps, warmup, sd_src, host, fused):
     feed = [{k: v for k, v in hb.items() if k != "eps"} for hb in host]      # the policy draws its own reparametrisation noise
     pf = InputPrefetcher(feed[0], dev, depth=2)          # the package's loader-side helper: H2D of batch i+1 under step i
 
+    loss_pin = [torch.zeros(1).pin_memory() for _ in range(2)]
+    loss_ev = [torch.cuda.Event() for _ in range(2)]
+
     def run(n):
         last = 0.0
         pf.submit(feed[0])
@@ -378,8 +383,13 @@ def policy_api_leg(dev, B, steps, warmup, sd_src, host, fused):
             out["loss"].backward()
             opt.step()
             opt.zero_grad()
-            last = float(out["loss"].item())
-        return last
+            loss_pin[i & 1].copy_(out["loss"].detach().reshape(1), non_blocking=True)     # D2H of this step's loss ...
+            loss_ev[i & 1].record()
+            if i > 0:                                                                    # ... read once the NEXT step is enqueued
+                loss_ev[(i - 1) & 1].synchronize()
+                last = float(loss_pin[(i - 1) & 1][0])
+        loss_ev[(n - 1) & 1].synchronize()
+        return float(loss_pin[(n - 1) & 1][0])
 
     run(max(4, warmup))
     torch.cuda.synchronize()
@@ -523,7 +533,11 @@ def run_ours(args):
                 scaling="strong" if strong else "weak", vs_baseline=None, dtype="bf16", data="synthetic",
                 config=dict(workload=workload_name(B, K_CAM), global_batch=B * world, parallelism=f"dp{world}"),
                 notes=dict(cuda_graph=gs is not None,
-                           grad_exchange=("none" if world == 1 else "peer-memory reduce+AdamW+broadcast kernel over NVLink (csrc/dp_p2p.cu)"
+                           grad_exchange=("none" if world == 1 else
+                                          ("NVLS reduce+AdamW+broadcast kernel (multimem.ld_reduce / multimem.st through the NVSwitch, csrc/dp_p2p.cu)"
+                                           if getattr(eng, "_dp_nvls", False) else
+                                           "peer-memory reduce+AdamW+broadcast kernel over NVLink (csrc/dp_p2p.cu)"
+                                           + (f"; NVLS unavailable: {getattr(eng, '_dp_nvls_error', '')[:80]}" if getattr(eng, "_dp_nvls_error", None) else ""))
                                           if p2p else "NCCL all-reduce per range, overlapped with backward (ACT_DP_P2P=0)"),
                            l2="4 rotating input batches; parameters+Adam state (1.3 GB) exceed the 126 MB L2 every step",
                            dropout=args.dropout, last_loss=loss_host,
@@ -586,7 +600,7 @@ def run_ours(args):
         try:
             line["e2e_policy_api"] = policy_api_leg(dev, B, args.steps, args.warmup, eng.flat_params, host, fused=True)
             line["e2e_policy_api"]["mode"] = ("ACTPolicy(fused_step=True): loss.backward() deferred into optimizer.step(), step replayed "
-                                              "from two CUDA graphs; pinned host batch -> H2D, loss.item() every step")
+                                              "from two CUDA graphs; pinned host batch -> H2D, loss D2H every step (pinned, read one step later)")
             line["e2e_policy_api_unfused"] = policy_api_leg(dev, B, max(5, args.steps // 2), 3, eng.flat_params, host, fused=False)
             line["e2e_policy_api_unfused"]["mode"] = "ACTPolicy default: backward at loss.backward(), AdamW at optimizer.step(), direct launches"
         except Exception as ex:

@@ -114,7 +114,10 @@ int act_reparam_fwd(const float* latent_info, const float* eps, float* mu, float
 int act_reparam_bwd(const float* dz, const float* eps, const float* logvar, const float* d_mu_kl,
                     const float* d_logvar_kl, float* d_latent_info, int B, int Z, void* stream);
 /* resnet stem: max-pool 3x3/s2/p1 on NHWC bf16 (+arg-max bytes) and its ReLU-fused backward (torchvision resnet18
- * `maxpool`, backbone.py:121-124).  The stem conv itself is an implicit GEMM inside the engine (no im2col). */
+ * `maxpool`, backbone.py:121-124).  The stem conv itself is an implicit GEMM inside the engine (no im2col).
+ * argmax holds the winning tap 0..8 (first maximum in kh,kw order, as torch), or 9 when the window maximum is not positive
+ * (nothing passes the fused ReLU); act_maxpool_bwd therefore accepts x == NULL and then takes the ReLU mask from the record
+ * alone (the engine's path: 79 MB less to read at batch 8); with x given it also applies (x > 0) explicitly. */
 int act_maxpool_fwd(const void* x, void* y, uint8_t* argmax, int N, int H, int W, int C, void* stream);
 int act_maxpool_bwd(const void* dy, const uint8_t* argmax, const void* x, void* dx, int N, int H, int W, int C,
                     void* stream);
@@ -213,6 +216,22 @@ int act_engine_dp_export(act_engine* e, void* blob, int capacity);
 int act_engine_dp_connect(act_engine* e, int rank, int world, const void* blobs, int blob_bytes);
 int act_engine_dp_set_peers(act_engine* e, int rank, int world, void* const* grads, void* const* params,
                             void* const* shadow, void* const* signal);
+/* NVLS (NVSwitch multicast) form of the same exchange, no reference counterpart: when the four exchange buffers live in
+ * symmetric memory that also has a multicast mapping (the Python host takes it from torch.distributed._symmetric_memory:
+ * plumbing only), the kernel of act_engine_backward_and_step_p2p loads the switch-reduced gradient with ONE
+ * multimem.ld_reduce and stores parameters + shadow to all ranks with ONE multimem.st each, so every rank moves
+ * 4 + 6 B per owned parameter over NVLink instead of (world-1) * (4 + 6) B.
+ *   act_engine_dp_use_buffers  (before act_engine_dp_set_peers) moves the bf16 shadow into caller-owned memory and adopts a
+ *                              caller-owned flag block of act_engine_dp_signal_bytes() bytes;
+ *   act_engine_dp_set_multicast (after act_engine_dp_set_peers) gives the multicast addresses of the gradient / parameter /
+ *                              shadow buffers (all three or, to switch back to per-peer accesses, three NULLs).
+ * act_multimem_reduce_f32 / act_multimem_bcast_f32 are diagnostics of such a mapping (dst = sum over ranks of src / every
+ * rank's dst = src; n a multiple of 4, 16-byte aligned). */
+int act_engine_dp_use_buffers(act_engine* e, void* shadow, void* signal);
+int64_t act_engine_dp_signal_bytes(void);
+int act_engine_dp_set_multicast(act_engine* e, void* mc_grads, void* mc_params, void* mc_shadow);
+int act_multimem_reduce_f32(const float* mc_src, float* dst_local, int64_t n, void* stream);
+int act_multimem_bcast_f32(float* mc_dst, const float* src_local, int64_t n, void* stream);
 int act_engine_backward_and_step_p2p(act_engine* e, int step, float loss_grad, void* stream);
 int act_engine_dp_status(act_engine* e);
 /* Marks peer `peer_rank` as having arrived at every barrier up to `epoch` (writes this engine's own flag block).  For

@@ -176,6 +176,32 @@ def test_maxpool_fwd_bwd():
     # ties between equal positive bf16 values may resolve to a different tap than torch; they are rare
     bad = ((dx.float() - refdx).abs() > 2e-2 * (1 + refdx.abs())).float().mean().item()
     assert bad < 2e-3, bad
+    # x == NULL: the ReLU mask comes from the arg-max record (tap 9 = window maximum not positive) -- same result
+    dx2 = torch.full_like(x, 7.0)
+    ck(L().act_maxpool_bwd(p(dy), p(idx), None, p(dx2), N, H, W, Cc, st()))
+    assert torch.equal(dx2, dx)
+
+
+@pytest.mark.parametrize("shape", [(1, 30, 50, 64), (2, 17, 23, 8)])
+def test_maxpool_bwd_odd_sizes(shape):
+    N, H, W, Cc = shape
+    Ho, Wo = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+    x = torch.relu(rnd(N, H, W, Cc, seed=5)).bfloat16()
+    y = torch.empty(N, Ho, Wo, Cc, device="cuda", dtype=torch.bfloat16)
+    idx = torch.empty(N, Ho, Wo, Cc, device="cuda", dtype=torch.uint8)
+    ck(L().act_maxpool_fwd(p(x), p(y), p(idx), N, H, W, Cc, st()))
+    xr = x.float().permute(0, 3, 1, 2).clone().requires_grad_(True)
+    ref = F.max_pool2d(xr, 3, 2, 1)
+    assert torch.equal(y.float(), ref.permute(0, 2, 3, 1))
+    dy = rnd(N, Ho, Wo, Cc, seed=6).bfloat16()
+    for xin in (x, None):
+        dx = torch.full_like(x, 7.0)
+        ck(L().act_maxpool_bwd(p(dy), p(idx), p(xin) if xin is not None else None, p(dx), N, H, W, Cc, st()))
+        xr.grad = None
+        ref.backward(dy.float().permute(0, 3, 1, 2), retain_graph=True)
+        refdx = (xr.grad * (xr > 0)).permute(0, 2, 3, 1)
+        bad = ((dx.float() - refdx).abs() > 2e-2 * (1 + refdx.abs())).float().mean().item()
+        assert bad < 4e-3, bad
 
 
 @pytest.mark.parametrize("shape", [(2, 48, 64, 64), (1, 30, 50, 64), (3, 17, 23, 128)])

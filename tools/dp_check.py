@@ -26,6 +26,8 @@ eng.set_lr(1e-3, 1e-3)
 P2P = os.environ.get("ACT_DP_P2P", "0") == "1"
 if P2P:
     eng.dp_connect(dist.group.WORLD)       # gradient exchange inside the optimiser kernel over peer memory (csrc/dp_p2p.cu)
+    if rank == 0:
+        print("dp_check exchange:", "NVLS multicast" if eng._dp_nvls else f"peer loads/stores ({getattr(eng, '_dp_nvls_error', 'multicast off')})", flush=True)
 NSTEPS = int(os.environ.get('ACT_DP_STEPS', '2'))
 snaps = []
 for _ in range(NSTEPS):
