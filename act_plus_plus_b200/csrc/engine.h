@@ -113,6 +113,7 @@ class Engine {
   // backward_and_step they are folded, exchanged and updated early; only the small remainder trails the branch.
   long long bb_l4_off_[8] = {0}, bb_l4_n_[8] = {0}, bb_rest_off_[8] = {0}, bb_rest_n_[8] = {0};
   bool bb_early_ = false;                        // set while backbone_bwd_and_step runs
+  bool bb_split_ = false;                        // single-GPU step: AdamW + re-pack of everything but conv1 right after the fold
   // backward(0) + adamw() with the optimiser of each parameter region trailing that region's last weight gradient, so
   // the HBM-bound AdamW of the transformer / CVAE regions overlaps the tensor-bound backbone backward
   // grads_ready: data-parallel hook.  Called on the host while the step is enqueued, once per contiguous range of the
@@ -230,11 +231,19 @@ class Engine {
   cudaEvent_t dp_ev_[DP_MAX_SITES] = {}, dp_done_ = nullptr;
   int dp_site_ = 0;
   bool dp_pack_pending_ = false;                // backbone updated by the p2p step: re-pack after the closing barrier
-  int repack_conv_operands(cudaStream_t st);
+  int repack_conv_operands(cudaStream_t st, int cam = -1, bool stem = true);   // cam < 0: every camera
   int repack_pair_operands(int cam, cudaStream_t st);   // after the packed conv operands of that camera were rebuilt
   bool dp_fused_ = false;                       // true while backward_and_step(p2p = true) is being enqueued
   std::vector<void*> dp_opened_;
   std::vector<std::pair<long long, long long>> dp_ranges_;   // ranges exchanged by the last p2p step
+  // peer-memory step: the ranges that become final last (backbone, CVAE head / tail) are not exchanged one by one with a
+  // barrier each, but collected here and exchanged behind ONE barrier by kernels running side by side (dp_flush_deferred)
+  struct DpSeg { AdamWArgs a; long long off; cudaStream_t producer; bool repack; };
+  std::vector<DpSeg> dp_deferred_;
+  bool dp_defer_ = false, dp_defer_now_ = false;   // policy of this step / active for the range being enqueued
+  cudaStream_t dp_aux_[3] = {};
+  cudaEvent_t dp_aux_ev_[8] = {};
+  int dp_flush_deferred();
   int dp_sync_point(cudaStream_t producer);     // dp_stream_ waits for `producer`, then a cross-rank flag barrier on dp_stream_
   std::vector<void*> allocs_;
   long long ws_bytes_ = 0;

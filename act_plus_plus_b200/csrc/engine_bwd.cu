@@ -311,10 +311,10 @@ int Engine::cvae_bwd(cudaStream_t st) {
   const float* cls_out = cvae_a_[nl - 1].x2;
   g = SgemmArgs(); g.I = 2 * Z; g.J = d; g.R = B; g.A = d_info_; g.ai = act::lin(1); g.ar = act::lin(2 * Z);
   g.B = cls_out; g.br = act::lin(ts); g.bj = act::lin(1); g.C = G("latent_proj.weight"); g.ci = act::lin(d); g.cj = act::lin(1); g.accumulate = 1;
-  RUN(sgemm_generic(g, st));
+  RUN(sgemm_generic(g, wg_fork(st)));                      // parameter gradients only: beside the chain, on the weight-gradient lanes
   g = SgemmArgs(); g.I = 1; g.J = 2 * Z; g.R = B; g.A = one_; g.ai = act::lin(0); g.ar = act::lin(0);
   g.B = d_info_; g.br = act::lin(2 * Z); g.bj = act::lin(1); g.C = G("latent_proj.bias"); g.ci = act::lin(0); g.cj = act::lin(1); g.accumulate = 1;
-  RUN(sgemm_generic(g, st));
+  RUN(sgemm_generic(g, wg_fork(st)));
   // gradient wrt the encoder output: only the cls rows are non-zero
   ACT_CUDA(cudaMemsetAsync(gC_, 0, sizeof(float) * Mc * d, st));
   g = SgemmArgs(); g.I = B; g.J = d; g.R = 2 * Z; g.A = d_info_; g.ai = act::lin(2 * Z); g.ar = act::lin(1);
@@ -336,23 +336,24 @@ int Engine::cvae_bwd(cudaStream_t st) {
     }
   }
   RUN(add_out(gC_, gD_, d_tokC_, 1LL * Mc * d, st));
-  // token 0: cls_embed ; token 1: encoder_joint_proj(qpos) ; tokens 2..: encoder_action_proj(actions)
+  // token 0: cls_embed ; token 1: encoder_joint_proj(qpos) ; tokens 2..: encoder_action_proj(actions).  Five independent tiny
+  // reductions at the very end of the branch: spread over the weight-gradient lanes (the optimiser lane gathers them)
   g = SgemmArgs(); g.I = 1; g.J = d; g.R = B; g.A = one_; g.ai = act::lin(0); g.ar = act::lin(0);
   g.B = d_tokC_; g.br = act::lin(ts); g.bj = act::lin(1); g.C = G("cls_embed.weight"); g.ci = act::lin(0); g.cj = act::lin(1); g.accumulate = 1;
-  RUN(sgemm_generic(g, st));
+  RUN(sgemm_generic(g, wg_fork(st)));
   g = SgemmArgs(); g.I = d; g.J = S; g.R = B; g.A = d_tokC_ + d; g.ai = act::lin(1); g.ar = act::lin(ts);
   g.B = in_qpos_; g.br = act::lin(S); g.bj = act::lin(1); g.C = G("encoder_joint_proj.weight"); g.ci = act::lin(S); g.cj = act::lin(1); g.accumulate = 1;
-  RUN(sgemm_generic(g, st));
+  RUN(sgemm_generic(g, wg_fork(st)));
   g = SgemmArgs(); g.I = 1; g.J = d; g.R = B; g.A = one_; g.ai = act::lin(0); g.ar = act::lin(0);
   g.B = d_tokC_ + d; g.br = act::lin(ts); g.bj = act::lin(1); g.C = G("encoder_joint_proj.bias"); g.ci = act::lin(0); g.cj = act::lin(1); g.accumulate = 1;
-  RUN(sgemm_generic(g, st));
+  RUN(sgemm_generic(g, wg_fork(st)));
   // dW[c][a] += sum_t dTok[t][c] * actions[t][a], issued transposed (rows = a, columns = c) so lanes run along c
   g = SgemmArgs(); g.I = A; g.J = d; g.R = B * nq; g.A = in_actions_; g.ai = act::lin(1); g.ar = batched(nq, in_actions_bs_, A);
   g.B = d_tokC_ + 2 * d; g.br = batched(nq, ts, d); g.bj = act::lin(1); g.C = G("encoder_action_proj.weight"); g.ci = act::lin(1); g.cj = act::lin(A); g.accumulate = 1;
-  RUN(sgemm_generic(g, st));
+  RUN(sgemm_generic(g, wg_fork(st)));
   g = SgemmArgs(); g.I = 1; g.J = d; g.R = B * nq; g.A = one_; g.ai = act::lin(0); g.ar = act::lin(0);
   g.B = d_tokC_ + 2 * d; g.br = batched(nq, ts, d); g.bj = act::lin(1); g.C = G("encoder_action_proj.bias"); g.ci = act::lin(0); g.cj = act::lin(1); g.accumulate = 1;
-  RUN(sgemm_generic(g, st));
+  RUN(sgemm_generic(g, wg_fork(st)));
   return 0;
 }
 
@@ -428,6 +429,17 @@ int Engine::backbone_bwd(int cam, int B, cudaStream_t st) {
   }
   wg = wg_gather(st);
   RUN(wgrad_fold_batched(folds, wg));
+  if (bb_split_) {
+    // single-GPU overlapped step: every weight of this camera except conv1 is final once the fold has run, so its AdamW
+    // and the re-pack of its conv operands start here, under the max-pool backward and the stem's weight gradient
+    // (conv1 follows in backbone_bwd_and_step); the step's tail loses ~100 us of serial optimiser + re-pack time
+    const long long c1 = cw.stem.gw - grads_, c1n = (64LL * 3 * 7 * 7 + 7) / 8 * 8;
+    const long long lo = bb_rest_off_[cam], hi = bb_l4_off_[cam] + bb_l4_n_[cam];
+    ACT_CHECK(c1 == lo && lo + c1n <= hi, "backbone span does not start with conv1.weight");
+    cudaStream_t ol = wg_gather(st, NWG);
+    if (adamw_range(lo + c1n, hi - lo - c1n, cfg_.lr_backbone, false, opt_step_, ol, 3)) return -1;
+    if (repack_conv_operands(ol, cam, false)) return -1;
+  }
   // stem: max-pool backward (+ReLU mask), then dW1 = scale * dy1^T (row windows of the normalised image)
   const int H1 = fh_[1], W1 = fw_[1];
   bf16* gpool = cgy_alloc(1LL * B * H1 * W1 * 64);
@@ -464,12 +476,30 @@ int Engine::backbone_bwd_and_step(cudaStream_t st) {
   cgy_off_ = 0;
   { static int early = -1; if (early < 0) { const char* e = getenv("ACT_BB_EARLY"); early = (e && e[0] == '1') ? 1 : 0; }   // opt-in: measured neutral at N=1, -0.4 % at N=2 (one more barrier site)
     bb_early_ = early != 0 && cfg_.num_cameras <= 8 && concurrent_; }
+  { static int split = -1; if (split < 0) { const char* e = getenv("ACT_BB_SPLIT"); split = (e && e[0] == '0') ? 0 : 1; }
+    bb_split_ = split != 0 && !bb_early_ && !dp_fused_ && !grads_cb_ && concurrent_ && cfg_.num_cameras <= 8; }
   tc_set_sm_reserve(sm_reserve_);
   for (int k = 0; k < cfg_.num_cameras; ++k)
-    if (backbone_bwd(k, cur_B_, st)) { tc_set_sm_reserve(0); return -1; }
+    if (backbone_bwd(k, cur_B_, st)) { tc_set_sm_reserve(0); bb_split_ = false; return -1; }
   tc_set_sm_reserve(0);
   cudaStream_t wg = wg_gather(st, NWG);
+  if (bb_split_) {                                          // what is left: conv1 of every camera and its packed operand
+    bb_split_ = false;
+    const long long c1n = (64LL * 3 * 7 * 7 + 7) / 8 * 8;
+    for (int k = 0; k < cfg_.num_cameras; ++k) {
+      if (adamw_range(bb_rest_off_[k], c1n, cfg_.lr_backbone, false, opt_step_, wg, 3)) return -1;
+      if (pack_stem_weights(cam_w_[k].stem.w32, cam_w_[k].stem.wpk, wg)) return -1;
+      ++launches_;
+    }
+    return 0;
+  }
   if (!bb_early_) {
+    if (dp_defer_) {                                        // peer-memory step: one barrier for this and the CVAE head (p2p_finish)
+      dp_defer_now_ = true;
+      const int rc = adamw_region(R_BACKBONE, opt_step_, wg, 8);
+      dp_defer_now_ = false;
+      return rc;
+    }
     if (grads_ready(region_off_[R_BACKBONE], region_n_[R_BACKBONE], wg)) return -1;
     return adamw_region(R_BACKBONE, opt_step_, wg, dp_fused_ ? 6 : 3);
   }
@@ -493,6 +523,8 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
   // the peer-memory step ends with a barrier: every rank has finished reading this rank's gradients and writing its
   // parameters before the caller's stream goes on (next zero_grad / forward)
   auto p2p_finish = [&]() -> int {
+    dp_defer_ = dp_defer_now_ = false;
+    if (dp_flush_deferred()) return -1;                    // backbone + CVAE head / tail behind one barrier
     if (dp_sync_point(st)) return -1;                      // (also starts a still-pending conv re-pack)
     ACT_CUDA(cudaEventRecord(dp_done_, dp_stream_));
     ACT_CUDA(cudaStreamWaitEvent(st, dp_done_, 0));
@@ -520,10 +552,16 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
   }
   struct Guard {                                            // the hook is only live inside this call
     Engine* e;
-    ~Guard() { e->grads_cb_ = nullptr; e->grads_cb_user_ = nullptr; e->inline_opt_on_ = false; e->inline_opt_step_ = 0; e->dp_bb_pending_ = false; e->dp_fused_ = false; e->dp_inline_from_ = 0; tc_set_sm_reserve(0); }
+    ~Guard() { e->grads_cb_ = nullptr; e->grads_cb_user_ = nullptr; e->inline_opt_on_ = false; e->inline_opt_step_ = 0; e->dp_bb_pending_ = false; e->dp_fused_ = false; e->dp_inline_from_ = 0; e->dp_defer_ = e->dp_defer_now_ = false; e->dp_deferred_.clear(); tc_set_sm_reserve(0); }
   } guard{this};
   grads_cb_ = cb; grads_cb_user_ = cb_user; opt_step_ = step;
   dp_fused_ = p2p; dp_site_ = 0; if (p2p) dp_ranges_.clear();
+  dp_deferred_.clear();
+  { static int defer = -1; if (defer < 0) { const char* e = getenv("ACT_DP_DEFER"); defer = (e && e[0] == '1') ? 1 : 0; }
+    // opt-in (measured neutral: 3.408 vs 3.406 ms/step at N=2, 3.58 vs 3.56 at N=8): with one camera the backbone and the
+    // CVAE branch end within ~50 us of each other, so their last ranges can share one barrier and run side by side.
+    // With several cameras the backbone branch is the long one and the CVAE ranges are better exchanged under it.
+    dp_defer_ = p2p && defer != 0 && cfg_.num_cameras == 1 && !cfg_.no_encoder; }
   static int inline_layers = -2;
   if (inline_layers == -2) { const char* e = getenv("ACT_DP_INLINE_LAYERS"); inline_layers = e ? atoi(e) : -1; }
   // peer-memory exchange: only the first `enc_layers / 2` CVAE layers of the backward (the highest-numbered ones) are
@@ -559,6 +597,13 @@ int Engine::backward_and_step(int step, float loss_grad, cudaStream_t st, GradsR
     const long long head_n = head_end - region_off_[R_CVAE];
     const long long tail_n = region_off_[R_CVAE] + region_n_[R_CVAE] - tail;
     const int bps = p2p ? 8 : 6;                            // nothing left to run beside these: whole chip
+    if (dp_defer_) {                                        // exchanged with the backbone behind one barrier (p2p_finish)
+      dp_defer_now_ = true;
+      const int rc2 = adamw_range(region_off_[R_CVAE], head_n, cfg_.lr, true, step, wg, bps) ||
+                      adamw_range(tail, tail_n, cfg_.lr, true, step, wg, bps);
+      dp_defer_now_ = false;
+      return rc2 ? -1 : 0;
+    }
     if (grads_ready(region_off_[R_CVAE], head_n, wg)) return -1;
     if (adamw_range(region_off_[R_CVAE], head_n, cfg_.lr, true, step, wg, bps)) return -1;
     if ((!p2p || head_n <= 0) && grads_ready(tail, tail_n, wg)) return -1;   // (peer memory: the head's barrier covers the tail)

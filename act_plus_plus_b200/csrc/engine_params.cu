@@ -459,7 +459,11 @@ int Engine::adamw_range(long long off, long long n, float lr, bool shadow, int s
   a.n = n; a.lr = lr; a.beta1 = cfg_.beta1; a.beta2 = cfg_.beta2; a.eps = cfg_.adam_eps; a.wd = cfg_.weight_decay;
   a.step = step; a.mode = 0; a.background = blocks_per_sm;
   ++launches_;
-  if (dp_fused_) { dp_ranges_.emplace_back(off, n); return dp_adamw_step(peers_, a, off, dp_stream_); }   // reduce + update + broadcast over peer memory
+  if (dp_fused_) {                                          // reduce + update + broadcast over peer memory
+    dp_ranges_.emplace_back(off, n);
+    if (dp_defer_now_) { dp_deferred_.push_back(DpSeg{a, off, st, false}); return 0; }
+    return dp_adamw_step(peers_, a, off, dp_stream_);
+  }
   return adamw_step(a, st);
 }
 int Engine::adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm) {
@@ -475,6 +479,11 @@ int Engine::adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm) {
   ++launches_;
   if (dp_fused_ && r != R_DEAD) {
     dp_ranges_.emplace_back(o, a.n);
+    if (dp_defer_now_) {
+      // (the conv re-pack may only be armed once this range's kernel is on the exchange stream: dp_flush_deferred)
+      dp_deferred_.push_back(DpSeg{a, o, st, r == R_BACKBONE});
+      return 0;
+    }
     if (dp_adamw_step(peers_, a, o, dp_stream_)) return -1;
     // the conv operands are re-packed from the fp32 masters once every rank's slice of them has landed here: that is
     // what the step's closing barrier guarantees, so the re-pack is deferred to it (repack_conv_operands)
@@ -486,12 +495,15 @@ int Engine::adamw_region(int r, int step, cudaStream_t st, int blocks_per_sm) {
   return repack_conv_operands(st);
 }
 
-int Engine::repack_conv_operands(cudaStream_t st) {
+int Engine::repack_conv_operands(cudaStream_t st, int cam, bool stem) {
   // packed conv operands (transposed / scaled layouts) are rebuilt from the fp32 masters, one launch per camera
   for (int k = 0; k < cfg_.num_cameras; ++k) {
+    if (cam >= 0 && k != cam) continue;
     CamW& c = cam_w_[k];
-    if (pack_stem_weights(c.stem.w32, c.stem.wpk, st)) return -1;
-    ++launches_;
+    if (stem) {
+      if (pack_stem_weights(c.stem.w32, c.stem.wpk, st)) return -1;
+      ++launches_;
+    }
     PackJobs jobs;
     for (int i = 0; i < 8; ++i) {
       BlockW& b = c.blk[i];
@@ -639,6 +651,38 @@ int Engine::dp_set_peers(int rank, int world, void* const* grads, void* const* p
     for (cudaEvent_t& e : dp_ev_) ACT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     ACT_CUDA(cudaEventCreateWithFlags(&dp_done_, cudaEventDisableTiming));
   }
+  return 0;
+}
+
+// One barrier for every deferred range (each rank's producers of all of them are waited for first), then their exchange
+// kernels side by side on the exchange stream and its helpers: the link sees one long transfer instead of three short
+// ones with a barrier and a ramp between them.
+int Engine::dp_flush_deferred() {
+  if (dp_deferred_.empty()) return 0;
+  ACT_CHECK(dp_deferred_.size() <= 4, "dp: too many deferred ranges");
+  if (!dp_aux_[0]) {
+    for (cudaStream_t& s : dp_aux_) ACT_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    for (cudaEvent_t& e : dp_aux_ev_) ACT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  for (size_t k = 1; k < dp_deferred_.size(); ++k) {
+    if (dp_deferred_[k].producer == dp_deferred_[0].producer || dp_deferred_[k].producer == dp_stream_) continue;
+    ACT_CUDA(cudaEventRecord(dp_aux_ev_[k], dp_deferred_[k].producer));
+    ACT_CUDA(cudaStreamWaitEvent(dp_stream_, dp_aux_ev_[k], 0));
+  }
+  if (dp_sync_point(dp_deferred_[0].producer)) return -1;
+  ACT_CUDA(cudaEventRecord(dp_aux_ev_[0], dp_stream_));
+  for (size_t k = 0; k < dp_deferred_.size(); ++k) {
+    cudaStream_t s = k == 0 ? dp_stream_ : dp_aux_[k - 1];
+    if (k > 0) ACT_CUDA(cudaStreamWaitEvent(s, dp_aux_ev_[0], 0));
+    ++launches_;
+    if (dp_adamw_step(peers_, dp_deferred_[k].a, dp_deferred_[k].off, s)) return -1;
+    if (dp_deferred_[k].repack) dp_pack_pending_ = true;     // re-pack behind the NEXT barrier (every rank's slice has landed)
+    if (k > 0) {
+      ACT_CUDA(cudaEventRecord(dp_aux_ev_[4 + k], s));
+      ACT_CUDA(cudaStreamWaitEvent(dp_stream_, dp_aux_ev_[4 + k], 0));
+    }
+  }
+  dp_deferred_.clear();
   return 0;
 }
 

@@ -35,7 +35,13 @@ __global__ void __launch_bounds__(256) sgemm_generic_kernel(SgemmArgs a) {
       }
       for (; r < r1; r += 8) acc += Ai[r * sa] * Bj[r * sb];
     } else {
-      for (int r = r0 + ty; r < r1; r += 8) acc += Ai[ioff(a.ar, r)] * Bj[ioff(a.br, r)];
+      int r = r0 + ty;
+      for (; r + 24 < r1; r += 32) {                             // four independent load pairs in flight
+        const float a0 = Ai[ioff(a.ar, r)], a1 = Ai[ioff(a.ar, r + 8)], a2 = Ai[ioff(a.ar, r + 16)], a3 = Ai[ioff(a.ar, r + 24)];
+        const float b0 = Bj[ioff(a.br, r)], b1 = Bj[ioff(a.br, r + 8)], b2 = Bj[ioff(a.br, r + 16)], b3 = Bj[ioff(a.br, r + 24)];
+        acc += a0 * b0 + a1 * b1 + a2 * b2 + a3 * b3;
+      }
+      for (; r < r1; r += 8) acc += Ai[ioff(a.ar, r)] * Bj[ioff(a.br, r)];
     }
   }
   part[ty][tx] = acc;
@@ -129,6 +135,9 @@ int sgemm_generic(const SgemmArgs& a, cudaStream_t st) {
     // enough blocks to fill the chip, at least 32 reduction steps per block
     const long long blocks = 1LL * jb * a.I;
     split = static_cast<int>(std::max<long long>(1, std::min<long long>((a.R + 31) / 32, (2 * 148 + blocks - 1) / blocks)));
+    // these launches sit at the very end of a dependency chain (token-projection gradients): a block is latency-bound, so
+    // no thread should walk more than ~8 dependent-latency steps even when the chip is already "full"
+    split = static_cast<int>(std::max<long long>(split, std::min<long long>((a.R + 63) / 64, 32)));
   }
   dim3 grid(jb, a.I, split);
   ACT_CUDA(launch_pdl(sgemm_generic_kernel, grid, dim3(32, 8), 0, st, a));

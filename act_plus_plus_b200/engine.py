@@ -386,8 +386,9 @@ class ActEngine:
 
     def dp_connect(self, group=None, multicast: Optional[bool] = None):
         """Map every rank's flat gradient / parameter / shadow buffers and barrier flags (one process per GPU on one node).
-        With NVSwitch multicast (default from 4 ranks up, where one switch-reduced load replaces world-1 peer loads:
-        +3 % at N=8; at N=2 it saves no traffic and measured 7 % slower; `multicast=` / ACT_DP_NVLS=0|1 override) the buffers move into
+        With NVSwitch multicast (default above 4 ranks, where one switch-reduced load replaces world-1 peer loads and one
+        store reaches every rank: 3.68 -> 3.57 ms/step at N=8; measured 0.7 % slower at N=4 and 7 % slower at N=2, where it
+        saves little or no link traffic; `multicast=` / ACT_DP_NVLS=0|1 override) the buffers move into
         symmetric memory and the exchange kernel uses multimem.ld_reduce / multimem.st; otherwise CUDA-IPC handles are
         exchanged and the kernel does per-peer loads and stores.  Collective: every rank must call it; if any rank fails,
         every rank raises RuntimeError (so callers can fall back to NCCL consistently)."""
@@ -400,7 +401,7 @@ class ActEngine:
         self._dp_nvls = False
         if multicast is None:
             env = os.environ.get("ACT_DP_NVLS", "auto")
-            multicast = world >= 4 if env == "auto" else env == "1"
+            multicast = world > 4 if env == "auto" else env == "1"
         if multicast and getattr(self, "_dp_world", 1) <= 1 and self._dp_connect_symmetric(group):
             return
         blob = C.create_string_buffer(self.DP_BLOB_BYTES)
