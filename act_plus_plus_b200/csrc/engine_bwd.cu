@@ -109,7 +109,7 @@ int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K
     MatDesc a, b; EpiDesc e;
     a.ptr = dO; a.ld = 512; a.sz0 = hd; a.sz1 = 1LL * Lq * 512;
     b.ptr = V; b.ld = ldv; b.sz0 = hd; b.sz1 = Lk * ldv;
-    if (tc_attn_scores_applicable(Lk, Lkp)) {
+    if (tc_attn_scores_applicable(Lk, Lkp, dropping)) {
       ++launches_;
       const DropDesc dd = dropping ? drop_site(drop) : DropDesc();
       if (tc_attn_scores(1, a, b, Lq, Lk, Lkp, h, B, 0.125f, nullptr, P, dS, st, dropping ? &dd : nullptr)) return -1;

@@ -240,7 +240,7 @@ int Engine::attn_fwd(const bf16* Q, long long ldq, const bf16* K, long long ldk,
   EpiDesc e;
   a.ptr = Q; a.ld = ldq; a.sz0 = hd; a.sz1 = Lq * ldq;
   b.ptr = K; b.ld = ldk; b.sz0 = hd; b.sz1 = Lk * ldk;
-  if (tc_attn_scores_applicable(Lk, Lkp)) {
+  if (tc_attn_scores_applicable(Lk, Lkp, dropping)) {
     // scores + mask + softmax in one kernel: the fp32 score tile stays in TMEM (csrc/attn_kernel.cuh)
     ++launches_;
     const DropDesc dd = dropping ? drop_site(drop) : DropDesc();

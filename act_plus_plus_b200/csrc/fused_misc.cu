@@ -444,67 +444,88 @@ int maxpool_bwd(const bf16* dy, const uint8_t* idx, const bf16* x, bf16* dx, int
 // ------------------------------------------------------------------------------------------ stem image pack
 // policy.py:268-272 normalisation fused with the layout change the implicit-GEMM stem conv reads: pixel x of row y
 // lands at out[b][y][x + 3][0..3] = {R, G, B, 0} (bf16), columns [0,3) and [W+3, Wp) are zero (horizontal padding).
-__global__ void stem_pack_image_kernel(const float* __restrict__ img, long long img_bs, bf16* __restrict__ out, int B,
-                                       int H, int W, int Wp) {
-  pdl_trigger(); pdl_wait();
-  const float mean[3] = {0.485f, 0.456f, 0.406f};
-  const float istd[3] = {1.f / 0.229f, 1.f / 0.224f, 1.f / 0.225f};
-  const long long total = 1LL * B * H * Wp;
-  for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
-    const int xp = static_cast<int>(i % Wp);
-    const long long r = i / Wp;
-    const int y = static_cast<int>(r % H), b = static_cast<int>(r / H);
-    const int x = xp - 3;
-    float v[3] = {0.f, 0.f, 0.f};
-    if (x >= 0 && x < W) {
-#pragma unroll
-      for (int c = 0; c < 3; ++c) v[c] = (__ldg(img + b * img_bs + (1LL * c * H + y) * W + x) - mean[c]) * istd[c];
-    }
-    __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], 0.f);
-    uint2 o;
-    o.x = *reinterpret_cast<uint32_t*>(&lo); o.y = *reinterpret_cast<uint32_t*>(&hi);
-    reinterpret_cast<uint2*>(out)[i] = o;
-  }
-}
-// Same for the dataset's native layout (utils.py:133-158 keeps uint8 HWC frames and divides by 255 on the host): pixel
+// U8 = the dataset's native layout (utils.py:133-158 keeps uint8 HWC frames and divides by 255 on the host): pixel
 // (y, x) of camera `cam` is img[b][cam][y][x][0..3) uint8; x/255 is formed in fp32 exactly like `image_data / 255.0`.
-__global__ void stem_pack_image_u8_kernel(const uint8_t* __restrict__ img, long long img_bs, bf16* __restrict__ out,
-                                          int B, int H, int W, int Wp) {
+// One thread = four consecutive output pixels (two 16-byte stores); interior groups of the uint8 form read their twelve
+// bytes as four aligned words re-aligned with funnel shifts (the one-pixel-per-thread form ran at 2.2 TB/s).
+template <bool U8>
+__global__ void __launch_bounds__(256) stem_pack_image_kernel(const void* __restrict__ img_, long long img_bs, bf16* __restrict__ out,
+                                                              int B, int H, int W, int Wp) {
   pdl_trigger(); pdl_wait();
   const float mean[3] = {0.485f, 0.456f, 0.406f};
   const float istd[3] = {1.f / 0.229f, 1.f / 0.224f, 1.f / 0.225f};
-  const long long total = 1LL * B * H * Wp;
+  const int G = (Wp + 3) / 4;
+  const long long total = 1LL * B * H * G;
   for (long long i = blockIdx.x * 1LL * blockDim.x + threadIdx.x; i < total; i += gridDim.x * 1LL * blockDim.x) {
-    const int xp = static_cast<int>(i % Wp);
-    const long long r = i / Wp;
+    const int q = static_cast<int>(i % G);
+    const long long r = i / G;
     const int y = static_cast<int>(r % H), b = static_cast<int>(r / H);
-    const int x = xp - 3;
-    float v[3] = {0.f, 0.f, 0.f};
-    if (x >= 0 && x < W) {
-      const uint8_t* px = img + b * img_bs + (1LL * y * W + x) * 3;
+    const int x0 = 4 * q - 3;
+    float v[4][3];
 #pragma unroll
-      for (int c = 0; c < 3; ++c) v[c] = (static_cast<float>(__ldg(px + c)) / 255.0f - mean[c]) * istd[c];
+    for (int j = 0; j < 4; ++j) { v[j][0] = 0.f; v[j][1] = 0.f; v[j][2] = 0.f; }
+    const bool interior = x0 >= 0 && x0 + 5 < W;
+    if (U8) {
+      const uint8_t* px = static_cast<const uint8_t*>(img_) + b * img_bs + (1LL * y * W + x0) * 3;
+      if (interior) {
+        const uint32_t mis = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(px) & 3u);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(px - mis);
+        const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2), w3 = __ldg(w + 3);
+        const uint32_t sh = mis * 8u;
+        const uint32_t r3[3] = {__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh)};
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            const int k = 3 * j + c;
+            v[j][c] = (static_cast<float>((r3[k >> 2] >> (8 * (k & 3))) & 0xffu) / 255.0f - mean[c]) * istd[c];
+          }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (x0 + j >= 0 && x0 + j < W) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) v[j][c] = (static_cast<float>(__ldg(px + 3 * j + c)) / 255.0f - mean[c]) * istd[c];
+          }
+      }
+    } else {
+      const float* im = static_cast<const float*>(img_) + b * img_bs + 1LL * y * W + x0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (interior || (x0 + j >= 0 && x0 + j < W)) {
+#pragma unroll
+          for (int c = 0; c < 3; ++c) v[j][c] = (__ldg(im + 1LL * c * H * W + j) - mean[c]) * istd[c];
+        }
     }
-    __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], 0.f);
-    uint2 o;
-    o.x = *reinterpret_cast<uint32_t*>(&lo); o.y = *reinterpret_cast<uint32_t*>(&hi);
-    reinterpret_cast<uint2*>(out)[i] = o;
+    uint32_t o[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      __nv_bfloat162 lo = __floats2bfloat162_rn(v[j][0], v[j][1]), hi = __floats2bfloat162_rn(v[j][2], 0.f);
+      o[2 * j] = *reinterpret_cast<uint32_t*>(&lo); o[2 * j + 1] = *reinterpret_cast<uint32_t*>(&hi);
+    }
+    uint2* dst = reinterpret_cast<uint2*>(out) + (1LL * b * H + y) * Wp + 4 * q;     // 8 bytes per pixel
+    if (4 * q + 3 < Wp && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
+      reinterpret_cast<uint4*>(dst)[0] = make_uint4(o[0], o[1], o[2], o[3]);
+      reinterpret_cast<uint4*>(dst)[1] = make_uint4(o[4], o[5], o[6], o[7]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (4 * q + j < Wp) dst[j] = make_uint2(o[2 * j], o[2 * j + 1]);
+    }
   }
 }
 int stem_pack_image_u8(const uint8_t* img_cam, long long img_bs, bf16* out, int B, int H, int W, int Wp, cudaStream_t st) {
-  const long long total = 1LL * B * H * Wp;
-  stem_pack_image_u8_kernel<<<static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16)), 256, 0, st>>>(img_cam, img_bs, out, B, H, W, Wp);
+  const long long total = 1LL * B * H * ((Wp + 3) / 4);
+  stem_pack_image_kernel<true><<<static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16)), 256, 0, st>>>(img_cam, img_bs, out, B, H, W, Wp);
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
 int stem_pack_image(const float* img_cam, long long img_bs, bf16* out, int B, int H, int W, int Wp, cudaStream_t st) {
-  const long long total = 1LL * B * H * Wp;
-  stem_pack_image_kernel<<<static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16)), 256, 0, st>>>(img_cam, img_bs, out, B, H, W, Wp);
+  const long long total = 1LL * B * H * ((Wp + 3) / 4);
+  stem_pack_image_kernel<false><<<static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16)), 256, 0, st>>>(img_cam, img_bs, out, B, H, W, Wp);
   ACT_CUDA(cudaGetLastError());
   return 0;
 }
-
-
 
 // ------------------------------------------------------------------------------------------ dropout utilities
 __global__ void dropout_mask_kernel(DropDesc d, uint32_t step, long long n8, long long n, uint8_t* __restrict__ out) {

@@ -94,7 +94,10 @@ void tc_set_sm_reserve(int n);
 // Attention scores fused with softmax (bwd = 0) / softmax backward (bwd = 1) for head_dim 64 and Lk <= 1024 keys
 // (one TMEM-resident pass up to 320 keys, two chunked passes beyond).  drop (optional, train mode): dropout on the
 // attention weights -- forward also writes out2 = dropout(P), backward masks dP (csrc/dropout.cuh).
-bool tc_attn_scores_applicable(int Lk, int Lkp);
+// need_fused: the caller cannot use the unfused pair (attention dropout lives in the fused kernels only).  Rows of more than
+// 320 keys (the chunked two-pass kernel) are routed to it only then or with ACT_ATTN_CHUNKED=1: at 902 keys it measures 439 /
+// 580 us (fwd / bwd, batch 16) against 209 / 294 us for tc_gemm + softmax, which is HBM-bound (profiles/r02_attn_902.md).
+bool tc_attn_scores_applicable(int Lk, int Lkp, bool need_fused = true);
 int tc_attn_scores(int bwd, const MatDesc& A, const MatDesc& B, int Lq, int Lk, int Lkp, int heads, int batch, float scale,
                    const uint8_t* mask, const bf16* P, bf16* out, cudaStream_t stream, const DropDesc* drop = nullptr,
                    bf16* out2 = nullptr);

@@ -548,9 +548,11 @@ static int launch_attn(const CUtensorMap& am, const CUtensorMap& bm, const AttnP
   return 0;
 }
 
-bool tc_attn_scores_applicable(int Lk, int Lkp) {
-  static int on = -1;
+bool tc_attn_scores_applicable(int Lk, int Lkp, bool need_fused) {
+  static int on = -1, chunked = -1;
   if (on < 0) { const char* e = getenv("ACT_FUSED_ATTN"); on = !(e && e[0] == '0'); }
+  if (chunked < 0) { const char* e = getenv("ACT_ATTN_CHUNKED"); chunked = (e && e[0] == '1') ? 1 : 0; }
+  if (Lk > 320 && !(need_fused || chunked)) return false;
   return on && Lk >= 1 && Lk <= AttnCCfg::NCH_MAX * AttnCCfg::CH && Lkp % 8 == 0 && Lkp >= Lk;
 }
 

@@ -160,7 +160,8 @@ def bench_attn():
     import ctypes as C
     lib = ops._lib.lib()
     st = lambda: torch.cuda.current_stream().cuda_stream
-    for (B, h, Lq, Lk) in ((8, 8, 302, 302), (8, 8, 102, 102), (8, 8, 100, 302), (8, 8, 100, 100)):
+    for (B, h, Lq, Lk) in ((8, 8, 302, 302), (8, 8, 102, 102), (8, 8, 100, 302), (8, 8, 100, 100), (16, 8, 902, 902), (16, 8, 100, 902),
+                           (2, 8, 902, 902)):
         d = 512
         Lkp = (Lk + 7) // 8 * 8
         qk = torch.randn(B, Lq, 2 * d, device="cuda").bfloat16()
@@ -177,8 +178,23 @@ def bench_attn():
         def unfused():
             ops.tc_gemm_raw(Lq, Lk, 64, h, B, qk, 0, 2 * d, 64, Lq * 2 * d, kk[:, :, d:], 0, 2 * d, 64, Lk * 2 * d, epi, 1, 0, 0)
             ops.check(lib.act_softmax_fwd(S.data_ptr(), None, P.data_ptr(), B * h * Lq, Lk, Lkp, h * Lq, st()), "softmax")
+        dO = torch.randn(B, Lq, d, device="cuda").bfloat16()
+        V = torch.randn(B, Lk, d, device="cuda").bfloat16()
+        dS = torch.zeros(B, h, Lq, Lkp, device="cuda", dtype=torch.bfloat16)
+
+        def fused_bwd():
+            ops.check(lib.act_attn_scores(1, dO.data_ptr(), d, 64, Lq * d, V.data_ptr(), d, 64, Lk * d, Lq, Lk, Lkp,
+                                          h, B, C.c_float(0.125), None, P.data_ptr(), dS.data_ptr(), st()), "attn_scores bwd")
+
+        epi2 = ops.make_epilogue(out_f32=S, ldc=Lkp, osz0=Lq * Lkp, osz1=h * Lq * Lkp, alpha=1.0)
+
+        def unfused_bwd():
+            ops.tc_gemm_raw(Lq, Lk, 64, h, B, dO, 0, d, 64, Lq * d, V, 0, d, 64, Lk * d, epi2, 1, 0, 0)
+            ops.check(lib.act_softmax_bwd(P.data_ptr(), S.data_ptr(), dS.data_ptr(), B * h * Lq, Lk, Lkp, C.c_float(0.125), st()), "softmax bwd")
         tf, tu = graph_time(fused), graph_time(unfused)
-        print(json.dumps(dict(kind="attn_scores", B=B, h=h, Lq=Lq, Lk=Lk, fused_us=round(tf, 2), unfused_us=round(tu, 2))), flush=True)
+        tfb, tub = graph_time(fused_bwd), graph_time(unfused_bwd)
+        print(json.dumps(dict(kind="attn_scores", B=B, h=h, Lq=Lq, Lk=Lk, fused_us=round(tf, 2), unfused_us=round(tu, 2),
+                              fused_bwd_us=round(tfb, 2), unfused_bwd_us=round(tub, 2))), flush=True)
 
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "attn":
