@@ -28,6 +28,11 @@ struct AttnParams {
   __nv_bfloat16* out2;
   // chunked kernel (Lk > 320): work item = (batch, head, group of consecutive query tiles); K/V stays resident per item
   int nch, groups, tiles_per_group;
+  // BWD, optional: the forward's attention output O = dropout(P) V and the incoming gradient dO as plain row views (row
+  // stride ld, head stride sz0, batch stride sz1, elements).  rowsum(P o dP) = dO_i . O_i (also under dropout), so the
+  // chunked kernel needs ONE pass over the keys instead of two when O is given.
+  const __nv_bfloat16* O; const __nv_bfloat16* dO;
+  long long o_ld, o_sz0, o_sz1, do_ld, do_sz0, do_sz1;
 };
 
 // bf16 store of one 32-column chunk of a row (columns [col0, col0+32) clipped to Lkp, Lkp % 8 == 0)
@@ -300,16 +305,23 @@ attn_scores_kernel(const __grid_constant__ CUtensorMap amap, const __grid_consta
 // Two [128 x 256] fp32 accumulators in TMEM (512 columns): the MMA of chunk i+2 is issued as soon as chunk i sits in
 // registers, so the tensor pipe runs under the softmax arithmetic.  Eight warps, all epilogue (two per TMEM lane
 // quadrant, half a chunk = 128 columns each); thread 0 doubles as TMA producer and MMA issuer.
+__device__ __forceinline__ float fast_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 struct AttnCCfg {
   static constexpr int CH = 256;
   static constexpr int NCH_MAX = 4;
   static constexpr int A_BYTES = 128 * 128;
   static constexpr int B_CH_BYTES = CH * 128;
-  static constexpr int SMEM = 1024 + 2 * A_BYTES + NCH_MAX * B_CH_BYTES + 2 * 2 * 128 * 4 + 8 * 8 + 16;
+  static constexpr int PARTS = 4;                       // threads per query row: 16 warps, four per TMEM lane quadrant
+  static constexpr int PCOLS = CH / PARTS;              // columns of a chunk per thread (64)
+  static constexpr int SMEM = 1024 + 2 * A_BYTES + NCH_MAX * B_CH_BYTES + 2 * PARTS * 128 * 4 + 8 * 8 + 16;
 };
 
 template <int BWD>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(512, 1)
 attn_scores_chunked_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ CUtensorMap bmap,
                            const __grid_constant__ AttnParams p) {
   using Cfg = AttnCCfg;
@@ -317,17 +329,20 @@ attn_scores_chunked_kernel(const __grid_constant__ CUtensorMap amap, const __gri
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* qbuf = smem;                                                 // [2][128 x 64] query tiles (A operand)
   uint8_t* kbuf = smem + 2 * Cfg::A_BYTES;                              // [nch][256 x 64] keys of this (batch, head)
-  float* xch = reinterpret_cast<float*>(kbuf + Cfg::NCH_MAX * Cfg::B_CH_BYTES);   // [2 values][2 halves][128 rows]
-  uint64_t* qfull = reinterpret_cast<uint64_t*>(xch + 2 * 2 * 128);
+  float* xch = reinterpret_cast<float*>(kbuf + Cfg::NCH_MAX * Cfg::B_CH_BYTES);   // [2 values][4 parts][128 rows]
+  uint64_t* qfull = reinterpret_cast<uint64_t*>(xch + 2 * Cfg::PARTS * 128);
   uint64_t* kfull = qfull + 2;
   uint64_t* tfull = kfull + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull + 2);
+  uint64_t* tempty = tfull + 2;                                         // one arrival per warp once its chunk sits in registers
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool leader = threadIdx.x == 0;
   const int pairs = p.heads * p.batch;
   const int items = pairs * p.groups;
-  const int nch = p.nch, total = 2 * nch;
+  const int nch = p.nch;
+  const bool single = BWD && p.O != nullptr;                            // dot = dO . O: no first pass
+  const int total = single ? nch : 2 * nch;
   constexpr uint32_t idesc = make_idesc_bf16(128, Cfg::CH, 0, 0);
 
   pdl_trigger();
@@ -336,6 +351,7 @@ attn_scores_chunked_kernel(const __grid_constant__ CUtensorMap amap, const __gri
     prefetch_tmap(&bmap);
     mbar_init(&qfull[0], 1); mbar_init(&qfull[1], 1); mbar_init(kfull, 1);
     mbar_init(&tfull[0], 1); mbar_init(&tfull[1], 1);
+    mbar_init(&tempty[0], 4 * Cfg::PARTS); mbar_init(&tempty[1], 4 * Cfg::PARTS);
     fence_mbar_init();
   }
   if (warp == 0) { __syncwarp(); tmem_alloc(tmem_slot, 512); }
@@ -345,7 +361,8 @@ attn_scores_chunked_kernel(const __grid_constant__ CUtensorMap amap, const __gri
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();
 
-  const int q = warp & 3, half = warp >> 2;
+  const int q = warp & 3, part = warp >> 2;               // TMEM lane quadrant / quarter of a chunk's columns
+  const float sl2 = p.scale * 1.4426950408889634f;       // forward works in the log2 domain: exp(x) = ex2(x * log2 e)
   const int r = q * 32 + lane;
   const uint64_t adesc0 = make_smem_desc(smem_u32(qbuf), 16, 1024);
   const uint64_t bdesc0 = make_smem_desc(smem_u32(kbuf), 16, 1024);
@@ -397,15 +414,39 @@ attn_scores_chunked_kernel(const __grid_constant__ CUtensorMap amap, const __gri
       const bool row_ok = gm < p.Lq;
       const long long row_off = ((static_cast<long long>(b) * p.heads + hd) * p.Lq + (row_ok ? gm : 0)) * p.Lkp;
       float m_run = -INFINITY, l_run = 0.f, m_tot = 0.f, inv = 0.f, dot = 0.f;
+      if (single) {
+        // D_i = sum_d dO[i, d] * O[i, d] over the head's 64 dims: 16 per part, met in shared memory
+        float part_dot = 0.f;
+        if (row_ok) {
+          const __nv_bfloat16* orow = p.O + static_cast<long long>(b) * p.o_sz1 + static_cast<long long>(hd) * p.o_sz0 + static_cast<long long>(gm) * p.o_ld + part * 16;
+          const __nv_bfloat16* grow = p.dO + static_cast<long long>(b) * p.do_sz1 + static_cast<long long>(hd) * p.do_sz0 + static_cast<long long>(gm) * p.do_ld + part * 16;
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const uint4 wo = __ldg(reinterpret_cast<const uint4*>(orow) + e), wg = __ldg(reinterpret_cast<const uint4*>(grow) + e);
+            const __nv_bfloat162* ho = reinterpret_cast<const __nv_bfloat162*>(&wo);
+            const __nv_bfloat162* hg = reinterpret_cast<const __nv_bfloat162*>(&wg);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              const float2 fo = __bfloat1622float2(ho[t]), fg = __bfloat1622float2(hg[t]);
+              part_dot += fo.x * fg.x + fo.y * fg.y;
+            }
+          }
+        }
+        __syncthreads();                                                // the previous tile's readers of xch are done
+        xch[part * 128 + r] = part_dot;
+        __syncthreads();
+#pragma unroll
+        for (int po = 0; po < Cfg::PARTS; ++po) dot += xch[po * 128 + r];
+      }
       for (int i = 0; i < total; ++i) {
-        const int c = i % nch, pass = i / nch, buf = i & 1;
+        const int c = i % nch, pass = single ? 1 : i / nch, buf = i & 1;
         mbar_wait(&tfull[buf], (buf ? use1 : use0) & 1);
         if (buf) ++use1; else ++use0;
         tc_fence_after();
-        const uint32_t tacc = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * Cfg::CH + half * 128;
-        float v[4][32];
+        const uint32_t tacc = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * Cfg::CH + part * Cfg::PCOLS;
+        float v[2][32];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < 2; ++k) {
           uint32_t u[32];
           tmem_ld_32x32(tacc + k * 32, u);
           tmem_ld_wait();
@@ -413,21 +454,34 @@ attn_scores_chunked_kernel(const __grid_constant__ CUtensorMap amap, const __gri
           for (int j = 0; j < 32; ++j) v[k][j] = __uint_as_float(u[j]);
         }
         tc_fence_before();
-        __syncthreads();                                                // chunk i is in registers everywhere: buffer free
-        if (leader && i + 2 < total) { tc_fence_after(); mma_step(slot, i + 2); }
+        // the accumulator buffer is free once every warp holds its part of chunk i in registers: the warps do not wait
+        // for each other (no CTA barrier per chunk), only the issuing thread waits for the sixteen arrivals
         __syncwarp();
-        const int colb = c * Cfg::CH + half * 128;
-        if (pass == 1 && c == 0) {                                      // partner's pass-1 partials (written before the barrier above)
-          const float mo = xch[(half ^ 1) * 128 + r], lo = xch[256 + (half ^ 1) * 128 + r];
+        if (lane == 0) mbar_arrive(&tempty[buf]);
+        if (leader) {
+          mbar_wait(&tempty[buf], ((buf ? use1 : use0) - 1) & 1);
+          if (i + 2 < total) { tc_fence_after(); mma_step(slot, i + 2); }
+        }
+        __syncwarp();
+        if (!single && i == nch) __syncthreads();                       // every part's pass-1 partials are in xch
+        const int colb = c * Cfg::CH + part * Cfg::PCOLS;
+        if (pass == 1 && c == 0 && !single) {                           // the other parts' pass-1 partials (written before the barrier above)
+          // (every part of a row combines the four partials in the same order: identical m_tot / inv / dot in all of them)
           if (!BWD) {
-            m_tot = fmaxf(m_run, mo);
+            m_tot = -INFINITY;
+#pragma unroll
+            for (int po = 0; po < Cfg::PARTS; ++po) m_tot = fmaxf(m_tot, xch[po * 128 + r]);
             if (m_tot == -INFINITY) { m_tot = 0.f; inv = 0.f; }
             else {
-              const float l = l_run * __expf(m_run - m_tot) + lo * __expf(mo - m_tot);
+              float l = 0.f;
+#pragma unroll
+              for (int po = 0; po < Cfg::PARTS; ++po) l += xch[Cfg::PARTS * 128 + po * 128 + r] * fast_ex2(xch[po * 128 + r] - m_tot);
               inv = l > 0.f ? 1.f / l : 0.f;
             }
           } else {
-            dot += mo;
+            dot = 0.f;
+#pragma unroll
+            for (int po = 0; po < Cfg::PARTS; ++po) dot += xch[po * 128 + r];
           }
         }
         if (!BWD) {
@@ -436,17 +490,17 @@ attn_scores_chunked_kernel(const __grid_constant__ CUtensorMap amap, const __gri
 #pragma unroll
             for (int e = 0; e < 8; ++e) m8[e] = -INFINITY;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
+            for (int k = 0; k < 2; ++k) {
               const int col0 = colb + k * 32;
               if (!mrow && col0 + 32 <= p.Lk) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) { v[k][j] *= p.scale; m8[j & 7] = fmaxf(m8[j & 7], v[k][j]); }
+                for (int j = 0; j < 32; ++j) { v[k][j] *= sl2; m8[j & 7] = fmaxf(m8[j & 7], v[k][j]); }
               } else {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                   const int col = col0 + j;
                   const bool dead = col >= p.Lk || (mrow && __ldg(mrow + min(col, p.Lk - 1)));
-                  v[k][j] = dead ? -INFINITY : v[k][j] * p.scale;
+                  v[k][j] = dead ? -INFINITY : v[k][j] * sl2;
                   m8[j & 7] = fmaxf(m8[j & 7], v[k][j]);
                 }
               }
@@ -456,30 +510,36 @@ attn_scores_chunked_kernel(const __grid_constant__ CUtensorMap amap, const __gri
             if (mn > -INFINITY) {
               float s8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-              for (int k = 0; k < 4; ++k)
+              for (int k = 0; k < 2; ++k)
 #pragma unroll
-                for (int j = 0; j < 32; ++j) s8[j & 7] += __expf(v[k][j] - mn);
-              l_run = l_run * __expf(m_run - mn) + (((s8[0] + s8[1]) + (s8[2] + s8[3])) + ((s8[4] + s8[5]) + (s8[6] + s8[7])));
+                for (int j = 0; j < 32; ++j) s8[j & 7] += fast_ex2(v[k][j] - mn);
+              l_run = l_run * fast_ex2(m_run - mn) + (((s8[0] + s8[1]) + (s8[2] + s8[3])) + ((s8[4] + s8[5]) + (s8[6] + s8[7])));
               m_run = mn;
             }
-            if (c == nch - 1) { xch[half * 128 + r] = m_run; xch[256 + half * 128 + r] = l_run; }
+            if (c == nch - 1) { xch[part * 128 + r] = m_run; xch[Cfg::PARTS * 128 + part * 128 + r] = l_run; }
           } else {
+            const float nm = -m_tot;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
+            for (int k = 0; k < 2; ++k) {
               const int col0 = colb + k * 32;
+              if (!mrow && col0 + 32 <= p.Lk) {                           // interior: no per-element liveness test
 #pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                const int col = col0 + j;
-                const bool dead = col >= p.Lk || (mrow && __ldg(mrow + min(col, p.Lk - 1)));
-                v[k][j] = dead ? 0.f : __expf(v[k][j] * p.scale - m_tot) * inv;
+                for (int j = 0; j < 32; ++j) v[k][j] = fast_ex2(fmaf(v[k][j], sl2, nm)) * inv;
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                  const int col = col0 + j;
+                  const bool dead = col >= p.Lk || (mrow && __ldg(mrow + min(col, p.Lk - 1)));
+                  v[k][j] = dead ? 0.f : fast_ex2(fmaf(v[k][j], sl2, nm)) * inv;
+                }
               }
             }
             if (row_ok) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k) attn_store_chunk(p.out + row_off, colb + k * 32, v[k], p.Lkp, p.vec32);
+              for (int k = 0; k < 2; ++k) attn_store_chunk(p.out + row_off, colb + k * 32, v[k], p.Lkp, p.vec32);
               if (drop_on(p.drop)) {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
+                for (int k = 0; k < 2; ++k) {
                   if (colb + k * 32 >= p.Lkp) continue;
                   drop_apply32(p.drop, static_cast<unsigned long long>(row_off + colb + k * 32), dstep, v[k]);
                   attn_store_chunk(p.out2 + row_off, colb + k * 32, v[k], p.Lkp, p.vec32);
@@ -491,12 +551,12 @@ attn_scores_chunked_kernel(const __grid_constant__ CUtensorMap amap, const __gri
           const __nv_bfloat16* prow = p.P + row_off;
           if (drop_on(p.drop)) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < 2; ++k)
               if (colb + k * 32 < p.Lkp) drop_apply32(p.drop, static_cast<unsigned long long>(row_off + colb + k * 32), dstep, v[k]);
           }
           float d4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
+          for (int k = 0; k < 2; ++k) {
             const int col0 = colb + k * 32;
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
@@ -518,10 +578,10 @@ attn_scores_chunked_kernel(const __grid_constant__ CUtensorMap amap, const __gri
           }
           if (pass == 0) {
             dot += (d4[0] + d4[1]) + (d4[2] + d4[3]);
-            if (c == nch - 1) { xch[half * 128 + r] = dot; }
+            if (c == nch - 1) { xch[part * 128 + r] = dot; }
           } else if (row_ok) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) attn_store_chunk(p.out + row_off, colb + k * 32, v[k], p.Lkp, p.vec32);
+            for (int k = 0; k < 2; ++k) attn_store_chunk(p.out + row_off, colb + k * 32, v[k], p.Lkp, p.vec32);
           }
         }
       }

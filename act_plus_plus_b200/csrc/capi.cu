@@ -87,6 +87,15 @@ extern "C" int act_attn_scores(int bwd, const void* A, int64_t lda, int64_t a_sz
   b.ptr = BF(Bm); b.ld = ldb; b.sz0 = b_sz0; b.sz1 = b_sz1;
   return tc_attn_scores(bwd, a, b, Lq, Lk, Lkp, heads, batch, scale, mask, BF(P), BFM(out), ST(stream));
 }
+extern "C" int act_attn_scores_bwd(const void* dO, int64_t ld_do, int64_t do_sz0, int64_t do_sz1, const void* V, int64_t ldv,
+                                   int64_t v_sz0, int64_t v_sz1, const void* O, int64_t ldo, int64_t o_sz0, int64_t o_sz1, int Lq,
+                                   int Lk, int Lkp, int heads, int batch, float scale, const void* P, void* dS, void* stream) {
+  MatDesc a, b, o;
+  a.ptr = BF(dO); a.ld = ld_do; a.sz0 = do_sz0; a.sz1 = do_sz1;
+  b.ptr = BF(V); b.ld = ldv; b.sz0 = v_sz0; b.sz1 = v_sz1;
+  o.ptr = BF(O); o.ld = ldo; o.sz0 = o_sz0; o.sz1 = o_sz1;
+  return tc_attn_scores(1, a, b, Lq, Lk, Lkp, heads, batch, scale, nullptr, BF(P), BFM(dS), ST(stream), nullptr, nullptr, O ? &o : nullptr);
+}
 extern "C" int act_colsum_bf16(const void* X, int64_t ld, int M, int N, float* out, void* stream) {
   return colsum_bf16(BF(X), ld, M, N, out, ST(stream));
 }

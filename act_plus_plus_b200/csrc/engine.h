@@ -190,7 +190,7 @@ class Engine {
   int attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv,
                const bf16* P, bf16* dQ, long long lddq, bf16* dK, long long lddk, bf16* dV, long long lddv, int B, int Lq,
                int Lk, cudaStream_t st, float* S = nullptr, bf16* dS = nullptr, bool use_aux = true, uint32_t drop = 0,
-               const bf16* P2 = nullptr);
+               const bf16* P2 = nullptr, const bf16* O = nullptr);   // O: the forward's attention output [B*Lq, 512] (optional)
   int enc_layer_fwd(const EncW& w, EncActs& a, const float* x, const float* pos, const float* next_pos, int L,
                     const uint8_t* mask, int B, bool emit_next, bf16* next_xb, bf16* next_xpb, cudaStream_t st, uint32_t site);
   int enc_layer_bwd(const EncW& w, EncActs& a, const float* x_in, const float* dx2, const float* dx2b, float* dx_out,

@@ -88,7 +88,7 @@ int Engine::linear_dwb(const bf16* dY, int M, const LinW& w, const bf16* X, cuda
 
 int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K, long long ldk, const bf16* V, long long ldv,
                      const bf16* P, bf16* dQ, long long lddq, bf16* dK, long long lddk, bf16* dV, long long lddv, int B,
-                     int Lq, int Lk, cudaStream_t st, float* S, bf16* dS, bool use_aux, uint32_t drop, const bf16* P2) {
+                     int Lq, int Lk, cudaStream_t st, float* S, bf16* dS, bool use_aux, uint32_t drop, const bf16* P2, const bf16* O) {
   if (!S) S = Sbuf_;
   if (!dS) dS = dSbuf_;
   const bool dropping = drop && drop_active_;      // O = dropout(P) V: dV sees the dropped weights, dP is masked again
@@ -112,7 +112,8 @@ int Engine::attn_bwd(const bf16* dO, const bf16* Q, long long ldq, const bf16* K
     if (tc_attn_scores_applicable(Lk, Lkp, dropping)) {
       ++launches_;
       const DropDesc dd = dropping ? drop_site(drop) : DropDesc();
-      if (tc_attn_scores(1, a, b, Lq, Lk, Lkp, h, B, 0.125f, nullptr, P, dS, st, dropping ? &dd : nullptr)) return -1;
+      MatDesc od; od.ptr = O; od.ld = 512; od.sz0 = hd; od.sz1 = 1LL * Lq * 512;      // rowsum(P o dP) = dO . O (long rows: one pass)
+      if (tc_attn_scores(1, a, b, Lq, Lk, Lkp, h, B, 0.125f, nullptr, P, dS, st, dropping ? &dd : nullptr, nullptr, O ? &od : nullptr)) return -1;
     } else {
       ACT_CHECK(!dropping, "attention dropout is implemented in the fused scores kernels only (ACT_FUSED_ATTN=0 is set)");
       e.flags = EPI_OUT_F32; e.out_f32 = S; e.ldc = Lkp; e.osz0 = ph; e.osz1 = pb;
@@ -169,7 +170,7 @@ int Engine::enc_layer_bwd(const EncW& w, EncActs& a, const float* x_in, const fl
   if (linear_dwb(g1b, M, w.sa.o, a.o, st)) return -1;
   if (linear_dx(g1b, M, w.sa.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
   if (attn_bwd(gb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gqk, 2 * d, gqk + d, 2 * d, gv, d, B, L, L, st, nullptr, nullptr,
-               true, site + 0, a.P2)) return -1;
+               true, site + 0, a.P2, a.o)) return -1;
   if (linear_dwb(gqk, M, w.sa.qk, a.xpb, st)) return -1;
   if (linear_dwb(gv, M, w.sa.v, a.xb, st)) return -1;
   cudaStream_t ax = aux_fork(st);                    // the two input gradients are independent
@@ -224,7 +225,7 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
   RUN(ln_bwd(gAz, nullptr, a.t2, a.mean2, a.rstd2, w.n2.g, dgB_, g2, w.n2.gg, w.n2.gb, Md, d, st, pdd5));
   if (linear_dwb(g2, Md, w.ca.o, a.co, st)) return -1;
   if (linear_dx(g2, Md, w.ca.o, 0, nullptr, nullptr, nullptr, gb2_, st)) return -1;
-  if (attn_bwd(gb2_, a.q, d, a.k, d, a.cv, d, a.cP, gq, d, gk, d, gcv, d, B, nq, L_, st, nullptr, nullptr, true, SITE_DEC + 4, a.cP2)) return -1;
+  if (attn_bwd(gb2_, a.q, d, a.k, d, a.cv, d, a.cP, gq, d, gk, d, gcv, d, B, nq, L_, st, nullptr, nullptr, true, SITE_DEC + 4, a.cP2, a.co)) return -1;
   if (linear_dwb(gq, Md, w.ca.q, a.y1pb, st)) return -1;
   if (linear_dx(gq, Md, w.ca.q, 0, nullptr, nullptr, dgE_, nullptr, st)) return -1;          // wrt y1 + query_pos
   if (linear_dwb(gk, Me, w.ca.k, mem_pb_, st)) return -1;
@@ -246,7 +247,7 @@ int Engine::transformer_bwd(float loss_grad, cudaStream_t st) {
     if (linear_dwb(g1, Md, w.sa.o, a.o, dl)) return -1;
     if (linear_dx(g1, Md, w.sa.o, 0, nullptr, nullptr, nullptr, dgb2_, dl)) return -1;
     if (attn_bwd(dgb2_, a.qk, 2 * d, a.qk + d, 2 * d, a.v, d, a.P, gqk, 2 * d, gqk + d, 2 * d, gv, d, B, nq, nq, dl, Sbuf2_, dSbuf2_, false,
-                 SITE_DEC + 0, a.P2)) return -1;
+                 SITE_DEC + 0, a.P2, a.o)) return -1;
     if (linear_dwb(gqk, Md, w.sa.qk, a.xpb, dl)) return -1;
     if (linear_dwb(gv, Md, w.sa.v, a.xb, dl)) return -1;
     if (linear_dx(gqk, Md, w.sa.qk, 0, nullptr, nullptr, dgE_, nullptr, dl)) return -1;

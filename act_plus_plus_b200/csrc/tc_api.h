@@ -95,12 +95,12 @@ void tc_set_sm_reserve(int n);
 // (one TMEM-resident pass up to 320 keys, two chunked passes beyond).  drop (optional, train mode): dropout on the
 // attention weights -- forward also writes out2 = dropout(P), backward masks dP (csrc/dropout.cuh).
 // need_fused: the caller cannot use the unfused pair (attention dropout lives in the fused kernels only).  Rows of more than
-// 320 keys (the chunked two-pass kernel) are routed to it only then or with ACT_ATTN_CHUNKED=1: at 902 keys it measures 439 /
-// 580 us (fwd / bwd, batch 16) against 209 / 294 us for tc_gemm + softmax, which is HBM-bound (profiles/r02_attn_902.md).
+// 320 keys take the chunked kernel (210 / 258 us fwd / bwd at 16 x 8 x 902 x 902 against 210 / 297 us for tc_gemm + softmax,
+// profiles/r02_attn_902.md); ACT_ATTN_CHUNKED=0 routes them to the unfused pair unless need_fused.
 bool tc_attn_scores_applicable(int Lk, int Lkp, bool need_fused = true);
 int tc_attn_scores(int bwd, const MatDesc& A, const MatDesc& B, int Lq, int Lk, int Lkp, int heads, int batch, float scale,
                    const uint8_t* mask, const bf16* P, bf16* out, cudaStream_t stream, const DropDesc* drop = nullptr,
-                   bf16* out2 = nullptr);
+                   bf16* out2 = nullptr, const MatDesc* O = nullptr);   // O (bwd, optional): the forward's attention output
    // persistent launches that follow leave n SMs free for a concurrent branch
 int tc_conv3(const ConvLaunch& c, cudaStream_t stream, int bn_hint = 0);
 

@@ -549,10 +549,12 @@ static int launch_attn(const CUtensorMap& am, const CUtensorMap& bm, const AttnP
 }
 
 bool tc_attn_scores_applicable(int Lk, int Lkp, bool need_fused) {
-  static int on = -1, chunked = -1;
+  static int on = -1;
   if (on < 0) { const char* e = getenv("ACT_FUSED_ATTN"); on = !(e && e[0] == '0'); }
-  if (chunked < 0) { const char* e = getenv("ACT_ATTN_CHUNKED"); chunked = (e && e[0] == '1') ? 1 : 0; }
-  if (Lk > 320 && !(need_fused || chunked)) return false;
+  if (Lk > 320 && !need_fused) {                             // (read per call: tests switch it inside one process)
+    const char* e = getenv("ACT_ATTN_CHUNKED");
+    if (e && e[0] == '0') return false;                      // A/B switch: tc_gemm + softmax for long rows
+  }
   return on && Lk >= 1 && Lk <= AttnCCfg::NCH_MAX * AttnCCfg::CH && Lkp % 8 == 0 && Lkp >= Lk;
 }
 
@@ -568,7 +570,7 @@ static int launch_attn_chunked(const CUtensorMap& am, const CUtensorMap& bm, con
   if (skip_class(CLS_ATTN)) return 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
-  ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(256), static_cast<size_t>(AttnCCfg::SMEM), stream, am, bm, p));
+  ACT_CUDA(launch_pdl(kern, dim3(ctas), dim3(128 * AttnCCfg::PARTS), static_cast<size_t>(AttnCCfg::SMEM), stream, am, bm, p));
   if (g_prof.on) { cudaEventRecord(e1, stream); g_prof.ev.push_back(e0); g_prof.ev.push_back(e1); g_prof.flops.push_back(g_next_flops); g_prof.label.push_back(g_next_label); }
   ACT_CUDA(cudaGetLastError());
   return 0;
@@ -577,7 +579,8 @@ static int launch_attn_chunked(const CUtensorMap& am, const CUtensorMap& bm, con
 // FWD: out = softmax(scale * A B^T + mask) with A = Q [Lq x 64], B = K [Lk x 64] per (head, batch)
 // BWD: out = scale * P o (dP - rowsum(dP o P)), dP = A B^T with A = dO, B = V
 int tc_attn_scores(int bwd, const MatDesc& A, const MatDesc& B, int Lq, int Lk, int Lkp, int heads, int batch, float scale,
-                   const uint8_t* mask, const bf16* P, bf16* out, cudaStream_t stream, const DropDesc* drop, bf16* out2) {
+                   const uint8_t* mask, const bf16* P, bf16* out, cudaStream_t stream, const DropDesc* drop, bf16* out2,
+                   const MatDesc* O) {
   ACT_CHECK(tc_attn_scores_applicable(Lk, Lkp), "fused attention scores need Lk <= 1024 and a padded stride % 8 == 0");
   ACT_CHECK(!(drop && drop_on(*drop)) || bwd || out2, "fused attention scores: dropout needs the second (dropped) output");
   ACT_CHECK(!(drop && drop_on(*drop)) || drop->step, "fused attention scores: dropout needs the device step counter");
@@ -587,6 +590,12 @@ int tc_attn_scores(int bwd, const MatDesc& A, const MatDesc& B, int Lq, int Lk, 
   AttnParams p;
   memset(&p, 0, sizeof(p));
   p.Lq = Lq; p.Lk = Lk; p.Lkp = Lkp; p.heads = heads; p.batch = batch; p.qtiles = (Lq + 127) / 128; p.scale = scale;
+  p.O = nullptr; p.dO = nullptr; p.o_ld = p.o_sz0 = p.o_sz1 = p.do_ld = p.do_sz0 = p.do_sz1 = 0;
+  if (bwd && O && O->ptr && !A.mn_major && (A.ld % 8) == 0 && (O->ld % 8) == 0 && (A.sz0 % 8) == 0 && (O->sz0 % 8) == 0 &&
+      (reinterpret_cast<uintptr_t>(A.ptr) & 15) == 0 && (reinterpret_cast<uintptr_t>(O->ptr) & 15) == 0) {   // 16-byte row pieces
+    p.O = O->ptr; p.o_ld = O->ld; p.o_sz0 = O->sz0; p.o_sz1 = O->sz1;
+    p.dO = A.ptr; p.do_ld = A.ld; p.do_sz0 = A.sz0; p.do_sz1 = A.sz1;
+  }
   p.mask = mask; p.P = P; p.out = out; p.vec32 = (Lkp % 16 == 0) ? 1 : 0;
   p.drop = drop ? *drop : DropDesc();            // (the memset above is not the "off" state: thresh 0 would drop everything)
   p.out2 = out2;

@@ -98,6 +98,11 @@ int act_softmax_bwd(const void* P, const float* dP, void* dS, int R, int L, int 
 int act_attn_scores(int bwd, const void* A, int64_t lda, int64_t a_sz0, int64_t a_sz1, const void* B, int64_t ldb, int64_t b_sz0,
                     int64_t b_sz1, int Lq, int Lk, int Lkp, int heads, int batch, float scale, const uint8_t* key_padding_mask,
                     const void* P, void* out, void* stream);
+/* The bwd = 1 form with the forward's attention output O = P V given as well (row view like dO): rowsum(dP o P) equals
+ * dO_i . O_i, so rows of more than 320 keys need one pass over the keys instead of two.  O == NULL: same as above. */
+int act_attn_scores_bwd(const void* dO, int64_t ld_do, int64_t do_sz0, int64_t do_sz1, const void* V, int64_t ldv, int64_t v_sz0,
+                        int64_t v_sz1, const void* O, int64_t ldo, int64_t o_sz0, int64_t o_sz1, int Lq, int Lk, int Lkp, int heads,
+                        int batch, float scale, const void* P, void* dS, void* stream);
 int act_colsum_bf16(const void* X, int64_t ld, int M, int N, float* out_accum, void* stream);
 /* fp32 mini-GEMM for the K<=32 / N<=64 projections (detr_vae.py:57-63,81-97) and their gradients:
  * C(i,j) (+)= alpha*sum_r A(i,r)B(r,j) (+bias[j]); each index maps as (idx/rpb)*bs + (idx%rpb)*s (maps = 3 int64). */

@@ -66,6 +66,41 @@ def test_forward_inference_matches_reference(case):
     assert err <= TOL_ABS, (case, err)
 
 
+def test_three_camera_forward_through_the_chunked_attention_kernel(monkeypatch):
+    """Rows of 902 keys take the chunked fused kernel by default; ACT_ATTN_CHUNKED=0 routes them to tc_gemm + softmax
+    (the round-1 path, kept as an A/B switch): same golden, same tolerances, and the two paths agree with each other far
+    inside the tolerance, forward and backward."""
+    gold, cfg, sd, cb, eng = _setup("full_k3_b2")
+    monkeypatch.setenv("ACT_ATTN_CHUNKED", "0")
+    ref = eng.forward(cb["qpos"], cb["image"], cb["actions"], cb["is_pad"], cb["eps"])
+    ref = {k: ref[k].clone() for k in ("a_hat", "mu", "logvar", "losses")}
+    eng.zero_grad()
+    eng.backward(0)
+    g_ref = eng.flat_grads.clone()
+    monkeypatch.delenv("ACT_ATTN_CHUNKED")
+    out = eng.forward(cb["qpos"], cb["image"], cb["actions"], cb["is_pad"], cb["eps"])
+    torch.cuda.synchronize()
+    for k in ("a_hat", "mu", "logvar"):
+        err = float((out[k].cpu() - torch.from_numpy(gold[k])).abs().max())
+        assert err <= TOL_ABS, (k, err)
+    between = float((out["a_hat"] - ref["a_hat"]).abs().max())
+    assert 0.0 < between <= 4e-3, between            # different kernels (not bit-equal), same arithmetic
+    # backward through the chunked dS kernel -- one pass over the keys, rowsum(P o dP) taken as dO . O -- against the
+    # unfused softmax backward: every region's gradient agrees to a fraction of the bf16 noise of the step
+    eng.zero_grad()
+    eng.backward(0)
+    torch.cuda.synchronize()
+    g = eng.flat_grads
+    assert torch.isfinite(g).all()
+    rel = {}
+    for r in range(3):
+        off, n = eng.region(r)
+        if n > 0:
+            rel[r] = float((g[off:off + n] - g_ref[off:off + n]).norm() / g_ref[off:off + n].norm().clamp_min(1e-20))
+    _report("full_k3_b2", "chunked_vs_unfused", dict(a_hat=between, **{f"grad_rel_region{r}": v for r, v in rel.items()}))
+    assert max(rel.values()) <= 2e-2, rel
+
+
 def test_inference_batch16_matches_reference_and_is_batch_invariant():
     """Inference golden at batch 16 on the full image (per-GPU batch of BASELINE configs[2] at N = 4; the rollout leg's
     many-environment regime), and: every sample's chunk is independent of what else is in the batch -- 128 copies of one

@@ -331,3 +331,14 @@ def test_attn_scores_fused_matches_torch(B, h, Lq, Lk, masked):
     err = (dS[..., :Lk].float() - ref_dS).abs().max().item()
     assert err <= 2e-2 * max(1.0, ref_dS.abs().max().item()), err
     assert (dS[..., Lk:].float() == 0).all()
+    # the same through act_attn_scores_bwd with the forward's output O = P V given: rowsum(dP o P) = dO . O, one pass over
+    # the keys for rows of more than 320 keys (shorter rows ignore O).  O is rounded to bf16 like the engine's buffer.
+    Of = (Pf @ v.float().view(B, Lk, h, hd).transpose(1, 2)).transpose(1, 2).reshape(B, Lq, d)
+    O = Of.bfloat16().contiguous()
+    dS2 = torch.full((B, h, Lq, Lkp), 7.0, device="cuda", dtype=torch.bfloat16)
+    ck(L().act_attn_scores_bwd(p(dO), d, hd, Lq * d, p(v), d, hd, Lk * d, p(O), d, hd, Lq * d, Lq, Lk, Lkp, h, B, C.c_float(0.125),
+                               p(P), p(dS2), st()))
+    torch.cuda.synchronize()
+    err2 = (dS2[..., :Lk].float() - ref_dS).abs().max().item()
+    assert err2 <= 2e-2 * max(1.0, ref_dS.abs().max().item()), err2
+    assert (dS2[..., Lk:].float() == 0).all()

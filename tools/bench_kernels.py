@@ -192,9 +192,14 @@ def bench_attn():
             ops.tc_gemm_raw(Lq, Lk, 64, h, B, dO, 0, d, 64, Lq * d, V, 0, d, 64, Lk * d, epi2, 1, 0, 0)
             ops.check(lib.act_softmax_bwd(P.data_ptr(), S.data_ptr(), dS.data_ptr(), B * h * Lq, Lk, Lkp, C.c_float(0.125), st()), "softmax bwd")
         tf, tu = graph_time(fused), graph_time(unfused)
-        tfb, tub = graph_time(fused_bwd), graph_time(unfused_bwd)
+        Oo = torch.randn(B, Lq, d, device="cuda").bfloat16()
+
+        def fused_bwd_o():
+            ops.check(lib.act_attn_scores_bwd(dO.data_ptr(), d, 64, Lq * d, V.data_ptr(), d, 64, Lk * d, Oo.data_ptr(), d, 64, Lq * d, Lq, Lk,
+                                              Lkp, h, B, C.c_float(0.125), P.data_ptr(), dS.data_ptr(), st()), "attn_scores_bwd")
+        tfb, tub, tfo = graph_time(fused_bwd), graph_time(unfused_bwd), graph_time(fused_bwd_o)
         print(json.dumps(dict(kind="attn_scores", B=B, h=h, Lq=Lq, Lk=Lk, fused_us=round(tf, 2), unfused_us=round(tu, 2),
-                              fused_bwd_us=round(tfb, 2), unfused_bwd_us=round(tub, 2))), flush=True)
+                              fused_bwd_us=round(tfb, 2), unfused_bwd_us=round(tub, 2), fused_bwd_with_O_us=round(tfo, 2))), flush=True)
 
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "attn":
