@@ -398,6 +398,9 @@ class ActEngine:
         from ._lib import last_error
         world, rank = dist.get_world_size(group), dist.get_rank(group)
         torch.cuda.synchronize(self.device)
+        if getattr(self, "_dp_mapped", None) is not None:        # re-connect after dp_disconnect(): the mappings are still open
+            self._dp_world, self._dp_rank = self._dp_mapped
+            return
         self._dp_nvls = False
         if multicast is None:
             env = os.environ.get("ACT_DP_NVLS", "auto")
@@ -422,6 +425,8 @@ class ActEngine:
 
     def dp_disconnect(self):
         """Go back to the NCCL / single-process step (the mappings stay open until the engine is destroyed)."""
+        if getattr(self, "_dp_world", 1) > 1:
+            self._dp_mapped = (self._dp_world, self._dp_rank)
         self._dp_world = 1
 
     @property
