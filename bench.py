@@ -497,19 +497,28 @@ def run_ours(args):
     # ---------------- timed region 2, end to end: pinned host inputs -> H2D -> step -> loss D2H, every step
     h2d = sum(v.numel() * v.element_size() for v in host[0].values())
     pf = InputPrefetcher(host[0], dev, depth=2)                      # staging buffers / copy stream: created once
-    loss_pin = torch.zeros(3).pin_memory()
+    loss_pin = [torch.zeros(3).pin_memory() for _ in range(2)]
+    loss_ev = [torch.cuda.Event() for _ in range(2)]
 
     def e2e_steps(n):
+        # the step's losses go to pinned host memory EVERY step; the host reads them once the next step is enqueued (the
+        # reference loop only detaches the loss dict per step, imitate_episodes.py:608: nothing makes it wait for the step
+        # it has just launched), so H2D of step i+1, the compute of step i and the read of step i-1 overlap
         pf.submit(host[0])
+        last = 0.0
         for i in range(n):
             if i + 1 < n:
                 pf.submit(host[(i + 1) % NB])                        # H2D of the next step's inputs runs under this step
             db = pf.next()
             ls = gs.step(db) if gs is not None else step_direct(db)
             pf.consumed()
-            loss_pin.copy_(ls, non_blocking=True)                    # device->host read of the step's losses
-            torch.cuda.current_stream().synchronize()
-        return float(loss_pin[2])
+            loss_pin[i & 1].copy_(ls, non_blocking=True)             # device->host read of the step's losses
+            loss_ev[i & 1].record()
+            if i > 0:
+                loss_ev[(i - 1) & 1].synchronize()
+                last = float(loss_pin[(i - 1) & 1][2])
+        loss_ev[(n - 1) & 1].synchronize()
+        return float(loss_pin[(n - 1) & 1][2]) if n > 0 else last
 
     e2e_steps(max(3, args.warmup))                                   # untimed warm-up of the host-driven loop
     barrier()
